@@ -1,0 +1,160 @@
+/*
+ * splat_b200.h -- C ABI of the B200-native (sm_100a) differentiable Gaussian-splat rasterizer.
+ *
+ * This is the drop-in boundary.  Every entry point takes plain device
+ * pointers, sizes and a cudaStream_t (passed as void*); there are no torch types.  The caller
+ * owns every buffer; the library never allocates or frees device memory (the only exception
+ * is the optional host-buffer session at the bottom, which exists for hosts that have no
+ * device allocator of their own).
+ *
+ * Reference interfaces replaced (paths relative to /root/reference; HX = hessian-diff-gaussian-
+ * rasterization-w-depth, DG = diff-gaussian-rasterization-w-depth.git):
+ *   splat_forward_geometry + splat_forward_render  <-  CudaRasterizer::Rasterizer::forward
+ *        (HX/cuda_rasterizer/rasterizer.h:36-60, rasterizer_impl.cu:198-339), bound to Python
+ *        as _C.rasterize_gaussians (HX/ext.cpp:15, HX/rasterize_points.cu:35-115)
+ *   splat_backward                                 <-  CudaRasterizer::Rasterizer::backward
+ *        (HX/cuda_rasterizer/rasterizer.h:62-92, rasterizer_impl.cu:343-433; DG variant
+ *        DG/cuda_rasterizer/rasterizer_impl.cu:343-435), bound as
+ *        _C.rasterize_gaussians_backward (HX/ext.cpp:16, HX/rasterize_points.cu:117-196)
+ *   splat_mark_visible                             <-  CudaRasterizer::Rasterizer::markVisible
+ *        (HX/cuda_rasterizer/rasterizer.h:28-34), bound as _C.mark_visible (HX/ext.cpp:17)
+ *   splat_*_state_bytes                            <-  required<GeometryState/ImageState/
+ *        BinningState>() (HX/cuda_rasterizer/rasterizer_impl.h:66-72)
+ *
+ * Conventions kept from the reference: matrices are passed "transposed" (element (r,c) of the
+ * math matrix is m[c*4+r], HX/cuda_rasterizer/auxiliary.h:58-77); quaternions are (w,x,y,z) and
+ * used un-normalised; colours/outputs are planar [3,H,W]; radii are int32, 0 == culled.
+ */
+#ifndef SPLAT_B200_H_
+#define SPLAT_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPLAT_ABI_VERSION 1
+
+/* Error codes.  Positive values >= 1000 are 1000 + cudaError_t of a failed runtime call. */
+enum {
+  SPLAT_OK = 0,
+  SPLAT_ERR_BAD_ARG = 1,          /* null/mis-sized argument; see splat_last_error()            */
+  SPLAT_ERR_SCRATCH_TOO_SMALL = 2,/* binning capacity exceeded (splat_forward only)             */
+  SPLAT_ERR_UNSUPPORTED = 3,      /* e.g. sh_degree > 3                                         */
+  SPLAT_ERR_CUDA_BASE = 1000
+};
+
+/* Camera / raster settings.  Mirrors GaussianRasterizationSettings
+ * (HX/hessian_diff_gaussian_rasterization_w_depth/__init__.py:140-151) field by field, plus the
+ * near-plane constant that distinguishes the two reference builds
+ * (HX/cuda_rasterizer/auxiliary.h:154 uses 0.001f, DG/cuda_rasterizer/auxiliary.h:154 uses 0.2f). */
+typedef struct SplatCamera {
+  int32_t image_height;
+  int32_t image_width;
+  float tanfovx;
+  float tanfovy;
+  const float* bg;          /* device, 3 floats                                   */
+  float scale_modifier;
+  const float* viewmatrix;  /* device, 16 floats, transposed layout               */
+  const float* projmatrix;  /* device, 16 floats, transposed layout               */
+  int32_t sh_degree;        /* 0..3 (only read when shs != NULL)                  */
+  const float* campos;      /* device, 3 floats (only read when shs != NULL)      */
+  int32_t prefiltered;      /* kept for API parity; a culled point is never fatal */
+  float near_plane;         /* 0.2f == DG semantics, 0.001f == HX semantics       */
+} SplatCamera;
+
+/* ---- scratch sizing (all sizes in bytes, all buffers must be 256-byte aligned) ------------- */
+size_t splat_geom_state_bytes(int32_t P);
+size_t splat_image_state_bytes(int32_t width, int32_t height);
+size_t splat_binning_state_bytes(int32_t width, int32_t height, int64_t R_capacity);
+
+/* ---- forward, phase 1: per-Gaussian geometry + per-tile counts + tile ranges ----------------
+ * Replaces preprocessCUDA + InclusiveSum + the blocking num_rendered read
+ * (HX/cuda_rasterizer/rasterizer_impl.cu:248-282).  Fully asynchronous.  On return (in stream
+ * order) geom_state holds depth/xy/conic_opacity(/rgb,clamped), image_state holds the bit-exact
+ * tile ranges, radii[P] is written, and *num_rendered_dev (device uint32) holds R.
+ * Exactly one of (scales && rotations) or cov3D_precomp must be non-NULL; exactly one of
+ * colors_precomp or shs must be non-NULL (same rule as HX/.../__init__.py:174-178). */
+int splat_forward_geometry(const SplatCamera* cam, int32_t P,
+                           const float* means3D,        /* [P,3] */
+                           const float* scales,         /* [P,3] or NULL */
+                           const float* rotations,      /* [P,4] or NULL */
+                           const float* opacities,      /* [P]   */
+                           const float* cov3D_precomp,  /* [P,6] or NULL */
+                           const float* shs,            /* [P,M,3] or NULL */
+                           int32_t M,
+                           const float* colors_precomp, /* [P,3] or NULL */
+                           void* geom_state, void* image_state,
+                           int32_t* radii,              /* [P] out */
+                           uint32_t* num_rendered_dev,  /* device scalar out */
+                           void* stream);
+
+/* ---- forward, phase 2: scatter instances to tiles, per-tile depth sort, blend ---------------
+ * Replaces duplicateWithKeys + DeviceRadixSort + identifyTileRanges + renderCUDA
+ * (HX/cuda_rasterizer/rasterizer_impl.cu:290-337).  R_capacity is the number of (tile,Gaussian)
+ * instances binning_state was sized for.  If the device-side R exceeds it, every kernel of this
+ * phase exits without touching memory out of bounds and the outputs are undefined; the caller
+ * learns R from *num_rendered_dev (phase 1) and simply calls phase 2 again with a larger state.
+ * out_depth may be NULL. */
+int splat_forward_render(const SplatCamera* cam, int32_t P,
+                         const float* colors_precomp,   /* [P,3] or NULL (then SH colours of phase 1) */
+                         const int32_t* radii,          /* [P] as written by phase 1 */
+                         const void* geom_state, void* image_state, void* binning_state,
+                         int64_t R_capacity,
+                         float* out_color,              /* [3,H,W] */
+                         float* out_depth,              /* [1,H,W] median depth, default 15.0 */
+                         void* stream);
+
+/* ---- backward -------------------------------------------------------------------------------
+ * power == 1 with fused == 0 reproduces DG (BACKWARD::render + BACKWARD::preprocess);
+ * fused != 0 reproduces HX's renderCUDAFused semantics: every per-(pixel,Gaussian) gradient
+ * term is raised to `power` before accumulation (HX/cuda_rasterizer/backward.cu:1093-1137);
+ * power == 2 is the fork's diagonal Gauss-Newton ("Hessian") accumulation.
+ * All dL_* outputs are fully written by the call (no pre-zeroing needed).  dL_dconic is a
+ * [P,4] scratch/output (x,y,_,w as in the reference's [P,2,2]).  dL_dsh may be NULL when shs is. */
+int splat_backward(const SplatCamera* cam, int32_t P, int64_t R,
+                   const float* means3D, const float* scales, const float* rotations,
+                   const float* cov3D_precomp, const float* shs, int32_t M,
+                   const float* colors_precomp, const int32_t* radii,
+                   const void* geom_state, const void* image_state, const void* binning_state,
+                   const float* dL_dout_color,          /* [3,H,W] */
+                   int32_t power, int32_t fused,
+                   float* dL_dmeans3D,  /* [P,3] */
+                   float* dL_dmeans2D,  /* [P,3] (z always 0) */
+                   float* dL_dcolors,   /* [P,3] */
+                   float* dL_dopacity,  /* [P]   */
+                   float* dL_dscales,   /* [P,3] */
+                   float* dL_drotations,/* [P,4] */
+                   float* dL_dcov3D,    /* [P,6] */
+                   float* dL_dconic,    /* [P,4] */
+                   float* dL_dsh,       /* [P,M,3] or NULL */
+                   void* stream);
+
+/* ---- markVisible (HX/cuda_rasterizer/rasterizer_impl.cu:54-66,141-153) ---------------------- */
+int splat_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
+                       const float* projmatrix, float near_plane, uint8_t* present, void* stream);
+
+/* ---- introspection used by the parity tests (read-only views into the states) ---------------
+ * ranges: uint2[T] exactly as identifyTileRanges leaves them (untouched tiles are (0,0));
+ * point_list: uint32[R] sorted Gaussian ids; n_contrib uint32[N]; final_T float[N]. */
+const void* splat_state_ranges(const void* image_state, int32_t width, int32_t height);
+const void* splat_state_n_contrib(const void* image_state, int32_t width, int32_t height);
+const void* splat_state_final_T(const void* image_state, int32_t width, int32_t height);
+const void* splat_state_point_list(const void* binning_state, int32_t width, int32_t height,
+                                   int64_t R_capacity);
+const void* splat_state_depths(const void* geom_state, int32_t P);
+const void* splat_state_means2D(const void* geom_state, int32_t P);
+const void* splat_state_conic_opacity(const void* geom_state, int32_t P);
+
+/* ---- misc ------------------------------------------------------------------------------------ */
+int splat_abi_version(void);
+const char* splat_strerror(int code);
+const char* splat_last_error(void);      /* thread-local detail string of the last failure */
+int splat_kernel_launch_count(void);     /* kernels launched by this library in this process */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPLAT_B200_H_ */

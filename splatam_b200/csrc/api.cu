@@ -1,0 +1,229 @@
+// api.cu -- the extern "C" boundary declared in include/splat_b200.h.
+// Argument validation, state carving and kernel sequencing only; no device allocation.
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include "kernels.cuh"
+
+namespace splat {
+
+int g_launch_count = 0;
+static thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int check_cuda(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return SPLAT_OK;
+  snprintf(g_err, sizeof(g_err), "CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+  return SPLAT_ERR_CUDA_BASE + (int)e;
+}
+
+static int check_cam(const SplatCamera* cam) {
+  if (!cam) return fail(SPLAT_ERR_BAD_ARG, "camera is NULL");
+  if (cam->image_width <= 0 || cam->image_height <= 0)
+    return fail(SPLAT_ERR_BAD_ARG, "bad image size %dx%d", cam->image_width, cam->image_height);
+  if (!cam->viewmatrix || !cam->projmatrix || !cam->bg)
+    return fail(SPLAT_ERR_BAD_ARG, "camera viewmatrix/projmatrix/bg must be device pointers");
+  return SPLAT_OK;
+}
+
+static void read_env_once() {
+  static bool done = false;
+  if (done) return;
+  done = true;
+  const char* e = getenv("SPLAT_B200_NO_CULL");
+  if (e && e[0] == '1') g_disable_cull = 1;
+}
+
+}  // namespace splat
+
+using namespace splat;
+
+extern "C" {
+
+size_t splat_geom_state_bytes(int32_t P) { return geom_bytes(P); }
+size_t splat_image_state_bytes(int32_t W, int32_t H) { return image_bytes(W, H); }
+size_t splat_binning_state_bytes(int32_t, int32_t, int64_t R) { return bin_bytes(R); }
+
+int splat_forward_geometry(const SplatCamera* cam, int32_t P, const float* means3D, const float* scales,
+                           const float* rotations, const float* opacities, const float* cov3D_precomp,
+                           const float* shs, int32_t M, const float* colors_precomp, void* geom_state,
+                           void* image_state, int32_t* radii, uint32_t* num_rendered_dev, void* stream) {
+  read_env_once();
+  if (int rc = check_cam(cam)) return rc;
+  if (P < 0) return fail(SPLAT_ERR_BAD_ARG, "P < 0");
+  if (!geom_state || !image_state || !num_rendered_dev) return fail(SPLAT_ERR_BAD_ARG, "state buffers must be non-NULL");
+  if (P > 0) {
+    if (!means3D || !opacities || !radii) return fail(SPLAT_ERR_BAD_ARG, "means3D/opacities/radii must be non-NULL");
+    const bool sr = scales && rotations;
+    if ((sr && cov3D_precomp) || (!sr && !cov3D_precomp) || ((scales != nullptr) != (rotations != nullptr)))
+      return fail(SPLAT_ERR_BAD_ARG, "Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+    if ((shs && colors_precomp) || (!shs && !colors_precomp))
+      return fail(SPLAT_ERR_BAD_ARG, "Please provide excatly one of either SHs or precomputed colors!");
+    if (shs) {
+      if (cam->sh_degree < 0 || cam->sh_degree > 3) return fail(SPLAT_ERR_UNSUPPORTED, "sh_degree must be 0..3");
+      if (M < (cam->sh_degree + 1) * (cam->sh_degree + 1)) return fail(SPLAT_ERR_BAD_ARG, "M too small for sh_degree");
+      if (!cam->campos) return fail(SPLAT_ERR_BAD_ARG, "campos required with SHs");
+    }
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int W = cam->image_width, H = cam->image_height;
+  const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y, T = gx * gy;
+  ImageView iv = image_view(image_state, W, H);
+  GeomView gv = geom_view(geom_state, P);
+  SPLAT_CUDA(cudaMemsetAsync(iv.tile_count, 0, (size_t)T * 4, st));
+  PreFwdArgs a;
+  a.P = P; a.W = W; a.H = H; a.gx = gx; a.gy = gy; a.M = M; a.sh_degree = cam->sh_degree;
+  a.tanx = cam->tanfovx; a.tany = cam->tanfovy;
+  a.fx = W / (2.0f * cam->tanfovx); a.fy = H / (2.0f * cam->tanfovy);
+  a.mod = cam->scale_modifier; a.near_plane = cam->near_plane;
+  a.means = means3D; a.scales = scales; a.rots = rotations; a.opac = opacities;
+  a.cov3D_pre = cov3D_precomp; a.shs = shs; a.colors_pre = colors_precomp;
+  a.V = cam->viewmatrix; a.Pm = cam->projmatrix; a.campos = cam->campos;
+  a.g = gv; a.tile_count = iv.tile_count; a.radii = radii;
+  if (int rc = launch_preprocess_fwd(a, st)) return rc;
+  return launch_tile_scan(T, iv, num_rendered_dev, (uint32_t)sort_smem_cap(), st);
+}
+
+int splat_forward_render(const SplatCamera* cam, int32_t P, const float* colors_precomp, const int32_t* radii,
+                         const void* geom_state,
+                         void* image_state, void* binning_state, int64_t R_capacity, float* out_color,
+                         float* out_depth, void* stream) {
+  read_env_once();
+  if (int rc = check_cam(cam)) return rc;
+  if (!geom_state || !image_state || !binning_state || !out_color) return fail(SPLAT_ERR_BAD_ARG, "NULL buffer");
+  if (R_capacity < 0 || R_capacity > 0xffffffffll) return fail(SPLAT_ERR_BAD_ARG, "R_capacity out of range");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int W = cam->image_width, H = cam->image_height;
+  const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y, T = gx * gy;
+  ImageView iv = image_view(image_state, W, H);
+  GeomView gv = geom_view(const_cast<void*>(geom_state), P);
+  BinView bv = bin_view(binning_state, R_capacity);
+  const uint32_t Rcap = (uint32_t)R_capacity;
+  if (P > 0 && !radii) return fail(SPLAT_ERR_BAD_ARG, "radii is NULL");
+  if (int rc = launch_scatter(P, gx, gy, radii, gv, iv, bv, Rcap, st)) return rc;
+  if (int rc = launch_tile_sort(T, iv, bv, Rcap, st)) return rc;
+  RenderFwdArgs r;
+  r.W = W; r.H = H; r.gx = gx;
+  r.ranges = iv.ranges; r.point_list = bv.point_list;
+  r.xy = gv.xy; r.conic_opacity = gv.conic_opacity; r.depths = gv.depths;
+  r.colors = colors_precomp ? colors_precomp : gv.rgb;
+  r.bg = cam->bg;
+  r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.out_color = out_color; r.out_depth = out_depth;
+  r.hdr = iv.hdr; r.Rcap = Rcap;
+  return launch_render_fwd(r, T, st);
+}
+
+
+int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* means3D, const float* scales,
+                   const float* rotations, const float* cov3D_precomp, const float* shs, int32_t M,
+                   const float* colors_precomp, const int32_t* radii, const void* geom_state,
+                   const void* image_state, const void* binning_state, const float* dL_dout_color,
+                   int32_t power, int32_t fused, float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors,
+                   float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
+                   float* dL_dconic, float* dL_dsh, void* stream) {
+  read_env_once();
+  if (int rc = check_cam(cam)) return rc;
+  if (P < 0 || R < 0) return fail(SPLAT_ERR_BAD_ARG, "P or R negative");
+  if (P == 0) return SPLAT_OK;
+  if (!means3D || !radii || !geom_state || !image_state || !binning_state || !dL_dout_color)
+    return fail(SPLAT_ERR_BAD_ARG, "NULL input buffer");
+  if (!dL_dmeans3D || !dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dscales || !dL_drotations ||
+      !dL_dcov3D || !dL_dconic)
+    return fail(SPLAT_ERR_BAD_ARG, "NULL gradient buffer");
+  if (shs && !dL_dsh) return fail(SPLAT_ERR_BAD_ARG, "dL_dsh required with SHs");
+  const bool sr = scales && rotations;
+  if (!sr && !cov3D_precomp) return fail(SPLAT_ERR_BAD_ARG, "need scales+rotations or cov3D_precomp");
+  const bool hess = fused && power != 1;
+  if (hess && power != 2)
+    return fail(SPLAT_ERR_UNSUPPORTED, "backward_power must be 1 or 2 (the reference only ever uses those, ros_handler.py:884)");
+  if (hess && shs) return fail(SPLAT_ERR_UNSUPPORTED, "SH + Hessian backward is undefined in the reference (backward.cu:1067)");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int W = cam->image_width, H = cam->image_height;
+  const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y, T = gx * gy;
+  ImageView iv = image_view(const_cast<void*>(image_state), W, H);
+  GeomView gv = geom_view(const_cast<void*>(geom_state), P);
+  BinView bv = bin_view(const_cast<void*>(binning_state), R);
+  const float fx = W / (2.0f * cam->tanfovx), fy = H / (2.0f * cam->tanfovy);
+
+  RenderBwdArgs r;
+  r.W = W; r.H = H; r.gx = gx; r.ranges = iv.ranges; r.point_list = bv.point_list;
+  r.xy = gv.xy; r.conic_opacity = gv.conic_opacity;
+  r.colors = colors_precomp ? colors_precomp : gv.rgb; r.bg = cam->bg;
+  r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.dL_dpix = dL_dout_color;
+  r.dL_dmean2D = dL_dmeans2D; r.dL_dconic = dL_dconic; r.dL_dopacity = dL_dopacity; r.dL_dcolors = dL_dcolors;
+  r.acc = nullptr;
+  if (!hess) {
+    SPLAT_CUDA(cudaMemsetAsync(dL_dmeans2D, 0, (size_t)P * 12, st));
+    SPLAT_CUDA(cudaMemsetAsync(dL_dconic, 0, (size_t)P * 16, st));
+    SPLAT_CUDA(cudaMemsetAsync(dL_dopacity, 0, (size_t)P * 4, st));
+    SPLAT_CUDA(cudaMemsetAsync(dL_dcolors, 0, (size_t)P * 12, st));
+    if (R > 0) if (int rc = launch_render_bwd(r, T, 0, st)) return rc;
+    PreBwdArgs b;
+    b.P = P; b.M = M; b.sh_degree = cam->sh_degree; b.tanx = cam->tanfovx; b.tany = cam->tanfovy;
+    b.fx = fx; b.fy = fy; b.mod = cam->scale_modifier;
+    b.means = means3D; b.scales = sr ? scales : nullptr; b.rots = sr ? rotations : nullptr;
+    b.cov3D_pre = cov3D_precomp; b.shs = shs; b.clamped = gv.clamped; b.campos = cam->campos;
+    b.V = cam->viewmatrix; b.Pm = cam->projmatrix; b.radii = radii;
+    b.dL_dmean2D = dL_dmeans2D; b.dL_dconic = dL_dconic; b.dL_dcolor = dL_dcolors;
+    b.dL_dmeans = dL_dmeans3D; b.dL_dcov3D = dL_dcov3D; b.dL_dscales = dL_dscales; b.dL_drots = dL_drotations;
+    b.dL_dsh = dL_dsh;
+    return launch_preprocess_bwd(b, st);
+  }
+  // Hessian: the [P,20] moment accumulator borrows the keys/keys_alt area of the binning state
+  // (dead after the forward sort) when it is large enough, else the call is refused.
+  const size_t need = (size_t)P * 20 * 4;
+  const size_t have = align_up((size_t)(R > 0 ? R : 1) * 8) * 2;
+  if (have < need)
+    return fail(SPLAT_ERR_SCRATCH_TOO_SMALL, "Hessian accumulator needs %zu bytes, binning state offers %zu", need, have);
+  float* acc = reinterpret_cast<float*>(bv.keys);
+  SPLAT_CUDA(cudaMemsetAsync(acc, 0, need, st));
+  r.acc = acc;
+  if (R > 0) if (int rc = launch_render_bwd(r, T, 1, st)) return rc;
+  HessArgs h;
+  h.P = P; h.tanx = cam->tanfovx; h.tany = cam->tanfovy; h.fx = fx; h.fy = fy; h.mod = cam->scale_modifier;
+  h.means = means3D; h.scales = sr ? scales : nullptr; h.rots = sr ? rotations : nullptr; h.cov3D_pre = cov3D_precomp;
+  h.V = cam->viewmatrix; h.Pm = cam->projmatrix; h.radii = radii; h.acc = acc;
+  h.dL_dmeans = dL_dmeans3D; h.dL_dmean2D = dL_dmeans2D; h.dL_dcolors = dL_dcolors; h.dL_dopacity = dL_dopacity;
+  h.dL_dscales = dL_dscales; h.dL_drots = dL_drotations; h.dL_dcov3D = dL_dcov3D; h.dL_dconic = dL_dconic;
+  return launch_hessian_finalize(h, st);
+}
+
+int splat_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                       float near_plane, uint8_t* present, void* stream) {
+  (void)projmatrix;  // the reference computes p_proj but only tests view-space z (auxiliary.h:150-154)
+  if (P < 0) return fail(SPLAT_ERR_BAD_ARG, "P < 0");
+  if (P == 0) return SPLAT_OK;
+  if (!means3D || !viewmatrix || !present) return fail(SPLAT_ERR_BAD_ARG, "NULL buffer");
+  return launch_mark_visible(P, means3D, viewmatrix, near_plane, present, (cudaStream_t)stream);
+}
+
+const void* splat_state_ranges(const void* s, int32_t W, int32_t H) { return image_view(const_cast<void*>(s), W, H).ranges; }
+const void* splat_state_n_contrib(const void* s, int32_t W, int32_t H) { return image_view(const_cast<void*>(s), W, H).n_contrib; }
+const void* splat_state_final_T(const void* s, int32_t W, int32_t H) { return image_view(const_cast<void*>(s), W, H).final_T; }
+const void* splat_state_point_list(const void* s, int32_t, int32_t, int64_t R) { return bin_view(const_cast<void*>(s), R).point_list; }
+const void* splat_state_depths(const void* s, int32_t P) { return geom_view(const_cast<void*>(s), P).depths; }
+const void* splat_state_means2D(const void* s, int32_t P) { return geom_view(const_cast<void*>(s), P).xy; }
+const void* splat_state_conic_opacity(const void* s, int32_t P) { return geom_view(const_cast<void*>(s), P).conic_opacity; }
+
+int splat_abi_version(void) { return SPLAT_ABI_VERSION; }
+const char* splat_last_error(void) { return g_err; }
+int splat_kernel_launch_count(void) { return g_launch_count; }
+const char* splat_strerror(int code) {
+  switch (code) {
+    case SPLAT_OK: return "ok";
+    case SPLAT_ERR_BAD_ARG: return "bad argument";
+    case SPLAT_ERR_SCRATCH_TOO_SMALL: return "scratch buffer too small";
+    case SPLAT_ERR_UNSUPPORTED: return "unsupported configuration";
+    default: return code >= SPLAT_ERR_CUDA_BASE ? "CUDA runtime error" : "unknown error";
+  }
+}
+
+}  // extern "C"

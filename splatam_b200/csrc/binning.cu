@@ -1,0 +1,285 @@
+// binning.cu -- tile binning without a device-wide sort.
+//
+// The reference bins by (1) prefix-summing tiles_touched over all P Gaussians, (2) emitting one
+// 64-bit key (tile<<32 | depth bits) per instance, (3) a device-wide stable LSD radix sort over
+// 32+log2(T) bits (6 passes at Replica size) and (4) a boundary-detect pass for the tile ranges
+// (HX/cuda_rasterizer/rasterizer_impl.cu:70-138,277-319).  The sorted order that pipeline
+// defines is: by tile, then by depth bits, ties by ascending Gaussian index (emission order +
+// stable sort).  That order is a TOTAL order, so any algorithm that produces it is bit-identical.
+//
+// B200 design: counts per tile are already known after preprocess (RED.ADD in L2), so
+//   tile_scan     one CTA: exclusive scan over T tile counts -> ranges (bit-exact, (0,0) for
+//                 empty tiles as identifyTileRanges leaves them), cursors, R.
+//   scatter       one thread per Gaussian: atomic cursor per tile, writes (depth<<32 | id) into
+//                 the tile's bucket (bucket order is arbitrary, fixed up by the sort).
+//   tile_sort     one CTA per tile: LSD radix sort of the bucket on the depth word inside shared
+//                 memory (only the 8-bit digits that actually vary inside the bucket, typically
+//                 3 of 4), then an exact tie fix-up by Gaussian id; writes point_list.
+// HBM traffic: 8 B/instance write + 8 B read + 4 B write, instead of ~150 B/instance for the
+// 6-pass device-wide sort.  Buckets that do not fit in shared memory take the same code path on
+// global ping-pong buffers.
+#include "kernels.cuh"
+
+namespace splat {
+
+// ------------------------------------------------------------------------------------------ scan
+__global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* __restrict__ tile_count,
+                                                         uint32_t* __restrict__ tile_cursor,
+                                                         uint2* __restrict__ ranges, ImageHeader* hdr,
+                                                         uint32_t* __restrict__ num_rendered_out,
+                                                         uint32_t sort_cap) {
+  __shared__ uint32_t warp_tot[32];
+  __shared__ uint32_t carry_s;
+  __shared__ uint32_t max_s, big_s;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) { carry_s = 0; max_s = 0; big_s = 0; }
+  __syncthreads();
+  uint32_t lmax = 0, lbig = 0;
+  for (int base = 0; base < T; base += 1024) {
+    const int t = base + tid;
+    const uint32_t c = t < T ? tile_count[t] : 0u;
+    lmax = max(lmax, c);
+    lbig += c > sort_cap;
+    uint32_t v = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t n = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += n;
+    }
+    if (lane == 31) warp_tot[wid] = v;
+    __syncthreads();
+    if (wid == 0) {
+      uint32_t w = warp_tot[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= o) w += n;
+      }
+      warp_tot[lane] = w;  // inclusive over warps
+    }
+    __syncthreads();
+    const uint32_t carry = carry_s;
+    const uint32_t incl = carry + v + (wid ? warp_tot[wid - 1] : 0u);
+    if (t < T) {
+      const uint32_t start = incl - c;
+      tile_cursor[t] = start;
+      ranges[t] = c ? make_uint2(start, incl) : make_uint2(0u, 0u);
+    }
+    __syncthreads();
+    if (tid == 1023) carry_s = incl;
+    __syncthreads();
+  }
+  atomicMax(&max_s, lmax);
+  atomicAdd(&big_s, lbig);
+  __syncthreads();
+  if (tid == 0) {
+    hdr->num_rendered = carry_s;
+    hdr->max_tile_count = max_s;
+    hdr->big_tile_count = big_s;
+    *num_rendered_out = carry_s;
+  }
+}
+
+// --------------------------------------------------------------------------------------- scatter
+__global__ void __launch_bounds__(256) scatter_kernel(int P, int gx, int gy, const int* __restrict__ radii,
+                                                      const float2* __restrict__ xy,
+                                                      const float* __restrict__ depths,
+                                                      uint32_t* __restrict__ tile_cursor,
+                                                      uint64_t* __restrict__ keys,
+                                                      const ImageHeader* __restrict__ hdr, uint32_t Rcap) {
+  if (hdr->num_rendered > Rcap) return;  // capacity exceeded: caller re-runs phase 2
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned lane = threadIdx.x & 31u;
+  int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+  uint64_t kv = 0;
+  bool vis = false;
+  if (idx < P) {
+    const int r = radii[idx];
+    if (r > 0) {
+      vis = true;
+      tile_rect(xy[idx], r, gx, gy, x0, y0, x1, y1);
+      kv = ((uint64_t)__float_as_uint(depths[idx]) << 32) | (uint32_t)idx;
+    }
+  }
+  const int ntile = vis ? (x1 - x0) * (y1 - y0) : 0;
+  const bool big = ntile > 32;
+  if (vis && !big) {
+    for (int y = y0; y < y1; ++y)
+      for (int x = x0; x < x1; ++x) {
+        const uint32_t pos = atomicAdd(tile_cursor + y * gx + x, 1u);
+        keys[pos] = kv;
+      }
+  }
+  unsigned bigmask = __ballot_sync(0xffffffffu, big);
+  while (bigmask) {
+    const int src = __ffs(bigmask) - 1;
+    bigmask &= bigmask - 1;
+    const int bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
+    const int bx1 = __shfl_sync(0xffffffffu, x1, src), by1 = __shfl_sync(0xffffffffu, y1, src);
+    const uint64_t bkv = __shfl_sync(0xffffffffu, kv, src);
+    const int w = bx1 - bx0, n = w * (by1 - by0);
+    for (int t = lane; t < n; t += 32) {
+      const uint32_t pos = atomicAdd(tile_cursor + (by0 + t / w) * gx + bx0 + t % w, 1u);
+      keys[pos] = bkv;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------- tile sort
+#define SORT_THREADS 256
+#define SORT_WARPS 8
+
+// One stable LSD pass on digit (key >> shift) & 0xff over n keys, src -> dst (shared or global).
+// hist: SORT_WARPS*256 uint32 in shared memory, layout [digit][warp].
+__device__ __forceinline__ void radix_pass(const uint64_t* src, uint64_t* dst, int n, int shift,
+                                           uint32_t* hist, uint32_t* wsum) {
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  for (int i = tid; i < 256 * SORT_WARPS; i += SORT_THREADS) hist[i] = 0;
+  __syncthreads();
+  // each warp owns a contiguous, 32-aligned slice of the input
+  const int per = ((n + SORT_WARPS - 1) / SORT_WARPS + 31) & ~31;
+  const int lo = min(n, wid * per), hi = min(n, lo + per);
+  for (int i = lo + lane; i < hi; i += 32) {
+    const uint32_t d = (uint32_t)(src[i] >> shift) & 0xffu;
+    atomicAdd(&hist[d * SORT_WARPS + wid], 1u);
+  }
+  __syncthreads();
+  // exclusive scan over 256*SORT_WARPS counters in (digit, warp) order: thread t owns digit t
+  {
+    uint32_t c[SORT_WARPS], tot = 0;
+#pragma unroll
+    for (int w = 0; w < SORT_WARPS; ++w) { c[w] = hist[tid * SORT_WARPS + w]; tot += c[w]; }
+    uint32_t v = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t nn = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += nn;
+    }
+    if (lane == 31) wsum[wid] = v;
+    __syncthreads();
+    uint32_t base = v - tot;
+    for (int w = 0; w < wid; ++w) base += wsum[w];
+#pragma unroll
+    for (int w = 0; w < SORT_WARPS; ++w) { hist[tid * SORT_WARPS + w] = base; base += c[w]; }
+  }
+  __syncthreads();
+  // ranked scatter, warp by warp in input order
+  for (int i0 = lo; i0 < hi; i0 += 32) {
+    const int i = i0 + lane;
+    const bool valid = i < hi;
+    const uint64_t k = valid ? src[i] : 0ull;
+    const uint32_t d = valid ? ((uint32_t)(k >> shift) & 0xffu) : (256u + lane);
+    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    const uint32_t rank = __popc(peers & lanemask_lt());
+    uint32_t base = 0;
+    if (valid) base = hist[d * SORT_WARPS + wid];
+    __syncwarp();
+    if (valid && rank == 0) hist[d * SORT_WARPS + wid] = base + __popc(peers);
+    __syncwarp();
+    if (valid) dst[base + rank] = k;
+  }
+  __syncthreads();
+}
+
+// Sorts bucket `tile` ascending by (depth bits, gaussian id) and writes the ids to point_list.
+// smem_cap = number of keys each of the two shared buffers holds.
+__global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __restrict__ ranges,
+                                                                 uint64_t* __restrict__ keys,
+                                                                 uint64_t* __restrict__ keys_alt,
+                                                                 uint32_t* __restrict__ point_list,
+                                                                 const ImageHeader* __restrict__ hdr,
+                                                                 uint32_t Rcap, int smem_cap) {
+  if (hdr->num_rendered > Rcap) return;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ uint32_t hist[256 * SORT_WARPS];
+  __shared__ uint32_t wsum[SORT_WARPS];
+  __shared__ uint32_t red_or[SORT_WARPS];
+  const uint2 rg = ranges[blockIdx.x];
+  const int n = (int)(rg.y - rg.x);
+  if (n <= 0) return;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  uint64_t* gsrc = keys + rg.x;
+  uint32_t* out = point_list + rg.x;
+  if (n == 1) {
+    if (tid == 0) out[0] = (uint32_t)gsrc[0];
+    return;
+  }
+  uint64_t* bufA;
+  uint64_t* bufB;
+  const bool in_smem = n <= smem_cap;
+  if (in_smem) {
+    bufA = reinterpret_cast<uint64_t*>(smem_raw);
+    bufB = bufA + smem_cap;
+    for (int i = tid; i < n; i += SORT_THREADS) bufA[i] = gsrc[i];
+  } else {
+    bufA = gsrc;
+    bufB = keys_alt + rg.x;
+  }
+  __syncthreads();
+  // which depth bits vary inside this bucket?
+  const uint32_t k0 = (uint32_t)(bufA[0] >> 32);
+  uint32_t diff = 0;
+  for (int i = tid; i < n; i += SORT_THREADS) diff |= (uint32_t)(bufA[i] >> 32) ^ k0;
+  diff = __reduce_or_sync(0xffffffffu, diff);
+  if (lane == 0) red_or[wid] = diff;
+  __syncthreads();
+  diff = 0;
+#pragma unroll
+  for (int w = 0; w < SORT_WARPS; ++w) diff |= red_or[w];
+  uint64_t* src = bufA;
+  uint64_t* dst = bufB;
+  if (diff) {
+    const int lo_bit = __ffs(diff) - 1, hi_bit = 31 - __clz(diff);
+    for (int sh = lo_bit; sh <= hi_bit; sh += 8) {
+      radix_pass(src, dst, n, 32 + sh, hist, wsum);
+      uint64_t* t = src; src = dst; dst = t;
+    }
+  }
+  // exact tie fix-up: inside a run of equal depth bits order by ascending gaussian id
+  for (int i = tid; i < n; i += SORT_THREADS) {
+    const uint64_t k = src[i];
+    const uint32_t d = (uint32_t)(k >> 32), id = (uint32_t)k;
+    int pos = i;
+    const bool tl = i > 0 && (uint32_t)(src[i - 1] >> 32) == d;
+    const bool tr = i + 1 < n && (uint32_t)(src[i + 1] >> 32) == d;
+    if (tl || tr) {
+      int lo = i, below = 0;
+      while (lo > 0 && (uint32_t)(src[lo - 1] >> 32) == d) { --lo; below += (uint32_t)src[lo] < id; }
+      int hi = i + 1;
+      while (hi < n && (uint32_t)(src[hi] >> 32) == d) { below += (uint32_t)src[hi] < id; ++hi; }
+      pos = lo + below;
+    }
+    out[pos] = id;
+  }
+}
+
+int launch_tile_scan(int T, const ImageView& iv, uint32_t* num_rendered_out, uint32_t sort_cap, cudaStream_t st) {
+  tile_scan_kernel<<<1, 1024, 0, st>>>(T, iv.tile_count, iv.tile_cursor, iv.ranges, iv.hdr, num_rendered_out, sort_cap);
+  SPLAT_LAUNCH_CHECK("tile_scan_kernel");
+  return SPLAT_OK;
+}
+
+int launch_scatter(int P, int gx, int gy, const int* radii, const GeomView& g, const ImageView& iv,
+                   const BinView& b, uint32_t Rcap, cudaStream_t st) {
+  if (P <= 0) return SPLAT_OK;
+  scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, gx, gy, radii, g.xy, g.depths, iv.tile_cursor, b.keys, iv.hdr, Rcap);
+  SPLAT_LAUNCH_CHECK("scatter_kernel");
+  return SPLAT_OK;
+}
+
+static const int kSortSmemCap = 4096;  // keys per shared buffer (2 x 32 KB)
+int sort_smem_cap() { return kSortSmemCap; }
+
+int launch_tile_sort(int T, const ImageView& iv, const BinView& b, uint32_t Rcap, cudaStream_t st) {
+  static bool attr_set = false;
+  const int smem = kSortSmemCap * 8 * 2;
+  if (!attr_set) {
+    SPLAT_CUDA(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  tile_sort_kernel<<<T, SORT_THREADS, smem, st>>>(iv.ranges, b.keys, b.keys_alt, b.point_list, iv.hdr, Rcap, kSortSmemCap);
+  SPLAT_LAUNCH_CHECK("tile_sort_kernel");
+  return SPLAT_OK;
+}
+
+}  // namespace splat

@@ -1,0 +1,217 @@
+// common.cuh -- shared device helpers, state layouts and launch bookkeeping for libsplat_b200.
+//
+// sm_100a only.  The math helpers restate the per-Gaussian projection algebra of the reference
+// (HX/cuda_rasterizer/forward.cu:74-152, auxiliary.h:41-77,139-163) with a small column-major
+// mat3 type of our own (the reference uses glm; element [c][r] == column c, row r, SURVEY.md
+// Appendix A).  Expression trees are kept in the reference's association order on purpose:
+// radii / tile rects must come out bit-identical, and nvcc's FMA contraction follows the tree.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/splat_b200.h"
+
+#define TILE_X 16
+#define TILE_Y 16
+#define TILE_PIX 256
+#define NUM_CH 3
+
+namespace splat {
+
+// ---------------------------------------------------------------- launch bookkeeping
+extern int g_launch_count;
+inline void count_launch(int n = 1) { g_launch_count += n; }
+
+// ---------------------------------------------------------------- state layouts
+__host__ __device__ inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+struct GeomView {
+  float* depths;          // [P] view-space z
+  float2* xy;             // [P] pixel-space mean
+  float4* conic_opacity;  // [P] (A, B, C, opacity)
+  float* rgb;             // [P,3] SH-evaluated colours (SH path only)
+  uint8_t* clamped;       // [P,3] SH clamp flags
+};
+inline size_t geom_bytes(int P) {
+  size_t p = (size_t)(P > 0 ? P : 1);
+  return align_up(p * 4) + align_up(p * 8) + align_up(p * 16) + align_up(p * 12) + align_up(p * 3);
+}
+inline GeomView geom_view(void* base, int P) {
+  size_t p = (size_t)(P > 0 ? P : 1);
+  char* c = (char*)base;
+  GeomView v;
+  v.depths = (float*)c;          c += align_up(p * 4);
+  v.xy = (float2*)c;             c += align_up(p * 8);
+  v.conic_opacity = (float4*)c;  c += align_up(p * 16);
+  v.rgb = (float*)c;             c += align_up(p * 12);
+  v.clamped = (uint8_t*)c;
+  return v;
+}
+
+struct ImageHeader {          // first 256 bytes of the image state
+  uint32_t num_rendered;      // R, written by tile_scan
+  uint32_t max_tile_count;    // longest tile list
+  uint32_t big_tile_count;    // number of tiles over the smem sort capacity
+  uint32_t pad[61];
+};
+struct ImageView {
+  ImageHeader* hdr;
+  uint32_t* tile_count;   // [T] instances per tile (atomics in preprocess)
+  uint32_t* tile_cursor;  // [T] scatter cursors (start .. end)
+  uint2* ranges;          // [T] (start,end) -- bit-exact vs identifyTileRanges
+  float* final_T;         // [N]
+  uint32_t* n_contrib;    // [N]
+};
+inline int num_tiles(int W, int H) { return ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y); }
+inline size_t image_bytes(int W, int H) {
+  size_t T = (size_t)num_tiles(W, H), N = (size_t)W * H;
+  return 256 + align_up(T * 4) * 2 + align_up(T * 8) + align_up(N * 4) * 2;
+}
+inline ImageView image_view(void* base, int W, int H) {
+  size_t T = (size_t)num_tiles(W, H), N = (size_t)W * H;
+  char* c = (char*)base;
+  ImageView v;
+  v.hdr = (ImageHeader*)c;     c += 256;
+  v.tile_count = (uint32_t*)c; c += align_up(T * 4);
+  v.tile_cursor = (uint32_t*)c;c += align_up(T * 4);
+  v.ranges = (uint2*)c;        c += align_up(T * 8);
+  v.final_T = (float*)c;       c += align_up(N * 4);
+  v.n_contrib = (uint32_t*)c;
+  return v;
+}
+
+struct BinView {
+  uint64_t* keys;        // [Rcap] (depth_bits << 32) | gaussian id, bucketed by tile (unsorted in-bucket)
+  uint64_t* keys_alt;    // [Rcap] ping-pong buffer for lists that do not fit in shared memory
+  uint32_t* point_list;  // [Rcap] sorted gaussian ids
+};
+inline size_t bin_bytes(int64_t Rcap) {
+  size_t r = (size_t)(Rcap > 0 ? Rcap : 1);
+  return align_up(r * 8) * 2 + align_up(r * 4);
+}
+inline BinView bin_view(void* base, int64_t Rcap) {
+  size_t r = (size_t)(Rcap > 0 ? Rcap : 1);
+  char* c = (char*)base;
+  BinView v;
+  v.keys = (uint64_t*)c;      c += align_up(r * 8);
+  v.keys_alt = (uint64_t*)c;  c += align_up(r * 8);
+  v.point_list = (uint32_t*)c;
+  return v;
+}
+
+// ---------------------------------------------------------------- small math
+struct Mat3 {  // column-major: m[c][r]
+  float m[3][3];
+};
+// R = A * B (math product), R[c][r] = sum_k A[k][r] * B[c][k], k ascending.
+__device__ __forceinline__ Mat3 mat_mul(const Mat3& A, const Mat3& B) {
+  Mat3 R;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+      R.m[c][r] = A.m[0][r] * B.m[c][0] + A.m[1][r] * B.m[c][1] + A.m[2][r] * B.m[c][2];
+  return R;
+}
+__device__ __forceinline__ Mat3 mat_transpose(const Mat3& A) {
+  Mat3 R;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int r = 0; r < 3; ++r) R.m[c][r] = A.m[r][c];
+  return R;
+}
+
+// point (x,y,z,1) through a "transposed" 4x4: rows 0..2 (HX auxiliary.h:58-66)
+__device__ __forceinline__ float3 xform_point_4x3(const float3 p, const float* __restrict__ m) {
+  float3 t;
+  t.x = m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12];
+  t.y = m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13];
+  t.z = m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14];
+  return t;
+}
+__device__ __forceinline__ float4 xform_point_4x4(const float3 p, const float* __restrict__ m) {
+  float4 t;
+  t.x = m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12];
+  t.y = m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13];
+  t.z = m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14];
+  t.w = m[3] * p.x + m[7] * p.y + m[11] * p.z + m[15];
+  return t;
+}
+
+// NDC -> pixel; the reference evaluates this in double (auxiliary.h:41-44) and we must too.
+__device__ __forceinline__ float ndc_to_pix(float v, int S) { return ((v + 1.0) * S - 1.0) * 0.5; }
+
+// Tile rectangle touched by a splat of integer radius r centred at p (auxiliary.h:46-56).
+__device__ __forceinline__ void tile_rect(const float2 p, int r, int gx, int gy, int& x0, int& y0,
+                                          int& x1, int& y1) {
+  x0 = min(gx, max(0, (int)((p.x - r) / TILE_X)));
+  y0 = min(gy, max(0, (int)((p.y - r) / TILE_Y)));
+  x1 = min(gx, max(0, (int)((p.x + r + TILE_X - 1) / TILE_X)));
+  y1 = min(gy, max(0, (int)((p.y + r + TILE_Y - 1) / TILE_Y)));
+}
+
+// Sigma = (S R)^T (S R) from scale*mod and UN-normalised quaternion (w,x,y,z)
+// (forward.cu:118-152).  Output: upper triangle xx,xy,xz,yy,yz,zz.
+__device__ __forceinline__ void cov3d_from_scale_rot(const float3 s, float mod, const float4 q,
+                                                     float* cov) {
+  Mat3 S = {{{mod * s.x, 0.f, 0.f}, {0.f, mod * s.y, 0.f}, {0.f, 0.f, mod * s.z}}};
+  const float r = q.x, x = q.y, y = q.z, z = q.w;
+  Mat3 R = {{{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+             {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+             {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}}};
+  Mat3 Mx = mat_mul(S, R);
+  Mat3 Sg = mat_mul(mat_transpose(Mx), Mx);
+  cov[0] = Sg.m[0][0]; cov[1] = Sg.m[0][1]; cov[2] = Sg.m[0][2];
+  cov[3] = Sg.m[1][1]; cov[4] = Sg.m[1][2]; cov[5] = Sg.m[2][2];
+}
+
+// EWA 2D covariance (forward.cu:74-113): returns (a, b, c) with the +0.3 dilation applied.
+__device__ __forceinline__ float3 cov2d_ewa(const float3 mean, float fx, float fy, float tanx,
+                                            float tany, const float* cov3D,
+                                            const float* __restrict__ V) {
+  float3 t = xform_point_4x3(mean, V);
+  const float limx = 1.3f * tanx, limy = 1.3f * tany;
+  const float txtz = t.x / t.z, tytz = t.y / t.z;
+  t.x = fminf(limx, fmaxf(-limx, txtz)) * t.z;
+  t.y = fminf(limy, fmaxf(-limy, tytz)) * t.z;
+  Mat3 J = {{{fx / t.z, 0.f, -(fx * t.x) / (t.z * t.z)},
+             {0.f, fy / t.z, -(fy * t.y) / (t.z * t.z)},
+             {0.f, 0.f, 0.f}}};
+  Mat3 Wm = {{{V[0], V[4], V[8]}, {V[1], V[5], V[9]}, {V[2], V[6], V[10]}}};
+  Mat3 Tm = mat_mul(Wm, J);
+  Mat3 Vrk = {{{cov3D[0], cov3D[1], cov3D[2]}, {cov3D[1], cov3D[3], cov3D[4]}, {cov3D[2], cov3D[4], cov3D[5]}}};
+  Mat3 c = mat_mul(mat_mul(mat_transpose(Tm), mat_transpose(Vrk)), Tm);
+  return make_float3(c.m[0][0] + 0.3f, c.m[0][1], c.m[1][1] + 0.3f);
+}
+
+// ---------------------------------------------------------------- warp helpers
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ unsigned lanemask_lt() {
+  unsigned m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+
+}  // namespace splat
+
+// ---------------------------------------------------------------- error plumbing (api.cu)
+namespace splat {
+int fail(int code, const char* fmt, ...);
+int check_cuda(cudaError_t e, const char* what);
+}  // namespace splat
+#define SPLAT_CUDA(x)                                           \
+  do {                                                          \
+    int _rc = splat::check_cuda((x), #x);                       \
+    if (_rc) return _rc;                                        \
+  } while (0)
+#define SPLAT_LAUNCH_CHECK(name)                                \
+  do {                                                          \
+    int _rc = splat::check_cuda(cudaGetLastError(), name);      \
+    if (_rc) return _rc;                                        \
+    splat::count_launch();                                      \
+  } while (0)

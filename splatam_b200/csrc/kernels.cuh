@@ -1,0 +1,68 @@
+// kernels.cuh -- argument blocks and host-side launchers of every kernel in libsplat_b200.
+#pragma once
+#include "common.cuh"
+
+namespace splat {
+
+struct PreFwdArgs {
+  int P, W, H, gx, gy, M, sh_degree;
+  float tanx, tany, fx, fy, mod, near_plane;
+  const float* means; const float* scales; const float* rots; const float* opac;
+  const float* cov3D_pre; const float* shs; const float* colors_pre;
+  const float* V; const float* Pm; const float* campos;
+  GeomView g; uint32_t* tile_count; int* radii;
+};
+
+struct PreBwdArgs {
+  int P, M, sh_degree;
+  float tanx, tany, fx, fy, mod;
+  const float* means; const float* scales; const float* rots; const float* cov3D_pre;
+  const float* shs; const uint8_t* clamped; const float* campos;
+  const float* V; const float* Pm; const int* radii;
+  const float* dL_dmean2D;  // [P,3]
+  const float* dL_dconic;   // [P,4]
+  const float* dL_dcolor;   // [P,3] (SH backward input)
+  float* dL_dmeans; float* dL_dcov3D; float* dL_dscales; float* dL_drots; float* dL_dsh;
+};
+
+struct HessArgs {
+  int P;
+  float tanx, tany, fx, fy, mod;
+  const float* means; const float* scales; const float* rots; const float* cov3D_pre;
+  const float* V; const float* Pm; const int* radii; const float* acc;
+  float* dL_dmeans; float* dL_dmean2D; float* dL_dcolors; float* dL_dopacity;
+  float* dL_dscales; float* dL_drots; float* dL_dcov3D; float* dL_dconic;
+};
+
+struct RenderFwdArgs {
+  int W, H, gx;
+  const uint2* ranges; const uint32_t* point_list;
+  const float2* xy; const float4* conic_opacity; const float* depths; const float* colors;
+  const float* bg;
+  float* final_T; uint32_t* n_contrib; float* out_color; float* out_depth;
+  const ImageHeader* hdr; uint32_t Rcap;
+};
+
+struct RenderBwdArgs {
+  int W, H, gx;
+  const uint2* ranges; const uint32_t* point_list;
+  const float2* xy; const float4* conic_opacity; const float* colors; const float* bg;
+  const float* final_T; const uint32_t* n_contrib; const float* dL_dpix;
+  float* acc;   // MODE 0: unused.  MODE 1: [P,20] moment accumulator
+  float* dL_dmean2D; float* dL_dconic; float* dL_dopacity; float* dL_dcolors;
+};
+
+int launch_preprocess_fwd(const PreFwdArgs& a, cudaStream_t st);
+int launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t st);
+int launch_hessian_finalize(const HessArgs& a, cudaStream_t st);
+int launch_mark_visible(int P, const float* means, const float* V, float near_plane, uint8_t* present, cudaStream_t st);
+int launch_tile_scan(int T, const ImageView& iv, uint32_t* num_rendered_out, uint32_t sort_cap, cudaStream_t st);
+int launch_scatter(int P, int gx, int gy, const int* radii, const GeomView& g, const ImageView& iv,
+                   const BinView& b, uint32_t Rcap, cudaStream_t st);
+int launch_tile_sort(int T, const ImageView& iv, const BinView& b, uint32_t Rcap, cudaStream_t st);
+int sort_smem_cap();
+int launch_render_fwd(const RenderFwdArgs& a, int T, cudaStream_t st);
+int launch_render_bwd(const RenderBwdArgs& a, int T, int mode, cudaStream_t st);
+extern int g_disable_cull;
+
+}  // namespace splat

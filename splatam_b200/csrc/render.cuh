@@ -1,0 +1,60 @@
+// render.cuh -- pieces shared by the forward and backward blend kernels.
+//
+// Tile = 16x16 pixels, CTA = 256 threads = 8 warps (same tile semantics as the reference,
+// HX/cuda_rasterizer/config.h:15-17, so tile-rect culling is identical), but the thread->pixel
+// map is ours: warp w owns the 8x4 sub-tile (w&1, w>>1) so that a warp can reject a whole
+// Gaussian whose footprint misses its 32 pixels with ONE lane-parallel test + ballot.
+#pragma once
+#include "common.cuh"
+
+namespace splat {
+
+#define BATCH 256
+
+struct SubTile {
+  int px, py;        // this lane's pixel
+  float fx0, fx1;    // sub-tile x extent [fx0, fx1] in pixel coordinates
+  float fy0, fy1;
+};
+
+__device__ __forceinline__ SubTile make_subtile(int tile_x, int tile_y) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  SubTile s;
+  const int sx0 = tile_x * TILE_X + (wid & 1) * 8;
+  const int sy0 = tile_y * TILE_Y + (wid >> 1) * 4;
+  s.px = sx0 + (lane & 7);
+  s.py = sy0 + (lane >> 3);
+  s.fx0 = (float)sx0; s.fx1 = (float)(sx0 + 7);
+  s.fy0 = (float)sy0; s.fy1 = (float)(sy0 + 3);
+  return s;
+}
+
+// Conservative screen-space bounding box of the set of pixels at which the reference's tests
+//   power <= 0  &&  min(0.99, o*exp(power)) >= 1/255        (forward.cu:341-350)
+// can pass, as (xmin, xmax, ymin, ymax).  The level set power >= -tau, tau = ln(255 o), is the
+// ellipse d^T Q d <= 2 tau whose half extents are sqrt(2 tau C/det), sqrt(2 tau A/det).  Margins:
+//  * tau is padded by the worst-case float error of `power` over the tile (cancellation between
+//    the three quadratic terms), of expf and of the product;
+//  * ill-conditioned conics (det tiny vs A*C, where the rounded conic may not even be positive
+//    definite) are never culled: their box is infinite.
+// A pair outside the box is guaranteed to be skipped by the reference, so skipping it here is
+// exact (n_contrib, T and colours are unchanged).
+__device__ __forceinline__ float4 cull_box(const float2 xy, const float4 co, float tile_cx, float tile_cy) {
+  const float A = co.x, B = co.y, C = co.z, o = co.w;
+  const float inf = __int_as_float(0x7f800000);
+  if (o < 1.0f / 255.0f) return make_float4(inf, -inf, inf, -inf);  // can never reach 1/255
+  const float det = A * C - B * B;
+  if (!(A > 0.f && C > 0.f && det > 1e-3f * A * C)) return make_float4(-inf, inf, -inf, inf);
+  const float Dx = fabsf(xy.x - tile_cx) + 8.5f, Dy = fabsf(xy.y - tile_cy) + 8.5f;
+  const float delta = 1e-6f * (A * Dx * Dx + C * Dy * Dy + 2.f * fabsf(B) * Dx * Dy);
+  const float tau = __logf(255.0f * o) * 1.00001f + 1e-4f + delta;
+  const float k = 2.004f * tau / det;
+  const float ex = sqrtf(k * C) + 0.01f, ey = sqrtf(k * A) + 0.01f;
+  return make_float4(xy.x - ex, xy.x + ex, xy.y - ey, xy.y + ey);
+}
+
+__device__ __forceinline__ bool box_hits(const float4 bb, const SubTile& s) {
+  return bb.y >= s.fx0 && bb.x <= s.fx1 && bb.w >= s.fy0 && bb.z <= s.fy1;
+}
+
+}  // namespace splat

@@ -1,0 +1,291 @@
+"""Host-side mirror of the reference rasterizer's Python API on top of libsplat_b200.
+
+Same names, argument meaning, exception texts and gradient order as
+HX/hessian_diff_gaussian_rasterization_w_depth/__init__.py:17-204 (and the DG twin,
+DG/diff_gaussian_rasterization/__init__.py), so `scripts/splatam.py` and `scripts/ros_handler.py`
+run unchanged.  PyTorch is only plumbing here: it owns device memory and the stream; every kernel
+is in libsplat_b200.so and is reached through the C ABI (splatam_b200/_lib.py).
+
+What is different from the reference host code, by design:
+  * no blocking `cudaMemcpy` of num_rendered in the middle of the forward
+    (HX/cuda_rasterizer/rasterizer_impl.cu:281-282): phase 2 is launched speculatively into a
+    binning buffer sized from the previous call's R; the host only waits for the 4-byte R that
+    phase 1 produced (the GPU is already busy with phase 2 by then) and relaunches phase 2 in the
+    rare case the capacity was exceeded;
+  * one flat gradient allocation per backward instead of nine `torch::zeros`
+    (HX/rasterize_points.cu:151-159).
+"""
+import ctypes as C
+import threading
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from ._lib import SplatCamera, check, lib
+
+NEAR_DG = 0.2     # DG/cuda_rasterizer/auxiliary.h:154
+NEAR_HX = 0.001   # HX/cuda_rasterizer/auxiliary.h:154
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+
+
+_tls = threading.local()
+_capacity_hint = {}   # (device index, H, W) -> last num_rendered
+
+
+def _pinned_scalar(device):
+    cache = getattr(_tls, "pinned", None)
+    if cache is None:
+        cache = _tls.pinned = {}
+    key = device.index
+    if key not in cache:
+        cache[key] = torch.zeros(1, dtype=torch.int32).pin_memory()
+    return cache[key]
+
+
+def _f32(t, name):
+    if t.dtype != torch.float32:
+        raise RuntimeError("%s must be float32, got %s" % (name, t.dtype))
+    if not t.is_cuda:
+        raise RuntimeError("%s must be a CUDA tensor" % name)
+    return t.contiguous()
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None and t.numel() > 0 else C.c_void_p(0)
+
+
+def _camera(rs, near, keep):
+    cam = SplatCamera()
+    cam.image_height = int(rs.image_height)
+    cam.image_width = int(rs.image_width)
+    cam.tanfovx = float(rs.tanfovx)
+    cam.tanfovy = float(rs.tanfovy)
+    bg = _f32(rs.bg, "bg")
+    vm = _f32(rs.viewmatrix, "viewmatrix")
+    pm = _f32(rs.projmatrix, "projmatrix")
+    keep += [bg, vm, pm]
+    cam.bg = bg.data_ptr()
+    cam.scale_modifier = float(rs.scale_modifier)
+    cam.viewmatrix = vm.data_ptr()
+    cam.projmatrix = pm.data_ptr()
+    cam.sh_degree = int(rs.sh_degree)
+    if rs.campos is not None and rs.campos.numel() >= 3 and rs.campos.is_cuda:
+        cp = _f32(rs.campos, "campos")
+        keep.append(cp)
+        cam.campos = cp.data_ptr()
+    else:
+        cam.campos = None
+    cam.prefiltered = int(bool(rs.prefiltered))
+    cam.near_plane = float(near)
+    return cam
+
+
+class RasterState:
+    """Opaque per-call state saved for the backward pass (the reference's geomBuffer /
+    binningBuffer / imgBuffer byte tensors, HX/rasterize_points.cu:73-78)."""
+    __slots__ = ("geom", "image", "binning", "capacity", "num_rendered", "P", "H", "W")
+
+
+def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rotations, cov3D_precomp, sh):
+    """Runs both forward phases.  Returns (color, radii, depth, RasterState)."""
+    if means3D.dim() != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    dev = means3D.device
+    P = means3D.shape[0]
+    H, W = int(rs.image_height), int(rs.image_width)
+    st = RasterState()
+    st.P, st.H, st.W = P, H, W
+    if P == 0:  # HX/rasterize_points.cu:81 -- outputs stay at their fill value 0
+        st.geom = st.image = st.binning = torch.empty(0, dtype=torch.uint8, device=dev)
+        st.capacity = st.num_rendered = 0
+        return (torch.zeros(3, H, W, device=dev), torch.zeros(0, dtype=torch.int32, device=dev),
+                torch.zeros(1, H, W, device=dev), st)
+    keep = []
+    cam = _camera(rs, near, keep)
+    with torch.cuda.device(dev):
+        stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        M = sh.shape[1] if sh.numel() else 0
+        out_color = torch.empty(3, H, W, dtype=torch.float32, device=dev)
+        out_depth = torch.empty(1, H, W, dtype=torch.float32, device=dev)
+        radii = torch.empty(P, dtype=torch.int32, device=dev)
+        st.geom = torch.empty(lib.splat_geom_state_bytes(P), dtype=torch.uint8, device=dev)
+        st.image = torch.empty(lib.splat_image_state_bytes(W, H), dtype=torch.uint8, device=dev)
+        nr_dev = torch.empty(1, dtype=torch.int32, device=dev)
+        check(lib.splat_forward_geometry(C.byref(cam), P, _ptr(means3D), _ptr(scales), _ptr(rotations),
+                                         _ptr(opacities), _ptr(cov3D_precomp), _ptr(sh), M,
+                                         _ptr(colors_precomp), _ptr(st.geom), _ptr(st.image), _ptr(radii),
+                                         _ptr(nr_dev), stream))
+        pinned = _pinned_scalar(dev)
+        pinned.copy_(nr_dev, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+
+        def phase2(cap):
+            st.capacity = cap
+            st.binning = torch.empty(lib.splat_binning_state_bytes(W, H, cap), dtype=torch.uint8, device=dev)
+            check(lib.splat_forward_render(C.byref(cam), P, _ptr(colors_precomp), _ptr(radii), _ptr(st.geom),
+                                           _ptr(st.image), _ptr(st.binning), cap, _ptr(out_color),
+                                           _ptr(out_depth), stream))
+
+        key = (dev.index, H, W)
+        hint = _capacity_hint.get(key)
+        launched = False
+        if hint is not None:
+            phase2(int(hint * 1.25) + 65536)
+            launched = True
+        ev.synchronize()
+        R = int(pinned.item())
+        _capacity_hint[key] = R
+        if not launched or R > st.capacity:
+            phase2(max(R, 1))
+        st.num_rendered = R
+    return out_color, radii, out_depth, st
+
+
+def rasterize_backward(rs, near, st, power, fused, means3D, colors_precomp, scales, rotations,
+                       cov3D_precomp, sh, radii, grad_out_color):
+    dev = means3D.device
+    P = st.P
+    M = sh.shape[1] if sh.numel() else 0
+    n_fixed = 3 + 3 + 3 + 1 + 3 + 4 + 6 + 4
+    with torch.cuda.device(dev):
+        flat = torch.empty(P * (n_fixed + 3 * M), dtype=torch.float32, device=dev)
+        off = 0
+
+        def take(k, shape):
+            nonlocal off
+            v = flat[off:off + P * k].view(shape)
+            off += P * k
+            return v
+        g_means3D = take(3, (P, 3)); g_means2D = take(3, (P, 3)); g_colors = take(3, (P, 3))
+        g_opac = take(1, (P, 1)); g_scales = take(3, (P, 3)); g_rots = take(4, (P, 4))
+        g_cov3D = take(6, (P, 6)); g_conic = take(4, (P, 2, 2)); g_sh = take(3 * M, (P, M, 3))
+        if P == 0:
+            return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D
+        keep = []
+        cam = _camera(rs, near, keep)
+        stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        grad = _f32(grad_out_color, "grad_out_color")
+        check(lib.splat_backward(C.byref(cam), P, st.capacity, _ptr(means3D), _ptr(scales), _ptr(rotations),
+                                 _ptr(cov3D_precomp), _ptr(sh), M, _ptr(colors_precomp), _ptr(radii),
+                                 _ptr(st.geom), _ptr(st.image), _ptr(st.binning), _ptr(grad),
+                                 int(power), int(bool(fused)),
+                                 _ptr(g_means3D), _ptr(g_means2D), _ptr(g_colors), _ptr(g_opac), _ptr(g_scales),
+                                 _ptr(g_rots), _ptr(g_cov3D), _ptr(g_conic), _ptr(g_sh), stream))
+    return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                raster_settings, backward_power, near, fused):
+        # the reference passes tensors through .contiguous() (HX/rasterize_points.cu:94-112)
+        means3D = _f32(means3D, "means3D")
+        opacities = _f32(opacities, "opacities")
+        sh = sh.contiguous()
+        colors_precomp = colors_precomp.contiguous()
+        scales = scales.contiguous()
+        rotations = rotations.contiguous()
+        cov3Ds_precomp = cov3Ds_precomp.contiguous()
+        for name, t in (("sh", sh), ("colors_precomp", colors_precomp), ("scales", scales),
+                        ("rotations", rotations), ("cov3D_precomp", cov3Ds_precomp)):
+            if t.numel() and (t.dtype != torch.float32 or not t.is_cuda):
+                raise RuntimeError("%s must be a float32 CUDA tensor" % name)
+        color, radii, depth, st = rasterize_forward(raster_settings, near, means3D, colors_precomp, opacities,
+                                                    scales, rotations, cov3Ds_precomp, sh)
+        ctx.raster_settings = raster_settings
+        ctx.num_rendered = st.num_rendered
+        ctx.backward_power = backward_power
+        ctx.state = st
+        ctx.near = near
+        ctx.fused = fused
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh)
+        return color, radii, depth
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _grad_radii, _grad_depth):
+        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh = ctx.saved_tensors
+        if grad_out_color is None:
+            grad_out_color = torch.zeros(3, ctx.state.H, ctx.state.W, device=means3D.device)
+        (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D) = rasterize_backward(
+            ctx.raster_settings, ctx.near, ctx.state, ctx.backward_power, ctx.fused, means3D, colors_precomp,
+            scales, rotations, cov3Ds_precomp, sh, radii, grad_out_color)
+        return (g_means3D, g_means2D,
+                g_sh if sh.numel() else None,
+                g_colors if colors_precomp.numel() else None,
+                g_opac,
+                g_scales if scales.numel() else None,
+                g_rots if rotations.numel() else None,
+                g_cov3D if cov3Ds_precomp.numel() else None,
+                None, None, None, None)
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                        raster_settings, backward_power=1, near=NEAR_HX, fused=True):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                     cov3Ds_precomp, raster_settings, backward_power, near, fused)
+
+
+class GaussianRasterizer(nn.Module):
+    """Drop-in for both reference `GaussianRasterizer` classes.  `NEAR_PLANE` / `FUSED_BACKWARD` are
+    set by the import-name packages (diff_gaussian_rasterization: 0.2 / DG two-stage backward;
+    hessian_diff_gaussian_rasterization_w_depth: 0.001 / HX fused semantics with backward_power)."""
+    NEAR_PLANE = NEAR_HX
+    FUSED_BACKWARD = True
+
+    def __init__(self, raster_settings, backward_power: int = 1):
+        super().__init__()
+        self.raster_settings = raster_settings
+        self.backward_power = backward_power
+
+    def markVisible(self, positions):
+        with torch.no_grad():
+            rs = self.raster_settings
+            positions = _f32(positions, "positions")
+            P = positions.shape[0]
+            present = torch.zeros(P, dtype=torch.bool, device=positions.device)
+            if P:
+                vm = _f32(rs.viewmatrix, "viewmatrix")
+                pm = _f32(rs.projmatrix, "projmatrix")
+                with torch.cuda.device(positions.device):
+                    check(lib.splat_mark_visible(P, _ptr(positions), _ptr(vm), _ptr(pm), float(self.NEAR_PLANE),
+                                                 _ptr(present), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        return present
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None):
+        raster_settings = self.raster_settings
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        empty = torch.Tensor([])
+        if shs is None:
+            shs = empty
+        if colors_precomp is None:
+            colors_precomp = empty
+        if scales is None:
+            scales = empty
+        if rotations is None:
+            rotations = empty
+        if cov3D_precomp is None:
+            cov3D_precomp = empty
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
+                                   cov3D_precomp, raster_settings, self.backward_power, self.NEAR_PLANE,
+                                   self.FUSED_BACKWARD)
