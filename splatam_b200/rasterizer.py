@@ -45,6 +45,7 @@ class GaussianRasterizationSettings(NamedTuple):
 
 _tls = threading.local()
 _capacity_hint = {}   # (device index, H, W) -> last num_rendered
+_CAP_GROWTH, _CAP_SLACK = 1.25, 65536   # speculative binning capacity = hint * growth + slack
 
 
 def _pinned_scalar(device):
@@ -100,6 +101,30 @@ class RasterState:
     binningBuffer / imgBuffer byte tensors, HX/rasterize_points.cu:73-78)."""
     __slots__ = ("geom", "image", "binning", "capacity", "num_rendered", "P", "H", "W")
 
+    def _view(self, buf, ptr, nbytes, dtype):
+        off = ptr - buf.data_ptr()
+        return buf[off:off + nbytes].view(dtype)
+
+    def views(self):
+        """Typed views into the state for the parity tests (splat_state_* of the C ABI):
+        ranges int32[T,2], n_contrib int32[H,W], final_T float32[H,W], point_list int32[R],
+        depths float32[P], means2D float32[P,2], conic_opacity float32[P,4]."""
+        W, H, P, R = self.W, self.H, self.P, self.num_rendered
+        T = ((W + 15) // 16) * ((H + 15) // 16)
+        img, geo, bn = self.image, self.geom, self.binning
+        ip, gp, bp = C.c_void_p(img.data_ptr()), C.c_void_p(geo.data_ptr()), C.c_void_p(bn.data_ptr())
+        return dict(
+            ranges=self._view(img, lib.splat_state_ranges(ip, W, H), 8 * T, torch.int32).view(T, 2),
+            n_contrib=self._view(img, lib.splat_state_n_contrib(ip, W, H), 4 * W * H, torch.int32).view(H, W),
+            final_T=self._view(img, lib.splat_state_final_T(ip, W, H), 4 * W * H, torch.float32).view(H, W),
+            point_list=self._view(bn, lib.splat_state_point_list(bp, W, H, self.capacity), 4 * R, torch.int32),
+            depths=self._view(geo, lib.splat_state_depths(gp, P), 4 * P, torch.float32),
+            means2D=self._view(geo, lib.splat_state_means2D(gp, P), 8 * P, torch.float32).view(P, 2),
+            conic_opacity=self._view(geo, lib.splat_state_conic_opacity(gp, P), 16 * P, torch.float32).view(P, 4))
+
+
+last_state = None   # most recent RasterState (debug / parity tests only)
+
 
 def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rotations, cov3D_precomp, sh):
     """Runs both forward phases.  Returns (color, radii, depth, RasterState)."""
@@ -146,7 +171,7 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
         hint = _capacity_hint.get(key)
         launched = False
         if hint is not None:
-            phase2(int(hint * 1.25) + 65536)
+            phase2(int(hint * _CAP_GROWTH) + _CAP_SLACK)
             launched = True
         ev.synchronize()
         R = int(pinned.item())
@@ -154,6 +179,8 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
         if not launched or R > st.capacity:
             phase2(max(R, 1))
         st.num_rendered = R
+    global last_state
+    last_state = st
     return out_color, radii, out_depth, st
 
 
