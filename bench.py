@@ -1,0 +1,456 @@
+#!/usr/bin/env python
+"""bench.py -- fwd+bwd render iterations/sec of the Gaussian-splat rasterizer hot path.
+
+Contract (one JSON line on rank 0):  python bench.py --gpus N --steps K --warmup W [--impl reference]
+  * workload (default) = BASELINE.json's metric config: Replica shape 1200x680, 1M Gaussians
+    ("surface" scene, 3 depth layers), 24-keyframe window; one step = one render iteration =
+    GaussianRasterizer forward + backward (power 1) of ONE keyframe against the full Gaussian set.
+  * N > 1 = keyframe-sharded mapping: every rank renders a different keyframe of the window per
+    step over replicated Gaussians, then ONE NCCL all-reduce of the flat Gaussian-gradient bucket
+    (weak scaling: value = N * steps / time).
+  * value   : inputs resident in HBM.      e2e : same step with the Gaussian parameters and
+    dL/dcolour coming from pinned HOST buffers and the rendered image + gradients copied back.
+  * roofline: dominant kernel (blend backward) against the measured non-tensor FP32 peak (this
+    path has no GEMM), plus roofline_hbm for the HBM-bound preprocess kernel against
+    MEASURED_PEAKS.json.  cpu_baseline: the CPU oracle on a bounded crop of the same workload.
+  * --impl reference : the UNMODIFIED reference CUDA extension (oracle/_ref, built from
+    /root/reference by oracle/build_ref.py) through the same harness; falls back to the CPU
+    oracle port when the prebuilt extension is not loadable.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "fwd+bwd render iters/sec at 1200x680, 1M Gaussians"
+UNIT = "iters/s"
+
+WORKLOADS = {
+    # name: (camera preset, P, layers, aniso_frac, power, n_keyframes)
+    "replica_1200x680_1M": ("REPLICA", 1_000_000, 3, 0.0, 1, 24),
+    "replica_1200x680_300k": ("REPLICA", 300_000, 1, 0.0, 1, 24),
+    "scannetpp_1752x1168_2M_hessian": ("SCANNETPP", 2_000_000, 3, 0.2, 2, 8),
+    "c1_64x64_10k": ("C1", 10_000, 1, 0.0, 1, 1),
+}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=48)
+    ap.add_argument("--warmup", type=int, default=6)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-cpu"])
+    ap.add_argument("--workload", default="replica_1200x680_1M", choices=list(WORKLOADS))
+    ap.add_argument("--variant", default="dg", choices=["dg", "hx"],
+                    help="which reference semantics/import name to run (dg = what scripts/splatam.py imports)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_workload(name, device):
+    from splatam_b200 import synth
+    cam_name, P, layers, aniso, power, nkf = WORKLOADS[name]
+    cam = getattr(synth, cam_name)
+    if cam_name == "C1":
+        sc = synth.cloud_scene(P, cam["w"], cam["h"], cam["fx"], cam["fy"], seed=0)
+    else:
+        sc = synth.surface_scene(P, cam["w"], cam["h"], cam["fx"], cam["fy"], cam["cx"], cam["cy"], seed=2,
+                                 layers=layers, aniso_frac=aniso)
+    cams = [synth.make_settings(w2c=synth.arc_pose(k, nkf) if nkf > 1 else None, **cam) for k in range(nkf)]
+    g = torch.Generator().manual_seed(77)
+    dL = torch.randn(3, cam["h"], cam["w"], generator=g) / (3.0 * cam["h"] * cam["w"])
+    if power == 2:
+        dL = torch.ones(3, cam["h"], cam["w"]) * 1e-3
+    return cam, sc, cams, dL, power
+
+
+# ------------------------------------------------------------------------------------------------
+LAYOUT = (("rotations", 4), ("means3D", 3), ("colors_precomp", 3), ("opacities", 1), ("scales", 3))  # float4 first
+
+
+class Runner:
+    """Holds the replicated Gaussian set in ONE flat device buffer (and its gradient bucket in
+    another) so that the multi-GPU exchange is a single all-reduce."""
+
+    def __init__(self, sc, cams, dL, power, variant, device):
+        from splatam_b200 import synth
+        self.P = sc["means3D"].shape[0]
+        self.device, self.power, self.variant = device, power, variant
+        self.cams = [synth.settings_to(c, device) for c in cams]
+        self.host_params = torch.cat([sc[k].reshape(-1) for k, _ in LAYOUT]).pin_memory()
+        self.host_dL = dL.contiguous().pin_memory()
+        self.flat_in = self.host_params.to(device)
+        self.dL = self.host_dL.to(device)
+        self.flat_grad = torch.zeros_like(self.flat_in)
+        self.host_grads = torch.empty_like(self.host_params).pin_memory()
+        self.host_color = torch.empty_like(self.host_dL).pin_memory()
+        self.views, self.gviews = {}, {}
+        off = 0
+        for k, w in LAYOUT:
+            n = self.P * w
+            self.views[k] = self.flat_in[off:off + n].view(self.P, w)
+            self.gviews[k] = self.flat_grad[off:off + n].view(self.P, w)
+            off += n
+        self.color = None
+
+    def h2d(self):
+        self.flat_in.copy_(self.host_params, non_blocking=True)
+        self.dL.copy_(self.host_dL, non_blocking=True)
+
+    def d2h(self):
+        self.host_color.copy_(self.color, non_blocking=True)
+        self.host_grads.copy_(self.flat_grad, non_blocking=True)
+
+    def bytes_h2d(self):
+        return self.host_params.numel() * 4 + self.host_dL.numel() * 4
+
+    def bytes_d2h(self):
+        return self.host_grads.numel() * 4 + self.host_color.numel() * 4
+
+
+class OursRunner(Runner):
+    def __init__(self, *a):
+        super().__init__(*a)
+        if self.variant == "hx":
+            import hessian_diff_gaussian_rasterization_w_depth as m
+            self.make = lambda rs: m.GaussianRasterizer(rs, backward_power=self.power)
+        else:
+            import diff_gaussian_rasterization as m
+            self.make = lambda rs: m.GaussianRasterizer(rs)
+        self.leaves = {k: v.detach().requires_grad_(True) for k, v in self.views.items()}
+        self.means2D = torch.zeros(self.P, 3, device=self.device, requires_grad=True)
+
+    def step(self, i):
+        rs = self.cams[i % len(self.cams)]
+        self.flat_grad.zero_()
+        for k, leaf in self.leaves.items():
+            leaf.grad = self.gviews[k]
+        self.means2D.grad = None
+        lv = self.leaves
+        color, radii, depth = self.make(rs)(means3D=lv["means3D"], means2D=self.means2D, opacities=lv["opacities"],
+                                            colors_precomp=lv["colors_precomp"], scales=lv["scales"],
+                                            rotations=lv["rotations"])
+        color.backward(self.dL)
+        self.color = color.detach()
+
+    def launches(self):
+        from splatam_b200._lib import lib
+        return lib.splat_kernel_launch_count()
+
+
+class RefCudaRunner(Runner):
+    """The unmodified reference extension (oracle/_ref) -- only bench.py --impl reference uses it."""
+
+    def __init__(self, *a):
+        super().__init__(*a)
+        from oracle import ref_ext
+        self.ref = ref_ext
+        ref_ext.load(self.variant)
+
+    def step(self, i):
+        rs = self.cams[i % len(self.cams)]
+        v = self.views
+        f = self.ref.forward(self.variant, rs, v["means3D"], v["colors_precomp"], v["opacities"], v["scales"],
+                             v["rotations"])
+        g = self.ref.backward(f, self.dL, self.power)
+        self.color = f["color"]
+        for k, gk in (("means3D", "means3D"), ("colors_precomp", "colors"), ("opacities", "opacities"),
+                      ("scales", "scales"), ("rotations", "rotations")):
+            self.gviews[k].copy_(g[gk])
+
+    def launches(self):
+        return 0
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_oracle_sample(cam, sc, cams, dL, power, crop=(192, 112)):
+    """CPU oracle (port) on a bounded centre crop of the workload.  Returns (value iters/s
+    extrapolated to the full image, cores, sample description)."""
+    from oracle import raster_oracle as O
+    from splatam_b200 import synth
+    W, H = cam["w"], cam["h"]
+    cw, ch = min(crop[0], W), min(crop[1], H)
+    cw, ch = cw // 16 * 16 or W, ch // 16 * 16 or H
+    x0, y0 = (W - cw) // 2 // 16 * 16, (H - ch) // 2 // 16 * 16
+    rs_full = cams[0]
+    w2c = rs_full.viewmatrix[0].t().contiguous()
+    rs = synth.make_settings(w=cw, h=ch, fx=cam["fx"], fy=cam["fy"], cx=cam["cx"] - x0, cy=cam["cy"] - y0, w2c=w2c)
+    V, Pm = rs.viewmatrix.reshape(16), rs.projmatrix.reshape(16)
+    dLc = dL[:, y0:y0 + ch, x0:x0 + cw].contiguous()
+    t0 = time.time()
+    pre = O.preprocess(sc["means3D"], sc["scales"], sc["rotations"], sc["opacities"], V, Pm, cw, ch, rs.tanfovx,
+                       rs.tanfovy, 0.2)
+    t1 = time.time()
+    pl, rg = O.binning(pre)
+    fwd = O.render_forward(pre, pl, rg, sc["colors_precomp"], rs.bg, cw, ch)
+    ctx = dict(rs=rs, near=0.2, pre=pre, point_list=pl, ranges=rg, fwd=fwd, means3D=sc["means3D"],
+               colors=sc["colors_precomp"], scales=sc["scales"], rotations=sc["rotations"])
+    t2 = time.time()
+    O.backward(ctx, dLc, power)
+    t3 = time.time()
+    ratio = (W * H) / float(cw * ch)
+    t_full = (t1 - t0) + ratio * (t3 - t1)
+    desc = ("CPU oracle (oracle/raster_oracle.py, torch %d threads) on centre crop %dx%d of %dx%d keyframe 0, all %d "
+            "Gaussians preprocessed (%.1fs), binning+blend fwd (%.1fs) + bwd (%.1fs) on the crop; value = 1/(t_pre + "
+            "%.1f x t_crop) i.e. blend time scaled by the pixel ratio"
+            % (torch.get_num_threads(), cw, ch, W, H, sc["means3D"].shape[0], t1 - t0, t2 - t1, t3 - t2, ratio))
+    return 1.0 / t_full, torch.get_num_threads(), desc
+
+
+# ------------------------------------------------------------------------------------------------
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f), "measured (MEASURED_PEAKS.json)"
+    return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md)"
+
+
+def pair_counts(runner, keyframes):
+    """(pairs_tested, pairs_blended) averaged over the given keyframes, from our own state
+    (n_contrib is identical in both implementations; blended pairs from a count-only re-blend)."""
+    import ctypes as C
+    from splatam_b200 import rasterizer as R
+    from splatam_b200._lib import lib, check
+    tested = blended = 0.0
+    for kf in keyframes:
+        runner.step(kf)
+        st = R.last_state
+        v = st.views()
+        tested += float(v["n_contrib"].sum())
+        keep = []
+        cam = R._camera(runner.cams[kf % len(runner.cams)], 0.2 if runner.variant == "dg" else 0.001, keep)
+        cnt = torch.zeros(st.H * st.W, dtype=torch.int32, device=runner.device)
+        scratch = torch.empty(3, st.H, st.W, device=runner.device)
+        check(lib.splat_debug_count_blended(C.byref(cam), st.P, C.c_void_p(runner.views["colors_precomp"].data_ptr()),
+                                            C.c_void_p(st.geom.data_ptr()), C.c_void_p(st.image.data_ptr()),
+                                            C.c_void_p(st.binning.data_ptr()), st.capacity,
+                                            C.c_void_p(scratch.data_ptr()), C.c_void_p(cnt.data_ptr()),
+                                            C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        blended += float(cnt.sum())
+    n = float(len(keyframes))
+    return tested / n, blended / n, float(R.last_state.num_rendered)
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    cam, sc, cams, dL, power = build_workload(args.workload, "cpu")
+    W, H, P = cam["w"], cam["h"], sc["means3D"].shape[0]
+    base = {"metric": METRIC if args.workload == "replica_1200x680_1M" else "fwd+bwd render iters/sec (%s)" % args.workload,
+            "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "image": [W, H], "gaussians": P, "keyframes": len(cams),
+                       "backward_power": power, "variant": args.variant,
+                       "parallelism": "keyframe-sharded x%d + 1 all-reduce of the flat gradient bucket" % world
+                       if world > 1 else "single GPU",
+                       "l2": "per-step working set (params 56 MB + geometry/binning state + gradients) exceeds the "
+                             "126 MB L2 and the camera rotates over the keyframe window; no explicit flush"}}
+
+    use_cuda_ref = False
+    if args.impl == "reference":
+        from oracle import ref_ext
+        use_cuda_ref = torch.cuda.is_available() and ref_ext.available(args.variant)
+    if args.impl == "reference-cpu" or (args.impl == "reference" and not use_cuda_ref):
+        # CPU port of the reference algorithm; rank 0 only
+        if rank != 0:
+            return
+        t0 = time.time()
+        vals = []
+        for _ in range(max(1, min(args.steps, 2))):
+            v, cores, desc = cpu_oracle_sample(cam, sc, cams, dL, power)
+            vals.append(v)
+        v = sum(vals) / len(vals)
+        out = dict(base, impl="reference", value=v, ms_per_step=1000.0 / v, n_gpus=args.gpus,
+                   cpu_baseline={"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
+                   e2e={"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                   gpu_launches=0, wall_s=time.time() - t0)
+        print(json.dumps(out))
+        return
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback for the product path)"
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+    RunnerCls = OursRunner if args.impl == "ours" else RefCudaRunner
+    runner = RunnerCls(sc, cams, dL, power, args.variant, device)
+
+    def full_step(i):
+        runner.step(i * world + rank)
+        if world > 1:
+            dist.all_reduce(runner.flat_grad)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(args.warmup, 3)):
+        full_step(i)
+    barrier()
+    prof = None
+    if args.impl == "ours":
+        from splatam_b200._lib import lib
+        lib.splat_profile_enable(1)
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = runner.launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        full_step(i)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    launches = runner.launches() - l0
+    if args.impl == "ours":
+        import ctypes as C
+        n = 8
+        ms_sum = (C.c_float * n)(); cnt = (C.c_int32 * n)()
+        lib.splat_profile_read(ms_sum, cnt, n)
+        lib.splat_profile_enable(0)
+        prof = {lib.splat_profile_kernel_name(k).decode(): (ms_sum[k], cnt[k]) for k in range(n) if cnt[k]}
+    t = torch.tensor([ms], device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = world * args.steps / (ms * 1e-3)
+
+    # ---- e2e: host buffers in, image + gradients out, every step
+    e2e = None
+    if not args.no_e2e:
+        for i in range(3):
+            runner.h2d(); full_step(i); runner.d2h(); torch.cuda.synchronize()
+        barrier()
+        e0.record()
+        for i in range(args.steps):
+            runner.h2d()
+            full_step(i)
+            runner.d2h()
+            torch.cuda.synchronize()
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * args.steps / (float(t.item()) * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": runner.bytes_h2d(), "d2h_bytes_per_step": runner.bytes_d2h()}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    out = dict(base, value=value, ms_per_step=ms / args.steps, clocks=clocks, e2e=e2e, gpu_launches=launches)
+    if args.impl != "ours":
+        out["impl"] = "reference"
+        out["reference_kind"] = "unmodified reference CUDA extension oracle/_ref/ref_%s_C.so (sm_100a build)" % args.variant
+    peaks, peak_src = measured_peaks()
+    if args.impl == "ours" and prof:
+        import ctypes as C
+        out["kernel_ms_per_step"] = {k: round(v[0] / args.steps, 5) for k, v in prof.items()}
+        kfs = sorted(set((i * world + rank) % len(cams) for i in range(args.steps)))[:6]
+        tested, blended, R = pair_counts(runner, kfs)
+        scratch = torch.zeros(16, device=device)
+        tf = C.c_float(0)
+        lib.splat_debug_fp32_peak(C.c_void_p(scratch.data_ptr()), C.byref(tf), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        fp32_peak = float(tf.value)
+        dom = max(("render_fwd", "render_bwd"), key=lambda k: prof.get(k, (0, 0))[0])
+        dom_ms = prof[dom][0] / max(prof[dom][1], 1)
+        flop = 13.0 * (tested - blended) + (75.0 if dom == "render_bwd" else 22.0) * blended
+        ach = flop / (dom_ms * 1e-3) / 1e12
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            with open(tpath) as f:
+                traffic = json.load(f)
+        out["roofline"] = {"bound": "fp32", "kernel": dom, "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s",
+                           "frac": ach / fp32_peak if fp32_peak else None,
+                           "traffic": (traffic or {}).get(dom),
+                           "peak_source": "in-run FFMA microbenchmark (non-tensor FP32; no GEMM on this path)",
+                           "algorithmic": {"pairs_tested": tested, "pairs_blended": blended, "num_rendered": R,
+                                           "flop_model": "13*(tested-blended) + %d*blended" % (75 if dom == "render_bwd" else 22)},
+                           "kernel_ms": dom_ms}
+        pre_ms = prof["preprocess_fwd"][0] / max(prof["preprocess_fwd"][1], 1)
+        gbs = 76.0 * P / (pre_ms * 1e-3) / 1e9
+        out["roofline_hbm"] = {"bound": "hbm", "kernel": "preprocess_fwd", "achieved": gbs, "peak": peaks["hbm_gbs"],
+                               "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "traffic": (traffic or {}).get("preprocess_fwd"),
+                               "peak_source": peak_src, "algorithmic_bytes_per_gaussian": 76, "kernel_ms": pre_ms}
+    if world == 1 and not args.no_cpu_baseline:
+        v, cores, desc = cpu_oracle_sample(cam, sc, cams, dL, power)
+        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

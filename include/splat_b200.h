@@ -112,6 +112,7 @@ int splat_forward_render(const SplatCamera* cam, int32_t P,
  * fused != 0 reproduces HX's renderCUDAFused semantics: every per-(pixel,Gaussian) gradient
  * term is raised to `power` before accumulation (HX/cuda_rasterizer/backward.cu:1093-1137);
  * power == 2 is the fork's diagonal Gauss-Newton ("Hessian") accumulation.
+ * `R` is the R_capacity that was passed to splat_forward_render (it fixes the state layout).
  * All dL_* outputs are fully written by the call (no pre-zeroing needed).  dL_dconic is a
  * [P,4] scratch/output (x,y,_,w as in the reference's [P,2,2]).  dL_dsh may be NULL when shs is. */
 int splat_backward(const SplatCamera* cam, int32_t P, int64_t R,
@@ -147,6 +148,18 @@ const void* splat_state_point_list(const void* binning_state, int32_t width, int
 const void* splat_state_depths(const void* geom_state, int32_t P);
 const void* splat_state_means2D(const void* geom_state, int32_t P);
 const void* splat_state_conic_opacity(const void* geom_state, int32_t P);
+
+/* ---- measurement helpers (used by bench.py; not on the product path) -----------------------
+ * splat_profile_enable(1) makes every kernel launch of this library record a cudaEvent pair on
+ * its stream; splat_profile_read() synchronises, returns the summed milliseconds and launch
+ * counts per kernel id (order given by splat_profile_kernel_name(0..7)) and resets. */
+int splat_profile_enable(int on);
+int splat_profile_read(float* ms_sum, int32_t* launches, int32_t n);
+const char* splat_profile_kernel_name(int kernel_id);
+int splat_debug_count_blended(const SplatCamera* cam, int32_t P, const float* colors, const void* geom_state,
+                              void* image_state, const void* binning_state, int64_t R_capacity,
+                              float* scratch_color, uint32_t* blended, void* stream);
+int splat_debug_fp32_peak(float* scratch_dev, float* tflops_out, void* stream);
 
 /* ---- misc ------------------------------------------------------------------------------------ */
 int splat_abi_version(void);

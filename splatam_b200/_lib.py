@@ -48,6 +48,11 @@ _SIGNATURES = {
     "splat_state_depths": (_P, [_P, C.c_int32]),
     "splat_state_means2D": (_P, [_P, C.c_int32]),
     "splat_state_conic_opacity": (_P, [_P, C.c_int32]),
+    "splat_profile_enable": (C.c_int, [C.c_int]),
+    "splat_profile_read": (C.c_int, [_P, _P, C.c_int32]),
+    "splat_profile_kernel_name": (C.c_char_p, [C.c_int]),
+    "splat_debug_count_blended": (C.c_int, [C.POINTER(SplatCamera), C.c_int32, _P, _P, _P, _P, C.c_int64, _P, _P, _P]),
+    "splat_debug_fp32_peak": (C.c_int, [_P, _P, _P]),
     "splat_abi_version": (C.c_int, []),
     "splat_strerror": (C.c_char_p, [C.c_int]),
     "splat_last_error": (C.c_char_p, []),

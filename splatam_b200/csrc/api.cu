@@ -4,11 +4,24 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 #include "kernels.cuh"
 
 namespace splat {
 
 int g_launch_count = 0;
+int g_prof_on = 0;
+struct ProfPair { cudaEvent_t a, b; };
+static std::vector<ProfPair> g_prof[K_COUNT];
+static std::vector<cudaEvent_t> g_prof_free;
+static cudaEvent_t prof_new_event() {
+  if (!g_prof_free.empty()) { cudaEvent_t e = g_prof_free.back(); g_prof_free.pop_back(); return e; }
+  cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+void prof_record(int id, cudaStream_t st, bool start) {
+  if (start) { ProfPair p; p.a = prof_new_event(); p.b = prof_new_event(); cudaEventRecord(p.a, st); g_prof[id].push_back(p); }
+  else if (!g_prof[id].empty()) cudaEventRecord(g_prof[id].back().b, st);
+}
 static thread_local char g_err[512] = "";
 
 int fail(int code, const char* fmt, ...) {
@@ -67,6 +80,7 @@ int splat_forward_geometry(const SplatCamera* cam, int32_t P, const float* means
       return fail(SPLAT_ERR_BAD_ARG, "Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
     if ((shs && colors_precomp) || (!shs && !colors_precomp))
       return fail(SPLAT_ERR_BAD_ARG, "Please provide excatly one of either SHs or precomputed colors!");
+    if (rotations && ((uintptr_t)rotations & 15)) return fail(SPLAT_ERR_BAD_ARG, "rotations must be 16-byte aligned");
     if (shs) {
       if (cam->sh_degree < 0 || cam->sh_degree > 3) return fail(SPLAT_ERR_UNSUPPORTED, "sh_degree must be 0..3");
       if (M < (cam->sh_degree + 1) * (cam->sh_degree + 1)) return fail(SPLAT_ERR_BAD_ARG, "M too small for sh_degree");
@@ -117,7 +131,7 @@ int splat_forward_render(const SplatCamera* cam, int32_t P, const float* colors_
   r.colors = colors_precomp ? colors_precomp : gv.rgb;
   r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.out_color = out_color; r.out_depth = out_depth;
-  r.hdr = iv.hdr; r.Rcap = Rcap;
+  r.hdr = iv.hdr; r.Rcap = Rcap; r.blended = nullptr;
   return launch_render_fwd(r, T, st);
 }
 
@@ -141,6 +155,8 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
   if (shs && !dL_dsh) return fail(SPLAT_ERR_BAD_ARG, "dL_dsh required with SHs");
   const bool sr = scales && rotations;
   if (!sr && !cov3D_precomp) return fail(SPLAT_ERR_BAD_ARG, "need scales+rotations or cov3D_precomp");
+  if ((rotations && ((uintptr_t)rotations & 15)) || ((uintptr_t)dL_drotations & 15) || ((uintptr_t)dL_dconic & 15))
+    return fail(SPLAT_ERR_BAD_ARG, "rotations, dL_drotations and dL_dconic must be 16-byte aligned");
   const bool hess = fused && power != 1;
   if (hess && power != 2)
     return fail(SPLAT_ERR_UNSUPPORTED, "backward_power must be 1 or 2 (the reference only ever uses those, ros_handler.py:884)");
@@ -212,6 +228,94 @@ const void* splat_state_point_list(const void* s, int32_t, int32_t, int64_t R) {
 const void* splat_state_depths(const void* s, int32_t P) { return geom_view(const_cast<void*>(s), P).depths; }
 const void* splat_state_means2D(const void* s, int32_t P) { return geom_view(const_cast<void*>(s), P).xy; }
 const void* splat_state_conic_opacity(const void* s, int32_t P) { return geom_view(const_cast<void*>(s), P).conic_opacity; }
+
+// Debug/measurement helper: re-runs the forward blend over an existing (geom, image, binning) state
+// WITHOUT culling and writes the number of blended pairs per pixel (F_alg of the roofline model).
+int splat_debug_count_blended(const SplatCamera* cam, int32_t P, const float* colors, const void* geom_state,
+                              void* image_state, const void* binning_state, int64_t R_capacity,
+                              float* scratch_color, uint32_t* blended, void* stream) {
+  if (int rc = check_cam(cam)) return rc;
+  if (!colors || !geom_state || !image_state || !binning_state || !scratch_color || !blended)
+    return fail(SPLAT_ERR_BAD_ARG, "NULL buffer");
+  const int W = cam->image_width, H = cam->image_height;
+  const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+  ImageView iv = image_view(image_state, W, H);
+  GeomView gv = geom_view(const_cast<void*>(geom_state), P);
+  BinView bv = bin_view(const_cast<void*>(binning_state), R_capacity);
+  RenderFwdArgs r;
+  r.W = W; r.H = H; r.gx = gx; r.ranges = iv.ranges; r.point_list = bv.point_list;
+  r.xy = gv.xy; r.conic_opacity = gv.conic_opacity; r.depths = gv.depths; r.colors = colors; r.bg = cam->bg;
+  r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.out_color = scratch_color; r.out_depth = nullptr;
+  r.hdr = iv.hdr; r.Rcap = (uint32_t)R_capacity; r.blended = blended;
+  return launch_render_fwd(r, gx * gy, (cudaStream_t)stream);
+}
+
+__global__ void __launch_bounds__(256) fp32_peak_kernel(float* out, int iters) {
+  float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f,
+        a6 = a0 + 6.f, a7 = a0 + 7.f;
+  const float b = 1.0000001f, c = 1e-7f;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      a0 = fmaf(a0, b, c); a1 = fmaf(a1, b, c); a2 = fmaf(a2, b, c); a3 = fmaf(a3, b, c);
+      a4 = fmaf(a4, b, c); a5 = fmaf(a5, b, c); a6 = fmaf(a6, b, c); a7 = fmaf(a7, b, c);
+    }
+  }
+  if (a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7 == 123.456f) out[0] = a0;
+}
+
+// Non-tensor FP32 peak of this device (FFMA microbenchmark, 2 FLOP per FMA): the roofline
+// denominator of the blend kernels.  MEASURED_PEAKS.json carries HBM and bf16-tensor peaks only.
+int splat_debug_fp32_peak(float* scratch_dev, float* tflops_out, void* stream) {
+  if (!scratch_dev || !tflops_out) return fail(SPLAT_ERR_BAD_ARG, "NULL buffer");
+  cudaStream_t st = (cudaStream_t)stream;
+  int dev = 0, sms = 0;
+  SPLAT_CUDA(cudaGetDevice(&dev));
+  SPLAT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int iters = 20000, blocks = sms * 8;
+  cudaEvent_t e0, e1;
+  SPLAT_CUDA(cudaEventCreate(&e0)); SPLAT_CUDA(cudaEventCreate(&e1));
+  float best = 0.f;
+  for (int rep = 0; rep < 4; ++rep) {
+    SPLAT_CUDA(cudaEventRecord(e0, st));
+    fp32_peak_kernel<<<blocks, 256, 0, st>>>(scratch_dev, iters);
+    SPLAT_CUDA(cudaEventRecord(e1, st));
+    SPLAT_CUDA(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    SPLAT_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    const double flop = 2.0 * 64.0 * iters * 256.0 * blocks;
+    const float tf = (float)(flop / (ms * 1e-3) / 1e12);
+    if (rep > 0 && tf > best) best = tf;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  *tflops_out = best;
+  return SPLAT_OK;
+}
+
+int splat_profile_enable(int on) { g_prof_on = on ? 1 : 0; return SPLAT_OK; }
+
+// Synchronises the device, sums the event-pair durations recorded since the last read and resets.
+int splat_profile_read(float* ms_sum, int32_t* launches, int32_t n) {
+  if (!ms_sum || !launches || n < K_COUNT) return fail(SPLAT_ERR_BAD_ARG, "need arrays of %d", (int)K_COUNT);
+  SPLAT_CUDA(cudaDeviceSynchronize());
+  for (int k = 0; k < K_COUNT; ++k) {
+    float tot = 0.f;
+    for (auto& p : g_prof[k]) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) tot += ms;
+      g_prof_free.push_back(p.a); g_prof_free.push_back(p.b);
+    }
+    ms_sum[k] = tot; launches[k] = (int32_t)g_prof[k].size();
+    g_prof[k].clear();
+  }
+  cudaGetLastError();
+  return SPLAT_OK;
+}
+const char* splat_profile_kernel_name(int k) {
+  static const char* names[K_COUNT] = {"preprocess_fwd", "tile_scan", "scatter", "tile_sort", "render_fwd",
+                                       "render_bwd", "preprocess_bwd", "hessian_finalize"};
+  return (k >= 0 && k < K_COUNT) ? names[k] : "";
+}
 
 int splat_abi_version(void) { return SPLAT_ABI_VERSION; }
 const char* splat_last_error(void) { return g_err; }

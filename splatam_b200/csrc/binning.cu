@@ -254,6 +254,7 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
 }
 
 int launch_tile_scan(int T, const ImageView& iv, uint32_t* num_rendered_out, uint32_t sort_cap, cudaStream_t st) {
+  ProfScope prof_(K_TILE_SCAN, st);
   tile_scan_kernel<<<1, 1024, 0, st>>>(T, iv.tile_count, iv.tile_cursor, iv.ranges, iv.hdr, num_rendered_out, sort_cap);
   SPLAT_LAUNCH_CHECK("tile_scan_kernel");
   return SPLAT_OK;
@@ -261,6 +262,7 @@ int launch_tile_scan(int T, const ImageView& iv, uint32_t* num_rendered_out, uin
 
 int launch_scatter(int P, int gx, int gy, const int* radii, const GeomView& g, const ImageView& iv,
                    const BinView& b, uint32_t Rcap, cudaStream_t st) {
+  ProfScope prof_(K_SCATTER, st);
   if (P <= 0) return SPLAT_OK;
   scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, gx, gy, radii, g.xy, g.depths, iv.tile_cursor, b.keys, iv.hdr, Rcap);
   SPLAT_LAUNCH_CHECK("scatter_kernel");
@@ -271,6 +273,7 @@ static const int kSortSmemCap = 4096;  // keys per shared buffer (2 x 32 KB)
 int sort_smem_cap() { return kSortSmemCap; }
 
 int launch_tile_sort(int T, const ImageView& iv, const BinView& b, uint32_t Rcap, cudaStream_t st) {
+  ProfScope prof_(K_TILE_SORT, st);
   static bool attr_set = false;
   const int smem = kSortSmemCap * 8 * 2;
   if (!attr_set) {

@@ -22,6 +22,17 @@ namespace splat {
 extern int g_launch_count;
 inline void count_launch(int n = 1) { g_launch_count += n; }
 
+// ---------------------------------------------------------------- per-kernel event profiling
+enum KernelId { K_PRE_FWD = 0, K_TILE_SCAN, K_SCATTER, K_TILE_SORT, K_RENDER_FWD, K_RENDER_BWD, K_PRE_BWD,
+                K_HESS_FIN, K_COUNT };
+extern int g_prof_on;
+void prof_record(int id, cudaStream_t st, bool start);
+struct ProfScope {  // cudaEvent pair around one launch, only when splat_profile_enable(1) was called
+  int id; cudaStream_t st;
+  ProfScope(int id_, cudaStream_t st_) : id(id_), st(st_) { if (g_prof_on) prof_record(id, st, true); }
+  ~ProfScope() { if (g_prof_on) prof_record(id, st, false); }
+};
+
 // ---------------------------------------------------------------- state layouts
 __host__ __device__ inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 

@@ -41,6 +41,7 @@ struct RenderFwdArgs {
   const float* bg;
   float* final_T; uint32_t* n_contrib; float* out_color; float* out_depth;
   const ImageHeader* hdr; uint32_t Rcap;
+  uint32_t* blended;  // debug: per-pixel count of blended pairs (NULL in production)
 };
 
 struct RenderBwdArgs {

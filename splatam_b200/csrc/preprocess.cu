@@ -380,6 +380,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
 }
 
 int launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t st) {
+  ProfScope prof_(K_PRE_BWD, st);
   if (a.P <= 0) return SPLAT_OK;
   preprocess_bwd_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
   SPLAT_LAUNCH_CHECK("preprocess_bwd_kernel");
@@ -456,6 +457,7 @@ __global__ void __launch_bounds__(128) hessian_finalize_kernel(const HessArgs a)
 }
 
 int launch_hessian_finalize(const HessArgs& a, cudaStream_t st) {
+  ProfScope prof_(K_HESS_FIN, st);
   if (a.P <= 0) return SPLAT_OK;
   hessian_finalize_kernel<<<(a.P + 127) / 128, 128, 0, st>>>(a);
   SPLAT_LAUNCH_CHECK("hessian_finalize_kernel");
@@ -463,6 +465,7 @@ int launch_hessian_finalize(const HessArgs& a, cudaStream_t st) {
 }
 
 int launch_preprocess_fwd(const PreFwdArgs& a, cudaStream_t st) {
+  ProfScope prof_(K_PRE_FWD, st);
   if (a.P <= 0) return SPLAT_OK;
   preprocess_fwd_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
   SPLAT_LAUNCH_CHECK("preprocess_fwd_kernel");

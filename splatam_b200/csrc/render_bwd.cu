@@ -204,6 +204,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const RenderBwdArgs a) 
 
 
 int launch_render_bwd(const RenderBwdArgs& a, int T, int mode, cudaStream_t st) {
+  ProfScope prof_(K_RENDER_BWD, st);
   if (T <= 0) return SPLAT_OK;
   if (mode == 0) {
     if (g_disable_cull) render_bwd_kernel<false, 0><<<T, 256, 0, st>>>(a);

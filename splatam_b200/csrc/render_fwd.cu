@@ -15,7 +15,7 @@
 namespace splat {
 
 
-template <bool CULL>
+template <bool CULL, bool COUNT>
 __global__ void __launch_bounds__(256) render_fwd_kernel(const RenderFwdArgs a) {
   if (a.hdr->num_rendered > a.Rcap) return;
   __shared__ float2 s_xy[BATCH];
@@ -35,7 +35,7 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const RenderFwdArgs a) 
   const int n = (int)(range.y - range.x);
 
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 15.0f;
-  uint32_t last = 0;
+  uint32_t last = 0, nblend = 0;
   bool done = !inside;
   bool warp_done = __all_sync(0xffffffffu, done);
 
@@ -82,6 +82,7 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const RenderFwdArgs a) 
         if (T > 0.5f && test_T < 0.5f) D = cd.w;
         T = test_T;
         last = (uint32_t)(base + jj + 1);
+        if (COUNT) ++nblend;
       }
       if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
     }
@@ -96,15 +97,18 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const RenderFwdArgs a) 
     a.out_color[HW + pix] = C1 + T * __ldg(a.bg + 1);
     a.out_color[2 * HW + pix] = C2 + T * __ldg(a.bg + 2);
     if (a.out_depth) a.out_depth[pix] = D;
+    if (COUNT) a.blended[pix] = nblend;
   }
 }
 
 int g_disable_cull = 0;
 
 int launch_render_fwd(const RenderFwdArgs& a, int T, cudaStream_t st) {
+  ProfScope prof_(K_RENDER_FWD, st);
   if (T <= 0) return SPLAT_OK;
-  if (g_disable_cull) render_fwd_kernel<false><<<T, 256, 0, st>>>(a);
-  else render_fwd_kernel<true><<<T, 256, 0, st>>>(a);
+  if (a.blended) render_fwd_kernel<false, true><<<T, 256, 0, st>>>(a);
+  else if (g_disable_cull) render_fwd_kernel<false, false><<<T, 256, 0, st>>>(a);
+  else render_fwd_kernel<true, false><<<T, 256, 0, st>>>(a);
   SPLAT_LAUNCH_CHECK("render_fwd_kernel");
   return SPLAT_OK;
 }

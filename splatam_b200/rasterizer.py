@@ -199,9 +199,11 @@ def rasterize_backward(rs, near, st, power, fused, means3D, colors_precomp, scal
             v = flat[off:off + P * k].view(shape)
             off += P * k
             return v
+        # float4-accessed arrays first so they stay 16-byte aligned for any P
+        g_rots = take(4, (P, 4)); g_conic = take(4, (P, 2, 2))
         g_means3D = take(3, (P, 3)); g_means2D = take(3, (P, 3)); g_colors = take(3, (P, 3))
-        g_opac = take(1, (P, 1)); g_scales = take(3, (P, 3)); g_rots = take(4, (P, 4))
-        g_cov3D = take(6, (P, 6)); g_conic = take(4, (P, 2, 2)); g_sh = take(3 * M, (P, M, 3))
+        g_opac = take(1, (P, 1)); g_scales = take(3, (P, 3))
+        g_cov3D = take(6, (P, 6)); g_sh = take(3 * M, (P, M, 3))
         if P == 0:
             return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D
         keep = []
@@ -228,6 +230,8 @@ class _RasterizeGaussians(torch.autograd.Function):
         colors_precomp = colors_precomp.contiguous()
         scales = scales.contiguous()
         rotations = rotations.contiguous()
+        if rotations.numel() and rotations.data_ptr() % 16:
+            rotations = rotations.clone()   # the kernels read quaternions as float4
         cov3Ds_precomp = cov3Ds_precomp.contiguous()
         for name, t in (("sh", sh), ("colors_precomp", colors_precomp), ("scales", scales),
                         ("rotations", rotations), ("cov3D_precomp", cov3Ds_precomp)):

@@ -15,7 +15,10 @@ pytestmark = pytest.mark.gpu
 
 FWD_TOL = 1e-5
 GRAD_TOL = 1e-3
-GRAD_FLOOR = 1e-5
+# |a-b| <= 1e-3*max(|a|,|b|) + 1e-6*||ref||_inf  (SURVEY.md 7.3).  Calibrated on a B200
+# (profiles/r01_grad_noise_calibration.txt): the reference extension's own run-to-run differences
+# (atomic order) reach 5.6e-3 with a 1e-8*||ref||_inf floor and 8.7e-4 with this one.
+GRAD_FLOOR = 1e-3
 
 
 def _pkg(variant):
