@@ -50,8 +50,10 @@ def parse():
     ap.add_argument("--warmup", type=int, default=6)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-cpu"])
     ap.add_argument("--workload", default="replica_1200x680_1M", choices=list(WORKLOADS))
-    ap.add_argument("--variant", default="dg", choices=["dg", "hx"],
-                    help="which reference semantics/import name to run (dg = what scripts/splatam.py imports)")
+    ap.add_argument("--variant", default="hx", choices=["dg", "hx"],
+                    help="which reference extension / import name to run: hx = the bundled fork "
+                         "hessian-diff-gaussian-rasterization-w-depth that BASELINE.json's north_star names (default); "
+                         "dg = the upstream submodule scripts/splatam.py imports.  The reference arm reports both.")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -127,41 +129,35 @@ def build_workload(name, device):
 
 
 # ------------------------------------------------------------------------------------------------
-LAYOUT = (("rotations", 4), ("means3D", 3), ("colors_precomp", 3), ("opacities", 1), ("scales", 3))  # float4 first
-
-
 class Runner:
-    """Holds the replicated Gaussian set in ONE flat device buffer (and its gradient bucket in
-    another) so that the multi-GPU exchange is a single all-reduce."""
+    """Holds the replicated Gaussian set in flat device buckets (splatam_b200.mapping.GradBucket: one
+    flat parameter buffer + one flat gradient buffer, so the multi-GPU exchange is a single
+    all-reduce).  Two buckets exist so the end-to-end leg can double-buffer host<->device copies."""
 
     def __init__(self, sc, cams, dL, power, variant, device):
-        from splatam_b200 import synth
+        from splatam_b200 import mapping, synth
         self.P = sc["means3D"].shape[0]
         self.device, self.power, self.variant = device, power, variant
         self.cams = [synth.settings_to(c, device) for c in cams]
-        self.host_params = torch.cat([sc[k].reshape(-1) for k, _ in LAYOUT]).pin_memory()
+        self.buckets = [mapping.GradBucket(sc, device) for _ in range(2)]
+        self.host_params = torch.cat([sc[k].reshape(-1) for k, _ in mapping.LAYOUT]).pin_memory()
         self.host_dL = dL.contiguous().pin_memory()
-        self.flat_in = self.host_params.to(device)
-        self.dL = self.host_dL.to(device)
-        self.flat_grad = torch.zeros_like(self.flat_in)
+        self.dLs = [self.host_dL.to(device) for _ in range(2)]
         self.host_grads = torch.empty_like(self.host_params).pin_memory()
         self.host_color = torch.empty_like(self.host_dL).pin_memory()
-        self.views, self.gviews = {}, {}
-        off = 0
-        for k, w in LAYOUT:
-            n = self.P * w
-            self.views[k] = self.flat_in[off:off + n].view(self.P, w)
-            self.gviews[k] = self.flat_grad[off:off + n].view(self.P, w)
-            off += n
-        self.color = None
+        self.colors = [None, None]
+        self.setup()
 
-    def h2d(self):
-        self.flat_in.copy_(self.host_params, non_blocking=True)
-        self.dL.copy_(self.host_dL, non_blocking=True)
+    def setup(self):
+        pass
 
-    def d2h(self):
-        self.host_color.copy_(self.color, non_blocking=True)
-        self.host_grads.copy_(self.flat_grad, non_blocking=True)
+    def h2d(self, b):
+        self.buckets[b].params.copy_(self.host_params, non_blocking=True)
+        self.dLs[b].copy_(self.host_dL, non_blocking=True)
+
+    def d2h(self, b):
+        self.host_color.copy_(self.colors[b], non_blocking=True)
+        self.host_grads.copy_(self.buckets[b].grads, non_blocking=True)
 
     def bytes_h2d(self):
         return self.host_params.numel() * 4 + self.host_dL.numel() * 4
@@ -171,29 +167,28 @@ class Runner:
 
 
 class OursRunner(Runner):
-    def __init__(self, *a):
-        super().__init__(*a)
+    def setup(self):
         if self.variant == "hx":
             import hessian_diff_gaussian_rasterization_w_depth as m
             self.make = lambda rs: m.GaussianRasterizer(rs, backward_power=self.power)
         else:
             import diff_gaussian_rasterization as m
             self.make = lambda rs: m.GaussianRasterizer(rs)
-        self.leaves = {k: v.detach().requires_grad_(True) for k, v in self.views.items()}
-        self.means2D = torch.zeros(self.P, 3, device=self.device, requires_grad=True)
+        self.leaves = [bk.leaves() for bk in self.buckets]
+        self.means2D = [torch.zeros(self.P, 3, device=self.device, requires_grad=True) for _ in range(2)]
 
-    def step(self, i):
-        rs = self.cams[i % len(self.cams)]
-        self.flat_grad.zero_()
-        for k, leaf in self.leaves.items():
-            leaf.grad = self.gviews[k]
-        self.means2D.grad = None
-        lv = self.leaves
-        color, radii, depth = self.make(rs)(means3D=lv["means3D"], means2D=self.means2D, opacities=lv["opacities"],
+    def step(self, kf, b=0):
+        rs = self.cams[kf % len(self.cams)]
+        bk, lv = self.buckets[b], self.leaves[b]
+        bk.zero_grad()
+        for k, leaf in lv.items():
+            leaf.grad = bk.gviews[k]
+        self.means2D[b].grad = None
+        color, radii, depth = self.make(rs)(means3D=lv["means3D"], means2D=self.means2D[b], opacities=lv["opacities"],
                                             colors_precomp=lv["colors_precomp"], scales=lv["scales"],
                                             rotations=lv["rotations"])
-        color.backward(self.dL)
-        self.color = color.detach()
+        color.backward(self.dLs[b])
+        self.colors[b] = color.detach()
 
     def launches(self):
         from splatam_b200._lib import lib
@@ -203,22 +198,22 @@ class OursRunner(Runner):
 class RefCudaRunner(Runner):
     """The unmodified reference extension (oracle/_ref) -- only bench.py --impl reference uses it."""
 
-    def __init__(self, *a):
-        super().__init__(*a)
+    def setup(self):
         from oracle import ref_ext
         self.ref = ref_ext
         ref_ext.load(self.variant)
 
-    def step(self, i):
-        rs = self.cams[i % len(self.cams)]
-        v = self.views
+    def step(self, kf, b=0):
+        rs = self.cams[kf % len(self.cams)]
+        bk = self.buckets[b]
+        v = bk.views
         f = self.ref.forward(self.variant, rs, v["means3D"], v["colors_precomp"], v["opacities"], v["scales"],
                              v["rotations"])
-        g = self.ref.backward(f, self.dL, self.power)
-        self.color = f["color"]
+        g = self.ref.backward(f, self.dLs[b], self.power)
+        self.colors[b] = f["color"]
         for k, gk in (("means3D", "means3D"), ("colors_precomp", "colors"), ("opacities", "opacities"),
                       ("scales", "scales"), ("rotations", "rotations")):
-            self.gviews[k].copy_(g[gk])
+            bk.gviews[k].copy_(g[gk])
 
     def launches(self):
         return 0
@@ -284,7 +279,7 @@ def pair_counts(runner, keyframes):
         cam = R._camera(runner.cams[kf % len(runner.cams)], 0.2 if runner.variant == "dg" else 0.001, keep)
         cnt = torch.zeros(st.H * st.W, dtype=torch.int32, device=runner.device)
         scratch = torch.empty(3, st.H, st.W, device=runner.device)
-        check(lib.splat_debug_count_blended(C.byref(cam), st.P, C.c_void_p(runner.views["colors_precomp"].data_ptr()),
+        check(lib.splat_debug_count_blended(C.byref(cam), st.P, C.c_void_p(runner.buckets[0].views["colors_precomp"].data_ptr()),
                                             C.c_void_p(st.geom.data_ptr()), C.c_void_p(st.image.data_ptr()),
                                             C.c_void_p(st.binning.data_ptr()), st.capacity,
                                             C.c_void_p(scratch.data_ptr()), C.c_void_p(cnt.data_ptr()),
@@ -292,6 +287,96 @@ def pair_counts(runner, keyframes):
         blended += float(cnt.sum())
     n = float(len(keyframes))
     return tested / n, blended / n, float(R.last_state.num_rendered)
+
+
+def timed_run(runner, sched, rank, world, steps, warmup, device, dist, on_timed_start=None):
+    """W warm-up + K timed steps of the device-resident loop.  Returns ms (max over ranks)."""
+    def full_step(i):
+        runner.step(int(sched[i % sched.shape[0], rank]))
+        if world > 1:
+            runner.buckets[0].all_reduce()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(warmup, 3)):
+        full_step(i)
+    barrier()
+    if on_timed_start is not None:
+        on_timed_start()
+    l0 = runner.launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(steps):
+        full_step(i)
+    e1.record()
+    barrier()
+    launches = runner.launches() - l0
+    t = torch.tensor([e0.elapsed_time(e1)], device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item()), launches
+
+
+def e2e_run(runner, sched, rank, world, steps, device, dist):
+    """End-to-end leg: EVERY step copies that step's inputs (all Gaussian parameters + dL/dcolour) from
+    pinned host memory to the device and reads the step's results (rendered image + the full gradient
+    bucket) back to pinned host memory.  The three stages run on three streams with double-buffered
+    device buffers (copy-in of step i+1 and copy-out of step i-1 overlap the render of step i); the
+    timed region ends when the last result is on the host.  Same harness for both arms."""
+    compute = torch.cuda.current_stream()
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+    in_ready = [torch.cuda.Event() for _ in range(2)]
+    comp_done = [torch.cuda.Event() for _ in range(2)]
+    out_done = [torch.cuda.Event() for _ in range(2)]
+
+    def copy_in(i):
+        b = i % 2
+        with torch.cuda.stream(s_in):
+            s_in.wait_event(comp_done[b])      # buffer b's previous render has consumed its inputs
+            runner.h2d(b)
+            in_ready[b].record(s_in)
+
+    def run(n):
+        for ev in comp_done + out_done:
+            ev.record(compute)
+        copy_in(0)
+        for i in range(n):
+            b = i % 2
+            if i + 1 < n:
+                copy_in(i + 1)
+            compute.wait_event(in_ready[b])
+            compute.wait_event(out_done[b])    # buffer b's previous results are on the host
+            runner.step(int(sched[i % sched.shape[0], rank]), b)
+            if world > 1:
+                runner.buckets[b].all_reduce()
+            comp_done[b].record(compute)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(comp_done[b])
+                runner.colors[b].record_stream(s_out)
+                runner.d2h(b)
+                out_done[b].record(s_out)
+        torch.cuda.synchronize()
+
+    run(3)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    run(steps)
+    e1.record()
+    torch.cuda.synchronize()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    ms = max(e0.elapsed_time(e1), 0.0)
+    t = torch.tensor([ms, wall_ms], device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t[0].item()), float(t[1].item())
 
 
 def main():
@@ -308,8 +393,9 @@ def main():
                        "backward_power": power, "variant": args.variant,
                        "parallelism": "keyframe-sharded x%d + 1 all-reduce of the flat gradient bucket" % world
                        if world > 1 else "single GPU",
-                       "l2": "per-step working set (params 56 MB + geometry/binning state + gradients) exceeds the "
-                             "126 MB L2 and the camera rotates over the keyframe window; no explicit flush"}}
+                       "l2": "per-step working set (56 MB parameters + 56 MB gradients + ~190 MB geometry/binning/"
+                             "instance state) exceeds the 126 MB L2 and the camera moves over the keyframe window "
+                             "every step; no explicit flush"}}
 
     use_cuda_ref = False
     if args.impl == "reference":
@@ -335,74 +421,46 @@ def main():
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback for the product path)"
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
+    dist = None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=device)
+    from splatam_b200 import mapping
+    sched = mapping.keyframe_schedule(len(cams), max(args.steps, 8), world, seed=11)
     RunnerCls = OursRunner if args.impl == "ours" else RefCudaRunner
     runner = RunnerCls(sc, cams, dL, power, args.variant, device)
 
-    def full_step(i):
-        runner.step(i * world + rank)
-        if world > 1:
-            dist.all_reduce(runner.flat_grad)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for i in range(max(args.warmup, 3)):
-        full_step(i)
-    barrier()
+    # W warm-up steps, then the timed region; per-kernel CUDA-event pairs (recorded by the library on
+    # the launching stream) are switched on for exactly the timed steps
     prof = None
-    if args.impl == "ours":
-        from splatam_b200._lib import lib
-        lib.splat_profile_enable(1)
     sampler = ClockSampler(local)
-    sampler.start()
-    l0 = runner.launches()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record()
-    for i in range(args.steps):
-        full_step(i)
-    e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
+
+    def on_timed_start():
+        if args.impl == "ours":
+            from splatam_b200._lib import lib
+            lib.splat_profile_enable(1)
+        sampler.start()
+
+    ms, launches = timed_run(runner, sched, rank, world, args.steps, args.warmup, device, dist, on_timed_start)
     clocks = sampler.stop()
-    launches = runner.launches() - l0
+    value = world * args.steps / (ms * 1e-3)
     if args.impl == "ours":
         import ctypes as C
+        from splatam_b200._lib import lib
         n = 8
         ms_sum = (C.c_float * n)(); cnt = (C.c_int32 * n)()
         lib.splat_profile_read(ms_sum, cnt, n)
         lib.splat_profile_enable(0)
         prof = {lib.splat_profile_kernel_name(k).decode(): (ms_sum[k], cnt[k]) for k in range(n) if cnt[k]}
-    t = torch.tensor([ms], device=device)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    value = world * args.steps / (ms * 1e-3)
 
     # ---- e2e: host buffers in, image + gradients out, every step
     e2e = None
     if not args.no_e2e:
-        for i in range(3):
-            runner.h2d(); full_step(i); runner.d2h(); torch.cuda.synchronize()
-        barrier()
-        e0.record()
-        for i in range(args.steps):
-            runner.h2d()
-            full_step(i)
-            runner.d2h()
-            torch.cuda.synchronize()
-        e1.record()
-        barrier()
-        t = torch.tensor([e0.elapsed_time(e1)], device=device)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * args.steps / (float(t.item()) * 1e-3), "unit": UNIT,
-               "h2d_bytes_per_step": runner.bytes_h2d(), "d2h_bytes_per_step": runner.bytes_d2h()}
+        ems, ewall = e2e_run(runner, sched, rank, world, args.steps, device, dist)
+        e2e = {"value": world * args.steps / (ems * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": runner.bytes_h2d(), "d2h_bytes_per_step": runner.bytes_d2h(),
+               "ms_per_step": ems / args.steps, "wall_ms_per_step": ewall / args.steps,
+               "pipeline": "3 streams, double-buffered: H2D(i+1) | render(i) | D2H(i-1)"}
 
     if rank != 0:
         if world > 1:
@@ -413,11 +471,22 @@ def main():
     if args.impl != "ours":
         out["impl"] = "reference"
         out["reference_kind"] = "unmodified reference CUDA extension oracle/_ref/ref_%s_C.so (sm_100a build)" % args.variant
+        # the other reference build, same harness, device-resident (hx = bundled fork with the fused
+        # Hessian-capable backward; dg = the upstream submodule scripts/splatam.py imports)
+        other = "dg" if args.variant == "hx" else "hx"
+        from oracle import ref_ext
+        if world == 1 and power == 1 and ref_ext.available(other):
+            del runner
+            torch.cuda.empty_cache()
+            r2 = RefCudaRunner(sc, cams, dL, power, other, device)
+            ms2, _ = timed_run(r2, sched, rank, world, min(args.steps, 16), 3, device, dist)
+            out["other_variant"] = {"variant": other, "value": min(args.steps, 16) / (ms2 * 1e-3), "unit": UNIT,
+                                    "ms_per_step": ms2 / min(args.steps, 16)}
     peaks, peak_src = measured_peaks()
     if args.impl == "ours" and prof:
         import ctypes as C
         out["kernel_ms_per_step"] = {k: round(v[0] / args.steps, 5) for k, v in prof.items()}
-        kfs = sorted(set((i * world + rank) % len(cams) for i in range(args.steps)))[:6]
+        kfs = sorted(set(int(sched[i % sched.shape[0], rank]) for i in range(args.steps)))[:6]
         tested, blended, R = pair_counts(runner, kfs)
         scratch = torch.zeros(16, device=device)
         tf = C.c_float(0)

@@ -1,0 +1,97 @@
+"""Keyframe-sharded mapping: host-side plumbing for the multi-GPU leg.
+
+The reference is single-GPU: each mapping iteration renders ONE randomly chosen keyframe of the
+window against all Gaussians and takes an optimiser step (scripts/splatam.py:848-889).  Renders of
+different keyframes are independent given the parameters and their Gaussian gradients add, so the
+path shards over keyframes: one process per GPU (torchrun), the Gaussian set replicated, rank r
+renders keyframe `schedule[step, r]`, then ONE all-reduce (NCCL over NVLink on the GPU box, gloo in
+the CPU tests) of a single flat gradient bucket.  Nothing else is exchanged.
+
+PyTorch is plumbing here (device memory, torch.distributed); the rendering itself is the C-ABI
+library.  This module is device-agnostic on purpose so the world_size-2 gloo tests exercise exactly
+the code bench.py runs.
+"""
+import torch
+
+# (name, floats per Gaussian).  float4-accessed arrays first so every view stays 16-byte aligned
+# for any P (the kernels read quaternions as float4).
+LAYOUT = (("rotations", 4), ("means3D", 3), ("colors_precomp", 3), ("opacities", 1), ("scales", 3))
+FLOATS_PER_GAUSSIAN = sum(w for _, w in LAYOUT)
+
+
+def keyframe_schedule(n_keyframes, steps, world, seed=0):
+    """int64 [steps, world]: keyframe rendered by each rank at each step.  Identical on every rank
+    (seeded, CPU generator) -- it replaces the reference's per-iteration `np.random.randint`
+    (scripts/splatam.py:851).  Within a step the ranks get DISTINCT keyframes whenever
+    world <= n_keyframes (consecutive slices of concatenated random permutations)."""
+    if n_keyframes <= 0 or steps < 0 or world <= 0:
+        raise ValueError("keyframe_schedule: n_keyframes, world must be positive and steps non-negative")
+    g = torch.Generator().manual_seed(int(seed))
+    need = steps * world
+    if world <= n_keyframes:
+        # pad each permutation to a multiple of `world` from the next one so a step never straddles
+        # a permutation boundary with a repeated keyframe
+        out = []
+        while sum(len(o) for o in out) < need:
+            perm = torch.randperm(n_keyframes, generator=g)
+            usable = (n_keyframes // world) * world
+            out.append(perm[:usable])
+        flat = torch.cat(out)[:need] if need else torch.zeros(0, dtype=torch.int64)
+    else:
+        flat = torch.randint(0, n_keyframes, (need,), generator=g)
+    return flat.reshape(steps, world)
+
+
+class GradBucket:
+    """The replicated Gaussian parameters in ONE flat buffer and their gradients in another, with
+    named [P, w] views (LAYOUT).  The rasterizer's autograd leaves write straight into the gradient
+    views, so the exchange is a single all-reduce with no pack kernel."""
+
+    def __init__(self, scene, device="cpu"):
+        self.P = int(scene["means3D"].shape[0])
+        for k, w in LAYOUT:
+            if tuple(scene[k].shape) != (self.P, w):
+                raise ValueError("GradBucket: %s must be [%d, %d], got %s" % (k, self.P, w, tuple(scene[k].shape)))
+        self.params = torch.cat([scene[k].reshape(-1).float() for k, _ in LAYOUT]).to(device)
+        self.grads = torch.zeros_like(self.params)
+        self.views, self.gviews = {}, {}
+        off = 0
+        for k, w in LAYOUT:
+            n = self.P * w
+            self.views[k] = self.params[off:off + n].view(self.P, w)
+            self.gviews[k] = self.grads[off:off + n].view(self.P, w)
+            off += n
+
+    def leaves(self):
+        """Autograd leaves aliasing the parameter views, with .grad aliasing the bucket."""
+        lv = {k: v.detach().requires_grad_(True) for k, v in self.views.items()}
+        for k, leaf in lv.items():
+            leaf.grad = self.gviews[k]
+        return lv
+
+    def zero_grad(self):
+        self.grads.zero_()
+
+    def all_reduce(self, group=None, average=False):
+        """Sum (or mean) of the gradient bucket over the ranks; no-op without a process group."""
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+            return self.grads
+        dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=group)
+        if average:
+            self.grads.div_(dist.get_world_size(group))
+        return self.grads
+
+    def nbytes(self):
+        return self.params.numel() * 4
+
+
+def mapping_step(bucket, render_fn, cams, schedule, step, rank, group=None, average=False):
+    """One keyframe-sharded mapping step: zero the bucket, render + backward this rank's keyframe
+    (render_fn(cam, leaves) must leave d(loss)/d(param) in the leaves' .grad, i.e. in the bucket),
+    all-reduce.  Returns the keyframe id rendered."""
+    kf = int(schedule[step, rank])
+    bucket.zero_grad()
+    render_fn(cams[kf], bucket.leaves())
+    bucket.all_reduce(group, average)
+    return kf

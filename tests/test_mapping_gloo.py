@@ -1,0 +1,118 @@
+"""CPU tests (-m "not gpu") of the keyframe-sharded mapping plumbing (splatam_b200/mapping.py):
+the schedule, the flat gradient bucket, and a world_size-2 `gloo` run of mapping_step whose
+all-reduced bucket must equal the single-process sum over the same keyframes.
+The "render" here is a deterministic differentiable stand-in on CPU tensors -- the rasterizer itself
+needs a GPU and is covered by the -m gpu tests; this file covers the N>1 host logic only."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from splatam_b200 import mapping, synth
+
+
+def _scene(P=257, seed=3):
+    return synth.cloud_scene(P, 64, 64, 64.0, 64.0, seed=seed)
+
+
+def _fake_render(cam, leaves):
+    """Differentiable stand-in: a loss that depends on every parameter and on the keyframe pose."""
+    w = cam  # a [4,4] pose
+    pts = leaves["means3D"] @ w[:3, :3].t() + w[:3, 3]
+    loss = (pts * leaves["colors_precomp"]).sum() + (leaves["opacities"].squeeze(1) * leaves["scales"].sum(1)).sum() \
+        + (leaves["rotations"] ** 2).sum() * float(w[0, 3] + 1.0)
+    loss.backward()
+
+
+def test_schedule_is_deterministic_and_distinct_within_a_step():
+    a = mapping.keyframe_schedule(24, 60, 8, seed=5)
+    b = mapping.keyframe_schedule(24, 60, 8, seed=5)
+    assert a.shape == (60, 8) and torch.equal(a, b)
+    assert int(a.min()) >= 0 and int(a.max()) < 24
+    for s in range(60):
+        assert len(set(a[s].tolist())) == 8
+    # every keyframe of the window gets rendered
+    assert len(set(a.flatten().tolist())) == 24
+    # more ranks than keyframes: still valid ids
+    c = mapping.keyframe_schedule(3, 5, 8, seed=1)
+    assert c.shape == (5, 8) and int(c.max()) < 3
+    assert mapping.keyframe_schedule(24, 0, 2).shape == (0, 2)
+    with pytest.raises(ValueError):
+        mapping.keyframe_schedule(0, 1, 1)
+
+
+def test_bucket_views_alias_the_flat_buffers():
+    sc = _scene()
+    bk = mapping.GradBucket(sc)
+    assert bk.params.numel() == bk.P * mapping.FLOATS_PER_GAUSSIAN == bk.grads.numel()
+    for k, w in mapping.LAYOUT:
+        assert torch.equal(bk.views[k], sc[k])
+        assert bk.views[k].data_ptr() % 16 == bk.params.data_ptr() % 16 or k != "rotations"
+    assert bk.views["rotations"].data_ptr() == bk.params.data_ptr()   # float4 array first => aligned for any P
+    lv = bk.leaves()
+    _fake_render(synth.arc_pose(1, 4), lv)
+    # autograd accumulated straight into the bucket (no pack step)
+    assert float(bk.grads.abs().sum()) > 0
+    assert lv["means3D"].grad.data_ptr() == bk.gviews["means3D"].data_ptr()
+    bk.zero_grad()
+    assert float(bk.grads.abs().sum()) == 0
+    with pytest.raises(ValueError):
+        mapping.GradBucket(dict(sc, scales=sc["scales"][:, :2]))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, steps, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.set_num_threads(1)
+        sc = _scene()
+        cams = [synth.arc_pose(k, 6) for k in range(6)]
+        sched = mapping.keyframe_schedule(6, steps, world, seed=9)
+        bk = mapping.GradBucket(sc)
+        outs = []
+        for s in range(steps):
+            kf = mapping.mapping_step(bk, _fake_render, cams, sched, s, rank)
+            assert kf == int(sched[s, rank])
+            outs.append(bk.grads.clone())
+        torch.save(torch.stack(outs), os.path.join(out_dir, "rank%d.pt" % rank))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_world_size_2_allreduce_equals_single_process_sum(tmp_path):
+    world, steps = 2, 3
+    mp.spawn(_worker, args=(world, _free_port(), steps, str(tmp_path)), nprocs=world, join=True)
+    r0 = torch.load(str(tmp_path / "rank0.pt"))
+    r1 = torch.load(str(tmp_path / "rank1.pt"))
+    assert torch.equal(r0, r1), "ranks disagree after the all-reduce"
+    # single-process reference: sum of the two keyframes' gradients per step
+    sc = _scene()
+    cams = [synth.arc_pose(k, 6) for k in range(6)]
+    sched = mapping.keyframe_schedule(6, steps, world, seed=9)
+    for s in range(steps):
+        tot = None
+        for r in range(world):
+            bk = mapping.GradBucket(sc)
+            _fake_render(cams[int(sched[s, r])], bk.leaves())
+            tot = bk.grads.clone() if tot is None else tot + bk.grads
+        assert torch.allclose(r0[s], tot, rtol=1e-6, atol=1e-6)
+
+
+def test_single_process_all_reduce_is_a_noop():
+    bk = mapping.GradBucket(_scene())
+    _fake_render(synth.arc_pose(0, 4), bk.leaves())
+    before = bk.grads.clone()
+    bk.all_reduce()
+    assert torch.equal(before, bk.grads)

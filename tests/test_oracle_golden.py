@@ -117,8 +117,11 @@ def test_oracle_manual_backward_matches_autograd():
     ((conic * gc).sum() + (pix * gm).sum()).backward()
     # the reference's dL_dmean2D is in NDC-scaled units: blend backward multiplies by 0.5*W / 0.5*H
     gm_ref = gm * torch.tensor([0.5 * W, 0.5 * H]).double()
+    # ... and its dL_dconic.y is half the derivative w.r.t. the off-diagonal (backward.cu:741 accumulates
+    # -0.5*gdx*d.y for a term whose true derivative is -gdx*d.y; backward.cu:212 multiplies dL_db by 2)
+    gc_ref = gc * torch.tensor([1.0, 0.5, 1.0]).double()
     dm, dcv, ds, dr = O.chain_backward(means.detach().float(), scales.detach().float(), rots.detach().float(),
-                                       c3.detach().float(), V, Pm, W, H, rs.tanfovx, rs.tanfovy, gc.float(),
+                                       c3.detach().float(), V, Pm, W, H, rs.tanfovx, rs.tanfovy, gc_ref.float(),
                                        gm_ref.float())
     txtz = (means.detach() @ V.double().reshape(4, 4)[:3, :3])
     unclamped = ((txtz[:, 0] / txtz[:, 2]).abs() < 1.3 * rs.tanfovx) & ((txtz[:, 1] / txtz[:, 2]).abs() < 1.3 * rs.tanfovy)
