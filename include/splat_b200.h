@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define SPLAT_ABI_VERSION 1
+#define SPLAT_ABI_VERSION 2
 
 /* Error codes.  Positive values >= 1000 are 1000 + cudaError_t of a failed runtime call. */
 enum {
@@ -73,8 +73,9 @@ size_t splat_binning_state_bytes(int32_t width, int32_t height, int64_t R_capaci
 /* ---- forward, phase 1: per-Gaussian geometry + per-tile counts + tile ranges ----------------
  * Replaces preprocessCUDA + InclusiveSum + the blocking num_rendered read
  * (HX/cuda_rasterizer/rasterizer_impl.cu:248-282).  Fully asynchronous.  On return (in stream
- * order) geom_state holds depth/xy/conic_opacity(/rgb,clamped), image_state holds the bit-exact
- * tile ranges, radii[P] is written, and *num_rendered_dev (device uint32) holds R.
+ * order) geom_state holds one 48-byte record per visible Gaussian (pixel mean, conic, opacity, depth,
+ * colour -- SH-evaluated if shs is given), image_state holds the bit-exact tile ranges, radii[P] is
+ * written, and *num_rendered_dev (device uint32) holds R.
  * Exactly one of (scales && rotations) or cov3D_precomp must be non-NULL; exactly one of
  * colors_precomp or shs must be non-NULL (same rule as HX/.../__init__.py:174-178). */
 int splat_forward_geometry(const SplatCamera* cam, int32_t P,
@@ -93,13 +94,14 @@ int splat_forward_geometry(const SplatCamera* cam, int32_t P,
 
 /* ---- forward, phase 2: scatter instances to tiles, per-tile depth sort, blend ---------------
  * Replaces duplicateWithKeys + DeviceRadixSort + identifyTileRanges + renderCUDA
- * (HX/cuda_rasterizer/rasterizer_impl.cu:290-337).  R_capacity is the number of (tile,Gaussian)
+ * (HX/cuda_rasterizer/rasterizer_impl.cu:290-337).  The sort also writes the sorted 48-byte instance
+ * records that the forward and backward blend kernels stream with the TMA unit.  R_capacity is the number of (tile,Gaussian)
  * instances binning_state was sized for.  If the device-side R exceeds it, every kernel of this
  * phase exits without touching memory out of bounds and the outputs are undefined; the caller
  * learns R from *num_rendered_dev (phase 1) and simply calls phase 2 again with a larger state.
  * out_depth may be NULL. */
 int splat_forward_render(const SplatCamera* cam, int32_t P,
-                         const float* colors_precomp,   /* [P,3] or NULL (then SH colours of phase 1) */
+                         const float* colors_precomp,   /* unused (colours were captured by phase 1); kept for symmetry */
                          const int32_t* radii,          /* [P] as written by phase 1 */
                          const void* geom_state, void* image_state, void* binning_state,
                          int64_t R_capacity,
@@ -114,7 +116,12 @@ int splat_forward_render(const SplatCamera* cam, int32_t P,
  * power == 2 is the fork's diagonal Gauss-Newton ("Hessian") accumulation.
  * `R` is the R_capacity that was passed to splat_forward_render (it fixes the state layout).
  * All dL_* outputs are fully written by the call (no pre-zeroing needed).  dL_dconic is a
- * [P,4] scratch/output (x,y,_,w as in the reference's [P,2,2]).  dL_dsh may be NULL when shs is. */
+ * [P,4] output (x,y,_,w as in the reference's [P,2,2]).  dL_dsh may be NULL when shs is.
+ * `scratch` is a 16-byte aligned device buffer of at least splat_backward_scratch_bytes(P, power)
+ * bytes (the packed per-Gaussian accumulator rows the blend-backward kernel reduces into); the
+ * call zeroes it itself.  colors_precomp is accepted for signature parity with the reference
+ * (HX/rasterize_points.h:43-65) but the colours of the forward call are used. */
+size_t splat_backward_scratch_bytes(int32_t P, int32_t power);
 int splat_backward(const SplatCamera* cam, int32_t P, int64_t R,
                    const float* means3D, const float* scales, const float* rotations,
                    const float* cov3D_precomp, const float* shs, int32_t M,
@@ -131,6 +138,7 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R,
                    float* dL_dcov3D,    /* [P,6] */
                    float* dL_dconic,    /* [P,4] */
                    float* dL_dsh,       /* [P,M,3] or NULL */
+                   void* scratch, size_t scratch_bytes,
                    void* stream);
 
 /* ---- markVisible (HX/cuda_rasterizer/rasterizer_impl.cu:54-66,141-153) ---------------------- */
@@ -145,9 +153,12 @@ const void* splat_state_n_contrib(const void* image_state, int32_t width, int32_
 const void* splat_state_final_T(const void* image_state, int32_t width, int32_t height);
 const void* splat_state_point_list(const void* binning_state, int32_t width, int32_t height,
                                    int64_t R_capacity);
-const void* splat_state_depths(const void* geom_state, int32_t P);
-const void* splat_state_means2D(const void* geom_state, int32_t P);
-const void* splat_state_conic_opacity(const void* geom_state, int32_t P);
+/* float[P,12] per-Gaussian records (x, y, conic A, B | conic C, opacity, view depth, - | r, g, b, -);
+ * only rows with radii > 0 are defined.  float[R,12] sorted instance records: same layout with the
+ * Gaussian id (uint32 bits) in slot 7 -- the byte stream the blend kernels' TMA ring consumes. */
+const void* splat_state_gaussian_records(const void* geom_state, int32_t P);
+const void* splat_state_instance_records(const void* binning_state, int32_t width, int32_t height,
+                                         int64_t R_capacity);
 
 /* ---- measurement helpers (used by bench.py; not on the product path) -----------------------
  * splat_profile_enable(1) makes every kernel launch of this library record a cudaEvent pair on

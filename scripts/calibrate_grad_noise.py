@@ -11,6 +11,7 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 from util import CASES, build_case, rel_err  # noqa: E402
 from test_gpu_parity import run_ours, run_ref  # noqa: E402
 
+FLOORS = tuple(float(x) for x in os.environ.get("FLOORS", "1e-6,1e-5,1e-4,1e-3").split(","))
 KEYS = ("means3D", "means2D", "colors", "opacities", "scales", "rotations")
 for case in CASES:
     for variant, power in (("dg", 1), ("hx", 1), ("hx", 2)):
@@ -21,7 +22,7 @@ for case in CASES:
         r2 = run_ref(variant, rs, sc, dL, power)["grads"]
         o1 = run_ours(variant, rs, sc, dL, power)["grads"]
         o2 = run_ours(variant, rs, sc, dL, power)["grads"]
-        for floor in (1e-6, 1e-5, 1e-4, 1e-3):
+        for floor in FLOORS:
             row = "%-14s %s p%d floor=%g |" % (case, variant, power, floor)
             for k in KEYS:
                 row += " %s rr=%.1e oo=%.1e or=%.1e |" % (k[:6], rel_err(r1[k], r2[k], floor), rel_err(o1[k], o2[k], floor),

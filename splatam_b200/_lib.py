@@ -39,15 +39,15 @@ _SIGNATURES = {
     "splat_forward_render": (C.c_int, [C.POINTER(SplatCamera), C.c_int32, _P, _P, _P, _P, _P, C.c_int64, _P, _P, _P]),
     "splat_backward": (C.c_int, [C.POINTER(SplatCamera), C.c_int32, C.c_int64, _P, _P, _P, _P, _P, C.c_int32,
                                  _P, _P, _P, _P, _P, _P, C.c_int32, C.c_int32,
-                                 _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+                                 _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
+    "splat_backward_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "splat_mark_visible": (C.c_int, [C.c_int32, _P, _P, _P, C.c_float, _P, _P]),
     "splat_state_ranges": (_P, [_P, C.c_int32, C.c_int32]),
     "splat_state_n_contrib": (_P, [_P, C.c_int32, C.c_int32]),
     "splat_state_final_T": (_P, [_P, C.c_int32, C.c_int32]),
     "splat_state_point_list": (_P, [_P, C.c_int32, C.c_int32, C.c_int64]),
-    "splat_state_depths": (_P, [_P, C.c_int32]),
-    "splat_state_means2D": (_P, [_P, C.c_int32]),
-    "splat_state_conic_opacity": (_P, [_P, C.c_int32]),
+    "splat_state_gaussian_records": (_P, [_P, C.c_int32]),
+    "splat_state_instance_records": (_P, [_P, C.c_int32, C.c_int32, C.c_int64]),
     "splat_profile_enable": (C.c_int, [C.c_int]),
     "splat_profile_read": (C.c_int, [_P, _P, C.c_int32]),
     "splat_profile_kernel_name": (C.c_char_p, [C.c_int]),
@@ -72,7 +72,7 @@ def _load():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing: intended
         fn.restype = res
         fn.argtypes = args
-    if lib.splat_abi_version() != 1:
+    if lib.splat_abi_version() != 2:
         raise ImportError("libsplat_b200.so ABI version mismatch")
     return lib
 

@@ -111,6 +111,7 @@ int splat_forward_render(const SplatCamera* cam, int32_t P, const float* colors_
                          void* image_state, void* binning_state, int64_t R_capacity, float* out_color,
                          float* out_depth, void* stream) {
   read_env_once();
+  (void)colors_precomp;  // already folded into the geometry records by phase 1
   if (int rc = check_cam(cam)) return rc;
   if (!geom_state || !image_state || !binning_state || !out_color) return fail(SPLAT_ERR_BAD_ARG, "NULL buffer");
   if (R_capacity < 0 || R_capacity > 0xffffffffll) return fail(SPLAT_ERR_BAD_ARG, "R_capacity out of range");
@@ -123,12 +124,10 @@ int splat_forward_render(const SplatCamera* cam, int32_t P, const float* colors_
   const uint32_t Rcap = (uint32_t)R_capacity;
   if (P > 0 && !radii) return fail(SPLAT_ERR_BAD_ARG, "radii is NULL");
   if (int rc = launch_scatter(P, gx, gy, radii, gv, iv, bv, Rcap, st)) return rc;
-  if (int rc = launch_tile_sort(T, iv, bv, Rcap, st)) return rc;
+  if (int rc = launch_tile_sort(T, iv, gv, bv, Rcap, st)) return rc;
   RenderFwdArgs r;
   r.W = W; r.H = H; r.gx = gx;
-  r.ranges = iv.ranges; r.point_list = bv.point_list;
-  r.xy = gv.xy; r.conic_opacity = gv.conic_opacity; r.depths = gv.depths;
-  r.colors = colors_precomp ? colors_precomp : gv.rgb;
+  r.ranges = iv.ranges; r.inst = bv.inst;
   r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.out_color = out_color; r.out_depth = out_depth;
   r.hdr = iv.hdr; r.Rcap = Rcap; r.blended = nullptr;
@@ -136,14 +135,19 @@ int splat_forward_render(const SplatCamera* cam, int32_t P, const float* colors_
 }
 
 
+size_t splat_backward_scratch_bytes(int32_t P, int32_t power) {
+  return align_up((size_t)(P > 0 ? P : 1) * (power == 1 ? 12 : 20) * sizeof(float));
+}
+
 int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* means3D, const float* scales,
                    const float* rotations, const float* cov3D_precomp, const float* shs, int32_t M,
                    const float* colors_precomp, const int32_t* radii, const void* geom_state,
                    const void* image_state, const void* binning_state, const float* dL_dout_color,
                    int32_t power, int32_t fused, float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors,
                    float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
-                   float* dL_dconic, float* dL_dsh, void* stream) {
+                   float* dL_dconic, float* dL_dsh, void* scratch, size_t scratch_bytes, void* stream) {
   read_env_once();
+  (void)colors_precomp;  // the colours travel inside the instance records written by the forward pass
   if (int rc = check_cam(cam)) return rc;
   if (P < 0 || R < 0) return fail(SPLAT_ERR_BAD_ARG, "P or R negative");
   if (P == 0) return SPLAT_OK;
@@ -161,6 +165,10 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
   if (hess && power != 2)
     return fail(SPLAT_ERR_UNSUPPORTED, "backward_power must be 1 or 2 (the reference only ever uses those, ros_handler.py:884)");
   if (hess && shs) return fail(SPLAT_ERR_UNSUPPORTED, "SH + Hessian backward is undefined in the reference (backward.cu:1067)");
+  const size_t need = splat_backward_scratch_bytes(P, hess ? 2 : 1);
+  if (!scratch || ((uintptr_t)scratch & 15)) return fail(SPLAT_ERR_BAD_ARG, "scratch must be a 16-byte aligned device buffer");
+  if (scratch_bytes < need)
+    return fail(SPLAT_ERR_SCRATCH_TOO_SMALL, "backward scratch needs %zu bytes, got %zu", need, scratch_bytes);
   cudaStream_t st = (cudaStream_t)stream;
   const int W = cam->image_width, H = cam->image_height;
   const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y, T = gx * gy;
@@ -168,19 +176,14 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
   GeomView gv = geom_view(const_cast<void*>(geom_state), P);
   BinView bv = bin_view(const_cast<void*>(binning_state), R);
   const float fx = W / (2.0f * cam->tanfovx), fy = H / (2.0f * cam->tanfovy);
+  float* acc = reinterpret_cast<float*>(scratch);
+  SPLAT_CUDA(cudaMemsetAsync(acc, 0, need, st));
 
   RenderBwdArgs r;
-  r.W = W; r.H = H; r.gx = gx; r.ranges = iv.ranges; r.point_list = bv.point_list;
-  r.xy = gv.xy; r.conic_opacity = gv.conic_opacity;
-  r.colors = colors_precomp ? colors_precomp : gv.rgb; r.bg = cam->bg;
+  r.W = W; r.H = H; r.gx = gx; r.ranges = iv.ranges; r.inst = bv.inst; r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.dL_dpix = dL_dout_color;
-  r.dL_dmean2D = dL_dmeans2D; r.dL_dconic = dL_dconic; r.dL_dopacity = dL_dopacity; r.dL_dcolors = dL_dcolors;
-  r.acc = nullptr;
+  r.acc = acc;
   if (!hess) {
-    SPLAT_CUDA(cudaMemsetAsync(dL_dmeans2D, 0, (size_t)P * 12, st));
-    SPLAT_CUDA(cudaMemsetAsync(dL_dconic, 0, (size_t)P * 16, st));
-    SPLAT_CUDA(cudaMemsetAsync(dL_dopacity, 0, (size_t)P * 4, st));
-    SPLAT_CUDA(cudaMemsetAsync(dL_dcolors, 0, (size_t)P * 12, st));
     if (R > 0) if (int rc = launch_render_bwd(r, T, 0, st)) return rc;
     PreBwdArgs b;
     b.P = P; b.M = M; b.sh_degree = cam->sh_degree; b.tanx = cam->tanfovx; b.tany = cam->tanfovy;
@@ -188,23 +191,16 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
     b.means = means3D; b.scales = sr ? scales : nullptr; b.rots = sr ? rotations : nullptr;
     b.cov3D_pre = cov3D_precomp; b.shs = shs; b.clamped = gv.clamped; b.campos = cam->campos;
     b.V = cam->viewmatrix; b.Pm = cam->projmatrix; b.radii = radii;
-    b.dL_dmean2D = dL_dmeans2D; b.dL_dconic = dL_dconic; b.dL_dcolor = dL_dcolors;
+    b.W = W; b.H = H; b.grec = gv.grec; b.acc = acc;
+    b.dL_dmean2D = dL_dmeans2D; b.dL_dconic = dL_dconic; b.dL_dcolor = dL_dcolors; b.dL_dopacity = dL_dopacity;
     b.dL_dmeans = dL_dmeans3D; b.dL_dcov3D = dL_dcov3D; b.dL_dscales = dL_dscales; b.dL_drots = dL_drotations;
     b.dL_dsh = dL_dsh;
     return launch_preprocess_bwd(b, st);
   }
-  // Hessian: the [P,20] moment accumulator borrows the keys/keys_alt area of the binning state
-  // (dead after the forward sort) when it is large enough, else the call is refused.
-  const size_t need = (size_t)P * 20 * 4;
-  const size_t have = align_up((size_t)(R > 0 ? R : 1) * 8) * 2;
-  if (have < need)
-    return fail(SPLAT_ERR_SCRATCH_TOO_SMALL, "Hessian accumulator needs %zu bytes, binning state offers %zu", need, have);
-  float* acc = reinterpret_cast<float*>(bv.keys);
-  SPLAT_CUDA(cudaMemsetAsync(acc, 0, need, st));
-  r.acc = acc;
   if (R > 0) if (int rc = launch_render_bwd(r, T, 1, st)) return rc;
   HessArgs h;
   h.P = P; h.tanx = cam->tanfovx; h.tany = cam->tanfovy; h.fx = fx; h.fy = fy; h.mod = cam->scale_modifier;
+  h.W = W; h.H = H;
   h.means = means3D; h.scales = sr ? scales : nullptr; h.rots = sr ? rotations : nullptr; h.cov3D_pre = cov3D_precomp;
   h.V = cam->viewmatrix; h.Pm = cam->projmatrix; h.radii = radii; h.acc = acc;
   h.dL_dmeans = dL_dmeans3D; h.dL_dmean2D = dL_dmeans2D; h.dL_dcolors = dL_dcolors; h.dL_dopacity = dL_dopacity;
@@ -225,9 +221,8 @@ const void* splat_state_ranges(const void* s, int32_t W, int32_t H) { return ima
 const void* splat_state_n_contrib(const void* s, int32_t W, int32_t H) { return image_view(const_cast<void*>(s), W, H).n_contrib; }
 const void* splat_state_final_T(const void* s, int32_t W, int32_t H) { return image_view(const_cast<void*>(s), W, H).final_T; }
 const void* splat_state_point_list(const void* s, int32_t, int32_t, int64_t R) { return bin_view(const_cast<void*>(s), R).point_list; }
-const void* splat_state_depths(const void* s, int32_t P) { return geom_view(const_cast<void*>(s), P).depths; }
-const void* splat_state_means2D(const void* s, int32_t P) { return geom_view(const_cast<void*>(s), P).xy; }
-const void* splat_state_conic_opacity(const void* s, int32_t P) { return geom_view(const_cast<void*>(s), P).conic_opacity; }
+const void* splat_state_gaussian_records(const void* s, int32_t P) { return geom_view(const_cast<void*>(s), P).grec; }
+const void* splat_state_instance_records(const void* s, int32_t, int32_t, int64_t R) { return bin_view(const_cast<void*>(s), R).inst; }
 
 // Debug/measurement helper: re-runs the forward blend over an existing (geom, image, binning) state
 // WITHOUT culling and writes the number of blended pairs per pixel (F_alg of the roofline model).
@@ -243,8 +238,8 @@ int splat_debug_count_blended(const SplatCamera* cam, int32_t P, const float* co
   GeomView gv = geom_view(const_cast<void*>(geom_state), P);
   BinView bv = bin_view(const_cast<void*>(binning_state), R_capacity);
   RenderFwdArgs r;
-  r.W = W; r.H = H; r.gx = gx; r.ranges = iv.ranges; r.point_list = bv.point_list;
-  r.xy = gv.xy; r.conic_opacity = gv.conic_opacity; r.depths = gv.depths; r.colors = colors; r.bg = cam->bg;
+  (void)colors; (void)gv;
+  r.W = W; r.H = H; r.gx = gx; r.ranges = iv.ranges; r.inst = bv.inst; r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.out_color = scratch_color; r.out_depth = nullptr;
   r.hdr = iv.hdr; r.Rcap = (uint32_t)R_capacity; r.blended = blended;
   return launch_render_fwd(r, gx * gy, (cudaStream_t)stream);

@@ -82,8 +82,7 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* 
 
 // --------------------------------------------------------------------------------------- scatter
 __global__ void __launch_bounds__(256) scatter_kernel(int P, int gx, int gy, const int* __restrict__ radii,
-                                                      const float2* __restrict__ xy,
-                                                      const float* __restrict__ depths,
+                                                      const float4* __restrict__ grec,
                                                       uint32_t* __restrict__ tile_cursor,
                                                       uint64_t* __restrict__ keys,
                                                       const ImageHeader* __restrict__ hdr, uint32_t Rcap) {
@@ -97,8 +96,10 @@ __global__ void __launch_bounds__(256) scatter_kernel(int P, int gx, int gy, con
     const int r = radii[idx];
     if (r > 0) {
       vis = true;
-      tile_rect(xy[idx], r, gx, gy, x0, y0, x1, y1);
-      kv = ((uint64_t)__float_as_uint(depths[idx]) << 32) | (uint32_t)idx;
+      const float2 p = __ldg(reinterpret_cast<const float2*>(grec + (size_t)idx * INST_F4));
+      const float depth = __ldg(reinterpret_cast<const float*>(grec + (size_t)idx * INST_F4 + 1) + 2);
+      tile_rect(p, r, gx, gy, x0, y0, x1, y1);
+      kv = ((uint64_t)__float_as_uint(depth) << 32) | (uint32_t)idx;
     }
   }
   const int ntile = vis ? (x1 - x0) * (y1 - y0) : 0;
@@ -187,6 +188,8 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
                                                                  uint64_t* __restrict__ keys,
                                                                  uint64_t* __restrict__ keys_alt,
                                                                  uint32_t* __restrict__ point_list,
+                                                                 float4* __restrict__ inst,
+                                                                 const float4* __restrict__ grec,
                                                                  const ImageHeader* __restrict__ hdr,
                                                                  uint32_t Rcap, int smem_cap) {
   if (hdr->num_rendered > Rcap) return;
@@ -200,8 +203,20 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   uint64_t* gsrc = keys + rg.x;
   uint32_t* out = point_list + rg.x;
+  float4* rec = inst + (size_t)rg.x * INST_F4;
+  // Emits list position `pos`: the sorted id and the 48-byte instance record the blend kernels stream.
+  auto emit = [&](int pos, uint64_t k) {
+    const uint32_t id = (uint32_t)k;
+    out[pos] = id;
+    const float4* src = grec + (size_t)id * INST_F4;
+    const float4 g0 = __ldg(src), g2 = __ldg(src + 2);
+    float4 g1 = __ldg(src + 1);
+    g1.w = __uint_as_float(id);
+    float4* q = rec + (size_t)pos * INST_F4;
+    q[0] = g0; q[1] = g1; q[2] = g2;
+  };
   if (n == 1) {
-    if (tid == 0) out[0] = (uint32_t)gsrc[0];
+    if (tid == 0) emit(0, gsrc[0]);
     return;
   }
   uint64_t* bufA;
@@ -249,7 +264,7 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
       while (hi < n && (uint32_t)(src[hi] >> 32) == d) { below += (uint32_t)src[hi] < id; ++hi; }
       pos = lo + below;
     }
-    out[pos] = id;
+    emit(pos, k);
   }
 }
 
@@ -264,7 +279,7 @@ int launch_scatter(int P, int gx, int gy, const int* radii, const GeomView& g, c
                    const BinView& b, uint32_t Rcap, cudaStream_t st) {
   ProfScope prof_(K_SCATTER, st);
   if (P <= 0) return SPLAT_OK;
-  scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, gx, gy, radii, g.xy, g.depths, iv.tile_cursor, b.keys, iv.hdr, Rcap);
+  scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, gx, gy, radii, g.grec, iv.tile_cursor, b.keys, iv.hdr, Rcap);
   SPLAT_LAUNCH_CHECK("scatter_kernel");
   return SPLAT_OK;
 }
@@ -272,7 +287,7 @@ int launch_scatter(int P, int gx, int gy, const int* radii, const GeomView& g, c
 static const int kSortSmemCap = 4096;  // keys per shared buffer (2 x 32 KB)
 int sort_smem_cap() { return kSortSmemCap; }
 
-int launch_tile_sort(int T, const ImageView& iv, const BinView& b, uint32_t Rcap, cudaStream_t st) {
+int launch_tile_sort(int T, const ImageView& iv, const GeomView& g, const BinView& b, uint32_t Rcap, cudaStream_t st) {
   ProfScope prof_(K_TILE_SORT, st);
   static bool attr_set = false;
   const int smem = kSortSmemCap * 8 * 2;
@@ -280,7 +295,8 @@ int launch_tile_sort(int T, const ImageView& iv, const BinView& b, uint32_t Rcap
     SPLAT_CUDA(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;
   }
-  tile_sort_kernel<<<T, SORT_THREADS, smem, st>>>(iv.ranges, b.keys, b.keys_alt, b.point_list, iv.hdr, Rcap, kSortSmemCap);
+  tile_sort_kernel<<<T, SORT_THREADS, smem, st>>>(iv.ranges, b.keys, b.keys_alt, b.point_list, b.inst, g.grec,
+                                                  iv.hdr, Rcap, kSortSmemCap);
   SPLAT_LAUNCH_CHECK("tile_sort_kernel");
   return SPLAT_OK;
 }

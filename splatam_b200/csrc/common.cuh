@@ -36,25 +36,26 @@ struct ProfScope {  // cudaEvent pair around one launch, only when splat_profile
 // ---------------------------------------------------------------- state layouts
 __host__ __device__ inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
+// Per-Gaussian forward geometry, one 48-byte record per Gaussian in the SAME layout as the sorted
+// instance records below (the tile sort copies it and patches the id in):
+//   q0 = (x, y, conic A, conic B)   q1 = (conic C, opacity, view depth, -)   q2 = (r, g, b, -)
+// Only records of visible Gaussians (radii > 0) are written / ever read.
+#define INST_F4 3
+#define INST_BYTES 48
+
 struct GeomView {
-  float* depths;          // [P] view-space z
-  float2* xy;             // [P] pixel-space mean
-  float4* conic_opacity;  // [P] (A, B, C, opacity)
-  float* rgb;             // [P,3] SH-evaluated colours (SH path only)
-  uint8_t* clamped;       // [P,3] SH clamp flags
+  float4* grec;           // [P * INST_F4]
+  uint8_t* clamped;       // [P,3] SH clamp flags (SH path only)
 };
 inline size_t geom_bytes(int P) {
   size_t p = (size_t)(P > 0 ? P : 1);
-  return align_up(p * 4) + align_up(p * 8) + align_up(p * 16) + align_up(p * 12) + align_up(p * 3);
+  return align_up(p * INST_BYTES) + align_up(p * 3);
 }
 inline GeomView geom_view(void* base, int P) {
   size_t p = (size_t)(P > 0 ? P : 1);
   char* c = (char*)base;
   GeomView v;
-  v.depths = (float*)c;          c += align_up(p * 4);
-  v.xy = (float2*)c;             c += align_up(p * 8);
-  v.conic_opacity = (float4*)c;  c += align_up(p * 16);
-  v.rgb = (float*)c;             c += align_up(p * 12);
+  v.grec = (float4*)c;           c += align_up(p * INST_BYTES);
   v.clamped = (uint8_t*)c;
   return v;
 }
@@ -91,14 +92,19 @@ inline ImageView image_view(void* base, int W, int H) {
   return v;
 }
 
+// One sorted (tile, Gaussian) instance as the blend kernels consume it: 48 bytes, written once by
+// the tile sort in list order so that a tile's list is ONE contiguous, 16-byte aligned byte range
+// that the TMA unit can stream into shared memory (cp.async.bulk).
+//   q0 = (x, y, conic A, conic B)   q1 = (conic C, opacity, depth, gaussian id bits)   q2 = (r, g, b, 0)
 struct BinView {
   uint64_t* keys;        // [Rcap] (depth_bits << 32) | gaussian id, bucketed by tile (unsorted in-bucket)
   uint64_t* keys_alt;    // [Rcap] ping-pong buffer for lists that do not fit in shared memory
   uint32_t* point_list;  // [Rcap] sorted gaussian ids
+  float4* inst;          // [Rcap * INST_F4] sorted instance records
 };
 inline size_t bin_bytes(int64_t Rcap) {
   size_t r = (size_t)(Rcap > 0 ? Rcap : 1);
-  return align_up(r * 8) * 2 + align_up(r * 4);
+  return align_up(r * 8) * 2 + align_up(r * 4) + align_up(r * INST_BYTES);
 }
 inline BinView bin_view(void* base, int64_t Rcap) {
   size_t r = (size_t)(Rcap > 0 ? Rcap : 1);
@@ -106,7 +112,8 @@ inline BinView bin_view(void* base, int64_t Rcap) {
   BinView v;
   v.keys = (uint64_t*)c;      c += align_up(r * 8);
   v.keys_alt = (uint64_t*)c;  c += align_up(r * 8);
-  v.point_list = (uint32_t*)c;
+  v.point_list = (uint32_t*)c; c += align_up(r * 4);
+  v.inst = (float4*)c;
   return v;
 }
 

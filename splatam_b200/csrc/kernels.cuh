@@ -19,9 +19,13 @@ struct PreBwdArgs {
   const float* means; const float* scales; const float* rots; const float* cov3D_pre;
   const float* shs; const uint8_t* clamped; const float* campos;
   const float* V; const float* Pm; const int* radii;
-  const float* dL_dmean2D;  // [P,3]
-  const float* dL_dconic;   // [P,4]
-  const float* dL_dcolor;   // [P,3] (SH backward input)
+  int W, H;
+  const float4* grec;           // [P*3] forward geometry records (conic + opacity)
+  const float* acc;             // [P,12] raw blend-backward sums (see render_bwd.cu)
+  float* dL_dmean2D;  // [P,3] out
+  float* dL_dconic;   // [P,4] out
+  float* dL_dcolor;   // [P,3] out (and SH backward input)
+  float* dL_dopacity; // [P] out
   float* dL_dmeans; float* dL_dcov3D; float* dL_dscales; float* dL_drots; float* dL_dsh;
 };
 
@@ -29,6 +33,7 @@ struct HessArgs {
   int P;
   float tanx, tany, fx, fy, mod;
   const float* means; const float* scales; const float* rots; const float* cov3D_pre;
+  int W, H;
   const float* V; const float* Pm; const int* radii; const float* acc;
   float* dL_dmeans; float* dL_dmean2D; float* dL_dcolors; float* dL_dopacity;
   float* dL_dscales; float* dL_drots; float* dL_dcov3D; float* dL_dconic;
@@ -36,8 +41,7 @@ struct HessArgs {
 
 struct RenderFwdArgs {
   int W, H, gx;
-  const uint2* ranges; const uint32_t* point_list;
-  const float2* xy; const float4* conic_opacity; const float* depths; const float* colors;
+  const uint2* ranges; const float4* inst;
   const float* bg;
   float* final_T; uint32_t* n_contrib; float* out_color; float* out_depth;
   const ImageHeader* hdr; uint32_t Rcap;
@@ -46,11 +50,9 @@ struct RenderFwdArgs {
 
 struct RenderBwdArgs {
   int W, H, gx;
-  const uint2* ranges; const uint32_t* point_list;
-  const float2* xy; const float4* conic_opacity; const float* colors; const float* bg;
+  const uint2* ranges; const float4* inst; const float* bg;
   const float* final_T; const uint32_t* n_contrib; const float* dL_dpix;
-  float* acc;   // MODE 0: unused.  MODE 1: [P,20] moment accumulator
-  float* dL_dmean2D; float* dL_dconic; float* dL_dopacity; float* dL_dcolors;
+  float* acc;   // MODE 0: [P,12] raw sums.  MODE 1: [P,20] moment accumulator.  Pre-zeroed.
 };
 
 int launch_preprocess_fwd(const PreFwdArgs& a, cudaStream_t st);
@@ -60,7 +62,7 @@ int launch_mark_visible(int P, const float* means, const float* V, float near_pl
 int launch_tile_scan(int T, const ImageView& iv, uint32_t* num_rendered_out, uint32_t sort_cap, cudaStream_t st);
 int launch_scatter(int P, int gx, int gy, const int* radii, const GeomView& g, const ImageView& iv,
                    const BinView& b, uint32_t Rcap, cudaStream_t st);
-int launch_tile_sort(int T, const ImageView& iv, const BinView& b, uint32_t Rcap, cudaStream_t st);
+int launch_tile_sort(int T, const ImageView& iv, const GeomView& g, const BinView& b, uint32_t Rcap, cudaStream_t st);
 int sort_smem_cap();
 int launch_render_fwd(const RenderFwdArgs& a, int T, cudaStream_t st);
 int launch_render_bwd(const RenderBwdArgs& a, int T, int mode, cudaStream_t st);

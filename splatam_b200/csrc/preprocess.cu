@@ -81,23 +81,30 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreFwdArgs a)
   int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
   if (idx < a.P) {
     int my_radius = 0;
+    // every input of this Gaussian is requested up front (independent loads in flight together);
+    // the few culled Gaussians cost their bytes, everyone else saves a dependent round trip
     const float3 p = make_float3(__ldg(a.means + 3 * idx), __ldg(a.means + 3 * idx + 1),
                                  __ldg(a.means + 3 * idx + 2));
+    float3 s = make_float3(0.f, 0.f, 0.f);
+    float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+    float cov3D[6];
+    if (a.cov3D_pre) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) cov3D[k] = __ldg(a.cov3D_pre + 6 * idx + k);
+    } else {
+      s = make_float3(__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1), __ldg(a.scales + 3 * idx + 2));
+      q = __ldg(reinterpret_cast<const float4*>(a.rots) + idx);
+    }
+    const float opacity = __ldg(a.opac + idx);
+    float3 rgb = make_float3(0.f, 0.f, 0.f);
+    if (a.colors_pre)
+      rgb = make_float3(__ldg(a.colors_pre + 3 * idx), __ldg(a.colors_pre + 3 * idx + 1), __ldg(a.colors_pre + 3 * idx + 2));
     const float3 pv = xform_point_4x3(p, a.V);
     if (pv.z > a.near_plane) {  // in_frustum: reject p_view.z <= near
       const float4 ph = xform_point_4x4(p, a.Pm);
       const float pw = 1.0f / (ph.w + 0.0000001f);
       const float ppx = ph.x * pw, ppy = ph.y * pw;
-      float cov3D[6];
-      if (a.cov3D_pre) {
-#pragma unroll
-        for (int k = 0; k < 6; ++k) cov3D[k] = __ldg(a.cov3D_pre + 6 * idx + k);
-      } else {
-        const float3 s = make_float3(__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1),
-                                     __ldg(a.scales + 3 * idx + 2));
-        const float4 q = __ldg(reinterpret_cast<const float4*>(a.rots) + idx);
-        cov3d_from_scale_rot(s, a.mod, q, cov3D);
-      }
+      if (!a.cov3D_pre) cov3d_from_scale_rot(s, a.mod, q, cov3D);
       const float3 cov = cov2d_ewa(p, a.fx, a.fy, a.tanx, a.tany, cov3D, a.V);
       const float det = cov.x * cov.z - cov.y * cov.y;
       if (det != 0.0f) {
@@ -127,11 +134,12 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreFwdArgs a)
             }
             r += 0.5f; gcol += 0.5f; bl += 0.5f;
             a.g.clamped[3 * idx + 0] = r < 0; a.g.clamped[3 * idx + 1] = gcol < 0; a.g.clamped[3 * idx + 2] = bl < 0;
-            a.g.rgb[3 * idx + 0] = fmaxf(r, 0.f); a.g.rgb[3 * idx + 1] = fmaxf(gcol, 0.f); a.g.rgb[3 * idx + 2] = fmaxf(bl, 0.f);
+            rgb = make_float3(fmaxf(r, 0.f), fmaxf(gcol, 0.f), fmaxf(bl, 0.f));
           }
-          a.g.depths[idx] = pv.z;
-          a.g.xy[idx] = pix;
-          a.g.conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, __ldg(a.opac + idx));
+          float4* rec = a.g.grec + (size_t)idx * INST_F4;
+          rec[0] = make_float4(pix.x, pix.y, conic.x, conic.y);
+          rec[1] = make_float4(conic.z, opacity, pv.z, 0.f);
+          rec[2] = make_float4(rgb.x, rgb.y, rgb.z, 0.f);
         }
       }
     }
@@ -308,8 +316,10 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means, cons
 }
 
 
-// One thread per Gaussian: DG's computeCov2DCUDA + preprocessCUDA backward in one pass.
-// Every output row is written (zeros for culled Gaussians), so the caller need not pre-zero.
+// One thread per Gaussian: finalises the raw blend-backward sums (render_bwd.cu MODE 0) into
+// dL_dcolors / dL_dopacity / dL_dmean2D / dL_dconic, then DG's computeCov2DCUDA + preprocessCUDA
+// backward in one pass.  Every output row is written (zeros for culled Gaussians: their
+// accumulator rows were never touched), so the caller need not pre-zero the outputs.
 __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= a.P) return;
@@ -317,7 +327,22 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
   float dscale[3] = {0.f, 0.f, 0.f}, drot[4] = {0.f, 0.f, 0.f, 0.f};
   const bool vis = a.radii[idx] > 0;
   const int nb = a.shs ? (a.sh_degree + 1) * (a.sh_degree + 1) : 0;
+  float3 dcol = make_float3(0.f, 0.f, 0.f);
+  float dop = 0.f, dm2x = 0.f, dm2y = 0.f;
+  float4 dcon = make_float4(0.f, 0.f, 0.f, 0.f);
   if (vis) {
+    // raw sums: [0..2] colour, [3] u*dx, [4] u*dy, [5] u*dx*dx, [6] u*dx*dy, [7] u*dy*dy, [8] u
+    const float4* row = reinterpret_cast<const float4*>(a.acc + (size_t)idx * 12);
+    const float4 r0 = __ldg(row), r1 = __ldg(row + 1), r2 = __ldg(row + 2);
+    const float4 g0 = __ldg(a.grec + (size_t)idx * INST_F4);
+    const float2 g1 = __ldg(reinterpret_cast<const float2*>(a.grec + (size_t)idx * INST_F4 + 1));
+    const float4 co = make_float4(g0.z, g0.w, g1.x, g1.y);   // conic A, B, C, opacity
+    const float o = co.w;
+    dcol = make_float3(r0.x, r0.y, r0.z);
+    dop = r2.x;                                                     // sum G * dL/dalpha
+    dm2x = -(co.x * r0.w + co.y * r1.x) * o * (0.5f * a.W);         // backward.cu:717-725
+    dm2y = -(co.z * r1.x + co.y * r0.w) * o * (0.5f * a.H);
+    dcon = make_float4(-0.5f * o * r1.y, -0.5f * o * r1.z, 0.f, -0.5f * o * r1.w);   // backward.cu:740-742
     const float3 mean = make_float3(__ldg(a.means + 3 * idx), __ldg(a.means + 3 * idx + 1),
                                     __ldg(a.means + 3 * idx + 2));
     float cov3D[6];
@@ -335,16 +360,14 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
     }
     GaussChain g;
     chain_setup(g, mean, cov3D, has_scale, s, a.mod, q, a.fx, a.fy, a.tanx, a.tany, a.V, a.Pm);
-    const float4 dc = __ldg(reinterpret_cast<const float4*>(a.dL_dconic) + idx);
-    chain_apply(g, dc.x, dc.y, dc.w, __ldg(a.dL_dmean2D + 3 * idx), __ldg(a.dL_dmean2D + 3 * idx + 1),
-                dmean, dcov, dscale, drot);
+    chain_apply(g, dcon.x, dcon.y, dcon.w, dm2x, dm2y, dmean, dcov, dscale, drot);
     if (a.shs) {  // SH backward (backward.cu:20-139): dL_dsh, and dL_dmean through the view direction
       const float3 c = make_float3(__ldg(a.campos), __ldg(a.campos + 1), __ldg(a.campos + 2));
       const float ox = mean.x - c.x, oy = mean.y - c.y, oz = mean.z - c.z;
       const float sum2 = ox * ox + oy * oy + oz * oz;
       const float inv = 1.0f / sqrtf(sum2);
       const float x = ox * inv, y = oy * inv, z = oz * inv;
-      float3 dRGB = make_float3(a.dL_dcolor[3 * idx], a.dL_dcolor[3 * idx + 1], a.dL_dcolor[3 * idx + 2]);
+      float3 dRGB = dcol;
       if (a.clamped[3 * idx + 0]) dRGB.x = 0.f;
       if (a.clamped[3 * idx + 1]) dRGB.y = 0.f;
       if (a.clamped[3 * idx + 2]) dRGB.z = 0.f;
@@ -370,6 +393,10 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
     float* dsh = a.dL_dsh + (size_t)idx * a.M * 3;
     for (int k = 0; k < a.M * 3; ++k) dsh[k] = 0.f;
   }
+  a.dL_dcolor[3 * idx] = dcol.x; a.dL_dcolor[3 * idx + 1] = dcol.y; a.dL_dcolor[3 * idx + 2] = dcol.z;
+  a.dL_dopacity[idx] = dop;
+  a.dL_dmean2D[3 * idx] = dm2x; a.dL_dmean2D[3 * idx + 1] = dm2y; a.dL_dmean2D[3 * idx + 2] = 0.f;
+  reinterpret_cast<float4*>(a.dL_dconic)[idx] = dcon;
 #pragma unroll
   for (int k = 0; k < 3; ++k) a.dL_dmeans[3 * idx + k] = dmean[k];
 #pragma unroll

@@ -9,7 +9,11 @@
 
 namespace splat {
 
-#define BATCH 256
+// Instance ring shared by both blend kernels: RING_NS stages of RING_CH records (48 B each), filled by
+// the TMA unit from a producer warp (warp 8) and consumed by warps 0..7 (one 8x4 sub-tile each).
+#define RING_CH 128
+#define RING_NS 4
+#define RING_THREADS 288
 
 struct SubTile {
   int px, py;        // this lane's pixel

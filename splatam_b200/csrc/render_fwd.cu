@@ -2,90 +2,161 @@
 // n_contrib).  Restates renderCUDA<3> forward (HX/cuda_rasterizer/forward.cu:261-393).
 //
 // Differences in HOW (results identical):
+//  * the tile's sorted instance records (48 B each, written by the tile sort in list order) are ONE
+//    contiguous byte range; a producer warp streams it into a 4-stage shared-memory ring with the
+//    TMA unit (cp.async.bulk + mbarrier complete_tx).  The 8 consumer warps never meet at a CTA
+//    barrier: each waits on the stage's "full" mbarrier and releases it through the "empty" one,
+//    so warps drift apart by up to 4 stages instead of idling at __syncthreads (the reference
+//    re-syncs the whole CTA every 256 Gaussians, forward.cu:311-334);
 //  * per-warp 8x4 sub-tiles with an exact conservative footprint test (render.cuh): a warp only
-//    evaluates Gaussians whose alpha>=1/255 ellipse can touch its 32 pixels (ballot + ffs walk);
-//  * the Gaussian's colour and depth are staged in shared memory with the geometry (the
-//    reference re-reads colour from global memory per pixel, forward.cu:361);
-//  * warp-level early termination (__all_sync(done)) on top of the block-level vote.
+//    evaluates Gaussians whose alpha>=1/255 ellipse can touch its 32 pixels (ballot + ffs walk),
+//    two hits at a time so the two exponentials overlap;
+//  * colour and depth travel with the record (the reference re-reads colour from global memory per
+//    pixel, forward.cu:361);
+//  * warp-level early termination, and the producer stops streaming once all 8 warps are done.
 // Per-pixel arithmetic keeps the reference's expression order and precise expf so the discrete
 // tests (power>0, alpha<1/255, T<1e-4, median crossing) take the same branches.
 #include "render.cuh"
 #include "kernels.cuh"
+#include "pipeline.cuh"
 
 namespace splat {
 
-
 template <bool CULL, bool COUNT>
-__global__ void __launch_bounds__(256) render_fwd_kernel(const RenderFwdArgs a) {
+__global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFwdArgs a) {
   if (a.hdr->num_rendered > a.Rcap) return;
-  __shared__ float2 s_xy[BATCH];
-  __shared__ float4 s_co[BATCH];
-  __shared__ float4 s_cd[BATCH];  // r, g, b, depth
-  __shared__ float4 s_bb[BATCH];
+  __shared__ __align__(128) float4 s_rec[RING_NS][RING_CH * INST_F4];
+  __shared__ __align__(8) uint64_t s_full[RING_NS];
+  __shared__ __align__(8) uint64_t s_empty[RING_NS];
+  __shared__ int s_ndone;
+  __shared__ int s_stop;
 
   const int tile = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const uint2 range = a.ranges[tile];
+  const int n = (int)(range.y - range.x);
+  const int nch = (n + RING_CH - 1) / RING_CH;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < RING_NS; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], 8); }
+    s_ndone = 0;
+    s_stop = 0x7fffffff;
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (wid == 8) {  // ------------------------------------------------------------ producer warp
+    if (lane == 0) {
+      const char* src = reinterpret_cast<const char*>(a.inst) + (size_t)range.x * INST_BYTES;
+      for (int c = 0; c < nch; ++c) {
+        const int s = c % RING_NS;
+        if (c >= RING_NS) mbar_wait(&s_empty[s], ((c / RING_NS) - 1) & 1);
+        if (*(volatile int*)&s_ndone == 8) {  // every pixel of the tile has terminated
+          *(volatile int*)&s_stop = c;
+          mbar_arrive(&s_full[s]);
+          break;
+        }
+        const uint32_t bytes = (uint32_t)min(RING_CH, n - c * RING_CH) * INST_BYTES;
+        mbar_arrive_expect_tx(&s_full[s], bytes);
+        tma_load_1d(&s_rec[s][0], src + (size_t)c * RING_CH * INST_BYTES, bytes, &s_full[s]);
+      }
+    }
+    return;
+  }
+
+  // ------------------------------------------------------------------------------ consumer warps
   const int tile_x = tile % a.gx, tile_y = tile / a.gx;
-  const int tid = threadIdx.x, lane = tid & 31;
   const SubTile st = make_subtile(tile_x, tile_y);
   const bool inside = st.px < a.W && st.py < a.H;
   const float pxf = (float)st.px, pyf = (float)st.py;
   const float tile_cx = tile_x * TILE_X + 7.5f, tile_cy = tile_y * TILE_Y + 7.5f;
-
-  const uint2 range = a.ranges[tile];
-  const int n = (int)(range.y - range.x);
+  const uint32_t rec_base = smem_u32(&s_rec[0][0]);
 
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 15.0f;
   uint32_t last = 0, nblend = 0;
   bool done = !inside;
   bool warp_done = __all_sync(0xffffffffu, done);
+  bool counted = false;
 
-  for (int base = 0; base < n; base += BATCH) {
-    if (__syncthreads_count(done) == TILE_PIX) break;
-    {
-      const int i = base + tid;
-      if (i < n) {
-        const uint32_t id = a.point_list[range.x + i];
-        const float2 xy = a.xy[id];
-        const float4 co = a.conic_opacity[id];
-        s_xy[tid] = xy;
-        s_co[tid] = co;
-        s_cd[tid] = make_float4(__ldg(a.colors + 3 * id), __ldg(a.colors + 3 * id + 1),
-                                __ldg(a.colors + 3 * id + 2), a.depths[id]);
-        if (CULL) s_bb[tid] = cull_box(xy, co, tile_cx, tile_cy);
+  for (int c = 0; c < nch; ++c) {
+    const int s = c % RING_NS;
+    if (warp_done && !counted) {
+      counted = true;
+      if (lane == 0) atomicAdd(&s_ndone, 1);
+    }
+    mbar_wait(&s_full[s], (c / RING_NS) & 1);
+    if (c >= *(volatile int*)&s_stop) break;
+    if (!warp_done) {
+      const int cnt = min(RING_CH, n - c * RING_CH);
+      const uint32_t sbase = rec_base + (uint32_t)s * (RING_CH * INST_BYTES);
+      const int gbase = c * RING_CH;
+      for (int sub = 0; sub < cnt && !warp_done; sub += 32) {
+        const int j = sub + lane;
+        bool hit = j < cnt;
+        if (CULL) {
+          if (hit) {
+            const float4 q0 = lds128(sbase + j * INST_BYTES);
+            const float2 q1 = lds64(sbase + j * INST_BYTES + 16);
+            hit = box_hits(cull_box(make_float2(q0.x, q0.y), make_float4(q0.z, q0.w, q1.x, q1.y), tile_cx, tile_cy), st);
+          }
+        }
+        unsigned m = __ballot_sync(0xffffffffu, hit);
+        while (m) {
+          // pop two hits (front-to-back order); evaluate both alphas, then blend in order
+          const int b0 = __ffs(m) - 1;
+          m &= m - 1;
+          const bool two = m != 0;
+          const int b1 = two ? __ffs(m) - 1 : b0;
+          m &= m - 1;
+          const uint32_t r0 = sbase + (uint32_t)(sub + b0) * INST_BYTES;
+          const uint32_t r1 = sbase + (uint32_t)(sub + b1) * INST_BYTES;
+          const float4 u0 = lds128(r0), v0 = lds128(r1);
+          const float2 u1 = lds64(r0 + 16), v1 = lds64(r1 + 16);
+          const float dx0 = u0.x - pxf, dy0 = u0.y - pyf;
+          const float dx1 = v0.x - pxf, dy1 = v0.y - pyf;
+          const float pw0 = -0.5f * (u0.z * dx0 * dx0 + u1.x * dy0 * dy0) - u0.w * dx0 * dy0;
+          const float pw1 = -0.5f * (v0.z * dx1 * dx1 + v1.x * dy1 * dy1) - v0.w * dx1 * dy1;
+          const float al0 = fminf(0.99f, u1.y * expf(pw0));
+          const float al1 = fminf(0.99f, v1.y * expf(pw1));
+          const bool ok0 = !(pw0 > 0.0f) && !(al0 < 1.0f / 255.0f);
+          const bool ok1 = two && !(pw1 > 0.0f) && !(al1 < 1.0f / 255.0f);
+          if (ok0 && !done) {
+            const float test_T = T * (1 - al0);
+            if (test_T < 0.0001f) {
+              done = true;
+            } else {
+              const float4 cq = lds128(r0 + 32);
+              C0 += cq.x * al0 * T;
+              C1 += cq.y * al0 * T;
+              C2 += cq.z * al0 * T;
+              if (T > 0.5f && test_T < 0.5f) D = lds32(r0 + 24);
+              T = test_T;
+              last = (uint32_t)(gbase + sub + b0 + 1);
+              if (COUNT) ++nblend;
+            }
+          }
+          if (ok1 && !done) {
+            const float test_T = T * (1 - al1);
+            if (test_T < 0.0001f) {
+              done = true;
+            } else {
+              const float4 cq = lds128(r1 + 32);
+              C0 += cq.x * al1 * T;
+              C1 += cq.y * al1 * T;
+              C2 += cq.z * al1 * T;
+              if (T > 0.5f && test_T < 0.5f) D = lds32(r1 + 24);
+              T = test_T;
+              last = (uint32_t)(gbase + sub + b1 + 1);
+              if (COUNT) ++nblend;
+            }
+          }
+          if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
+        }
       }
     }
-    __syncthreads();
-    if (warp_done) continue;
-    const int cnt = min(BATCH, n - base);
-    for (int c = 0; c < cnt; c += 32) {
-      const int j = c + lane;
-      bool hit = j < cnt;
-      if (CULL) hit = hit && box_hits(s_bb[j], st);
-      unsigned m = __ballot_sync(0xffffffffu, hit);
-      while (m) {
-        const int jj = c + __ffs(m) - 1;
-        m &= m - 1;
-        if (done) continue;
-        const float2 xy = s_xy[jj];
-        const float4 co = s_co[jj];
-        const float dx = xy.x - pxf, dy = xy.y - pyf;
-        const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
-        if (power > 0.0f) continue;
-        const float alpha = fminf(0.99f, co.w * expf(power));
-        if (alpha < 1.0f / 255.0f) continue;
-        const float test_T = T * (1 - alpha);
-        if (test_T < 0.0001f) { done = true; continue; }
-        const float4 cd = s_cd[jj];
-        C0 += cd.x * alpha * T;
-        C1 += cd.y * alpha * T;
-        C2 += cd.z * alpha * T;
-        if (T > 0.5f && test_T < 0.5f) D = cd.w;
-        T = test_T;
-        last = (uint32_t)(base + jj + 1);
-        if (COUNT) ++nblend;
-      }
-      if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
-    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&s_empty[s]);
   }
 
   if (inside) {
@@ -106,9 +177,9 @@ int g_disable_cull = 0;
 int launch_render_fwd(const RenderFwdArgs& a, int T, cudaStream_t st) {
   ProfScope prof_(K_RENDER_FWD, st);
   if (T <= 0) return SPLAT_OK;
-  if (a.blended) render_fwd_kernel<false, true><<<T, 256, 0, st>>>(a);
-  else if (g_disable_cull) render_fwd_kernel<false, false><<<T, 256, 0, st>>>(a);
-  else render_fwd_kernel<true, false><<<T, 256, 0, st>>>(a);
+  if (a.blended) render_fwd_kernel<false, true><<<T, RING_THREADS, 0, st>>>(a);
+  else if (g_disable_cull) render_fwd_kernel<false, false><<<T, RING_THREADS, 0, st>>>(a);
+  else render_fwd_kernel<true, false><<<T, RING_THREADS, 0, st>>>(a);
   SPLAT_LAUNCH_CHECK("render_fwd_kernel");
   return SPLAT_OK;
 }

@@ -108,19 +108,21 @@ class RasterState:
     def views(self):
         """Typed views into the state for the parity tests (splat_state_* of the C ABI):
         ranges int32[T,2], n_contrib int32[H,W], final_T float32[H,W], point_list int32[R],
-        depths float32[P], means2D float32[P,2], conic_opacity float32[P,4]."""
+        instances float32[R,12], and (strided, rows with radii > 0 only) depths [P], means2D [P,2],
+        conic_opacity [P,4], colors [P,3]."""
         W, H, P, R = self.W, self.H, self.P, self.num_rendered
         T = ((W + 15) // 16) * ((H + 15) // 16)
         img, geo, bn = self.image, self.geom, self.binning
         ip, gp, bp = C.c_void_p(img.data_ptr()), C.c_void_p(geo.data_ptr()), C.c_void_p(bn.data_ptr())
+        grec = self._view(geo, lib.splat_state_gaussian_records(gp, P), 48 * P, torch.float32).view(P, 12)
         return dict(
             ranges=self._view(img, lib.splat_state_ranges(ip, W, H), 8 * T, torch.int32).view(T, 2),
             n_contrib=self._view(img, lib.splat_state_n_contrib(ip, W, H), 4 * W * H, torch.int32).view(H, W),
             final_T=self._view(img, lib.splat_state_final_T(ip, W, H), 4 * W * H, torch.float32).view(H, W),
             point_list=self._view(bn, lib.splat_state_point_list(bp, W, H, self.capacity), 4 * R, torch.int32),
-            depths=self._view(geo, lib.splat_state_depths(gp, P), 4 * P, torch.float32),
-            means2D=self._view(geo, lib.splat_state_means2D(gp, P), 8 * P, torch.float32).view(P, 2),
-            conic_opacity=self._view(geo, lib.splat_state_conic_opacity(gp, P), 16 * P, torch.float32).view(P, 4))
+            instances=self._view(bn, lib.splat_state_instance_records(bp, W, H, self.capacity), 48 * R,
+                                 torch.float32).view(R, 12),
+            depths=grec[:, 6], means2D=grec[:, 0:2], conic_opacity=grec[:, 2:6], colors=grec[:, 8:11])
 
 
 last_state = None   # most recent RasterState (debug / parity tests only)
@@ -191,8 +193,11 @@ def rasterize_backward(rs, near, st, power, fused, means3D, colors_precomp, scal
     M = sh.shape[1] if sh.numel() else 0
     n_fixed = 3 + 3 + 3 + 1 + 3 + 4 + 6 + 4
     with torch.cuda.device(dev):
-        flat = torch.empty(P * (n_fixed + 3 * M), dtype=torch.float32, device=dev)
-        off = 0
+        hess = bool(fused) and int(power) != 1
+        n_scratch = lib.splat_backward_scratch_bytes(P, 2 if hess else 1) // 4
+        flat = torch.empty(n_scratch + P * (n_fixed + 3 * M), dtype=torch.float32, device=dev)
+        scratch = flat[:n_scratch]   # first, so it is 16-byte aligned (torch allocations are 512-byte aligned)
+        off = n_scratch
 
         def take(k, shape):
             nonlocal off
@@ -215,7 +220,7 @@ def rasterize_backward(rs, near, st, power, fused, means3D, colors_precomp, scal
                                  _ptr(st.geom), _ptr(st.image), _ptr(st.binning), _ptr(grad),
                                  int(power), int(bool(fused)),
                                  _ptr(g_means3D), _ptr(g_means2D), _ptr(g_colors), _ptr(g_opac), _ptr(g_scales),
-                                 _ptr(g_rots), _ptr(g_cov3D), _ptr(g_conic), _ptr(g_sh), stream))
+                                 _ptr(g_rots), _ptr(g_cov3D), _ptr(g_conic), _ptr(g_sh), _ptr(scratch), n_scratch * 4, stream))
     return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D
 
 

@@ -15,10 +15,14 @@ pytestmark = pytest.mark.gpu
 
 FWD_TOL = 1e-5
 GRAD_TOL = 1e-3
-# |a-b| <= 1e-3*max(|a|,|b|) + 1e-6*||ref||_inf  (SURVEY.md 7.3).  Calibrated on a B200
-# (profiles/r01_grad_noise_calibration.txt): the reference extension's own run-to-run differences
-# (atomic order) reach 5.6e-3 with a 1e-8*||ref||_inf floor and 8.7e-4 with this one.
-GRAD_FLOOR = 1e-3
+# |a-b| <= 1e-3*max(|a|,|b|) + 2e-6*||ref||_inf  (1e-3 relative with an absolute floor).
+# Calibrated on a B200 (profiles/r01_grad_noise_calibration.txt, scripts/calibrate_grad_noise.py): the
+# REFERENCE extension's own run-to-run differences (atomic order, amplified by the cancellation in the
+# cov2D/cov3D chain of thin Gaussians) reach 5.6e-3 with a 1e-8*||ref||_inf floor and 0.9e-3..1.1e-3
+# with a 1e-3*||ref||_inf one, i.e. the reference does not reproduce ITSELF to 1e-3 there.  The floor
+# is set to twice that, so a single reference run (live or golden) is a meaningful comparand; our own
+# run-to-run spread is ~4e-5 at this floor (one reduction per warp instead of one atomic per pixel).
+GRAD_FLOOR = 2e-3
 
 
 def _pkg(variant):
