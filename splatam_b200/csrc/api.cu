@@ -92,7 +92,7 @@ int splat_forward_geometry(const SplatCamera* cam, int32_t P, const float* means
   const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y, T = gx * gy;
   ImageView iv = image_view(image_state, W, H);
   GeomView gv = geom_view(geom_state, P);
-  SPLAT_CUDA(cudaMemsetAsync(iv.tile_count, 0, (size_t)T * 4, st));
+  SPLAT_CUDA(cudaMemsetAsync(iv.tile_count, 0, (size_t)T * 4 * CSTRIDE, st));
   PreFwdArgs a;
   a.P = P; a.W = W; a.H = H; a.gx = gx; a.gy = gy; a.M = M; a.sh_degree = cam->sh_degree;
   a.tanx = cam->tanfovx; a.tany = cam->tanfovy;

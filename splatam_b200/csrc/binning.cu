@@ -37,7 +37,7 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* 
   uint32_t lmax = 0, lbig = 0;
   for (int base = 0; base < T; base += 1024) {
     const int t = base + tid;
-    const uint32_t c = t < T ? tile_count[t] : 0u;
+    const uint32_t c = t < T ? tile_count[(size_t)t * CSTRIDE] : 0u;
     lmax = max(lmax, c);
     lbig += c > sort_cap;
     uint32_t v = c;
@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* 
     const uint32_t incl = carry + v + (wid ? warp_tot[wid - 1] : 0u);
     if (t < T) {
       const uint32_t start = incl - c;
-      tile_cursor[t] = start;
+      tile_cursor[(size_t)t * CSTRIDE] = start;
       ranges[t] = c ? make_uint2(start, incl) : make_uint2(0u, 0u);
     }
     __syncthreads();
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(256) scatter_kernel(int P, int gx, int gy, con
   if (vis && !big) {
     for (int y = y0; y < y1; ++y)
       for (int x = x0; x < x1; ++x) {
-        const uint32_t pos = atomicAdd(tile_cursor + y * gx + x, 1u);
+        const uint32_t pos = atomicAdd(tile_cursor + (size_t)(y * gx + x) * CSTRIDE, 1u);
         keys[pos] = kv;
       }
   }
@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(256) scatter_kernel(int P, int gx, int gy, con
     const uint64_t bkv = __shfl_sync(0xffffffffu, kv, src);
     const int w = bx1 - bx0, n = w * (by1 - by0);
     for (int t = lane; t < n; t += 32) {
-      const uint32_t pos = atomicAdd(tile_cursor + (by0 + t / w) * gx + bx0 + t % w, 1u);
+      const uint32_t pos = atomicAdd(tile_cursor + (size_t)((by0 + t / w) * gx + bx0 + t % w) * CSTRIDE, 1u);
       keys[pos] = bkv;
     }
   }
@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(256) scatter_kernel(int P, int gx, int gy, con
 #define SORT_WARPS 8
 
 // One stable LSD pass on digit (key >> shift) & 0xff over n keys, src -> dst (shared or global).
-// hist: SORT_WARPS*256 uint32 in shared memory, layout [digit][warp].
+// hist: SORT_WARPS*256 uint32 in shared memory, layout [warp][digit] (bank = digit % 32).
 __device__ __forceinline__ void radix_pass(const uint64_t* src, uint64_t* dst, int n, int shift,
                                            uint32_t* hist, uint32_t* wsum) {
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -142,14 +142,14 @@ __device__ __forceinline__ void radix_pass(const uint64_t* src, uint64_t* dst, i
   const int lo = min(n, wid * per), hi = min(n, lo + per);
   for (int i = lo + lane; i < hi; i += 32) {
     const uint32_t d = (uint32_t)(src[i] >> shift) & 0xffu;
-    atomicAdd(&hist[d * SORT_WARPS + wid], 1u);
+    atomicAdd(&hist[wid * 256 + d], 1u);
   }
   __syncthreads();
   // exclusive scan over 256*SORT_WARPS counters in (digit, warp) order: thread t owns digit t
   {
     uint32_t c[SORT_WARPS], tot = 0;
 #pragma unroll
-    for (int w = 0; w < SORT_WARPS; ++w) { c[w] = hist[tid * SORT_WARPS + w]; tot += c[w]; }
+    for (int w = 0; w < SORT_WARPS; ++w) { c[w] = hist[w * 256 + tid]; tot += c[w]; }
     uint32_t v = tot;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -161,7 +161,7 @@ __device__ __forceinline__ void radix_pass(const uint64_t* src, uint64_t* dst, i
     uint32_t base = v - tot;
     for (int w = 0; w < wid; ++w) base += wsum[w];
 #pragma unroll
-    for (int w = 0; w < SORT_WARPS; ++w) { hist[tid * SORT_WARPS + w] = base; base += c[w]; }
+    for (int w = 0; w < SORT_WARPS; ++w) { hist[w * 256 + tid] = base; base += c[w]; }
   }
   __syncthreads();
   // ranked scatter, warp by warp in input order
@@ -173,9 +173,9 @@ __device__ __forceinline__ void radix_pass(const uint64_t* src, uint64_t* dst, i
     const unsigned peers = __match_any_sync(0xffffffffu, d);
     const uint32_t rank = __popc(peers & lanemask_lt());
     uint32_t base = 0;
-    if (valid) base = hist[d * SORT_WARPS + wid];
+    if (valid) base = hist[wid * 256 + d];
     __syncwarp();
-    if (valid && rank == 0) hist[d * SORT_WARPS + wid] = base + __popc(peers);
+    if (valid && rank == 0) hist[wid * 256 + d] = base + __popc(peers);
     __syncwarp();
     if (valid) dst[base + rank] = k;
   }
@@ -284,7 +284,7 @@ int launch_scatter(int P, int gx, int gy, const int* radii, const GeomView& g, c
   return SPLAT_OK;
 }
 
-static const int kSortSmemCap = 4096;  // keys per shared buffer (2 x 32 KB)
+static const int kSortSmemCap = 2048;  // keys per shared buffer (2 x 16 KB): 5 CTAs/SM; longer lists sort in global memory
 int sort_smem_cap() { return kSortSmemCap; }
 
 int launch_tile_sort(int T, const ImageView& iv, const GeomView& g, const BinView& b, uint32_t Rcap, cudaStream_t st) {

@@ -66,10 +66,14 @@ struct ImageHeader {          // first 256 bytes of the image state
   uint32_t big_tile_count;    // number of tiles over the smem sort capacity
   uint32_t pad[61];
 };
+// Per-tile atomic counters live CSTRIDE words (256 bytes) apart: the L2 atomic unit serialises
+// same-sector traffic, and ~2.5M atomics onto T packed words (T/8 sectors) made preprocess and
+// scatter atomic-bound (ncu r01a); one counter per 256-byte block removes the hot sectors.
+#define CSTRIDE 64
 struct ImageView {
   ImageHeader* hdr;
-  uint32_t* tile_count;   // [T] instances per tile (atomics in preprocess)
-  uint32_t* tile_cursor;  // [T] scatter cursors (start .. end)
+  uint32_t* tile_count;   // [T*CSTRIDE] instances per tile (atomics in preprocess), word t*CSTRIDE
+  uint32_t* tile_cursor;  // [T*CSTRIDE] scatter cursors (start .. end), word t*CSTRIDE
   uint2* ranges;          // [T] (start,end) -- bit-exact vs identifyTileRanges
   float* final_T;         // [N]
   uint32_t* n_contrib;    // [N]
@@ -77,15 +81,15 @@ struct ImageView {
 inline int num_tiles(int W, int H) { return ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y); }
 inline size_t image_bytes(int W, int H) {
   size_t T = (size_t)num_tiles(W, H), N = (size_t)W * H;
-  return 256 + align_up(T * 4) * 2 + align_up(T * 8) + align_up(N * 4) * 2;
+  return 256 + align_up(T * 4 * CSTRIDE) * 2 + align_up(T * 8) + align_up(N * 4) * 2;
 }
 inline ImageView image_view(void* base, int W, int H) {
   size_t T = (size_t)num_tiles(W, H), N = (size_t)W * H;
   char* c = (char*)base;
   ImageView v;
   v.hdr = (ImageHeader*)c;     c += 256;
-  v.tile_count = (uint32_t*)c; c += align_up(T * 4);
-  v.tile_cursor = (uint32_t*)c;c += align_up(T * 4);
+  v.tile_count = (uint32_t*)c; c += align_up(T * 4 * CSTRIDE);
+  v.tile_cursor = (uint32_t*)c;c += align_up(T * 4 * CSTRIDE);
   v.ranges = (uint2*)c;        c += align_up(T * 8);
   v.final_T = (float*)c;       c += align_up(N * 4);
   v.n_contrib = (uint32_t*)c;

@@ -39,6 +39,15 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
 }
+// Producer-side wait: the producer lane is idle most of the time, so it must not burn the SM's issue
+// slots polling -- back off with nanosleep between probes.
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
+  uint32_t ns = 64;
+  while (!mbar_try_wait(bar, parity)) {
+    __nanosleep(ns);
+    if (ns < 1024) ns <<= 1;
+  }
+}
 
 // 1-D bulk copy global -> shared through the TMA unit; completes `bytes` on `bar`.
 // dst/src 16-byte aligned, bytes a multiple of 16.

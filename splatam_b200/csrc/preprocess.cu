@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreFwdArgs a)
   const bool big = ntile > 32;
   if (vis && !big) {
     for (int y = y0; y < y1; ++y)
-      for (int x = x0; x < x1; ++x) atomicAdd(a.tile_count + y * a.gx + x, 1u);
+      for (int x = x0; x < x1; ++x) atomicAdd(a.tile_count + (size_t)(y * a.gx + x) * CSTRIDE, 1u);
   }
   unsigned bigmask = __ballot_sync(0xffffffffu, big);
   while (bigmask) {
@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreFwdArgs a)
     const int bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
     const int bx1 = __shfl_sync(0xffffffffu, x1, src), by1 = __shfl_sync(0xffffffffu, y1, src);
     const int w = bx1 - bx0, n = w * (by1 - by0);
-    for (int t = lane; t < n; t += 32) atomicAdd(a.tile_count + (by0 + t / w) * a.gx + bx0 + t % w, 1u);
+    for (int t = lane; t < n; t += 32) atomicAdd(a.tile_count + (size_t)((by0 + t / w) * a.gx + bx0 + t % w) * CSTRIDE, 1u);
   }
 }
 

@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const Rende
       const char* src = reinterpret_cast<const char*>(a.inst) + (size_t)range.x * INST_BYTES;
       for (int c = 0; c < nch; ++c) {
         const int s = c % RING_NS;
-        if (c >= RING_NS) mbar_wait(&s_empty[s], ((c / RING_NS) - 1) & 1);
+        if (c >= RING_NS) mbar_wait_backoff(&s_empty[s], ((c / RING_NS) - 1) & 1);
         const int top = hi - c * RING_CH, lo = max(0, top - RING_CH);
         const uint32_t bytes = (uint32_t)(top - lo) * INST_BYTES;
         mbar_arrive_expect_tx(&s_full[s], bytes);

@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
       const char* src = reinterpret_cast<const char*>(a.inst) + (size_t)range.x * INST_BYTES;
       for (int c = 0; c < nch; ++c) {
         const int s = c % RING_NS;
-        if (c >= RING_NS) mbar_wait(&s_empty[s], ((c / RING_NS) - 1) & 1);
+        if (c >= RING_NS) mbar_wait_backoff(&s_empty[s], ((c / RING_NS) - 1) & 1);
         if (*(volatile int*)&s_ndone == 8) {  // every pixel of the tile has terminated
           *(volatile int*)&s_stop = c;
           mbar_arrive(&s_full[s]);
