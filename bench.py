@@ -509,10 +509,10 @@ def main():
                                            "flop_model": "13*(tested-blended) + %d*blended" % (75 if dom == "render_bwd" else 22)},
                            "kernel_ms": dom_ms}
         pre_ms = prof["preprocess_fwd"][0] / max(prof["preprocess_fwd"][1], 1)
-        gbs = 76.0 * P / (pre_ms * 1e-3) / 1e9
+        gbs = 108.0 * P / (pre_ms * 1e-3) / 1e9
         out["roofline_hbm"] = {"bound": "hbm", "kernel": "preprocess_fwd", "achieved": gbs, "peak": peaks["hbm_gbs"],
                                "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "traffic": (traffic or {}).get("preprocess_fwd"),
-                               "peak_source": peak_src, "algorithmic_bytes_per_gaussian": 76, "kernel_ms": pre_ms}
+                               "peak_source": peak_src, "algorithmic_bytes_per_gaussian": 108, "kernel_ms": pre_ms}
     if world == 1 and not args.no_cpu_baseline:
         v, cores, desc = cpu_oracle_sample(cam, sc, cams, dL, power)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}

@@ -35,9 +35,11 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* 
   if (tid == 0) { carry_s = 0; max_s = 0; big_s = 0; }
   __syncthreads();
   uint32_t lmax = 0, lbig = 0;
+  uint32_t cnext = tid < T ? tile_count[(size_t)tid * CSTRIDE] : 0u;
   for (int base = 0; base < T; base += 1024) {
     const int t = base + tid;
-    const uint32_t c = t < T ? tile_count[(size_t)t * CSTRIDE] : 0u;
+    const uint32_t c = cnext;
+    cnext = (t + 1024) < T ? tile_count[(size_t)(t + 1024) * CSTRIDE] : 0u;  // prefetch under this round's barriers
     lmax = max(lmax, c);
     lbig += c > sort_cap;
     uint32_t v = c;

@@ -149,10 +149,12 @@ __global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const Rende
 #pragma unroll
           for (int i = 0; i < NV; ++i) v[i] = 0.f;
           uint32_t ids[GROUP];
+          bool anyg[GROUP];
           bool any = false;
 #pragma unroll
           for (int gsl = 0; gsl < GROUP; ++gsl) {
             ids[gsl] = 0xffffffffu;
+            anyg[gsl] = false;
             if (m) {
               const int b = 31 - __clz(m);
               m &= ~(1u << b);
@@ -200,23 +202,29 @@ __global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const Rende
                     for (int q = p; q < 5; ++q) v[k++] = u5[p] * u5[q];
                 }
               }
-              any = any || __any_sync(0xffffffffu, valid);
+              anyg[gsl] = __any_sync(0xffffffffu, valid);
+              any = any || anyg[gsl];
             }
           }
           if (!any) continue;
-          // transpose through shared memory: column = lane, row = value
+          // transpose through shared memory: column = lane, row = value.  Gaussians of the group that no
+          // pixel of this warp blended (all-zero rows) are skipped on both sides (warp-uniform branches).
 #pragma unroll
-          for (int i = 0; i < NV; ++i) sts32(tr_st + i * (TR_STRIDE * 4), v[i]);
+          for (int gsl = 0; gsl < GROUP; ++gsl)
+            if (anyg[gsl]) {
+#pragma unroll
+              for (int i = 0; i < VALS; ++i) sts32(tr_st + (gsl * VALS + i) * (TR_STRIDE * 4), v[gsl * VALS + i]);
+            }
           __syncwarp();
+          uint32_t id = ids[0];
+          bool mine = anyg[0];
+#pragma unroll
+          for (int q = 1; q < GROUP; ++q) if (my_g == q) { id = ids[q]; mine = anyg[q]; }
+          mine = mine && lane < NV;
           float tot = 0.f;
-          if (lane < NV) tot = row_sum32(tr_ld);
+          if (mine) tot = row_sum32(tr_ld);
           __syncwarp();
-          if (lane < NV) {
-            uint32_t id = ids[0];
-#pragma unroll
-            for (int q = 1; q < GROUP; ++q) if (my_g == q) id = ids[q];
-            if (id != 0xffffffffu && tot != 0.f) red_add_f32(a.acc + (size_t)id * STRIDE + my_k, tot);
-          }
+          if (mine && tot != 0.f) red_add_f32(a.acc + (size_t)id * STRIDE + my_k, tot);
         }
       }
     }

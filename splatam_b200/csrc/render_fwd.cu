@@ -73,10 +73,12 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
   const float tile_cx = tile_x * TILE_X + 7.5f, tile_cy = tile_y * TILE_Y + 7.5f;
   const uint32_t rec_base = smem_u32(&s_rec[0][0]);
 
-  float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 15.0f;
+  // A terminated pixel is encoded as T == 0 (a live T is >= 1e-4): every later candidate then computes
+  // test_T == 0 < 1e-4 and changes nothing, so the inner loop needs no separate `done` flag; the
+  // transmittance at termination is parked in T_end.
+  float T = inside ? 1.0f : 0.f, T_end = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 15.0f;
   uint32_t last = 0, nblend = 0;
-  bool done = !inside;
-  bool warp_done = __all_sync(0xffffffffu, done);
+  bool warp_done = __all_sync(0xffffffffu, T == 0.f);
   bool counted = false;
 
   for (int c = 0; c < nch; ++c) {
@@ -121,10 +123,10 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
           const float al1 = fminf(0.99f, v1.y * expf(pw1));
           const bool ok0 = !(pw0 > 0.0f) && !(al0 < 1.0f / 255.0f);
           const bool ok1 = two && !(pw1 > 0.0f) && !(al1 < 1.0f / 255.0f);
-          if (ok0 && !done) {
+          if (ok0) {
             const float test_T = T * (1 - al0);
             if (test_T < 0.0001f) {
-              done = true;
+              if (T != 0.f) { T_end = T; T = 0.f; }
             } else {
               const float4 cq = lds128(r0 + 32);
               C0 += cq.x * al0 * T;
@@ -136,10 +138,10 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
               if (COUNT) ++nblend;
             }
           }
-          if (ok1 && !done) {
+          if (ok1) {
             const float test_T = T * (1 - al1);
             if (test_T < 0.0001f) {
-              done = true;
+              if (T != 0.f) { T_end = T; T = 0.f; }
             } else {
               const float4 cq = lds128(r1 + 32);
               C0 += cq.x * al1 * T;
@@ -151,7 +153,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
               if (COUNT) ++nblend;
             }
           }
-          if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
+          if (__all_sync(0xffffffffu, T == 0.f)) { warp_done = true; break; }
         }
       }
     }
@@ -162,6 +164,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
   if (inside) {
     const int pix = st.py * a.W + st.px;
     const size_t HW = (size_t)a.W * a.H;
+    if (T == 0.f) T = T_end;
     a.final_T[pix] = T;
     a.n_contrib[pix] = last;
     a.out_color[pix] = C0 + T * __ldg(a.bg + 0);
