@@ -447,7 +447,7 @@ def main():
     if args.impl == "ours":
         import ctypes as C
         from splatam_b200._lib import lib
-        n = 8
+        n = 16
         ms_sum = (C.c_float * n)(); cnt = (C.c_int32 * n)()
         lib.splat_profile_read(ms_sum, cnt, n)
         lib.splat_profile_enable(0)

@@ -163,7 +163,7 @@ const void* splat_state_instance_records(const void* binning_state, int32_t widt
 /* ---- measurement helpers (used by bench.py; not on the product path) -----------------------
  * splat_profile_enable(1) makes every kernel launch of this library record a cudaEvent pair on
  * its stream; splat_profile_read() synchronises, returns the summed milliseconds and launch
- * counts per kernel id (order given by splat_profile_kernel_name(0..7)) and resets. */
+ * counts per kernel id (order given by splat_profile_kernel_name(k), k = 0.. until it returns "") and resets. */
 int splat_profile_enable(int on);
 int splat_profile_read(float* ms_sum, int32_t* launches, int32_t n);
 const char* splat_profile_kernel_name(int kernel_id);

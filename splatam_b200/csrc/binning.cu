@@ -129,29 +129,77 @@ __global__ void __launch_bounds__(256) scatter_kernel(int P, int gx, int gy, con
 }
 
 // ------------------------------------------------------------------------------------- tile sort
+// One CTA per tile.  The bucket's keys ((depth bits << 32) | id) are sorted by a ONE-pass bucket sort:
+// depth bits are mapped monotonically onto SORT_NB bins spanning [min, max] of the bucket (a tile's
+// depths occupy a narrow range, so bins hold ~1 key on average), a shared-memory histogram + scan
+// gives every bin its slice, keys are dropped into their slice in arbitrary order, and each key then
+// ranks itself inside its (tiny) bin by full 64-bit comparison.  (depth bits, id) is a total order,
+// so the result equals the reference's stable radix sort bit for bit; 7 CTA barriers instead of the
+// ~18 of a 3-pass LSD radix sort.  Lists longer than the shared-memory capacity take the same code
+// path on global ping-pong buffers.
 #define SORT_THREADS 256
-#define SORT_WARPS 8
+#define SORT_NB 2048
 
-// One stable LSD pass on digit (key >> shift) & 0xff over n keys, src -> dst (shared or global).
-// hist: SORT_WARPS*256 uint32 in shared memory, layout [warp][digit] (bank = digit % 32).
-__device__ __forceinline__ void radix_pass(const uint64_t* src, uint64_t* dst, int n, int shift,
-                                           uint32_t* hist, uint32_t* wsum) {
-  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  for (int i = tid; i < 256 * SORT_WARPS; i += SORT_THREADS) hist[i] = 0;
-  __syncthreads();
-  // each warp owns a contiguous, 32-aligned slice of the input
-  const int per = ((n + SORT_WARPS - 1) / SORT_WARPS + 31) & ~31;
-  const int lo = min(n, wid * per), hi = min(n, lo + per);
-  for (int i = lo + lane; i < hi; i += 32) {
-    const uint32_t d = (uint32_t)(src[i] >> shift) & 0xffu;
-    atomicAdd(&hist[wid * 256 + d], 1u);
+struct BinMap {
+  uint32_t dmin, scale;
+  bool direct;
+  __device__ __forceinline__ uint32_t operator()(uint64_t key) const {
+    const uint32_t x = (uint32_t)(key >> 32) - dmin;
+    return direct ? x : __umulhi(x, scale);
   }
+};
+
+__global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __restrict__ ranges,
+                                                                 uint64_t* __restrict__ keys,
+                                                                 uint64_t* __restrict__ keys_alt,
+                                                                 uint32_t* __restrict__ point_list,
+                                                                 const ImageHeader* __restrict__ hdr,
+                                                                 uint32_t Rcap, int smem_cap) {
+  if (hdr->num_rendered > Rcap) return;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ uint32_t bins[SORT_NB];
+  __shared__ uint32_t red_min[8], red_max[8], wsum[8];
+  const uint2 rg = ranges[blockIdx.x];
+  const int n = (int)(rg.y - rg.x);
+  if (n <= 0) return;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  uint64_t* gsrc = keys + rg.x;
+  uint32_t* out = point_list + rg.x;
+  if (n == 1) {
+    if (tid == 0) out[0] = (uint32_t)gsrc[0];
+    return;
+  }
+  const bool in_smem = n <= smem_cap;
+  uint64_t* A = in_smem ? reinterpret_cast<uint64_t*>(smem_raw) : gsrc;
+  uint64_t* B = in_smem ? A + smem_cap : keys_alt + rg.x;
+  // load + depth range of the bucket
+  uint32_t dmin = 0xffffffffu, dmax = 0u;
+  for (int i = tid; i < n; i += SORT_THREADS) {
+    const uint64_t k = gsrc[i];
+    if (in_smem) A[i] = k;
+    const uint32_t d = (uint32_t)(k >> 32);
+    dmin = min(dmin, d); dmax = max(dmax, d);
+  }
+  for (int i = tid; i < SORT_NB; i += SORT_THREADS) bins[i] = 0;
+  dmin = __reduce_min_sync(0xffffffffu, dmin);
+  dmax = __reduce_max_sync(0xffffffffu, dmax);
+  if (lane == 0) { red_min[wid] = dmin; red_max[wid] = dmax; }
   __syncthreads();
-  // exclusive scan over 256*SORT_WARPS counters in (digit, warp) order: thread t owns digit t
-  {
-    uint32_t c[SORT_WARPS], tot = 0;
 #pragma unroll
-    for (int w = 0; w < SORT_WARPS; ++w) { c[w] = hist[w * 256 + tid]; tot += c[w]; }
+  for (int w = 0; w < 8; ++w) { dmin = min(dmin, red_min[w]); dmax = max(dmax, red_max[w]); }
+  BinMap bin;
+  const uint32_t range = dmax - dmin;
+  bin.dmin = dmin;
+  bin.direct = range < SORT_NB;
+  bin.scale = bin.direct ? 0u : (uint32_t)(((uint64_t)SORT_NB << 32) / ((uint64_t)range + 1ull));
+  // histogram
+  for (int i = tid; i < n; i += SORT_THREADS) atomicAdd(&bins[bin(A[i])], 1u);
+  __syncthreads();
+  // exclusive scan over SORT_NB bins: thread t owns bins [8t, 8t+8)
+  {
+    uint32_t c[8], tot = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) { c[q] = bins[tid * 8 + q]; tot += c[q]; }
     uint32_t v = tot;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -163,111 +211,43 @@ __device__ __forceinline__ void radix_pass(const uint64_t* src, uint64_t* dst, i
     uint32_t base = v - tot;
     for (int w = 0; w < wid; ++w) base += wsum[w];
 #pragma unroll
-    for (int w = 0; w < SORT_WARPS; ++w) { hist[w * 256 + tid] = base; base += c[w]; }
+    for (int q = 0; q < 8; ++q) { bins[tid * 8 + q] = base; base += c[q]; }
   }
   __syncthreads();
-  // ranked scatter, warp by warp in input order
-  for (int i0 = lo; i0 < hi; i0 += 32) {
-    const int i = i0 + lane;
-    const bool valid = i < hi;
-    const uint64_t k = valid ? src[i] : 0ull;
-    const uint32_t d = valid ? ((uint32_t)(k >> shift) & 0xffu) : (256u + lane);
-    const unsigned peers = __match_any_sync(0xffffffffu, d);
-    const uint32_t rank = __popc(peers & lanemask_lt());
-    uint32_t base = 0;
-    if (valid) base = hist[wid * 256 + d];
-    __syncwarp();
-    if (valid && rank == 0) hist[wid * 256 + d] = base + __popc(peers);
-    __syncwarp();
-    if (valid) dst[base + rank] = k;
+  // placement: bins[] are cursors (start -> end)
+  for (int i = tid; i < n; i += SORT_THREADS) {
+    const uint64_t k = A[i];
+    B[atomicAdd(&bins[bin(k)], 1u)] = k;
   }
   __syncthreads();
+  // in-bin ranking by the full key; bins[b] now holds the END of bin b
+  for (int p = tid; p < n; p += SORT_THREADS) {
+    const uint64_t k = B[p];
+    const uint32_t b = bin(k);
+    const int lo = b ? (int)bins[b - 1] : 0, hi = (int)bins[b];
+    int rank = 0;
+    for (int q = lo; q < hi; ++q) rank += B[q] < k;
+    out[lo + rank] = (uint32_t)k;
+  }
 }
 
-// Sorts bucket `tile` ascending by (depth bits, gaussian id) and writes the ids to point_list.
-// smem_cap = number of keys each of the two shared buffers holds.
-__global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __restrict__ ranges,
-                                                                 uint64_t* __restrict__ keys,
-                                                                 uint64_t* __restrict__ keys_alt,
-                                                                 uint32_t* __restrict__ point_list,
-                                                                 float4* __restrict__ inst,
-                                                                 const float4* __restrict__ grec,
-                                                                 const ImageHeader* __restrict__ hdr,
-                                                                 uint32_t Rcap, int smem_cap) {
-  if (hdr->num_rendered > Rcap) return;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ uint32_t hist[256 * SORT_WARPS];
-  __shared__ uint32_t wsum[SORT_WARPS];
-  __shared__ uint32_t red_or[SORT_WARPS];
-  const uint2 rg = ranges[blockIdx.x];
-  const int n = (int)(rg.y - rg.x);
-  if (n <= 0) return;
-  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  uint64_t* gsrc = keys + rg.x;
-  uint32_t* out = point_list + rg.x;
-  float4* rec = inst + (size_t)rg.x * INST_F4;
-  // Emits list position `pos`: the sorted id and the 48-byte instance record the blend kernels stream.
-  auto emit = [&](int pos, uint64_t k) {
-    const uint32_t id = (uint32_t)k;
-    out[pos] = id;
-    const float4* src = grec + (size_t)id * INST_F4;
-    const float4 g0 = __ldg(src), g2 = __ldg(src + 2);
-    float4 g1 = __ldg(src + 1);
-    g1.w = __uint_as_float(id);
-    float4* q = rec + (size_t)pos * INST_F4;
-    q[0] = g0; q[1] = g1; q[2] = g2;
-  };
-  if (n == 1) {
-    if (tid == 0) emit(0, gsrc[0]);
-    return;
-  }
-  uint64_t* bufA;
-  uint64_t* bufB;
-  const bool in_smem = n <= smem_cap;
-  if (in_smem) {
-    bufA = reinterpret_cast<uint64_t*>(smem_raw);
-    bufB = bufA + smem_cap;
-    for (int i = tid; i < n; i += SORT_THREADS) bufA[i] = gsrc[i];
-  } else {
-    bufA = gsrc;
-    bufB = keys_alt + rg.x;
-  }
-  __syncthreads();
-  // which depth bits vary inside this bucket?
-  const uint32_t k0 = (uint32_t)(bufA[0] >> 32);
-  uint32_t diff = 0;
-  for (int i = tid; i < n; i += SORT_THREADS) diff |= (uint32_t)(bufA[i] >> 32) ^ k0;
-  diff = __reduce_or_sync(0xffffffffu, diff);
-  if (lane == 0) red_or[wid] = diff;
-  __syncthreads();
-  diff = 0;
-#pragma unroll
-  for (int w = 0; w < SORT_WARPS; ++w) diff |= red_or[w];
-  uint64_t* src = bufA;
-  uint64_t* dst = bufB;
-  if (diff) {
-    const int lo_bit = __ffs(diff) - 1, hi_bit = 31 - __clz(diff);
-    for (int sh = lo_bit; sh <= hi_bit; sh += 8) {
-      radix_pass(src, dst, n, 32 + sh, hist, wsum);
-      uint64_t* t = src; src = dst; dst = t;
-    }
-  }
-  // exact tie fix-up: inside a run of equal depth bits order by ascending gaussian id
-  for (int i = tid; i < n; i += SORT_THREADS) {
-    const uint64_t k = src[i];
-    const uint32_t d = (uint32_t)(k >> 32), id = (uint32_t)k;
-    int pos = i;
-    const bool tl = i > 0 && (uint32_t)(src[i - 1] >> 32) == d;
-    const bool tr = i + 1 < n && (uint32_t)(src[i + 1] >> 32) == d;
-    if (tl || tr) {
-      int lo = i, below = 0;
-      while (lo > 0 && (uint32_t)(src[lo - 1] >> 32) == d) { --lo; below += (uint32_t)src[lo] < id; }
-      int hi = i + 1;
-      while (hi < n && (uint32_t)(src[hi] >> 32) == d) { below += (uint32_t)src[hi] < id; ++hi; }
-      pos = lo + below;
-    }
-    emit(pos, k);
-  }
+// Sorted instance records: one thread per list position copies the 48-byte record of its Gaussian and
+// patches the id in (fully parallel gather; the grec array is L2 resident).
+__global__ void __launch_bounds__(256) emit_records_kernel(const uint32_t* __restrict__ point_list,
+                                                           const float4* __restrict__ grec,
+                                                           float4* __restrict__ inst,
+                                                           const ImageHeader* __restrict__ hdr, uint32_t Rcap) {
+  const uint32_t R = hdr->num_rendered;
+  if (R > Rcap) return;
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= R) return;
+  const uint32_t id = point_list[i];
+  const float4* src = grec + (size_t)id * INST_F4;
+  const float4 g0 = __ldg(src), g2 = __ldg(src + 2);
+  float4 g1 = __ldg(src + 1);
+  g1.w = __uint_as_float(id);
+  float4* q = inst + (size_t)i * INST_F4;
+  q[0] = g0; q[1] = g1; q[2] = g2;
 }
 
 int launch_tile_scan(int T, const ImageView& iv, uint32_t* num_rendered_out, uint32_t sort_cap, cudaStream_t st) {
@@ -286,20 +266,26 @@ int launch_scatter(int P, int gx, int gy, const int* radii, const GeomView& g, c
   return SPLAT_OK;
 }
 
-static const int kSortSmemCap = 2048;  // keys per shared buffer (2 x 16 KB): 5 CTAs/SM; longer lists sort in global memory
+static const int kSortSmemCap = 2048;  // keys per shared buffer (2 x 16 KB); longer lists sort in global memory
 int sort_smem_cap() { return kSortSmemCap; }
 
 int launch_tile_sort(int T, const ImageView& iv, const GeomView& g, const BinView& b, uint32_t Rcap, cudaStream_t st) {
-  ProfScope prof_(K_TILE_SORT, st);
-  static bool attr_set = false;
-  const int smem = kSortSmemCap * 8 * 2;
-  if (!attr_set) {
-    SPLAT_CUDA(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_set = true;
+  {
+    ProfScope prof_(K_TILE_SORT, st);
+    static bool attr_set = false;
+    const int smem = kSortSmemCap * 8 * 2;
+    if (!attr_set) {
+      SPLAT_CUDA(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      attr_set = true;
+    }
+    tile_sort_kernel<<<T, SORT_THREADS, smem, st>>>(iv.ranges, b.keys, b.keys_alt, b.point_list, iv.hdr, Rcap, kSortSmemCap);
+    SPLAT_LAUNCH_CHECK("tile_sort_kernel");
   }
-  tile_sort_kernel<<<T, SORT_THREADS, smem, st>>>(iv.ranges, b.keys, b.keys_alt, b.point_list, b.inst, g.grec,
-                                                  iv.hdr, Rcap, kSortSmemCap);
-  SPLAT_LAUNCH_CHECK("tile_sort_kernel");
+  if (Rcap > 0) {
+    ProfScope prof_(K_EMIT, st);
+    emit_records_kernel<<<(Rcap + 255) / 256, 256, 0, st>>>(b.point_list, g.grec, b.inst, iv.hdr, Rcap);
+    SPLAT_LAUNCH_CHECK("emit_records_kernel");
+  }
   return SPLAT_OK;
 }
 
