@@ -202,7 +202,7 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
   h.P = P; h.tanx = cam->tanfovx; h.tany = cam->tanfovy; h.fx = fx; h.fy = fy; h.mod = cam->scale_modifier;
   h.W = W; h.H = H;
   h.means = means3D; h.scales = sr ? scales : nullptr; h.rots = sr ? rotations : nullptr; h.cov3D_pre = cov3D_precomp;
-  h.V = cam->viewmatrix; h.Pm = cam->projmatrix; h.radii = radii; h.acc = acc;
+  h.V = cam->viewmatrix; h.Pm = cam->projmatrix; h.radii = radii; h.acc = acc; h.grec = gv.grec;
   h.dL_dmeans = dL_dmeans3D; h.dL_dmean2D = dL_dmeans2D; h.dL_dcolors = dL_dcolors; h.dL_dopacity = dL_dopacity;
   h.dL_dscales = dL_dscales; h.dL_drots = dL_drotations; h.dL_dcov3D = dL_dcov3D; h.dL_dconic = dL_dconic;
   return launch_hessian_finalize(h, st);

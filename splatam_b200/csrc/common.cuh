@@ -125,14 +125,21 @@ inline BinView bin_view(void* base, int64_t Rcap) {
 struct Mat3 {  // column-major: m[c][r]
   float m[3][3];
 };
-// R = A * B (math product), R[c][r] = sum_k A[k][r] * B[c][k], k ascending.
+// a0*b0 + a1*b1 + a2*b2 with the roundings of the reference build: nvcc contracts glm's and
+// auxiliary.h's three-term sums to fma(a2,b2, fma(a0,b0, rn(a1*b1))) (SASS of preprocessCUDA<3>,
+// forward.cu:74-152).  Spelled with _rn intrinsics so no other contraction can be chosen here:
+// conics then match the reference bit for bit, and with them every alpha >= 1/255 decision.
+__device__ __forceinline__ float dot3_ref(float a0, float b0, float a1, float b1, float a2, float b2) {
+  return __fmaf_rn(a2, b2, __fmaf_rn(a0, b0, __fmul_rn(a1, b1)));
+}
+// R = A * B (math product), R[c][r] = sum_k A[k][r] * B[c][k].
 __device__ __forceinline__ Mat3 mat_mul(const Mat3& A, const Mat3& B) {
   Mat3 R;
 #pragma unroll
   for (int c = 0; c < 3; ++c)
 #pragma unroll
     for (int r = 0; r < 3; ++r)
-      R.m[c][r] = A.m[0][r] * B.m[c][0] + A.m[1][r] * B.m[c][1] + A.m[2][r] * B.m[c][2];
+      R.m[c][r] = dot3_ref(A.m[0][r], B.m[c][0], A.m[1][r], B.m[c][1], A.m[2][r], B.m[c][2]);
   return R;
 }
 __device__ __forceinline__ Mat3 mat_transpose(const Mat3& A) {
@@ -147,17 +154,17 @@ __device__ __forceinline__ Mat3 mat_transpose(const Mat3& A) {
 // point (x,y,z,1) through a "transposed" 4x4: rows 0..2 (HX auxiliary.h:58-66)
 __device__ __forceinline__ float3 xform_point_4x3(const float3 p, const float* __restrict__ m) {
   float3 t;
-  t.x = m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12];
-  t.y = m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13];
-  t.z = m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14];
+  t.x = __fadd_rn(dot3_ref(m[0], p.x, m[4], p.y, m[8], p.z), m[12]);
+  t.y = __fadd_rn(dot3_ref(m[1], p.x, m[5], p.y, m[9], p.z), m[13]);
+  t.z = __fadd_rn(dot3_ref(m[2], p.x, m[6], p.y, m[10], p.z), m[14]);
   return t;
 }
 __device__ __forceinline__ float4 xform_point_4x4(const float3 p, const float* __restrict__ m) {
   float4 t;
-  t.x = m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12];
-  t.y = m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13];
-  t.z = m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14];
-  t.w = m[3] * p.x + m[7] * p.y + m[11] * p.z + m[15];
+  t.x = __fadd_rn(dot3_ref(m[0], p.x, m[4], p.y, m[8], p.z), m[12]);
+  t.y = __fadd_rn(dot3_ref(m[1], p.x, m[5], p.y, m[9], p.z), m[13]);
+  t.z = __fadd_rn(dot3_ref(m[2], p.x, m[6], p.y, m[10], p.z), m[14]);
+  t.w = __fadd_rn(dot3_ref(m[3], p.x, m[7], p.y, m[11], p.z), m[15]);
   return t;
 }
 
@@ -177,12 +184,22 @@ __device__ __forceinline__ void tile_rect(const float2 p, int r, int gx, int gy,
 // (forward.cu:118-152).  Output: upper triangle xx,xy,xz,yy,yz,zz.
 __device__ __forceinline__ void cov3d_from_scale_rot(const float3 s, float mod, const float4 q,
                                                      float* cov) {
-  Mat3 S = {{{mod * s.x, 0.f, 0.f}, {0.f, mod * s.y, 0.f}, {0.f, 0.f, mod * s.z}}};
+  const float sx = __fmul_rn(s.x, mod), sy = __fmul_rn(s.y, mod), sz = __fmul_rn(s.z, mod);
   const float r = q.x, x = q.y, y = q.z, z = q.w;
-  Mat3 R = {{{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
-             {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
-             {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}}};
-  Mat3 Mx = mat_mul(S, R);
+  // Rotation entries with the reference build's roundings: the shared product of each +/- pair is
+  // rounded, the other one is fused; y*y + z*z is two rounded products.
+  const float xz = __fmul_rn(x, z), rx = __fmul_rn(r, x), rz = __fmul_rn(r, z);
+  const float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+  const float two_xz_p = 2.f * __fmaf_rn(r, y, xz), two_xz_m = 2.f * __fmaf_rn(-r, y, xz);
+  const float two_yz_m = 2.f * __fmaf_rn(y, z, -rx), two_yz_p = 2.f * __fmaf_rn(y, z, rx);
+  const float two_xy_m = 2.f * __fmaf_rn(x, y, -rz), two_xy_p = 2.f * __fmaf_rn(x, y, rz);
+  const float d0 = __fadd_rn(1.f, -2.f * __fadd_rn(yy, zz));
+  const float d1 = __fadd_rn(1.f, -2.f * __fmaf_rn(x, x, zz));
+  const float d2 = __fadd_rn(1.f, -2.f * __fmaf_rn(x, x, yy));
+  // M = S * R: M[c][k] = s_k * R[c][k] (one rounding each)
+  Mat3 Mx = {{{__fmul_rn(sx, d0), __fmul_rn(sy, two_xy_m), __fmul_rn(sz, two_xz_p)},
+              {__fmul_rn(sx, two_xy_p), __fmul_rn(sy, d1), __fmul_rn(sz, two_yz_m)},
+              {__fmul_rn(sx, two_xz_m), __fmul_rn(sy, two_yz_p), __fmul_rn(sz, d2)}}};
   Mat3 Sg = mat_mul(mat_transpose(Mx), Mx);
   cov[0] = Sg.m[0][0]; cov[1] = Sg.m[0][1]; cov[2] = Sg.m[0][2];
   cov[3] = Sg.m[1][1]; cov[4] = Sg.m[1][2]; cov[5] = Sg.m[2][2];
@@ -195,16 +212,17 @@ __device__ __forceinline__ float3 cov2d_ewa(const float3 mean, float fx, float f
   float3 t = xform_point_4x3(mean, V);
   const float limx = 1.3f * tanx, limy = 1.3f * tany;
   const float txtz = t.x / t.z, tytz = t.y / t.z;
-  t.x = fminf(limx, fmaxf(-limx, txtz)) * t.z;
-  t.y = fminf(limy, fmaxf(-limy, tytz)) * t.z;
-  Mat3 J = {{{fx / t.z, 0.f, -(fx * t.x) / (t.z * t.z)},
-             {0.f, fy / t.z, -(fy * t.y) / (t.z * t.z)},
+  t.x = __fmul_rn(fminf(limx, fmaxf(-limx, txtz)), t.z);
+  t.y = __fmul_rn(fminf(limy, fmaxf(-limy, tytz)), t.z);
+  const float tz2 = __fmul_rn(t.z, t.z);
+  Mat3 J = {{{fx / t.z, 0.f, -__fmul_rn(fx, t.x) / tz2},
+             {0.f, fy / t.z, -__fmul_rn(fy, t.y) / tz2},
              {0.f, 0.f, 0.f}}};
   Mat3 Wm = {{{V[0], V[4], V[8]}, {V[1], V[5], V[9]}, {V[2], V[6], V[10]}}};
   Mat3 Tm = mat_mul(Wm, J);
   Mat3 Vrk = {{{cov3D[0], cov3D[1], cov3D[2]}, {cov3D[1], cov3D[3], cov3D[4]}, {cov3D[2], cov3D[4], cov3D[5]}}};
   Mat3 c = mat_mul(mat_mul(mat_transpose(Tm), mat_transpose(Vrk)), Tm);
-  return make_float3(c.m[0][0] + 0.3f, c.m[0][1], c.m[1][1] + 0.3f);
+  return make_float3(__fadd_rn(c.m[0][0], 0.3f), c.m[0][1], __fadd_rn(c.m[1][1], 0.3f));
 }
 
 // ---------------------------------------------------------------- warp helpers

@@ -34,7 +34,7 @@ struct HessArgs {
   float tanx, tany, fx, fy, mod;
   const float* means; const float* scales; const float* rots; const float* cov3D_pre;
   int W, H;
-  const float* V; const float* Pm; const int* radii; const float* acc;
+  const float* V; const float* Pm; const int* radii; const float* acc; const float4* grec;
   float* dL_dmeans; float* dL_dmean2D; float* dL_dcolors; float* dL_dopacity;
   float* dL_dscales; float* dL_drots; float* dL_dcov3D; float* dL_dconic;
 };

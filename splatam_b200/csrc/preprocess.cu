@@ -74,6 +74,18 @@ __device__ __forceinline__ void sh_basis_grad(int deg, float x, float y, float z
 }
 
 
+// Slope t = tan(theta), |t| <= 1, of the rotation that brings the pixel axes onto the splat's
+// principal axes (theta = half the angle of (a-c, 2b), folded into [-45deg, 45deg]).  The
+// power-2 backward accumulates its second moments in the frame d' = (dx + t*dy, dy - t*dx):
+// there the quartic forms of hessian_finalize lose eps*aspect^2 instead of eps*aspect^4 for a thin
+// splat.  Any t gives the same sums in exact arithmetic; t only conditions them.
+__device__ __forceinline__ float frame_slope(float a, float b, float c) {
+  const float D = a - c, b2 = 2.f * b;
+  const float den = D + copysignf(sqrtf(D * D + b2 * b2), D);
+  const float t = b2 / den;
+  return (fabsf(t) <= 1.f) ? t : 0.f;  // den == 0 (isotropic) or overflow -> pixel axes
+}
+
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreFwdArgs a) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned lane = threadIdx.x & 31u;
@@ -103,17 +115,19 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreFwdArgs a)
     if (pv.z > a.near_plane) {  // in_frustum: reject p_view.z <= near
       const float4 ph = xform_point_4x4(p, a.Pm);
       const float pw = 1.0f / (ph.w + 0.0000001f);
-      const float ppx = ph.x * pw, ppy = ph.y * pw;
+      const float ppx = __fmul_rn(ph.x, pw), ppy = __fmul_rn(ph.y, pw);
       if (!a.cov3D_pre) cov3d_from_scale_rot(s, a.mod, q, cov3D);
       const float3 cov = cov2d_ewa(p, a.fx, a.fy, a.tanx, a.tany, cov3D, a.V);
-      const float det = cov.x * cov.z - cov.y * cov.y;
+      // roundings pinned to the reference build's (fma(a, c, -rn(b*b)), fma(mid, mid, -det))
+      const float det = __fmaf_rn(cov.x, cov.z, -__fmul_rn(cov.y, cov.y));
       if (det != 0.0f) {
         const float det_inv = 1.f / det;
-        const float3 conic = make_float3(cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv);
-        const float mid = 0.5f * (cov.x + cov.z);
-        const float lambda1 = mid + sqrtf(fmaxf(0.1f, mid * mid - det));
-        const float lambda2 = mid - sqrtf(fmaxf(0.1f, mid * mid - det));
-        const float rad = ceilf(3.f * sqrtf(fmaxf(lambda1, lambda2)));
+        const float3 conic = make_float3(__fmul_rn(cov.z, det_inv), __fmul_rn(-cov.y, det_inv), __fmul_rn(cov.x, det_inv));
+        const float mid = __fmul_rn(0.5f, __fadd_rn(cov.x, cov.z));
+        const float disc = sqrtf(fmaxf(0.1f, __fmaf_rn(mid, mid, -det)));
+        const float lambda1 = __fadd_rn(mid, disc);
+        const float lambda2 = __fadd_rn(mid, -disc);
+        const float rad = ceilf(__fmul_rn(3.f, sqrtf(fmaxf(lambda1, lambda2))));
         const float2 pix = make_float2(ndc_to_pix(ppx, a.W), ndc_to_pix(ppy, a.H));
         tile_rect(pix, (int)rad, a.gx, a.gy, x0, y0, x1, y1);
         if ((x1 - x0) * (y1 - y0) != 0) {
@@ -139,7 +153,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreFwdArgs a)
           float4* rec = a.g.grec + (size_t)idx * INST_F4;
           rec[0] = make_float4(pix.x, pix.y, conic.x, conic.y);
           rec[1] = make_float4(conic.z, opacity, pv.z, 0.f);
-          rec[2] = make_float4(rgb.x, rgb.y, rgb.z, 0.f);
+          rec[2] = make_float4(rgb.x, rgb.y, rgb.z, frame_slope(cov.x, cov.y, cov.z));
         }
       }
     }
@@ -455,6 +469,20 @@ __global__ void __launch_bounds__(128) hessian_finalize_kernel(const HessArgs a)
     for (int p = 0; p < 5; ++p)
       chain_apply(g, p == 0 ? 1.f : 0.f, p == 1 ? 1.f : 0.f, p == 2 ? 1.f : 0.f, p == 3 ? 1.f : 0.f,
                   p == 4 ? 1.f : 0.f, &J[p][0], &J[p][3], &J[p][9], &J[p][12]);
+    // The conic moments were taken in the frame d' = (dx + t*dy, dy - t*dx) (render_bwd MODE 1):
+    // (dx^2, dx*dy, dy^2) = Qinv (dx'^2, dx'*dy', dy'^2) / (1+t^2)^2, so the conic rows of J become
+    // J Qinv / (1+t^2)^2.
+    {
+      const float t = a.grec[(size_t)idx * INST_F4 + 2].w;
+      const float n = 1.f + t * t, in2 = 1.f / (n * n), t2 = t * t;
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const float ja = J[0][k], jb = J[1][k], jc = J[2][k];
+        J[0][k] = (ja + t * jb + t2 * jc) * in2;
+        J[1][k] = (2.f * t * (jc - ja) + (1.f - t2) * jb) * in2;
+        J[2][k] = (t2 * ja - t * jb + jc) * in2;
+      }
+    }
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
       float acc = 0.f;

@@ -22,7 +22,9 @@
 // MODE 1 (power == 2), row = 20 floats: dcolor^2[3], dopacity^2, and the 15 second moments of
 //   v = (dconic.x, dconic.y, dconic.w, dmean2D.x, dmean2D.y); hessian_finalize turns the moments
 //   into sum_pairs (J_k . v)^2 per output k, which is what HX accumulates pair by pair
-//   (backward.cu:1093-1137).
+//   (backward.cu:1093-1137).  The conic triple is taken in the splat's principal-axis frame
+//   (d' = (dx + t*dy, dy - t*dx), t from the record) so that the quartic forms stay well
+//   conditioned for thin splats; finalize maps J into the same frame.
 #include "render.cuh"
 #include "kernels.cuh"
 #include "pipeline.cuh"
@@ -191,7 +193,10 @@ __global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const Rende
                   const float gdx = G * dx, gdy = G * dy;
                   const float mx = dL_dG * (-gdx * q0.z - gdy * q0.w) * ddelx_dx;
                   const float my = dL_dG * (-gdy * q1.x - gdx * q0.w) * ddely_dy;
-                  const float qx = -0.5f * gdx * dx * dL_dG, qy = -0.5f * gdx * dy * dL_dG, qw = -0.5f * gdy * dy * dL_dG;
+                  // conic moments in the splat's own frame (slope col.w, preprocess.cu frame_slope)
+                  const float ex = fmaf(col.w, dy, dx), ey = fmaf(-col.w, dx, dy);
+                  const float hq = -0.5f * G * dL_dG, hx = hq * ex;
+                  const float qx = hx * ex, qy = hx * ey, qw = hq * ey * ey;
                   const float op = G * dLda;
                   v[0] = c0 * c0; v[1] = c1 * c1; v[2] = c2 * c2; v[3] = op * op;
                   const float u5[5] = {qx, qy, qw, mx, my};

@@ -15,14 +15,15 @@ pytestmark = pytest.mark.gpu
 
 FWD_TOL = 1e-5
 GRAD_TOL = 1e-3
-# |a-b| <= 1e-3*max(|a|,|b|) + 2e-6*||ref||_inf  (1e-3 relative with an absolute floor).
+# |a-b| <= 1e-3*max(|a|,|b|) + 1e-6*||ref||_inf  (1e-3 relative with an absolute floor),
+# plus -- in the live comparisons -- twice the reference's own run-to-run difference on that entry.
 # Calibrated on a B200 (profiles/r01_grad_noise_calibration.txt, scripts/calibrate_grad_noise.py): the
 # REFERENCE extension's own run-to-run differences (atomic order, amplified by the cancellation in the
 # cov2D/cov3D chain of thin Gaussians) reach 5.6e-3 with a 1e-8*||ref||_inf floor and 0.9e-3..1.1e-3
-# with a 1e-3*||ref||_inf one, i.e. the reference does not reproduce ITSELF to 1e-3 there.  The floor
-# is set to twice that, so a single reference run (live or golden) is a meaningful comparand; our own
+# with a 1e-3*||ref||_inf one, i.e. the reference does not reproduce ITSELF to 1e-3 on a few entries.
+# Live tests therefore run the reference twice and add its self-difference to the allowance; our own
 # run-to-run spread is ~4e-5 at this floor (one reduction per warp instead of one atomic per pixel).
-GRAD_FLOOR = 2e-3
+GRAD_FLOOR = 1e-3
 
 
 def _pkg(variant):
@@ -67,10 +68,17 @@ def run_ref(variant, rs, sc, dL, power=1):
                 point_list=ref_ext.binning_point_list(f).clone())
 
 
-def _check_grads(ours, ref, keys=("means3D", "means2D", "colors", "opacities", "scales", "rotations")):
+def _check_grads(ours, ref, keys=("means3D", "means2D", "colors", "opacities", "scales", "rotations"), ref2=None):
+    """|ours - ref| <= GRAD_TOL * (max(|ours|,|ref|) + GRAD_FLOOR*||ref||_inf) [+ 2*|ref - ref2|].
+    `ref2` is a SECOND run of the same reference build on the same inputs: where the reference does not
+    reproduce itself (atomic order), its own run-to-run difference on that entry is added to the allowance."""
     worst = {}
     for k in keys:
-        worst[k] = rel_err(ours[k], ref[k], GRAD_FLOOR)
+        a, b = ours[k].double().flatten(), ref[k].double().flatten()
+        allow = GRAD_TOL * (torch.maximum(a.abs(), b.abs()) + GRAD_FLOOR * float(b.abs().max()) + 1e-30)
+        if ref2 is not None:
+            allow = allow + 2.0 * (b - ref2[k].double().flatten()).abs()
+        worst[k] = float(((a - b).abs() / allow).max()) * GRAD_TOL
     bad = {k: v for k, v in worst.items() if not v <= GRAD_TOL}
     assert not bad, "gradient mismatch (rel err): %s (all: %s)" % (bad, worst)
 
@@ -93,7 +101,7 @@ def test_vs_reference_extension(case, variant):
     assert rel_err(ours["views"]["final_T"], ref["final_T"], 1e-6) <= FWD_TOL
     assert rel_err(ours["color"], ref["color"], 1e-6) <= FWD_TOL
     assert rel_err(ours["depth"], ref["depth"], 1e-6) <= FWD_TOL
-    _check_grads(ours["grads"], ref["grads"])
+    _check_grads(ours["grads"], ref["grads"], ref2=run_ref(variant, rs, sc, dL)["grads"])
 
 
 @pytest.mark.parametrize("case", ["cloud_small", "surface_small", "c1_cloud"])
@@ -103,7 +111,7 @@ def test_hessian_vs_reference_extension(case):
     dL = torch.ones(3, rs.image_height, rs.image_width, device="cuda") * 1e-3
     ours = run_ours("hx", rs, sc, dL, power=2)
     ref = run_ref("hx", rs, sc, dL, power=2)
-    _check_grads(ours["grads"], ref["grads"])
+    _check_grads(ours["grads"], ref["grads"], ref2=run_ref("hx", rs, sc, dL, power=2)["grads"])
 
 
 @pytest.mark.parametrize("case", ["cloud_small", "cloud_ragged", "surface_small"])
@@ -174,8 +182,12 @@ def test_against_golden_fixtures():
         assert np.array_equal(ours["views"]["ranges"].cpu().numpy(), z["ranges"]), fn
         assert np.array_equal(ours["views"]["n_contrib"].cpu().numpy().ravel(), z["n_contrib"].ravel()), fn
         assert rel_err(ours["color"].cpu(), torch.from_numpy(z["color"]), 1e-6) <= FWD_TOL, fn
+        # a fixture is ONE stored reference run (its atomic-order noise is frozen in): 99.9% of the entries
+        # must meet the 1e-3 bar and none may be off by more than 5e-3
         for k in ("means3D", "means2D", "colors", "opacities", "scales", "rotations"):
-            assert rel_err(ours["grads"][k].cpu(), torch.from_numpy(z["g_" + k]), GRAD_FLOOR) <= GRAD_TOL, (fn, k)
+            g_ref = torch.from_numpy(z["g_" + k])
+            assert frac_bad(ours["grads"][k].cpu(), g_ref, GRAD_TOL, GRAD_FLOOR) <= 1e-3, (fn, k)
+            assert rel_err(ours["grads"][k].cpu(), g_ref, GRAD_FLOOR) <= 5 * GRAD_TOL, (fn, k)
 
 
 def test_edge_cases():
@@ -215,3 +227,97 @@ def test_edge_cases():
     R._capacity_hint.clear()
     b = run(sc)
     assert torch.equal(a, b)
+
+
+# ------------------------------------------------------------------------------------------------
+# Full-size cases (BASELINE.json configs C2/C3/C4 shapes).  The CPU oracle would need minutes here, so
+# the comparand is the live reference extension on the same box plus size-independent properties.
+def _full_case(P, cam_name, layers, aniso=0.0, seed=2, kf=0, nkf=24):
+    from splatam_b200 import synth
+    cam = getattr(synth, cam_name)
+    sc = synth.surface_scene(P, cam["w"], cam["h"], cam["fx"], cam["fy"], cam["cx"], cam["cy"], seed=seed,
+                             layers=layers, aniso_frac=aniso)
+    rs = synth.make_settings(w2c=synth.arc_pose(kf, nkf), device="cuda", **cam)
+    sc = {k: v.cuda() for k, v in sc.items()}
+    g = torch.Generator().manual_seed(77)
+    dL = (torch.randn(3, cam["h"], cam["w"], generator=g) / (3.0 * cam["h"] * cam["w"])).cuda()
+    return rs, sc, dL
+
+
+@pytest.mark.parametrize("variant,P,cam_name,layers,kf", [("dg", 1_000_000, "REPLICA", 3, 5),
+                                                         ("hx", 1_000_000, "REPLICA", 3, 17),
+                                                         ("dg", 300_000, "REPLICA", 1, 0)])
+def test_full_size_vs_reference_extension(variant, P, cam_name, layers, kf):
+    rs, sc, dL = _full_case(P, cam_name, layers, kf=kf)
+    ours = run_ours(variant, rs, sc, dL)
+    ref = run_ref(variant, rs, sc, dL)
+    H, W = rs.image_height, rs.image_width
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    assert torch.equal(ours["radii"], ref["radii"])
+    assert ours["num_rendered"] == ref["num_rendered"]
+    assert torch.equal(ours["views"]["ranges"], ref["ranges"][:T])
+    assert torch.equal(ours["views"]["point_list"], ref["point_list"])
+    assert torch.equal(ours["views"]["n_contrib"].flatten(), ref["n_contrib"])
+    assert rel_err(ours["color"], ref["color"], 1e-6) <= FWD_TOL
+    assert rel_err(ours["depth"], ref["depth"], 1e-6) <= FWD_TOL
+    # The "surface" scene is isotropic (SplaTAM's own initialisation): dL/drotation is EXACTLY zero in exact
+    # arithmetic, and both implementations return pure cancellation noise for it (the reference's is atomic-order
+    # noise), so that array is compared against its natural scale |dL/dscale| * |scale| instead of against itself.
+    _check_grads(ours["grads"], ref["grads"], keys=("means3D", "means2D", "colors", "opacities", "scales"),
+                 ref2=run_ref(variant, rs, sc, dL)["grads"])
+    nat = float((ref["grads"]["scales"].abs() * sc["scales"]).max())
+    assert float(ours["grads"]["rotations"].abs().max()) <= 1e-3 * nat
+    assert float(ref["grads"]["rotations"].abs().max()) <= 1e-3 * nat
+
+
+def test_full_size_hessian_vs_reference_extension():
+    """C4 shape: 1752x1168, 2M Gaussians (20% anisotropic), backward_power=2 with dL = 1e-3 (ros_handler.py:885)."""
+    rs, sc, _ = _full_case(2_000_000, "SCANNETPP", 3, aniso=0.2, seed=3, kf=2, nkf=8)
+    dL = torch.ones(3, rs.image_height, rs.image_width, device="cuda") * 1e-3
+    ours = run_ours("hx", rs, sc, dL, power=2)
+    ref = run_ref("hx", rs, sc, dL, power=2)
+    assert torch.equal(ours["radii"], ref["radii"])
+    assert torch.equal(ours["views"]["n_contrib"].flatten(), ref["n_contrib"])
+    assert rel_err(ours["color"], ref["color"], 1e-6) <= FWD_TOL
+    _check_grads(ours["grads"], ref["grads"], ref2=run_ref("hx", rs, sc, dL, power=2)["grads"])
+
+
+def test_full_size_properties():
+    """Size-independent properties at the C3 shape: sorted lists, R = sum of tile counts, deterministic
+    forward, backward linear in dL/dcolour, zero gradient in -> zero gradient out."""
+    rs, sc, dL = _full_case(1_000_000, "REPLICA", 3, kf=11)
+    a = run_ours("hx", rs, sc, dL)
+    v = a["views"]
+    rg = v["ranges"].long()
+    lens = rg[:, 1] - rg[:, 0]
+    assert int(lens.sum()) == a["num_rendered"] and int(lens.min()) >= 0
+    nz = lens > 0
+    starts = torch.sort(rg[nz, 0])[0]
+    ends = torch.sort(rg[nz, 1])[0]
+    assert int(starts[0]) == 0 and int(ends[-1]) == a["num_rendered"] and torch.equal(starts[1:], ends[:-1])
+    # inside every tile list: ascending (depth bits, id)
+    inst = v["instances"]
+    depth_bits = inst[:, 6].contiguous().view(torch.int32).long()
+    ids = inst[:, 7].contiguous().view(torch.int32).long()
+    assert torch.equal(ids, v["point_list"].long())
+    key = depth_bits * (1 << 32) + ids
+    tile_of = torch.repeat_interleave(torch.arange(rg.shape[0], device="cuda"), lens)
+    same_tile = tile_of[1:] == tile_of[:-1]
+    assert bool((key[1:][same_tile] > key[:-1][same_tile]).all())
+    # n_contrib never exceeds the tile's list length
+    H, W = rs.image_height, rs.image_width
+    gx = (W + 15) // 16
+    ty, tx = torch.meshgrid(torch.arange(H, device="cuda") // 16, torch.arange(W, device="cuda") // 16, indexing="ij")
+    assert bool((v["n_contrib"].long() <= lens[ty * gx + tx]).all())
+    # deterministic forward
+    b = run_ours("hx", rs, sc, dL)
+    assert torch.equal(a["color"], b["color"]) and torch.equal(a["depth"], b["depth"])
+    # linearity / zero
+    c = run_ours("hx", rs, sc, 2.0 * dL)
+    for k in a["grads"]:
+        if k == "rotations":  # isotropic scene: exactly zero in exact arithmetic, atomic-order noise here
+            continue
+        assert rel_err(c["grads"][k], 2.0 * a["grads"][k], GRAD_FLOOR) <= GRAD_TOL, k
+    z = run_ours("hx", rs, sc, torch.zeros_like(dL))
+    for k in z["grads"]:
+        assert float(z["grads"][k].abs().max()) == 0.0, k
