@@ -229,6 +229,100 @@ def test_edge_cases():
     assert torch.equal(a, b)
 
 
+def _cov3d_from(sc):
+    """A symmetric PSD cov3D_precomp [P,6] (xx,xy,xz,yy,yz,zz) built in torch from the case's scales/rotations."""
+    q = torch.nn.functional.normalize(sc["rotations"], dim=1)
+    r, x, y, z = q.unbind(1)
+    R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+                     2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+                     2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], 1).view(-1, 3, 3)
+    L = R * sc["scales"][:, None, :]
+    S = L @ L.transpose(1, 2)
+    return torch.stack([S[:, 0, 0], S[:, 0, 1], S[:, 0, 2], S[:, 1, 1], S[:, 1, 2], S[:, 2, 2]], 1).contiguous()
+
+
+@pytest.mark.parametrize("deg", [0, 1, 2, 3])
+def test_sh_and_cov3d_precomp_vs_reference_extension(deg):
+    """The paths SplaTAM itself never takes: colours from spherical harmonics of degree 0..3 with the
+    clamp mask, and a precomputed 3D covariance -- forward and backward against the upstream (DG) extension, whose
+    SH backward is the defined one (the fork's fused kernel mis-strides dL_dsh, backward.cu:1067)."""
+    import diff_gaussian_rasterization as m
+    from oracle import ref_ext
+    if not ref_ext.available("dg"):
+        pytest.skip("oracle/_ref/ref_dg_C.so not built")
+    rs, sc, dL = build_case("cloud_small", "cuda")
+    rs = rs._replace(sh_degree=deg)
+    P = sc["means3D"].shape[0]
+    g = torch.Generator().manual_seed(50 + deg)
+    sh = (torch.randn(P, 16, 3, generator=g) * 0.5).cuda()      # M = 16 coefficients stored, (deg+1)^2 active
+    sh[:, 0] += 0.3                                              # some colours clamp at 0, most do not
+    cov = _cov3d_from(sc)
+    leaves = dict(means3D=sc["means3D"].clone().requires_grad_(True), opac=sc["opacities"].clone().requires_grad_(True),
+                  sh=sh.clone().requires_grad_(True), cov=cov.clone().requires_grad_(True))
+    means2D = torch.zeros_like(sc["means3D"], requires_grad=True)
+    color, radii, depth = m.GaussianRasterizer(rs)(means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opac"],
+                                                   shs=leaves["sh"], cov3D_precomp=leaves["cov"])
+    color.backward(dL)
+    f = ref_ext.forward("dg", rs, sc["means3D"], None, sc["opacities"], None, None, sh=sh, cov3D_precomp=cov)
+    gr = ref_ext.backward(f, dL)
+    gr2 = ref_ext.backward(f, dL)
+    assert torch.equal(radii, f["radii"])
+    assert rel_err(color.detach(), f["color"], 1e-6) <= FWD_TOL
+    assert rel_err(depth.detach(), f["depth"], 1e-6) <= FWD_TOL
+    ours = dict(means3D=leaves["means3D"].grad, means2D=means2D.grad, opacities=leaves["opac"].grad,
+                sh=leaves["sh"].grad, cov3D=leaves["cov"].grad)
+    _check_grads(ours, gr, keys=("means3D", "means2D", "opacities", "sh", "cov3D"), ref2=gr2)
+    act = (deg + 1) ** 2
+    assert float(ours["sh"][:, act:].abs().max() if act < 16 else 0.0) == 0.0   # inactive coefficients get no gradient
+
+
+def test_hx_sh_forward_and_cov3d_backward_vs_reference_extension():
+    """Fork (HX) variant: SH colours forward (degree 3), and the fused backward through cov3D_precomp with
+    precomputed colours, power 1 and 2."""
+    import hessian_diff_gaussian_rasterization_w_depth as m
+    from oracle import ref_ext
+    if not ref_ext.available("hx"):
+        pytest.skip("oracle/_ref/ref_hx_C.so not built")
+    rs, sc, dL = build_case("cloud_small", "cuda")
+    P = sc["means3D"].shape[0]
+    g = torch.Generator().manual_seed(60)
+    sh = (torch.randn(P, 16, 3, generator=g) * 0.5).cuda()
+    sh[:, 0] += 0.3
+    cov = _cov3d_from(sc)
+    rs3 = rs._replace(sh_degree=3)
+    color, radii, depth = m.GaussianRasterizer(rs3)(means3D=sc["means3D"], means2D=torch.zeros_like(sc["means3D"]),
+                                                    opacities=sc["opacities"], shs=sh, scales=sc["scales"],
+                                                    rotations=sc["rotations"])
+    f = ref_ext.forward("hx", rs3, sc["means3D"], None, sc["opacities"], sc["scales"], sc["rotations"], sh=sh)
+    assert torch.equal(radii, f["radii"]) and rel_err(color, f["color"], 1e-6) <= FWD_TOL
+    for power in (1, 2):
+        leaves = dict(means3D=sc["means3D"].clone().requires_grad_(True), opac=sc["opacities"].clone().requires_grad_(True),
+                      col=sc["colors_precomp"].clone().requires_grad_(True), cov=cov.clone().requires_grad_(True))
+        means2D = torch.zeros_like(sc["means3D"], requires_grad=True)
+        color, radii, depth = m.GaussianRasterizer(rs, backward_power=power)(
+            means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opac"], colors_precomp=leaves["col"],
+            cov3D_precomp=leaves["cov"])
+        color.backward(dL)
+        f = ref_ext.forward("hx", rs, sc["means3D"], sc["colors_precomp"], sc["opacities"], None, None, cov3D_precomp=cov)
+        gr, gr2 = ref_ext.backward(f, dL, power), ref_ext.backward(f, dL, power)
+        assert torch.equal(radii, f["radii"]) and rel_err(color.detach(), f["color"], 1e-6) <= FWD_TOL
+        ours = dict(means3D=leaves["means3D"].grad, means2D=means2D.grad, opacities=leaves["opac"].grad,
+                    colors=leaves["col"].grad, cov3D=leaves["cov"].grad)
+        _check_grads(ours, gr, keys=("means3D", "means2D", "opacities", "colors", "cov3D"), ref2=gr2)
+
+
+def test_mark_visible_vs_reference_extension():
+    import hessian_diff_gaussian_rasterization_w_depth as hx
+    import diff_gaussian_rasterization as dg
+    from oracle import ref_ext
+    rs, sc, _ = build_case("c1_cloud", "cuda")
+    for variant, m in (("hx", hx), ("dg", dg)):
+        if not ref_ext.available(variant):
+            pytest.skip("reference build missing")
+        ref = ref_ext.load(variant).mark_visible(sc["means3D"], rs.viewmatrix, rs.projmatrix)
+        assert torch.equal(m.GaussianRasterizer(rs).markVisible(sc["means3D"]), ref)
+
+
 # ------------------------------------------------------------------------------------------------
 # Full-size cases (BASELINE.json configs C2/C3/C4 shapes).  The CPU oracle would need minutes here, so
 # the comparand is the live reference extension on the same box plus size-independent properties.
