@@ -134,12 +134,14 @@ class Runner:
     flat parameter buffer + one flat gradient buffer, so the multi-GPU exchange is a single
     all-reduce).  Two buckets exist so the end-to-end leg can double-buffer host<->device copies."""
 
+    DIRECT = False
+
     def __init__(self, sc, cams, dL, power, variant, device):
         from splatam_b200 import mapping, synth
         self.P = sc["means3D"].shape[0]
         self.device, self.power, self.variant = device, power, variant
         self.cams = [synth.settings_to(c, device) for c in cams]
-        self.buckets = [mapping.GradBucket(sc, device) for _ in range(2)]
+        self.buckets = [mapping.GradBucket(sc, device, direct=self.DIRECT) for _ in range(2)]
         self.host_params = torch.cat([sc[k].reshape(-1) for k, _ in mapping.LAYOUT]).pin_memory()
         self.host_dL = dL.contiguous().pin_memory()
         self.dLs = [self.host_dL.to(device) for _ in range(2)]
@@ -167,6 +169,8 @@ class Runner:
 
 
 class OursRunner(Runner):
+    DIRECT = True   # backward kernels write the gradients straight into the flat bucket (no autograd adds, no fill)
+
     def setup(self):
         if self.variant == "hx":
             import hessian_diff_gaussian_rasterization_w_depth as m
@@ -181,8 +185,6 @@ class OursRunner(Runner):
         rs = self.cams[kf % len(self.cams)]
         bk, lv = self.buckets[b], self.leaves[b]
         bk.zero_grad()
-        for k, leaf in lv.items():
-            leaf.grad = bk.gviews[k]
         self.means2D[b].grad = None
         color, radii, depth = self.make(rs)(means3D=lv["means3D"], means2D=self.means2D[b], opacities=lv["opacities"],
                                             colors_precomp=lv["colors_precomp"], scales=lv["scales"],

@@ -39,8 +39,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
 }
-// Producer-side wait: the producer lane is idle most of the time, so it must not burn the SM's issue
-// slots polling -- back off with nanosleep between probes.
+// Stage release (one lane per warp): returns true for the LAST of the CTA's `nwarps` releases of this
+// stage, which then owns the refill.  The fences order every warp's shared-memory reads of the
+// stage before the refill's TMA writes.
+__device__ __forceinline__ bool ring_release(int* cnt, int nwarps) {
+  __threadfence_block();
+  const bool last = atomicAdd(cnt, 1) == nwarps - 1;
+  if (last) {
+    *(volatile int*)cnt = 0;
+    __threadfence_block();
+  }
+  return last;
+}
+
+// Polling wait with nanosleep back-off (kept for single-lane producers).
 __device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
   uint32_t ns = 64;
   while (!mbar_try_wait(bar, parity)) {

@@ -10,10 +10,13 @@
 namespace splat {
 
 // Instance ring shared by both blend kernels: RING_NS stages of RING_CH records (48 B each), filled by
-// the TMA unit from a producer warp (warp 8) and consumed by warps 0..7 (one 8x4 sub-tile each).
+// the TMA unit and consumed by the CTA's 8 warps (one 8x4 sub-tile each).  There is no producer
+// warp: a stage is released through a shared-memory counter, and the warp whose release is the
+// eighth issues the refill of that stage itself (one elected lane, ~10 instructions per 6 KB) -- a
+// polling producer lane cost 6.6% of the backward kernel's issue slots (profiles/r01c).
 #define RING_CH 128
 #define RING_NS 4
-#define RING_THREADS 288
+#define RING_THREADS 256
 
 struct SubTile {
   int px, py;        // this lane's pixel

@@ -5,7 +5,7 @@
 // Reference: every blended (pixel,Gaussian) pair issues 9 (DG) or 25 (HX) global float atomics and
 // the CTA re-syncs every 256 Gaussians.  Here:
 //   1. the tile's instance records are streamed BACK TO FRONT through the same TMA + mbarrier ring
-//      as the forward pass (producer warp 8, consumer warps 0..7, no CTA barrier in the loop);
+//      as the forward pass (no CTA barrier in the loop; the last warp to release a stage refills it);
 //   2. each warp walks only the Gaussians whose footprint can touch its 8x4 pixels (render.cuh);
 //   3. the per-pair partials of up to GROUP Gaussians are summed over the warp's 32 pixels by a
 //      transpose through a padded per-warp shared-memory tile: lane l stores value k at
@@ -71,45 +71,42 @@ __global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const Rende
   constexpr int NV = VALS * GROUP;
   extern __shared__ __align__(128) unsigned char smem_dyn[];
   __shared__ __align__(8) uint64_t s_full[RING_NS];
-  __shared__ __align__(8) uint64_t s_empty[RING_NS];
+  __shared__ int s_rel[RING_NS];
   __shared__ int s_max[8];
 
   const int tile = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const uint2 range = a.ranges[tile];
   const int tile_x = tile % a.gx, tile_y = tile / a.gx;
-  const SubTile st = make_subtile(tile_x, tile_y);   // (warp 8 computes a dummy sub-tile; unused)
-  const bool inside = wid < 8 && st.px < a.W && st.py < a.H;
+  const SubTile st = make_subtile(tile_x, tile_y);
+  const bool inside = st.px < a.W && st.py < a.H;
   const int pix = st.py * a.W + st.px;
   const int last = inside ? (int)a.n_contrib[pix] : 0;
   const int warp_hi = __reduce_max_sync(0xffffffffu, last);
 
   if (tid == 0) {
 #pragma unroll
-    for (int s = 0; s < RING_NS; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], 8); }
+    for (int s = 0; s < RING_NS; ++s) { mbar_init(&s_full[s], 1); s_rel[s] = 0; }
     mbar_fence_init();
   }
-  if (lane == 0 && wid < 8) s_max[wid] = warp_hi;
+  if (lane == 0) s_max[wid] = warp_hi;
   __syncthreads();
   int hi = 0;  // list positions >= max(n_contrib) over the tile are never touched by anyone
 #pragma unroll
   for (int w = 0; w < 8; ++w) hi = max(hi, s_max[w]);
   const int nch = (hi + RING_CH - 1) / RING_CH;
 
-  if (wid == 8) {  // ------------------------------------------------------------ producer warp
-    if (lane == 0) {
-      const char* src = reinterpret_cast<const char*>(a.inst) + (size_t)range.x * INST_BYTES;
-      for (int c = 0; c < nch; ++c) {
-        const int s = c % RING_NS;
-        if (c >= RING_NS) mbar_wait_backoff(&s_empty[s], ((c / RING_NS) - 1) & 1);
-        const int top = hi - c * RING_CH, lo = max(0, top - RING_CH);
-        const uint32_t bytes = (uint32_t)(top - lo) * INST_BYTES;
-        mbar_arrive_expect_tx(&s_full[s], bytes);
-        tma_load_1d(smem_dyn + s * (RING_CH * INST_BYTES), src + (size_t)lo * INST_BYTES, bytes, &s_full[s]);
-      }
-    }
-    return;
-  }
+  // chunk c = list positions [max(0, hi-(c+1)*RING_CH), hi - c*RING_CH), streamed into stage c % RING_NS
+  const char* src = reinterpret_cast<const char*>(a.inst) + (size_t)range.x * INST_BYTES;
+  auto fill = [&](int c) {
+    const int s = c % RING_NS;
+    const int top = hi - c * RING_CH, lo = max(0, top - RING_CH);
+    const uint32_t bytes = (uint32_t)(top - lo) * INST_BYTES;
+    mbar_arrive_expect_tx(&s_full[s], bytes);
+    tma_load_1d(smem_dyn + s * (RING_CH * INST_BYTES), src + (size_t)lo * INST_BYTES, bytes, &s_full[s]);
+  };
+  if (tid == 0)
+    for (int c = 0; c < min(nch, RING_NS); ++c) fill(c);
 
   // ------------------------------------------------------------------------------ consumer warps
   const float pxf = (float)st.px, pyf = (float)st.py;
@@ -148,8 +145,6 @@ __global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const Rende
         unsigned m = __ballot_sync(0xffffffffu, hit);
         while (m) {
           float v[NV];
-#pragma unroll
-          for (int i = 0; i < NV; ++i) v[i] = 0.f;
           uint32_t ids[GROUP];
           bool anyg[GROUP];
           bool any = false;
@@ -169,11 +164,18 @@ __global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const Rende
               const float G = expf(power);
               const float alpha = fminf(0.99f, q1.y * G);
               const bool valid = pos < last && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-              if (valid) {
-                const float rc = rcp_newton(1.f - alpha);
+              // Warp-uniform branch, then straight-line code for all 32 pixels: a pixel that does not
+              // blend this Gaussian runs the same arithmetic with alpha = G = 0, which leaves its
+              // running state bit-identical (1/(1-0) == 1 exactly, T*1 == T, and the deferred
+              // accum_rec update 0*c + 1*accum is exact) and makes all of its partials exactly 0.
+              anyg[gsl] = __any_sync(0xffffffffu, valid);
+              if (anyg[gsl]) {
+                any = true;
+                const float al = valid ? alpha : 0.f, Gv = valid ? G : 0.f;
+                const float rc = rcp_newton(1.f - al);
                 T = T * rc;
                 const float4 col = lds128(r + 32);
-                const float w = alpha * T;
+                const float w = al * T;
                 const float ola = 1.f - last_alpha;
                 ar0 = last_alpha * lc0 + ola * ar0;
                 ar1 = last_alpha * lc1 + ola * ar1;
@@ -181,23 +183,23 @@ __global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const Rende
                 lc0 = col.x; lc1 = col.y; lc2 = col.z;
                 float dLda = (col.x - ar0) * dp0 + (col.y - ar1) * dp1 + (col.z - ar2) * dp2;
                 dLda = dLda * T + nTb * rc;
-                last_alpha = alpha;
+                last_alpha = al;
                 const float c0 = w * dp0, c1 = w * dp1, c2 = w * dp2;
                 if (MODE == 0) {
                   float* o = &v[gsl * VALS];
-                  const float u = G * dLda, udx = u * dx, udy = u * dy;
+                  const float u = Gv * dLda, udx = u * dx, udy = u * dy;
                   o[0] = c0; o[1] = c1; o[2] = c2;
                   o[3] = udx; o[4] = udy; o[5] = udx * dx; o[6] = udx * dy; o[7] = udy * dy; o[8] = u;
                 } else {
                   const float dL_dG = q1.y * dLda;
-                  const float gdx = G * dx, gdy = G * dy;
+                  const float gdx = Gv * dx, gdy = Gv * dy;
                   const float mx = dL_dG * (-gdx * q0.z - gdy * q0.w) * ddelx_dx;
                   const float my = dL_dG * (-gdy * q1.x - gdx * q0.w) * ddely_dy;
                   // conic moments in the splat's own frame (slope col.w, preprocess.cu frame_slope)
                   const float ex = fmaf(col.w, dy, dx), ey = fmaf(-col.w, dx, dy);
-                  const float hq = -0.5f * G * dL_dG, hx = hq * ex;
+                  const float hq = -0.5f * Gv * dL_dG, hx = hq * ex;
                   const float qx = hx * ex, qy = hx * ey, qw = hq * ey * ey;
-                  const float op = G * dLda;
+                  const float op = Gv * dLda;
                   v[0] = c0 * c0; v[1] = c1 * c1; v[2] = c2 * c2; v[3] = op * op;
                   const float u5[5] = {qx, qy, qw, mx, my};
                   int k = 4;
@@ -207,8 +209,6 @@ __global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const Rende
                     for (int q = p; q < 5; ++q) v[k++] = u5[p] * u5[q];
                 }
               }
-              anyg[gsl] = __any_sync(0xffffffffu, valid);
-              any = any || anyg[gsl];
             }
           }
           if (!any) continue;
@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const Rende
       }
     }
     __syncwarp();
-    if (lane == 0) mbar_arrive(&s_empty[s]);
+    if (lane == 0 && ring_release(&s_rel[s], 8) && c + RING_NS < nch) fill(c + RING_NS);
   }
 }
 

@@ -3,17 +3,18 @@
 //
 // Differences in HOW (results identical):
 //  * the tile's sorted instance records (48 B each, written by the tile sort in list order) are ONE
-//    contiguous byte range; a producer warp streams it into a 4-stage shared-memory ring with the
-//    TMA unit (cp.async.bulk + mbarrier complete_tx).  The 8 consumer warps never meet at a CTA
-//    barrier: each waits on the stage's "full" mbarrier and releases it through the "empty" one,
-//    so warps drift apart by up to 4 stages instead of idling at __syncthreads (the reference
-//    re-syncs the whole CTA every 256 Gaussians, forward.cu:311-334);
+//    contiguous byte range, streamed into a 4-stage shared-memory ring by the TMA unit
+//    (cp.async.bulk + mbarrier complete_tx).  The 8 warps never meet at a CTA barrier: each waits
+//    on the stage's "full" mbarrier and releases the stage through a counter; the warp whose
+//    release is the eighth issues the refill.  Warps drift apart by up to 4 stages instead of
+//    idling at __syncthreads (the reference re-syncs the whole CTA every 256 Gaussians,
+//    forward.cu:311-334);
 //  * per-warp 8x4 sub-tiles with an exact conservative footprint test (render.cuh): a warp only
 //    evaluates Gaussians whose alpha>=1/255 ellipse can touch its 32 pixels (ballot + ffs walk),
 //    two hits at a time so the two exponentials overlap;
 //  * colour and depth travel with the record (the reference re-reads colour from global memory per
 //    pixel, forward.cu:361);
-//  * warp-level early termination, and the producer stops streaming once all 8 warps are done.
+//  * warp-level early termination, and the ring stops being refilled once all 8 warps are done.
 // Per-pixel arithmetic keeps the reference's expression order and precise expf so the discrete
 // tests (power>0, alpha<1/255, T<1e-4, median crossing) take the same branches.
 #include "render.cuh"
@@ -27,7 +28,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
   if (a.hdr->num_rendered > a.Rcap) return;
   __shared__ __align__(128) float4 s_rec[RING_NS][RING_CH * INST_F4];
   __shared__ __align__(8) uint64_t s_full[RING_NS];
-  __shared__ __align__(8) uint64_t s_empty[RING_NS];
+  __shared__ int s_rel[RING_NS];
   __shared__ int s_ndone;
   __shared__ int s_stop;
 
@@ -39,31 +40,22 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
 
   if (tid == 0) {
 #pragma unroll
-    for (int s = 0; s < RING_NS; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], 8); }
+    for (int s = 0; s < RING_NS; ++s) { mbar_init(&s_full[s], 1); s_rel[s] = 0; }
     s_ndone = 0;
     s_stop = 0x7fffffff;
     mbar_fence_init();
   }
   __syncthreads();
 
-  if (wid == 8) {  // ------------------------------------------------------------ producer warp
-    if (lane == 0) {
-      const char* src = reinterpret_cast<const char*>(a.inst) + (size_t)range.x * INST_BYTES;
-      for (int c = 0; c < nch; ++c) {
-        const int s = c % RING_NS;
-        if (c >= RING_NS) mbar_wait_backoff(&s_empty[s], ((c / RING_NS) - 1) & 1);
-        if (*(volatile int*)&s_ndone == 8) {  // every pixel of the tile has terminated
-          *(volatile int*)&s_stop = c;
-          mbar_arrive(&s_full[s]);
-          break;
-        }
-        const uint32_t bytes = (uint32_t)min(RING_CH, n - c * RING_CH) * INST_BYTES;
-        mbar_arrive_expect_tx(&s_full[s], bytes);
-        tma_load_1d(&s_rec[s][0], src + (size_t)c * RING_CH * INST_BYTES, bytes, &s_full[s]);
-      }
-    }
-    return;
-  }
+  const char* src = reinterpret_cast<const char*>(a.inst) + (size_t)range.x * INST_BYTES;
+  auto fill = [&](int c) {
+    const int s = c % RING_NS;
+    const uint32_t bytes = (uint32_t)min(RING_CH, n - c * RING_CH) * INST_BYTES;
+    mbar_arrive_expect_tx(&s_full[s], bytes);
+    tma_load_1d(&s_rec[s][0], src + (size_t)c * RING_CH * INST_BYTES, bytes, &s_full[s]);
+  };
+  if (tid == 0)
+    for (int c = 0; c < min(nch, RING_NS); ++c) fill(c);
 
   // ------------------------------------------------------------------------------ consumer warps
   const int tile_x = tile % a.gx, tile_y = tile / a.gx;
@@ -158,7 +150,15 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
       }
     }
     __syncwarp();
-    if (lane == 0) mbar_arrive(&s_empty[s]);
+    if (lane == 0 && ring_release(&s_rel[s], 8) && c + RING_NS < nch) {
+      if (*(volatile int*)&s_ndone == 8) {  // every pixel of the tile has terminated: stop streaming
+        atomicMin(&s_stop, c + RING_NS);  // stages already in flight drain; every warp leaves at this chunk
+        __threadfence_block();
+        mbar_arrive(&s_full[s]);
+      } else {
+        fill(c + RING_NS);
+      }
+    }
   }
 
   if (inside) {

@@ -44,10 +44,16 @@ def keyframe_schedule(n_keyframes, steps, world, seed=0):
 
 class GradBucket:
     """The replicated Gaussian parameters in ONE flat buffer and their gradients in another, with
-    named [P, w] views (LAYOUT).  The rasterizer's autograd leaves write straight into the gradient
-    views, so the exchange is a single all-reduce with no pack kernel."""
+    named [P, w] views (LAYOUT), so the exchange is a single all-reduce with no pack kernel.
 
-    def __init__(self, scene, device="cpu"):
+    direct=True marks every leaf with the rasterizer's gradient-sink attribute: the backward kernels
+    then WRITE each gradient array straight into its bucket view (splatam_b200.rasterizer
+    `_collect_sinks`) -- no autograd accumulate kernels and no zero fill, because one render assigns
+    every row.  Use it when a step is exactly one render per bucket (the mapping step); leave it off
+    when several losses accumulate into the same leaves."""
+
+    def __init__(self, scene, device="cpu", direct=False):
+        self.direct = bool(direct)
         self.P = int(scene["means3D"].shape[0])
         for k, w in LAYOUT:
             if tuple(scene[k].shape) != (self.P, w):
@@ -67,10 +73,13 @@ class GradBucket:
         lv = {k: v.detach().requires_grad_(True) for k, v in self.views.items()}
         for k, leaf in lv.items():
             leaf.grad = self.gviews[k]
+            if self.direct:
+                setattr(leaf, "_splat_grad_sink", self.gviews[k])
         return lv
 
     def zero_grad(self):
-        self.grads.zero_()
+        if not self.direct:   # a direct bucket is fully overwritten by the next render
+            self.grads.zero_()
 
     def all_reduce(self, group=None, average=False):
         """Sum (or mean) of the gradient bucket over the ranks; no-op without a process group."""

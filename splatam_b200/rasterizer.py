@@ -186,8 +186,29 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
     return out_color, radii, out_depth, st
 
 
+SINK_ATTR = "_splat_grad_sink"
+_SINK_SHAPES = {"means3D": 3, "colors_precomp": 3, "opacities": 1, "scales": 3, "rotations": 4}
+
+
+def _collect_sinks(**named):
+    """Gradient sinks (opt-in, mapping.GradBucket): an input tensor carrying a `_splat_grad_sink` attribute gets
+    its gradient WRITTEN (assigned, not accumulated -- every row is written by the backward kernels) straight
+    into that buffer, and autograd receives None for it: no AccumulateGrad add, no pre-zeroing."""
+    sinks = {}
+    for k, t in named.items():
+        sk = getattr(t, SINK_ATTR, None)
+        if sk is None:
+            continue
+        w = _SINK_SHAPES[k]
+        if (sk.dtype != torch.float32 or not sk.is_contiguous() or tuple(sk.shape) != (t.shape[0], w)
+                or sk.device != t.device or sk.data_ptr() % (16 if w == 4 else 4)):
+            raise RuntimeError("gradient sink of %s must be a contiguous float32 [P,%d] tensor on the same device" % (k, w))
+        sinks[k] = sk
+    return sinks or None
+
+
 def rasterize_backward(rs, near, st, power, fused, means3D, colors_precomp, scales, rotations,
-                       cov3D_precomp, sh, radii, grad_out_color):
+                       cov3D_precomp, sh, radii, grad_out_color, sinks=None):
     dev = means3D.device
     P = st.P
     M = sh.shape[1] if sh.numel() else 0
@@ -209,6 +230,10 @@ def rasterize_backward(rs, near, st, power, fused, means3D, colors_precomp, scal
         g_means3D = take(3, (P, 3)); g_means2D = take(3, (P, 3)); g_colors = take(3, (P, 3))
         g_opac = take(1, (P, 1)); g_scales = take(3, (P, 3))
         g_cov3D = take(6, (P, 6)); g_sh = take(3 * M, (P, M, 3))
+        if sinks and P:
+            g_means3D = sinks.get("means3D", g_means3D); g_colors = sinks.get("colors_precomp", g_colors)
+            g_opac = sinks.get("opacities", g_opac); g_scales = sinks.get("scales", g_scales)
+            g_rots = sinks.get("rotations", g_rots)
         if P == 0:
             return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D
         keep = []
@@ -227,7 +252,7 @@ def rasterize_backward(rs, near, st, power, fused, means3D, colors_precomp, scal
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                raster_settings, backward_power, near, fused):
+                raster_settings, backward_power, near, fused, sinks=None):
         # the reference passes tensors through .contiguous() (HX/rasterize_points.cu:94-112)
         means3D = _f32(means3D, "means3D")
         opacities = _f32(opacities, "opacities")
@@ -250,6 +275,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.state = st
         ctx.near = near
         ctx.fused = fused
+        ctx.sinks = sinks
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh)
         return color, radii, depth
 
@@ -260,21 +286,24 @@ class _RasterizeGaussians(torch.autograd.Function):
             grad_out_color = torch.zeros(3, ctx.state.H, ctx.state.W, device=means3D.device)
         (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D) = rasterize_backward(
             ctx.raster_settings, ctx.near, ctx.state, ctx.backward_power, ctx.fused, means3D, colors_precomp,
-            scales, rotations, cov3Ds_precomp, sh, radii, grad_out_color)
-        return (g_means3D, g_means2D,
+            scales, rotations, cov3Ds_precomp, sh, radii, grad_out_color, ctx.sinks)
+        sunk = ctx.sinks or {}
+        return (g_means3D if "means3D" not in sunk else None, g_means2D,
                 g_sh if sh.numel() else None,
-                g_colors if colors_precomp.numel() else None,
-                g_opac,
-                g_scales if scales.numel() else None,
-                g_rots if rotations.numel() else None,
+                g_colors if colors_precomp.numel() and "colors_precomp" not in sunk else None,
+                g_opac if "opacities" not in sunk else None,
+                g_scales if scales.numel() and "scales" not in sunk else None,
+                g_rots if rotations.numel() and "rotations" not in sunk else None,
                 g_cov3D if cov3Ds_precomp.numel() else None,
-                None, None, None, None)
+                None, None, None, None, None)
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         raster_settings, backward_power=1, near=NEAR_HX, fused=True):
+    sinks = _collect_sinks(means3D=means3D, colors_precomp=colors_precomp, opacities=opacities, scales=scales,
+                           rotations=rotations)
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                                     cov3Ds_precomp, raster_settings, backward_power, near, fused)
+                                     cov3Ds_precomp, raster_settings, backward_power, near, fused, sinks)
 
 
 class GaussianRasterizer(nn.Module):

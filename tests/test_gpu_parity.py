@@ -311,6 +311,32 @@ def test_hx_sh_forward_and_cov3d_backward_vs_reference_extension():
         _check_grads(ours, gr, keys=("means3D", "means2D", "opacities", "colors", "cov3D"), ref2=gr2)
 
 
+def test_gradient_sink_matches_autograd():
+    """mapping.GradBucket(direct=True): the backward kernels write the five Gaussian gradient arrays straight into
+    the flat bucket (no autograd accumulate); same numbers as the ordinary autograd path, stale contents overwritten."""
+    import hessian_diff_gaussian_rasterization_w_depth as m
+    from splatam_b200 import mapping
+    rs, sc, dL = build_case("cloud_small", "cuda")
+    ours = run_ours("hx", rs, sc, dL)
+    bk = mapping.GradBucket(sc, "cuda", direct=True)
+    bk.grads.fill_(123.0)                       # must be fully overwritten (rows of culled Gaussians become 0)
+    lv = bk.leaves()
+    means2D = torch.zeros_like(sc["means3D"], requires_grad=True)
+    color, radii, depth = m.GaussianRasterizer(rs)(means3D=lv["means3D"], means2D=means2D, opacities=lv["opacities"],
+                                                   colors_precomp=lv["colors_precomp"], scales=lv["scales"],
+                                                   rotations=lv["rotations"])
+    color.backward(dL)
+    torch.cuda.synchronize()
+    assert torch.equal(color.detach(), ours["color"])
+    got = dict(means3D=bk.gviews["means3D"], colors=bk.gviews["colors_precomp"], opacities=bk.gviews["opacities"],
+               scales=bk.gviews["scales"], rotations=bk.gviews["rotations"], means2D=means2D.grad)
+    for k in got:
+        assert lv.get({"colors": "colors_precomp"}.get(k, k)) is None or \
+            lv[{"colors": "colors_precomp"}.get(k, k)].grad.data_ptr() == got[k].data_ptr()
+    _check_grads(got, ours["grads"])
+    assert float(bk.grads.abs().max()) < 123.0
+
+
 def test_mark_visible_vs_reference_extension():
     import hessian_diff_gaussian_rasterization_w_depth as hx
     import diff_gaussian_rasterization as dg

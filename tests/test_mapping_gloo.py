@@ -116,3 +116,22 @@ def test_single_process_all_reduce_is_a_noop():
     before = bk.grads.clone()
     bk.all_reduce()
     assert torch.equal(before, bk.grads)
+
+
+def test_direct_bucket_marks_leaves_and_skips_the_fill():
+    """direct=True: leaves carry the rasterizer's gradient-sink attribute aliasing the bucket views, and zero_grad
+    leaves the buffer alone (the next render overwrites every row)."""
+    from splatam_b200 import rasterizer  # noqa: F401  (SINK_ATTR lives with its consumer)
+    bk = mapping.GradBucket(_scene(), direct=True)
+    lv = bk.leaves()
+    for k, _ in mapping.LAYOUT:
+        sk = getattr(lv[k], rasterizer.SINK_ATTR)
+        assert sk.data_ptr() == bk.gviews[k].data_ptr() and lv[k].grad.data_ptr() == sk.data_ptr()
+    bk.grads.fill_(7.0)
+    bk.zero_grad()
+    assert float(bk.grads.min()) == 7.0
+    plain = mapping.GradBucket(_scene())
+    assert not hasattr(plain.leaves()["means3D"], rasterizer.SINK_ATTR)
+    plain.grads.fill_(7.0)
+    plain.zero_grad()
+    assert float(plain.grads.abs().max()) == 0.0
