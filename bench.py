@@ -46,8 +46,8 @@ WORKLOADS = {
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=48)
-    ap.add_argument("--warmup", type=int, default=6)
+    ap.add_argument("--steps", type=int, default=192)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-cpu"])
     ap.add_argument("--workload", default="replica_1200x680_1M", choices=list(WORKLOADS))
     ap.add_argument("--variant", default="hx", choices=["dg", "hx"],
@@ -67,14 +67,17 @@ class ClockSampler:
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.rows = []
+        self.rows = []        # (arrival time, csv line)
         self.proc = None
         self.index = index
+        self.t0 = self.t1 = None
 
     def start(self):
+        """Started BEFORE the warm-up: the fork and nvidia-smi's NVML start-up (which takes driver locks and can
+        stall kernel launches for milliseconds) stay out of the timed region; the loop then samples every 25 ms."""
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "25"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -83,7 +86,13 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append(line.strip())
+            self.rows.append((time.time(), line.strip()))
+
+    def mark_start(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
 
     def stop(self):
         if self.proc is None:
@@ -95,7 +104,9 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        t0, t1 = self.t0 or 0.0, self.t1 or float("inf")
+        rows = [r for t, r in self.rows if t0 <= t <= t1 + 0.03]   # samples taken during the timed region
+        for r in rows:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 7:
                 continue
@@ -291,6 +302,9 @@ def pair_counts(runner, keyframes):
     return tested / n, blended / n, float(R.last_state.num_rendered)
 
 
+LAST_HOST = {}
+
+
 def timed_run(runner, sched, rank, world, steps, warmup, device, dist, on_timed_start=None):
     """W warm-up + K timed steps of the device-resident loop.  Returns ms (max over ranks)."""
     def full_step(i):
@@ -311,11 +325,17 @@ def timed_run(runner, sched, rank, world, steps, warmup, device, dist, on_timed_
     l0 = runner.launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    from splatam_b200 import rasterizer as _R
+    w0, h0 = _R.host_stats["wait_s"], time.perf_counter()
     e0.record()
     for i in range(steps):
         full_step(i)
     e1.record()
+    h1, w1 = time.perf_counter(), _R.host_stats["wait_s"]
     barrier()
+    # host view of the same region: time to enqueue the K steps, and how much of it the host spent blocked on the
+    # per-forward num_rendered read-back (blocked ~ all of it => the GPU is the bottleneck, as it should be)
+    LAST_HOST.update(enqueue_ms_per_step=(h1 - h0) * 1e3 / steps, blocked_ms_per_step=(w1 - w0) * 1e3 / steps)
     launches = runner.launches() - l0
     t = torch.tensor([e0.elapsed_time(e1)], device=device)
     if world > 1:
@@ -437,23 +457,34 @@ def main():
     prof = None
     sampler = ClockSampler(local)
 
+    sampler.start()
+
     def on_timed_start():
-        if args.impl == "ours":
-            from splatam_b200._lib import lib
-            lib.splat_profile_enable(1)
-        sampler.start()
+        sampler.mark_start()
 
     ms, launches = timed_run(runner, sched, rank, world, args.steps, args.warmup, device, dist, on_timed_start)
+    sampler.mark_end()
+    LAST_HOST_MAIN = dict(LAST_HOST)
     clocks = sampler.stop()
     value = world * args.steps / (ms * 1e-3)
     if args.impl == "ours":
+        # Per-kernel durations: a SECOND pass over the same K steps with the library's cudaEvent pairs switched on
+        # (on the launching stream).  Kept out of the timed region above: 16 extra event records per step cost
+        # ~30-50 us of stream time, which would be charged to the headline number.
         import ctypes as C
         from splatam_b200._lib import lib
+        lib.splat_profile_enable(1)
+        ms_prof, _ = timed_run(runner, sched, rank, world, args.steps, 3, device, dist)
         n = 16
-        ms_sum = (C.c_float * n)(); cnt = (C.c_int32 * n)()
+        ms_sum = (C.c_float * n)(); cnt = (C.c_int32 * n)(); gaps = (C.c_float * n)()
         lib.splat_profile_read(ms_sum, cnt, n)
+        lib.splat_profile_read_gaps(gaps, n)
         lib.splat_profile_enable(0)
-        prof = {lib.splat_profile_kernel_name(k).decode(): (ms_sum[k], cnt[k]) for k in range(n) if cnt[k]}
+        names = [lib.splat_profile_kernel_name(k).decode() for k in range(n)]
+        prof = {names[k]: (ms_sum[k], cnt[k]) for k in range(n) if cnt[k]}
+        prof_gaps = {names[k]: gaps[k] for k in range(n) if cnt[k]}
+        # the profiled pass runs 3 warm-up steps first: scale the sums to the K timed steps
+        prof_steps = args.steps + 3
 
     # ---- e2e: host buffers in, image + gradients out, every step
     e2e = None
@@ -469,7 +500,10 @@ def main():
             dist.destroy_process_group()
         return
 
+    host = dict(LAST_HOST_MAIN)
     out = dict(base, value=value, ms_per_step=ms / args.steps, clocks=clocks, e2e=e2e, gpu_launches=launches)
+    if args.impl == "ours":
+        out["host"] = {k: round(v, 4) for k, v in host.items()}
     if args.impl != "ours":
         out["impl"] = "reference"
         out["reference_kind"] = "unmodified reference CUDA extension oracle/_ref/ref_%s_C.so (sm_100a build)" % args.variant
@@ -487,7 +521,9 @@ def main():
     peaks, peak_src = measured_peaks()
     if args.impl == "ours" and prof:
         import ctypes as C
-        out["kernel_ms_per_step"] = {k: round(v[0] / args.steps, 5) for k, v in prof.items()}
+        out["kernel_ms_per_step"] = {k: round(v[0] / prof_steps, 5) for k, v in prof.items()}
+        out["idle_ms_before_kernel_per_step"] = {k: round(v / prof_steps, 5) for k, v in prof_gaps.items()}
+        out["profiled_pass_ms_per_step"] = round(ms_prof / args.steps, 5)
         kfs = sorted(set(int(sched[i % sched.shape[0], rank]) for i in range(args.steps)))[:6]
         tested, blended, R = pair_counts(runner, kfs)
         scratch = torch.zeros(16, device=device)

@@ -166,6 +166,9 @@ const void* splat_state_instance_records(const void* binning_state, int32_t widt
  * counts per kernel id (order given by splat_profile_kernel_name(k), k = 0.. until it returns "") and resets. */
 int splat_profile_enable(int on);
 int splat_profile_read(float* ms_sum, int32_t* launches, int32_t n);
+/* idle milliseconds on the stream before each kernel id (previous profiled launch's end -> its start),
+ * for the pairs consumed by the last splat_profile_read(). */
+int splat_profile_read_gaps(float* gap_ms_sum, int32_t n);
 const char* splat_profile_kernel_name(int kernel_id);
 int splat_debug_count_blended(const SplatCamera* cam, int32_t P, const float* colors, const void* geom_state,
                               void* image_state, const void* binning_state, int64_t R_capacity,

@@ -50,6 +50,7 @@ _SIGNATURES = {
     "splat_state_instance_records": (_P, [_P, C.c_int32, C.c_int32, C.c_int64]),
     "splat_profile_enable": (C.c_int, [C.c_int]),
     "splat_profile_read": (C.c_int, [_P, _P, C.c_int32]),
+    "splat_profile_read_gaps": (C.c_int, [_P, C.c_int32]),
     "splat_profile_kernel_name": (C.c_char_p, [C.c_int]),
     "splat_debug_count_blended": (C.c_int, [C.POINTER(SplatCamera), C.c_int32, _P, _P, _P, _P, C.c_int64, _P, _P, _P]),
     "splat_debug_fp32_peak": (C.c_int, [_P, _P, _P]),

@@ -11,7 +11,9 @@ namespace splat {
 
 int g_launch_count = 0;
 int g_prof_on = 0;
-struct ProfPair { cudaEvent_t a, b; };
+struct ProfPair { cudaEvent_t a, b, prev; };   // prev = end event of the launch before this one (idle-gap accounting)
+static cudaEvent_t g_prof_last_end = nullptr;
+static float g_prof_gap[K_COUNT];
 static std::vector<ProfPair> g_prof[K_COUNT];
 static std::vector<cudaEvent_t> g_prof_free;
 static cudaEvent_t prof_new_event() {
@@ -19,8 +21,13 @@ static cudaEvent_t prof_new_event() {
   cudaEvent_t e; cudaEventCreate(&e); return e;
 }
 void prof_record(int id, cudaStream_t st, bool start) {
-  if (start) { ProfPair p; p.a = prof_new_event(); p.b = prof_new_event(); cudaEventRecord(p.a, st); g_prof[id].push_back(p); }
-  else if (!g_prof[id].empty()) cudaEventRecord(g_prof[id].back().b, st);
+  if (start) {
+    ProfPair p; p.a = prof_new_event(); p.b = prof_new_event(); p.prev = g_prof_last_end;
+    cudaEventRecord(p.a, st); g_prof[id].push_back(p);
+  } else if (!g_prof[id].empty()) {
+    cudaEventRecord(g_prof[id].back().b, st);
+    g_prof_last_end = g_prof[id].back().b;
+  }
 }
 static thread_local char g_err[512] = "";
 
@@ -127,7 +134,7 @@ int splat_forward_render(const SplatCamera* cam, int32_t P, const float* colors_
   if (int rc = launch_tile_sort(T, iv, gv, bv, Rcap, st)) return rc;
   RenderFwdArgs r;
   r.W = W; r.H = H; r.gx = gx;
-  r.ranges = iv.ranges; r.inst = bv.inst;
+  r.ranges = iv.ranges; r.inst = bv.inst; r.order = iv.tile_order;
   r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.out_color = out_color; r.out_depth = out_depth;
   r.hdr = iv.hdr; r.Rcap = Rcap; r.blended = nullptr;
@@ -180,7 +187,7 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
   SPLAT_CUDA(cudaMemsetAsync(acc, 0, need, st));
 
   RenderBwdArgs r;
-  r.W = W; r.H = H; r.gx = gx; r.ranges = iv.ranges; r.inst = bv.inst; r.bg = cam->bg;
+  r.W = W; r.H = H; r.gx = gx; r.order = iv.tile_order; r.ranges = iv.ranges; r.inst = bv.inst; r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.dL_dpix = dL_dout_color;
   r.acc = acc;
   if (!hess) {
@@ -239,7 +246,7 @@ int splat_debug_count_blended(const SplatCamera* cam, int32_t P, const float* co
   BinView bv = bin_view(const_cast<void*>(binning_state), R_capacity);
   RenderFwdArgs r;
   (void)colors; (void)gv;
-  r.W = W; r.H = H; r.gx = gx; r.ranges = iv.ranges; r.inst = bv.inst; r.bg = cam->bg;
+  r.W = W; r.H = H; r.gx = gx; r.order = iv.tile_order; r.ranges = iv.ranges; r.inst = bv.inst; r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.out_color = scratch_color; r.out_depth = nullptr;
   r.hdr = iv.hdr; r.Rcap = (uint32_t)R_capacity; r.blended = blended;
   return launch_render_fwd(r, gx * gy, (cudaStream_t)stream);
@@ -293,6 +300,14 @@ int splat_profile_enable(int on) { g_prof_on = on ? 1 : 0; return SPLAT_OK; }
 int splat_profile_read(float* ms_sum, int32_t* launches, int32_t n) {
   if (!ms_sum || !launches || n < K_COUNT) return fail(SPLAT_ERR_BAD_ARG, "need arrays of %d", (int)K_COUNT);
   SPLAT_CUDA(cudaDeviceSynchronize());
+  for (int k = 0; k < K_COUNT; ++k) {  // gaps first: they reference other pairs' end events
+    float gap = 0.f;
+    for (auto& p : g_prof[k]) {
+      float ms = 0.f;
+      if (p.prev && cudaEventElapsedTime(&ms, p.prev, p.a) == cudaSuccess) gap += ms;
+    }
+    g_prof_gap[k] = gap;
+  }
   for (int k = 0; k < K_COUNT; ++k) {
     float tot = 0.f;
     for (auto& p : g_prof[k]) {
@@ -303,7 +318,16 @@ int splat_profile_read(float* ms_sum, int32_t* launches, int32_t n) {
     ms_sum[k] = tot; launches[k] = (int32_t)g_prof[k].size();
     g_prof[k].clear();
   }
+  g_prof_last_end = nullptr;
   cudaGetLastError();
+  return SPLAT_OK;
+}
+// Idle time on the stream BEFORE each kernel (previous profiled launch's end -> this launch's start),
+// summed per kernel id over the pairs consumed by the last splat_profile_read.  Includes whatever
+// foreign work (torch kernels, copies) ran in between.
+int splat_profile_read_gaps(float* gap_ms_sum, int32_t n) {
+  if (!gap_ms_sum || n < K_COUNT) return fail(SPLAT_ERR_BAD_ARG, "need an array of %d", (int)K_COUNT);
+  for (int k = 0; k < K_COUNT; ++k) gap_ms_sum[k] = g_prof_gap[k];
   return SPLAT_OK;
 }
 const char* splat_profile_kernel_name(int k) {

@@ -23,12 +23,15 @@
 namespace splat {
 
 // ------------------------------------------------------------------------------------------ scan
+#define SCAN_KEEP 8192
 __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* __restrict__ tile_count,
                                                          uint32_t* __restrict__ tile_cursor,
                                                          uint2* __restrict__ ranges, ImageHeader* hdr,
                                                          uint32_t* __restrict__ num_rendered_out,
-                                                         uint32_t sort_cap) {
+                                                         uint32_t sort_cap, uint32_t* __restrict__ tile_order) {
   __shared__ uint32_t warp_tot[32];
+  __shared__ uint32_t s_hist[64];
+  __shared__ uint32_t s_cnt[SCAN_KEEP];   // the counts, kept for the ordering passes below
   __shared__ uint32_t carry_s;
   __shared__ uint32_t max_s, big_s;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -39,6 +42,7 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* 
   for (int base = 0; base < T; base += 1024) {
     const int t = base + tid;
     const uint32_t c = cnext;
+    if (t < SCAN_KEEP) s_cnt[t] = c;
     cnext = (t + 1024) < T ? tile_count[(size_t)(t + 1024) * CSTRIDE] : 0u;  // prefetch under this round's barriers
     lmax = max(lmax, c);
     lbig += c > sort_cap;
@@ -80,6 +84,34 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* 
     hdr->big_tile_count = big_s;
     *num_rendered_out = carry_s;
   }
+  // Launch order for the blend kernels: longest lists first (counting sort into 64 length classes), so
+  // the last CTAs of the grid are the cheap ones and the SMs drain together instead of waiting for a
+  // heavy tile that happened to sit at the end of the row-major order.  Results do not depend on it.
+  if (tid < 64) s_hist[tid] = 0;
+  __syncthreads();
+  const uint64_t mx = (uint64_t)max_s + 1;
+  for (int t = tid; t < T; t += 1024) {
+    const uint32_t c = t < SCAN_KEEP ? s_cnt[t] : tile_count[(size_t)t * CSTRIDE];
+    atomicAdd(&s_hist[63 - (uint32_t)(((uint64_t)c * 64) / mx)], 1u);
+  }
+  __syncthreads();
+  if (wid == 0) {  // exclusive scan of the 64 class sizes
+    uint32_t a = s_hist[lane], b = s_hist[lane + 32];
+    uint32_t ia = a, ib = b;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t na = __shfl_up_sync(0xffffffffu, ia, o), nb = __shfl_up_sync(0xffffffffu, ib, o);
+      if (lane >= o) { ia += na; ib += nb; }
+    }
+    const uint32_t tot_a = __shfl_sync(0xffffffffu, ia, 31);
+    s_hist[lane] = ia - a;
+    s_hist[lane + 32] = tot_a + ib - b;
+  }
+  __syncthreads();
+  for (int t = tid; t < T; t += 1024) {
+    const uint32_t c = t < SCAN_KEEP ? s_cnt[t] : tile_count[(size_t)t * CSTRIDE];
+    tile_order[atomicAdd(&s_hist[63 - (uint32_t)(((uint64_t)c * 64) / mx)], 1u)] = (uint32_t)t;
+  }
 }
 
 // --------------------------------------------------------------------------------------- scatter
@@ -106,6 +138,9 @@ __global__ void __launch_bounds__(256) scatter_kernel(int P, int gx, int gy, con
   }
   const int ntile = vis ? (x1 - x0) * (y1 - y0) : 0;
   const bool big = ntile > 32;
+  // (Sharing one cursor atomic between the lanes of a warp that sit on the same tile -- match_any +
+  // popc -- was measured and is SLOWER here, 63 vs 50 us at C3: the match costs more than the
+  // contention it removes.)
   if (vis && !big) {
     for (int y = y0; y < y1; ++y)
       for (int x = x0; x < x1; ++x) {
@@ -231,28 +266,28 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
   }
 }
 
-// Sorted instance records: one thread per list position copies the 48-byte record of its Gaussian and
-// patches the id in (fully parallel gather; the grec array is L2 resident).
+// Sorted instance records: one thread per 16-byte quad (three per list position) copies its third of the
+// Gaussian's 48-byte record; the middle quad carries the id.  Stores are fully coalesced (thread t
+// writes quad t) and each record is read by three adjacent lanes; the grec array is L2 resident.
 __global__ void __launch_bounds__(256) emit_records_kernel(const uint32_t* __restrict__ point_list,
                                                            const float4* __restrict__ grec,
                                                            float4* __restrict__ inst,
                                                            const ImageHeader* __restrict__ hdr, uint32_t Rcap) {
   const uint32_t R = hdr->num_rendered;
   if (R > Rcap) return;
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= R) return;
-  const uint32_t id = point_list[i];
-  const float4* src = grec + (size_t)id * INST_F4;
-  const float4 g0 = __ldg(src), g2 = __ldg(src + 2);
-  float4 g1 = __ldg(src + 1);
-  g1.w = __uint_as_float(id);
-  float4* q = inst + (size_t)i * INST_F4;
-  q[0] = g0; q[1] = g1; q[2] = g2;
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (size_t)R * INST_F4) return;
+  const uint32_t i = (uint32_t)(t / INST_F4), q = (uint32_t)(t - (size_t)i * INST_F4);
+  const uint32_t id = __ldg(point_list + i);
+  float4 v = __ldg(grec + (size_t)id * INST_F4 + q);
+  if (q == 1) v.w = __uint_as_float(id);
+  inst[t] = v;
 }
 
 int launch_tile_scan(int T, const ImageView& iv, uint32_t* num_rendered_out, uint32_t sort_cap, cudaStream_t st) {
   ProfScope prof_(K_TILE_SCAN, st);
-  tile_scan_kernel<<<1, 1024, 0, st>>>(T, iv.tile_count, iv.tile_cursor, iv.ranges, iv.hdr, num_rendered_out, sort_cap);
+  tile_scan_kernel<<<1, 1024, 0, st>>>(T, iv.tile_count, iv.tile_cursor, iv.ranges, iv.hdr, num_rendered_out, sort_cap,
+                                       iv.tile_order);
   SPLAT_LAUNCH_CHECK("tile_scan_kernel");
   return SPLAT_OK;
 }
@@ -283,7 +318,8 @@ int launch_tile_sort(int T, const ImageView& iv, const GeomView& g, const BinVie
   }
   if (Rcap > 0) {
     ProfScope prof_(K_EMIT, st);
-    emit_records_kernel<<<(Rcap + 255) / 256, 256, 0, st>>>(b.point_list, g.grec, b.inst, iv.hdr, Rcap);
+    const size_t quads = (size_t)Rcap * INST_F4;
+    emit_records_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, st>>>(b.point_list, g.grec, b.inst, iv.hdr, Rcap);
     SPLAT_LAUNCH_CHECK("emit_records_kernel");
   }
   return SPLAT_OK;

@@ -77,11 +77,12 @@ struct ImageView {
   uint2* ranges;          // [T] (start,end) -- bit-exact vs identifyTileRanges
   float* final_T;         // [N]
   uint32_t* n_contrib;    // [N]
+  uint32_t* tile_order;   // [T] tiles by descending list length (64 length classes): launch order of the blend kernels
 };
 inline int num_tiles(int W, int H) { return ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y); }
 inline size_t image_bytes(int W, int H) {
   size_t T = (size_t)num_tiles(W, H), N = (size_t)W * H;
-  return 256 + align_up(T * 4 * CSTRIDE) * 2 + align_up(T * 8) + align_up(N * 4) * 2;
+  return 256 + align_up(T * 4 * CSTRIDE) * 2 + align_up(T * 8) + align_up(N * 4) * 2 + align_up(T * 4);
 }
 inline ImageView image_view(void* base, int W, int H) {
   size_t T = (size_t)num_tiles(W, H), N = (size_t)W * H;
@@ -92,7 +93,8 @@ inline ImageView image_view(void* base, int W, int H) {
   v.tile_cursor = (uint32_t*)c;c += align_up(T * 4 * CSTRIDE);
   v.ranges = (uint2*)c;        c += align_up(T * 8);
   v.final_T = (float*)c;       c += align_up(N * 4);
-  v.n_contrib = (uint32_t*)c;
+  v.n_contrib = (uint32_t*)c;  c += align_up(N * 4);
+  v.tile_order = (uint32_t*)c;
   return v;
 }
 

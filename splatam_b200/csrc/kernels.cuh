@@ -41,6 +41,7 @@ struct HessArgs {
 
 struct RenderFwdArgs {
   int W, H, gx;
+  const uint32_t* order;  // blockIdx.x -> tile (ImageView::tile_order)
   const uint2* ranges; const float4* inst;
   const float* bg;
   float* final_T; uint32_t* n_contrib; float* out_color; float* out_depth;
@@ -50,6 +51,7 @@ struct RenderFwdArgs {
 
 struct RenderBwdArgs {
   int W, H, gx;
+  const uint32_t* order;
   const uint2* ranges; const float4* inst; const float* bg;
   const float* final_T; const uint32_t* n_contrib; const float* dL_dpix;
   float* acc;   // MODE 0: [P,12] raw sums.  MODE 1: [P,20] moment accumulator.  Pre-zeroed.

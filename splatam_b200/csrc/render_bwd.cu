@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const Rende
   __shared__ int s_rel[RING_NS];
   __shared__ int s_max[8];
 
-  const int tile = blockIdx.x;
+  const int tile = (int)a.order[blockIdx.x];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const uint2 range = a.ranges[tile];
   const int tile_x = tile % a.gx, tile_y = tile / a.gx;

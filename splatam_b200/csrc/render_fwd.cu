@@ -32,7 +32,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
   __shared__ int s_ndone;
   __shared__ int s_stop;
 
-  const int tile = blockIdx.x;
+  const int tile = (int)a.order[blockIdx.x];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const uint2 range = a.ranges[tile];
   const int n = (int)(range.y - range.x);

@@ -16,6 +16,7 @@ What is different from the reference host code, by design:
     (HX/rasterize_points.cu:151-159).
 """
 import ctypes as C
+import time
 import threading
 from typing import NamedTuple
 
@@ -70,6 +71,22 @@ def _ptr(t):
     return C.c_void_p(t.data_ptr()) if t is not None and t.numel() > 0 else C.c_void_p(0)
 
 
+class _NullCtx:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+_NULL = _NullCtx()
+
+
+def _on_device(dev):
+    """torch.cuda.device(dev) only when dev is not already current (the context manager costs ~15 us per use)."""
+    return _NULL if torch.cuda.current_device() == dev.index else torch.cuda.device(dev)
+
+
 def _camera(rs, near, keep):
     cam = SplatCamera()
     cam.image_height = int(rs.image_height)
@@ -99,7 +116,7 @@ def _camera(rs, near, keep):
 class RasterState:
     """Opaque per-call state saved for the backward pass (the reference's geomBuffer /
     binningBuffer / imgBuffer byte tensors, HX/rasterize_points.cu:73-78)."""
-    __slots__ = ("geom", "image", "binning", "capacity", "num_rendered", "P", "H", "W")
+    __slots__ = ("geom", "image", "binning", "capacity", "num_rendered", "P", "H", "W", "cam", "keep", "plan")
 
     def _view(self, buf, ptr, nbytes, dtype):
         off = ptr - buf.data_ptr()
@@ -128,8 +145,9 @@ class RasterState:
 last_state = None   # most recent RasterState (debug / parity tests only)
 
 
-def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rotations, cov3D_precomp, sh):
-    """Runs both forward phases.  Returns (color, radii, depth, RasterState)."""
+def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rotations, cov3D_precomp, sh, bwd=None):
+    """Runs both forward phases.  Returns (color, radii, depth, RasterState).  bwd = (power, fused, sinks) when a
+    backward pass will follow: its buffers are then prepared here, ahead of the blocking read-back."""
     if means3D.dim() != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     dev = means3D.device
@@ -137,6 +155,7 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
     H, W = int(rs.image_height), int(rs.image_width)
     st = RasterState()
     st.P, st.H, st.W = P, H, W
+    st.plan = None
     if P == 0:  # HX/rasterize_points.cu:81 -- outputs stay at their fill value 0
         st.geom = st.image = st.binning = torch.empty(0, dtype=torch.uint8, device=dev)
         st.capacity = st.num_rendered = 0
@@ -144,7 +163,8 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
                 torch.zeros(1, H, W, device=dev), st)
     keep = []
     cam = _camera(rs, near, keep)
-    with torch.cuda.device(dev):
+    st.cam, st.keep = cam, keep   # the backward pass reuses the struct (and keeps its tensors alive)
+    with _on_device(dev):
         stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         M = sh.shape[1] if sh.numel() else 0
         out_color = torch.empty(3, H, W, dtype=torch.float32, device=dev)
@@ -175,7 +195,13 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
         if hint is not None:
             phase2(int(hint * _CAP_GROWTH) + _CAP_SLACK)
             launched = True
+        if bwd is not None:
+            st.plan = _plan_backward(st, dev, bwd[0], bwd[1], means3D, colors_precomp, scales, rotations,
+                                     cov3D_precomp, sh, radii, bwd[2])
+        t_w = time.perf_counter()
         ev.synchronize()
+        host_stats["wait_s"] += time.perf_counter() - t_w
+        host_stats["forwards"] += 1
         R = int(pinned.item())
         _capacity_hint[key] = R
         if not launched or R > st.capacity:
@@ -185,6 +211,10 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
     last_state = st
     return out_color, radii, out_depth, st
 
+
+# Host-side accounting: seconds the host spent blocked on the num_rendered read-back.  A step whose wait is ~0
+# means the GPU was waiting for the host, not the other way round (bench.py reports the per-step mean).
+host_stats = {"wait_s": 0.0, "forwards": 0}
 
 SINK_ATTR = "_splat_grad_sink"
 _SINK_SHAPES = {"means3D": 3, "colors_precomp": 3, "opacities": 1, "scales": 3, "rotations": 4}
@@ -207,46 +237,62 @@ def _collect_sinks(**named):
     return sinks or None
 
 
+def _plan_backward(st, dev, power, fused, means3D, colors_precomp, scales, rotations, cov3D_precomp, sh, radii, sinks):
+    """Everything of the backward call that does not depend on dL/dcolour: the flat gradient/scratch allocation, the
+    returned views and the packed C arguments.  rasterize_forward runs this BEFORE it blocks on the num_rendered
+    read-back, so that after the wake-up the host only has to hand the backward launch to the (then busy) GPU."""
+    P = st.P
+    M = sh.shape[1] if sh.numel() else 0
+    hess = bool(fused) and int(power) != 1
+    n_scratch = lib.splat_backward_scratch_bytes(P, 2 if hess else 1) // 4
+    sinks = sinks if (sinks and P) else {}
+    # one flat allocation: [scratch | rotations 4 | conic 4 | means3D 3 | means2D 3 | colors 3 | opacity 1 |
+    # scales 3 | cov3D 6 | sh 3M]; float4-accessed arrays first so they stay 16-byte aligned for any P (torch
+    # allocations are 512-byte aligned).  Arrays that have a sink are not carved at all.
+    layout = (("rotations", 4, (P, 4)), ("conic", 4, None), ("means3D", 3, (P, 3)), ("means2D", 3, (P, 3)),
+              ("colors_precomp", 3, (P, 3)), ("opacities", 1, (P, 1)), ("scales", 3, (P, 3)), ("cov3D", 6, (P, 6)),
+              ("sh", 3 * M, (P, M, 3)))
+    total = n_scratch + sum(P * k for name, k, _ in layout if name not in sinks)
+    flat = torch.empty(total, dtype=torch.float32, device=dev)
+    base = flat.data_ptr()
+    ptrs, outs = {}, {}
+    off = n_scratch
+    for name, k, shape in layout:
+        if name in sinks:
+            ptrs[name] = sinks[name].data_ptr()
+            continue
+        ptrs[name] = base + 4 * off if P * k else 0
+        if shape is not None:
+            outs[name] = flat[off:off + P * k].view(shape)
+        off += P * k
+    result = (outs.get("means3D"), outs["means2D"], outs["sh"], outs.get("colors_precomp"), outs.get("opacities"),
+              outs.get("scales"), outs.get("rotations"), outs["cov3D"])
+    vp = C.c_void_p
+    head = (_ptr(means3D), _ptr(scales), _ptr(rotations), _ptr(cov3D_precomp), _ptr(sh), M, _ptr(colors_precomp),
+            _ptr(radii))
+    tail = (int(power), int(bool(fused)), vp(ptrs["means3D"]), vp(ptrs["means2D"]), vp(ptrs["colors_precomp"]),
+            vp(ptrs["opacities"]), vp(ptrs["scales"]), vp(ptrs["rotations"]), vp(ptrs["cov3D"]), vp(ptrs["conic"]),
+            vp(ptrs["sh"]), vp(base), n_scratch * 4)
+    return dict(flat=flat, result=result, head=head, tail=tail, key=(int(power), bool(fused)))
+
+
 def rasterize_backward(rs, near, st, power, fused, means3D, colors_precomp, scales, rotations,
                        cov3D_precomp, sh, radii, grad_out_color, sinks=None):
     dev = means3D.device
     P = st.P
-    M = sh.shape[1] if sh.numel() else 0
-    n_fixed = 3 + 3 + 3 + 1 + 3 + 4 + 6 + 4
-    with torch.cuda.device(dev):
-        hess = bool(fused) and int(power) != 1
-        n_scratch = lib.splat_backward_scratch_bytes(P, 2 if hess else 1) // 4
-        flat = torch.empty(n_scratch + P * (n_fixed + 3 * M), dtype=torch.float32, device=dev)
-        scratch = flat[:n_scratch]   # first, so it is 16-byte aligned (torch allocations are 512-byte aligned)
-        off = n_scratch
-
-        def take(k, shape):
-            nonlocal off
-            v = flat[off:off + P * k].view(shape)
-            off += P * k
-            return v
-        # float4-accessed arrays first so they stay 16-byte aligned for any P
-        g_rots = take(4, (P, 4)); g_conic = take(4, (P, 2, 2))
-        g_means3D = take(3, (P, 3)); g_means2D = take(3, (P, 3)); g_colors = take(3, (P, 3))
-        g_opac = take(1, (P, 1)); g_scales = take(3, (P, 3))
-        g_cov3D = take(6, (P, 6)); g_sh = take(3 * M, (P, M, 3))
-        if sinks and P:
-            g_means3D = sinks.get("means3D", g_means3D); g_colors = sinks.get("colors_precomp", g_colors)
-            g_opac = sinks.get("opacities", g_opac); g_scales = sinks.get("scales", g_scales)
-            g_rots = sinks.get("rotations", g_rots)
+    with _on_device(dev):
+        plan = st.plan
+        st.plan = None   # a plan's buffers are handed to autograd once
+        if plan is None or plan["key"] != (int(power), bool(fused)):
+            plan = _plan_backward(st, dev, power, fused, means3D, colors_precomp, scales, rotations, cov3D_precomp, sh,
+                                  radii, sinks)
         if P == 0:
-            return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D
-        keep = []
-        cam = _camera(rs, near, keep)
+            return plan["result"]
         stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         grad = _f32(grad_out_color, "grad_out_color")
-        check(lib.splat_backward(C.byref(cam), P, st.capacity, _ptr(means3D), _ptr(scales), _ptr(rotations),
-                                 _ptr(cov3D_precomp), _ptr(sh), M, _ptr(colors_precomp), _ptr(radii),
-                                 _ptr(st.geom), _ptr(st.image), _ptr(st.binning), _ptr(grad),
-                                 int(power), int(bool(fused)),
-                                 _ptr(g_means3D), _ptr(g_means2D), _ptr(g_colors), _ptr(g_opac), _ptr(g_scales),
-                                 _ptr(g_rots), _ptr(g_cov3D), _ptr(g_conic), _ptr(g_sh), _ptr(scratch), n_scratch * 4, stream))
-    return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D
+        check(lib.splat_backward(C.byref(st.cam), P, st.capacity, *plan["head"], _ptr(st.geom), _ptr(st.image),
+                                 _ptr(st.binning), _ptr(grad), *plan["tail"], stream))
+    return plan["result"]
 
 
 class _RasterizeGaussians(torch.autograd.Function):
@@ -267,8 +313,9 @@ class _RasterizeGaussians(torch.autograd.Function):
                         ("rotations", rotations), ("cov3D_precomp", cov3Ds_precomp)):
             if t.numel() and (t.dtype != torch.float32 or not t.is_cuda):
                 raise RuntimeError("%s must be a float32 CUDA tensor" % name)
+        bwd = (backward_power, fused, sinks) if any(ctx.needs_input_grad) else None
         color, radii, depth, st = rasterize_forward(raster_settings, near, means3D, colors_precomp, opacities,
-                                                    scales, rotations, cov3Ds_precomp, sh)
+                                                    scales, rotations, cov3Ds_precomp, sh, bwd)
         ctx.raster_settings = raster_settings
         ctx.num_rendered = st.num_rendered
         ctx.backward_power = backward_power
