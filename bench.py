@@ -54,6 +54,9 @@ def parse():
                     help="which reference extension / import name to run: hx = the bundled fork "
                          "hessian-diff-gaussian-rasterization-w-depth that BASELINE.json's north_star names (default); "
                          "dg = the upstream submodule scripts/splatam.py imports.  The reference arm reports both.")
+    ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
+                    help="N>1 gradient exchange: peer = the library's own two-shot all-reduce over NVLink peer memory "
+                         "(torch symmetric memory for the allocation); nccl = torch.distributed.all_reduce")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -77,7 +80,7 @@ class ClockSampler:
         stall kernel launches for milliseconds) stay out of the timed region; the loop then samples every 25 ms."""
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "25"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -146,13 +149,14 @@ class Runner:
     all-reduce).  Two buckets exist so the end-to-end leg can double-buffer host<->device copies."""
 
     DIRECT = False
+    PEER_GROUP = None   # set by main() for the N>1 arm of OURS: gradient exchange through peer memory
 
     def __init__(self, sc, cams, dL, power, variant, device):
         from splatam_b200 import mapping, synth
         self.P = sc["means3D"].shape[0]
         self.device, self.power, self.variant = device, power, variant
         self.cams = [synth.settings_to(c, device) for c in cams]
-        self.buckets = [mapping.GradBucket(sc, device, direct=self.DIRECT) for _ in range(2)]
+        self.buckets = [mapping.GradBucket(sc, device, direct=self.DIRECT, peer_group=self.PEER_GROUP) for _ in range(2)]
         self.host_params = torch.cat([sc[k].reshape(-1) for k, _ in mapping.LAYOUT]).pin_memory()
         self.host_dL = dL.contiguous().pin_memory()
         self.dLs = [self.host_dL.to(device) for _ in range(2)]
@@ -401,7 +405,21 @@ def e2e_run(runner, sched, rank, world, steps, device, dist):
     return float(t[0].item()), float(t[1].item())
 
 
+_REAL_STDOUT = None
+
+
+def emit(obj):
+    """The ONE JSON line goes to the process's original stdout; everything else that libraries print to fd 1
+    (e.g. NCCL's version banner) was redirected to stderr at start-up."""
+    _REAL_STDOUT.write(json.dumps(obj) + "\n")
+    _REAL_STDOUT.flush()
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -437,7 +455,7 @@ def main():
                    cpu_baseline={"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
                    e2e={"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                    gpu_launches=0, wall_s=time.time() - t0)
-        print(json.dumps(out))
+        emit(out)
         return
 
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback for the product path)"
@@ -450,6 +468,10 @@ def main():
     from splatam_b200 import mapping
     sched = mapping.keyframe_schedule(len(cams), max(args.steps, 8), world, seed=11)
     RunnerCls = OursRunner if args.impl == "ours" else RefCudaRunner
+    if world > 1 and args.impl == "ours" and args.collective == "peer":
+        OursRunner.PEER_GROUP = dist.group.WORLD
+        base["config"]["parallelism"] = ("keyframe-sharded x%d + 1 all-reduce of the flat gradient bucket "
+                                         "(own two-shot kernel over NVLink peer memory)" % world)
     runner = RunnerCls(sc, cams, dL, power, args.variant, device)
 
     # W warm-up steps, then the timed region; per-kernel CUDA-event pairs (recorded by the library on
@@ -457,7 +479,8 @@ def main():
     prof = None
     sampler = ClockSampler(local)
 
-    sampler.start()
+    if rank == 0:   # one sampler per job: nvidia-smi polls take driver locks, N of them perturb a lock-stepped job
+        sampler.start()
 
     def on_timed_start():
         sampler.mark_start()
@@ -554,7 +577,7 @@ def main():
     if world == 1 and not args.no_cpu_baseline:
         v, cores, desc = cpu_oracle_sample(cam, sc, cams, dL, power)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
-    print(json.dumps(out))
+    emit(out)
     if world > 1:
         dist.destroy_process_group()
 

@@ -145,6 +145,18 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R,
 int splat_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
                        const float* projmatrix, float near_plane, uint8_t* present, void* stream);
 
+/* ---- multi-GPU exchange (new; the reference is single-GPU, configs/replica/splatam.py:8) -------
+ * Sum of one flat float32 bucket over the `world` ranks of one NVSwitch node, in place, on `stream`.
+ * buffers[j] / flag_pads[j] are the device addresses, valid in THIS process, of rank j's bucket and of
+ * rank j's flag pad (>= 256 bytes, zero-initialised once) -- e.g. the buffer_ptrs of two
+ * torch.distributed._symmetric_memory rendezvous handles.  `epoch` must be the same on every rank and
+ * increase by one per call.  n_floats % 4 == 0, buffers 16-byte aligned.  Rank r reduces slice r over
+ * peer loads and stores the sums into every rank's bucket; all ranks end up with bit-identical sums.
+ * multicast_buffer != 0: the NVSwitch multicast address of the same bucket; the sums are then formed inside the
+ * switch (multimem.ld_reduce / multimem.st) and each link carries the bucket once instead of 2(N-1)/N times. */
+int splat_peer_allreduce_sum(const uint64_t* buffers, const uint64_t* flag_pads, uint64_t multicast_buffer,
+                             int32_t rank, int32_t world, uint32_t epoch, int64_t n_floats, void* stream);
+
 /* ---- introspection used by the parity tests (read-only views into the states) ---------------
  * ranges: uint2[T] exactly as identifyTileRanges leaves them (untouched tiles are (0,0));
  * point_list: uint32[R] sorted Gaussian ids; n_contrib uint32[N]; final_T float[N]. */

