@@ -169,10 +169,14 @@ class Runner:
         pass
 
     def h2d(self, b):
+        if os.environ.get("SPLAT_E2E_SKIP") == "h2d":
+            return
         self.buckets[b].params.copy_(self.host_params, non_blocking=True)
         self.dLs[b].copy_(self.host_dL, non_blocking=True)
 
     def d2h(self, b):
+        if os.environ.get("SPLAT_E2E_SKIP") == "d2h":
+            return
         self.host_color.copy_(self.colors[b], non_blocking=True)
         self.host_grads.copy_(self.buckets[b].grads, non_blocking=True)
 
@@ -359,11 +363,21 @@ def e2e_run(runner, sched, rank, world, steps, device, dist):
     comp_done = [torch.cuda.Event() for _ in range(2)]
     out_done = [torch.cuda.Event() for _ in range(2)]
 
+    trace = {} if os.environ.get("SPLAT_E2E_TRACE") else None
+
+    def mark(name, i, stream):
+        if trace is not None and i < 10:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(stream)
+            trace[(name, i)] = ev
+
     def copy_in(i):
         b = i % 2
         with torch.cuda.stream(s_in):
             s_in.wait_event(comp_done[b])      # buffer b's previous render has consumed its inputs
+            mark("h2d0", i, s_in)
             runner.h2d(b)
+            mark("h2d1", i, s_in)
             in_ready[b].record(s_in)
 
     def run(n):
@@ -376,16 +390,26 @@ def e2e_run(runner, sched, rank, world, steps, device, dist):
                 copy_in(i + 1)
             compute.wait_event(in_ready[b])
             compute.wait_event(out_done[b])    # buffer b's previous results are on the host
+            mark("r0", i, compute)
             runner.step(int(sched[i % sched.shape[0], rank]), b)
             if world > 1:
                 runner.buckets[b].all_reduce()
+            mark("r1", i, compute)
             comp_done[b].record(compute)
             with torch.cuda.stream(s_out):
                 s_out.wait_event(comp_done[b])
                 runner.colors[b].record_stream(s_out)
+                mark("d2h0", i, s_out)
                 runner.d2h(b)
+                mark("d2h1", i, s_out)
                 out_done[b].record(s_out)
         torch.cuda.synchronize()
+        if trace:
+            t0 = trace[("r0", 0)]
+            for i in range(min(n, 10)):
+                sys.stderr.write("step %d: " % i + "  ".join("%s %.2f" % (k, t0.elapsed_time(trace[(k, i)])) for k in
+                                 ("h2d0", "h2d1", "r0", "r1", "d2h0", "d2h1") if (k, i) in trace) + "\n")
+            trace.clear()
 
     run(3)
     if world > 1:
@@ -468,11 +492,30 @@ def main():
     from splatam_b200 import mapping
     sched = mapping.keyframe_schedule(len(cams), max(args.steps, 8), world, seed=11)
     RunnerCls = OursRunner if args.impl == "ours" else RefCudaRunner
+    runner = None
     if world > 1 and args.impl == "ours" and args.collective == "peer":
+        # gradient exchange through the library's own peer-memory all-reduce (csrc/allreduce.cu); if symmetric memory
+        # cannot be set up on this fabric every rank agrees to use NCCL instead and the JSON line says so
         OursRunner.PEER_GROUP = dist.group.WORLD
-        base["config"]["parallelism"] = ("keyframe-sharded x%d + 1 all-reduce of the flat gradient bucket "
-                                         "(own two-shot kernel over NVLink peer memory)" % world)
-    runner = RunnerCls(sc, cams, dL, power, args.variant, device)
+        why = ""
+        try:
+            runner = RunnerCls(sc, cams, dL, power, args.variant, device)
+        except Exception as e:  # noqa: BLE001
+            why = repr(e)[:160]
+            runner = None
+        ok = torch.tensor([0.0 if runner is None else 1.0], device=device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if float(ok.item()) == 1.0:
+            mode = "NVSwitch in-switch reduction (multimem)" if runner.buckets[0].peer.multicast else "two-shot over NVLink peer loads/stores"
+            base["config"]["parallelism"] = ("keyframe-sharded x%d + 1 all-reduce of the flat gradient bucket "
+                                             "(own kernel, %s)" % (world, mode))
+        else:
+            sys.stderr.write("peer-memory all-reduce unavailable (%s); using NCCL\n" % why)
+            OursRunner.PEER_GROUP = None
+            runner = None
+            base["config"]["parallelism"] += " (NCCL: peer-memory path unavailable)"
+    if runner is None:
+        runner = RunnerCls(sc, cams, dL, power, args.variant, device)
 
     # W warm-up steps, then the timed region; per-kernel CUDA-event pairs (recorded by the library on
     # the launching stream) are switched on for exactly the timed steps

@@ -75,7 +75,8 @@ size_t splat_binning_state_bytes(int32_t width, int32_t height, int64_t R_capaci
  * (HX/cuda_rasterizer/rasterizer_impl.cu:248-282).  Fully asynchronous.  On return (in stream
  * order) geom_state holds one 48-byte record per visible Gaussian (pixel mean, conic, opacity, depth,
  * colour -- SH-evaluated if shs is given), image_state holds the bit-exact tile ranges, radii[P] is
- * written, and *num_rendered_dev (device uint32) holds R.
+ * written, and *num_rendered_dev holds R (a uint32 in device memory OR in mapped pinned host memory: the
+ * Python host passes a pinned word so that reading R back needs no copy-engine transfer).
  * Exactly one of (scales && rotations) or cov3D_precomp must be non-NULL; exactly one of
  * colors_precomp or shs must be non-NULL (same rule as HX/.../__init__.py:174-178). */
 int splat_forward_geometry(const SplatCamera* cam, int32_t P,

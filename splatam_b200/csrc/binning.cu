@@ -82,7 +82,8 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* 
     hdr->num_rendered = carry_s;
     hdr->max_tile_count = max_s;
     hdr->big_tile_count = big_s;
-    *num_rendered_out = carry_s;
+    *num_rendered_out = carry_s;   // may be mapped pinned host memory: the host reads it after the stream event
+    __threadfence_system();
   }
   // Launch order for the blend kernels: longest lists first (counting sort into 64 length classes), so
   // the last CTAs of the grid are the cheap ones and the SMs drain together instead of waiting for a

@@ -172,13 +172,14 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
         radii = torch.empty(P, dtype=torch.int32, device=dev)
         st.geom = torch.empty(lib.splat_geom_state_bytes(P), dtype=torch.uint8, device=dev)
         st.image = torch.empty(lib.splat_image_state_bytes(W, H), dtype=torch.uint8, device=dev)
-        nr_dev = torch.empty(1, dtype=torch.int32, device=dev)
+        # R is written by the scan kernel STRAIGHT into pinned host memory (UVA: the pinned page is device-addressable).
+        # A cudaMemcpyAsync of the word would queue behind whatever bulk device->host copy is in flight on the copy
+        # engine (e.g. the previous step's 60 MB gradient read-back) and stall the host for its whole duration.
+        pinned = _pinned_scalar(dev)
         check(lib.splat_forward_geometry(C.byref(cam), P, _ptr(means3D), _ptr(scales), _ptr(rotations),
                                          _ptr(opacities), _ptr(cov3D_precomp), _ptr(sh), M,
                                          _ptr(colors_precomp), _ptr(st.geom), _ptr(st.image), _ptr(radii),
-                                         _ptr(nr_dev), stream))
-        pinned = _pinned_scalar(dev)
-        pinned.copy_(nr_dev, non_blocking=True)
+                                         C.c_void_p(pinned.data_ptr()), stream))
         ev = torch.cuda.Event()
         ev.record()
 
@@ -324,6 +325,10 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.fused = fused
         ctx.sinks = sinks
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh)
+        # radii and depth are not differentiable in the reference (only grad_out_color is read,
+        # HX/.../__init__.py:91-123): do not let autograd materialise zero gradients for them every backward
+        ctx.mark_non_differentiable(radii)
+        ctx.set_materialize_grads(False)
         return color, radii, depth
 
     @staticmethod
