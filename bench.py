@@ -54,6 +54,10 @@ def parse():
                     help="which reference extension / import name to run: hx = the bundled fork "
                          "hessian-diff-gaussian-rasterization-w-depth that BASELINE.json's north_star names (default); "
                          "dg = the upstream submodule scripts/splatam.py imports.  The reference arm reports both.")
+    ap.add_argument("--rgbd", default="off", choices=["off", "fused", "two-pass"],
+                    help="SURVEY 8f-1 (next row, not the headline): one step = RGB + depth + silhouette render and its "
+                         "backward.  fused = ONE pass of render_rgbd_sil (ours only); two-pass = two passes of the "
+                         "3-channel API as scripts/splatam.py:255-259 does (either arm)")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
                     help="N>1 gradient exchange: peer = the library's own two-shot all-reduce over NVLink peer memory "
                          "(torch symmetric memory for the allocation); nccl = torch.distributed.all_reduce")
@@ -150,6 +154,8 @@ class Runner:
 
     DIRECT = False
     PEER_GROUP = None   # set by main() for the N>1 arm of OURS: gradient exchange through peer memory
+    RGBD = "off"        # "off": the 3-channel pass of the headline metric.  "fused" / "two-pass": one SplaTAM render
+                        # iteration = RGB + (depth, silhouette, depth^2) (scripts/splatam.py:255-259), SURVEY 8f-1
 
     def __init__(self, sc, cams, dL, power, variant, device):
         from splatam_b200 import mapping, synth
@@ -158,6 +164,10 @@ class Runner:
         self.cams = [synth.settings_to(c, device) for c in cams]
         self.buckets = [mapping.GradBucket(sc, device, direct=self.DIRECT, peer_group=self.PEER_GROUP) for _ in range(2)]
         self.host_params = torch.cat([sc[k].reshape(-1) for k, _ in mapping.LAYOUT]).pin_memory()
+        if self.RGBD != "off":   # dL for the three extra planes (depth ~ metres: scaled so all planes matter)
+            g = torch.Generator().manual_seed(78)
+            extra = torch.randn(3, dL.shape[1], dL.shape[2], generator=g) / (3.0 * dL.shape[1] * dL.shape[2])
+            dL = torch.cat([dL, extra * torch.tensor([0.3, 1.0, 0.05]).view(3, 1, 1)], 0)
         self.host_dL = dL.contiguous().pin_memory()
         self.dLs = [self.host_dL.to(device) for _ in range(2)]
         self.host_grads = torch.empty_like(self.host_params).pin_memory()
@@ -205,10 +215,21 @@ class OursRunner(Runner):
         bk, lv = self.buckets[b], self.leaves[b]
         bk.zero_grad()
         self.means2D[b].grad = None
-        color, radii, depth = self.make(rs)(means3D=lv["means3D"], means2D=self.means2D[b], opacities=lv["opacities"],
-                                            colors_precomp=lv["colors_precomp"], scales=lv["scales"],
-                                            rotations=lv["rotations"])
-        color.backward(self.dLs[b])
+        kw = dict(means3D=lv["means3D"], means2D=self.means2D[b], opacities=lv["opacities"], scales=lv["scales"],
+                  rotations=lv["rotations"])
+        if self.RGBD == "off":
+            color, radii, depth = self.make(rs)(colors_precomp=lv["colors_precomp"], **kw)
+            color.backward(self.dLs[b])
+        elif self.RGBD == "fused":
+            color, radii, depth = self.make(rs).render_rgbd_sil(colors_precomp=lv["colors_precomp"], **kw)
+            color.backward(self.dLs[b])
+        else:   # two passes through the drop-in API, as scripts/splatam.py:255-259 + utils/slam_helpers.py:124-139 do
+            im, radii, depth = self.make(rs)(colors_precomp=lv["colors_precomp"], **kw)
+            pts4 = torch.cat([lv["means3D"], torch.ones_like(lv["means3D"][:, :1])], 1)
+            z = (pts4 @ rs.viewmatrix.reshape(4, 4))[:, 2]
+            depth_sil, _, _ = self.make(rs)(colors_precomp=torch.stack([z, torch.ones_like(z), z * z], 1), **kw)
+            color = torch.cat([im, depth_sil], 0)
+            color.backward(self.dLs[b])
         self.colors[b] = color.detach()
 
     def launches(self):
@@ -230,11 +251,23 @@ class RefCudaRunner(Runner):
         v = bk.views
         f = self.ref.forward(self.variant, rs, v["means3D"], v["colors_precomp"], v["opacities"], v["scales"],
                              v["rotations"])
-        g = self.ref.backward(f, self.dLs[b], self.power)
+        g = self.ref.backward(f, self.dLs[b][:3], self.power)
         self.colors[b] = f["color"]
         for k, gk in (("means3D", "means3D"), ("colors_precomp", "colors"), ("opacities", "opacities"),
                       ("scales", "scales"), ("rotations", "rotations")):
             bk.gviews[k].copy_(g[gk])
+        if self.RGBD != "off":   # the reference's second pass: colours = (z, 1, z*z), its gradients add
+            Vm = rs.viewmatrix.reshape(4, 4)
+            z = v["means3D"] @ Vm[:3, 2] + Vm[3, 2]
+            f2 = self.ref.forward(self.variant, rs, v["means3D"], torch.stack([z, torch.ones_like(z), z * z], 1),
+                                  v["opacities"], v["scales"], v["rotations"])
+            g2 = self.ref.backward(f2, self.dLs[b][3:], self.power)
+            for k, gk in (("means3D", "means3D"), ("opacities", "opacities"), ("scales", "scales"),
+                          ("rotations", "rotations")):
+                bk.gviews[k].add_(g2[gk])
+            dz = g2["colors"][:, 0] + 2.0 * z * g2["colors"][:, 2]
+            bk.gviews["means3D"].addr_(dz, Vm[:3, 2])
+            self.colors[b] = torch.cat([f["color"], f2["color"]], 0)
 
     def launches(self):
         return 0
@@ -492,6 +525,13 @@ def main():
     from splatam_b200 import mapping
     sched = mapping.keyframe_schedule(len(cams), max(args.steps, 8), world, seed=11)
     RunnerCls = OursRunner if args.impl == "ours" else RefCudaRunner
+    if args.rgbd != "off":
+        if args.impl != "ours" and args.rgbd == "fused":
+            raise SystemExit("--rgbd fused exists only in this repo; the reference arm runs --rgbd two-pass")
+        Runner.RGBD = args.rgbd
+        OursRunner.DIRECT = args.rgbd == "fused"    # two backward passes accumulate: no assign-style gradient sinks
+        base["metric"] = "RGB+depth+silhouette render iteration (fwd+bwd) iters/sec at %dx%d, %d Gaussians" % (W, H, P)
+        base["config"]["rgbd"] = args.rgbd
     runner = None
     if world > 1 and args.impl == "ours" and args.collective == "peer":
         # gradient exchange through the library's own peer-memory all-reduce (csrc/allreduce.cu); if symmetric memory

@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define SPLAT_ABI_VERSION 2
+#define SPLAT_ABI_VERSION 3
 
 /* Error codes.  Positive values >= 1000 are 1000 + cudaError_t of a failed runtime call. */
 enum {
@@ -63,6 +63,12 @@ typedef struct SplatCamera {
   const float* campos;      /* device, 3 floats (only read when shs != NULL)      */
   int32_t prefiltered;      /* kept for API parity; a culled point is never fatal */
   float near_plane;         /* 0.2f == DG semantics, 0.001f == HX semantics       */
+  int32_t depth_sil;        /* 0: 3 feature channels (the reference's pass).  1: fused RGB + depth + silhouette:
+                             * out_color / dL_dout_color have SIX planes, planes 3..5 render the features
+                             * (z, 1, z*z), z = view-space depth -- what scripts/splatam.py:257-259 obtains from a
+                             * second rasterizer pass with colors_precomp = get_depth_and_silhouette()
+                             * (utils/slam_helpers.py:124-139); their gradient reaches dL_dmeans3D through z.
+                             * power must be 1. */
 } SplatCamera;
 
 /* ---- scratch sizing (all sizes in bytes, all buffers must be 256-byte aligned) ------------- */

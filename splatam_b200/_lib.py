@@ -26,6 +26,7 @@ class SplatCamera(C.Structure):
         ("campos", C.c_void_p),
         ("prefiltered", C.c_int32),
         ("near_plane", C.c_float),
+        ("depth_sil", C.c_int32),
     ]
 
 
@@ -74,7 +75,7 @@ def _load():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing: intended
         fn.restype = res
         fn.argtypes = args
-    if lib.splat_abi_version() != 2:
+    if lib.splat_abi_version() != 3:
         raise ImportError("libsplat_b200.so ABI version mismatch")
     return lib
 

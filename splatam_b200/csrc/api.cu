@@ -137,7 +137,7 @@ int splat_forward_render(const SplatCamera* cam, int32_t P, const float* colors_
   r.ranges = iv.ranges; r.inst = bv.inst; r.order = iv.tile_order;
   r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.out_color = out_color; r.out_depth = out_depth;
-  r.hdr = iv.hdr; r.Rcap = Rcap; r.blended = nullptr;
+  r.hdr = iv.hdr; r.Rcap = Rcap; r.blended = nullptr; r.depth_sil = cam->depth_sil ? 1 : 0;
   return launch_render_fwd(r, T, st);
 }
 
@@ -172,6 +172,7 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
   if (hess && power != 2)
     return fail(SPLAT_ERR_UNSUPPORTED, "backward_power must be 1 or 2 (the reference only ever uses those, ros_handler.py:884)");
   if (hess && shs) return fail(SPLAT_ERR_UNSUPPORTED, "SH + Hessian backward is undefined in the reference (backward.cu:1067)");
+  if (hess && cam->depth_sil) return fail(SPLAT_ERR_UNSUPPORTED, "the fused depth/silhouette channels support backward_power 1 only");
   const size_t need = splat_backward_scratch_bytes(P, hess ? 2 : 1);
   if (!scratch || ((uintptr_t)scratch & 15)) return fail(SPLAT_ERR_BAD_ARG, "scratch must be a 16-byte aligned device buffer");
   if (scratch_bytes < need)
@@ -191,8 +192,9 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.dL_dpix = dL_dout_color;
   r.acc = acc;
   if (!hess) {
-    if (R > 0) if (int rc = launch_render_bwd(r, T, 0, st)) return rc;
+    if (R > 0) if (int rc = launch_render_bwd(r, T, cam->depth_sil ? 2 : 0, st)) return rc;
     PreBwdArgs b;
+    b.depth_sil = cam->depth_sil ? 1 : 0;
     b.P = P; b.M = M; b.sh_degree = cam->sh_degree; b.tanx = cam->tanfovx; b.tany = cam->tanfovy;
     b.fx = fx; b.fy = fy; b.mod = cam->scale_modifier;
     b.means = means3D; b.scales = sr ? scales : nullptr; b.rots = sr ? rotations : nullptr;
@@ -248,7 +250,7 @@ int splat_debug_count_blended(const SplatCamera* cam, int32_t P, const float* co
   (void)colors; (void)gv;
   r.W = W; r.H = H; r.gx = gx; r.order = iv.tile_order; r.ranges = iv.ranges; r.inst = bv.inst; r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.out_color = scratch_color; r.out_depth = nullptr;
-  r.hdr = iv.hdr; r.Rcap = (uint32_t)R_capacity; r.blended = blended;
+  r.hdr = iv.hdr; r.Rcap = (uint32_t)R_capacity; r.blended = blended; r.depth_sil = 0;
   return launch_render_fwd(r, gx * gy, (cudaStream_t)stream);
 }
 

@@ -22,6 +22,7 @@ struct PreBwdArgs {
   int W, H;
   const float4* grec;           // [P*3] forward geometry records (conic + opacity)
   const float* acc;             // [P,12] raw blend-backward sums (see render_bwd.cu)
+  int depth_sil;                // fused RGB+depth+silhouette: acc[9], acc[10] = sums for the z and z*z channels
   float* dL_dmean2D;  // [P,3] out
   float* dL_dconic;   // [P,4] out
   float* dL_dcolor;   // [P,3] out (and SH backward input)
@@ -41,6 +42,7 @@ struct HessArgs {
 
 struct RenderFwdArgs {
   int W, H, gx;
+  int depth_sil;          // 1: six output planes, planes 3..5 = features (z, 1, z*z)
   const uint32_t* order;  // blockIdx.x -> tile (ImageView::tile_order)
   const uint2* ranges; const float4* inst;
   const float* bg;

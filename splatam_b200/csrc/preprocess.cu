@@ -375,6 +375,13 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
     GaussChain g;
     chain_setup(g, mean, cov3D, has_scale, s, a.mod, q, a.fx, a.fy, a.tanx, a.tany, a.V, a.Pm);
     chain_apply(g, dcon.x, dcon.y, dcon.w, dm2x, dm2y, dmean, dcov, dscale, drot);
+    if (a.depth_sil) {
+      // fused depth/silhouette channels: features (z, 1, z*z) with z = view depth = V[2]x + V[6]y + V[10]z + V[14]
+      // (utils/slam_helpers.py:124-139 computes them in torch); dL/dz = sum(alpha T dL/dpix3) + 2 z sum(alpha T dL/dpix5)
+      const float z = __ldg(reinterpret_cast<const float*>(a.grec + (size_t)idx * INST_F4 + 1) + 2);
+      const float dz = r2.y + 2.f * z * r2.z;
+      dmean[0] += dz * a.V[2]; dmean[1] += dz * a.V[6]; dmean[2] += dz * a.V[10];
+    }
     if (a.shs) {  // SH backward (backward.cu:20-139): dL_dsh, and dL_dmean through the view direction
       const float3 c = make_float3(__ldg(a.campos), __ldg(a.campos + 1), __ldg(a.campos + 2));
       const float ox = mean.x - c.x, oy = mean.y - c.y, oz = mean.z - c.z;

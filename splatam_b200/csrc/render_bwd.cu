@@ -19,6 +19,9 @@
 //     [0..2] alpha*T*dL/dpix[ch]   [3] u*dx  [4] u*dy  [5] u*dx*dx  [6] u*dx*dy  [7] u*dy*dy  [8] u
 //   The per-Gaussian factors (opacity, conic, 0.5*W, -0.5) that the reference multiplies in per pair
 //   (backward.cu:717-745) are applied once per Gaussian in preprocess_bwd -- the map is linear.
+// MODE 2 (power == 1, fused RGB + depth + silhouette): six feature channels (r, g, b, z, 1, z*z) share the
+//   pair's alpha and T; row = MODE 0's nine sums + [9] alpha*T*dL/dpix[3] + [10] alpha*T*dL/dpix[5] (the z and z*z
+//   "colour" gradients, which preprocess_bwd turns into dL/dmean through z; the constant channel has no parameter).
 // MODE 1 (power == 2), row = 20 floats: dcolor^2[3], dopacity^2, and the 15 second moments of
 //   v = (dconic.x, dconic.y, dconic.w, dmean2D.x, dmean2D.y); hessian_finalize turns the moments
 //   into sum_pairs (J_k . v)^2 per output k, which is what HX accumulates pair by pair
@@ -34,6 +37,7 @@ namespace splat {
 template <int MODE> struct BwdTraits;
 template <> struct BwdTraits<0> { static const int VALS = 9, GROUP = 3, STRIDE = 12; };
 template <> struct BwdTraits<1> { static const int VALS = 19, GROUP = 1, STRIDE = 20; };
+template <> struct BwdTraits<2> { static const int VALS = 11, GROUP = 2, STRIDE = 12; };
 
 #define TR_STRIDE 36                        // words per transposed row (32 lanes + 4 pad)
 #define TR_ROWS 27
@@ -66,7 +70,7 @@ __device__ __forceinline__ float row_sum32(uint32_t addr) {
 }
 
 template <bool CULL, int MODE>
-__global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const RenderBwdArgs a) {
+__global__ void __launch_bounds__(RING_THREADS, MODE == 2 ? 2 : 3) render_bwd_kernel(const RenderBwdArgs a) {
   constexpr int VALS = BwdTraits<MODE>::VALS, GROUP = BwdTraits<MODE>::GROUP, STRIDE = BwdTraits<MODE>::STRIDE;
   constexpr int NV = VALS * GROUP;
   extern __shared__ __align__(128) unsigned char smem_dyn[];
@@ -116,9 +120,13 @@ __global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const Rende
   float T = T_final;
   float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
   if (inside) { dp0 = a.dL_dpix[pix]; dp1 = a.dL_dpix[HW + pix]; dp2 = a.dL_dpix[2 * HW + pix]; }
-  const float bg_dot = __ldg(a.bg) * dp0 + __ldg(a.bg + 1) * dp1 + __ldg(a.bg + 2) * dp2;
+  float dp3 = 0.f, dp4 = 0.f, dp5 = 0.f;
+  if (MODE == 2 && inside) { dp3 = a.dL_dpix[3 * HW + pix]; dp4 = a.dL_dpix[4 * HW + pix]; dp5 = a.dL_dpix[5 * HW + pix]; }
+  float bg_dot = __ldg(a.bg) * dp0 + __ldg(a.bg + 1) * dp1 + __ldg(a.bg + 2) * dp2;
+  if (MODE == 2) bg_dot += __ldg(a.bg) * dp3 + __ldg(a.bg + 1) * dp4 + __ldg(a.bg + 2) * dp5;
   const float nTb = -T_final * bg_dot;
   float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
+  float ar3 = 0.f, ar4 = 0.f, ar5 = 0.f, lz = 0.f, l1 = 0.f;   // MODE 2: last features are (lz, l1, lz*lz), l1 = 0 before the first pair
   const float ddelx_dx = 0.5f * a.W, ddely_dy = 0.5f * a.H;
   const uint32_t rec_base = smem_u32(smem_dyn);
   const uint32_t tr_base = rec_base + RING_NS * RING_CH * INST_BYTES + wid * TR_WARP_BYTES;
@@ -182,14 +190,23 @@ __global__ void __launch_bounds__(RING_THREADS, 3) render_bwd_kernel(const Rende
                 ar2 = last_alpha * lc2 + ola * ar2;
                 lc0 = col.x; lc1 = col.y; lc2 = col.z;
                 float dLda = (col.x - ar0) * dp0 + (col.y - ar1) * dp1 + (col.z - ar2) * dp2;
+                if (MODE == 2) {
+                  const float z = q1.z;
+                  ar3 = last_alpha * lz + ola * ar3;
+                  ar4 = last_alpha * l1 + ola * ar4;
+                  ar5 = last_alpha * (lz * lz) + ola * ar5;
+                  lz = z; l1 = 1.f;
+                  dLda += (z - ar3) * dp3 + (1.f - ar4) * dp4 + (z * z - ar5) * dp5;
+                }
                 dLda = dLda * T + nTb * rc;
                 last_alpha = al;
                 const float c0 = w * dp0, c1 = w * dp1, c2 = w * dp2;
-                if (MODE == 0) {
+                if (MODE == 0 || MODE == 2) {
                   float* o = &v[gsl * VALS];
                   const float u = Gv * dLda, udx = u * dx, udy = u * dy;
                   o[0] = c0; o[1] = c1; o[2] = c2;
                   o[3] = udx; o[4] = udy; o[5] = udx * dx; o[6] = udx * dy; o[7] = udy * dy; o[8] = u;
+                  if (MODE == 2) { o[9] = w * dp3; o[10] = w * dp5; }
                 } else {
                   const float dL_dG = q1.y * dLda;
                   const float gdx = Gv * dx, gdy = Gv * dy;
@@ -247,9 +264,12 @@ int launch_render_bwd(const RenderBwdArgs& a, int T, int mode, cudaStream_t st) 
     SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
     SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
     SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+    SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
     attr_set = true;
   }
-  if (mode == 0) {
+  if (mode == 2) {
+    render_bwd_kernel<true, 2><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
+  } else if (mode == 0) {
     if (g_disable_cull) render_bwd_kernel<false, 0><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
     else render_bwd_kernel<true, 0><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
   } else {

@@ -23,7 +23,10 @@
 
 namespace splat {
 
-template <bool CULL, bool COUNT>
+// DS: fused RGB + depth + silhouette: three more accumulators for the features (z, 1, z*z), z = the
+// record's view depth, blended with the SAME alpha/T -- the second rasterizer pass of scripts/splatam.py:257-259
+// without its preprocess, sort and alpha evaluation.
+template <bool CULL, bool COUNT, bool DS>
 __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFwdArgs a) {
   if (a.hdr->num_rendered > a.Rcap) return;
   __shared__ __align__(128) float4 s_rec[RING_NS][RING_CH * INST_F4];
@@ -69,6 +72,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
   // test_T == 0 < 1e-4 and changes nothing, so the inner loop needs no separate `done` flag; the
   // transmittance at termination is parked in T_end.
   float T = inside ? 1.0f : 0.f, T_end = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 15.0f;
+  float C3 = 0.f, C4 = 0.f, C5 = 0.f;
   uint32_t last = 0, nblend = 0;
   bool warp_done = __all_sync(0xffffffffu, T == 0.f);
   bool counted = false;
@@ -124,6 +128,12 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
               C0 += cq.x * al0 * T;
               C1 += cq.y * al0 * T;
               C2 += cq.z * al0 * T;
+              if (DS) {
+                const float z = lds32(r0 + 24);
+                C3 += z * al0 * T;
+                C4 += al0 * T;
+                C5 += (z * z) * al0 * T;
+              }
               if (T > 0.5f && test_T < 0.5f) D = lds32(r0 + 24);
               T = test_T;
               last = (uint32_t)(gbase + sub + b0 + 1);
@@ -139,6 +149,12 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
               C0 += cq.x * al1 * T;
               C1 += cq.y * al1 * T;
               C2 += cq.z * al1 * T;
+              if (DS) {
+                const float z = lds32(r1 + 24);
+                C3 += z * al1 * T;
+                C4 += al1 * T;
+                C5 += (z * z) * al1 * T;
+              }
               if (T > 0.5f && test_T < 0.5f) D = lds32(r1 + 24);
               T = test_T;
               last = (uint32_t)(gbase + sub + b1 + 1);
@@ -170,6 +186,11 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
     a.out_color[pix] = C0 + T * __ldg(a.bg + 0);
     a.out_color[HW + pix] = C1 + T * __ldg(a.bg + 1);
     a.out_color[2 * HW + pix] = C2 + T * __ldg(a.bg + 2);
+    if (DS) {
+      a.out_color[3 * HW + pix] = C3 + T * __ldg(a.bg + 0);
+      a.out_color[4 * HW + pix] = C4 + T * __ldg(a.bg + 1);
+      a.out_color[5 * HW + pix] = C5 + T * __ldg(a.bg + 2);
+    }
     if (a.out_depth) a.out_depth[pix] = D;
     if (COUNT) a.blended[pix] = nblend;
   }
@@ -180,9 +201,10 @@ int g_disable_cull = 0;
 int launch_render_fwd(const RenderFwdArgs& a, int T, cudaStream_t st) {
   ProfScope prof_(K_RENDER_FWD, st);
   if (T <= 0) return SPLAT_OK;
-  if (a.blended) render_fwd_kernel<false, true><<<T, RING_THREADS, 0, st>>>(a);
-  else if (g_disable_cull) render_fwd_kernel<false, false><<<T, RING_THREADS, 0, st>>>(a);
-  else render_fwd_kernel<true, false><<<T, RING_THREADS, 0, st>>>(a);
+  if (a.blended) render_fwd_kernel<false, true, false><<<T, RING_THREADS, 0, st>>>(a);
+  else if (a.depth_sil) render_fwd_kernel<true, false, true><<<T, RING_THREADS, 0, st>>>(a);
+  else if (g_disable_cull) render_fwd_kernel<false, false, false><<<T, RING_THREADS, 0, st>>>(a);
+  else render_fwd_kernel<true, false, false><<<T, RING_THREADS, 0, st>>>(a);
   SPLAT_LAUNCH_CHECK("render_fwd_kernel");
   return SPLAT_OK;
 }

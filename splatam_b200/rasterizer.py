@@ -87,8 +87,9 @@ def _on_device(dev):
     return _NULL if torch.cuda.current_device() == dev.index else torch.cuda.device(dev)
 
 
-def _camera(rs, near, keep):
+def _camera(rs, near, keep, depth_sil=False):
     cam = SplatCamera()
+    cam.depth_sil = 1 if depth_sil else 0
     cam.image_height = int(rs.image_height)
     cam.image_width = int(rs.image_width)
     cam.tanfovx = float(rs.tanfovx)
@@ -145,7 +146,8 @@ class RasterState:
 last_state = None   # most recent RasterState (debug / parity tests only)
 
 
-def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rotations, cov3D_precomp, sh, bwd=None):
+def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rotations, cov3D_precomp, sh, bwd=None,
+                      depth_sil=False):
     """Runs both forward phases.  Returns (color, radii, depth, RasterState).  bwd = (power, fused, sinks) when a
     backward pass will follow: its buffers are then prepared here, ahead of the blocking read-back."""
     if means3D.dim() != 2 or means3D.shape[1] != 3:
@@ -159,15 +161,15 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
     if P == 0:  # HX/rasterize_points.cu:81 -- outputs stay at their fill value 0
         st.geom = st.image = st.binning = torch.empty(0, dtype=torch.uint8, device=dev)
         st.capacity = st.num_rendered = 0
-        return (torch.zeros(3, H, W, device=dev), torch.zeros(0, dtype=torch.int32, device=dev),
+        return (torch.zeros(6 if depth_sil else 3, H, W, device=dev), torch.zeros(0, dtype=torch.int32, device=dev),
                 torch.zeros(1, H, W, device=dev), st)
     keep = []
-    cam = _camera(rs, near, keep)
+    cam = _camera(rs, near, keep, depth_sil)
     st.cam, st.keep = cam, keep   # the backward pass reuses the struct (and keeps its tensors alive)
     with _on_device(dev):
         stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         M = sh.shape[1] if sh.numel() else 0
-        out_color = torch.empty(3, H, W, dtype=torch.float32, device=dev)
+        out_color = torch.empty(6 if depth_sil else 3, H, W, dtype=torch.float32, device=dev)
         out_depth = torch.empty(1, H, W, dtype=torch.float32, device=dev)
         radii = torch.empty(P, dtype=torch.int32, device=dev)
         st.geom = torch.empty(lib.splat_geom_state_bytes(P), dtype=torch.uint8, device=dev)
@@ -299,7 +301,7 @@ def rasterize_backward(rs, near, st, power, fused, means3D, colors_precomp, scal
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                raster_settings, backward_power, near, fused, sinks=None):
+                raster_settings, backward_power, near, fused, sinks=None, depth_sil=False):
         # the reference passes tensors through .contiguous() (HX/rasterize_points.cu:94-112)
         means3D = _f32(means3D, "means3D")
         opacities = _f32(opacities, "opacities")
@@ -316,7 +318,8 @@ class _RasterizeGaussians(torch.autograd.Function):
                 raise RuntimeError("%s must be a float32 CUDA tensor" % name)
         bwd = (backward_power, fused, sinks) if any(ctx.needs_input_grad) else None
         color, radii, depth, st = rasterize_forward(raster_settings, near, means3D, colors_precomp, opacities,
-                                                    scales, rotations, cov3Ds_precomp, sh, bwd)
+                                                    scales, rotations, cov3Ds_precomp, sh, bwd, depth_sil)
+        ctx.depth_sil = depth_sil
         ctx.raster_settings = raster_settings
         ctx.num_rendered = st.num_rendered
         ctx.backward_power = backward_power
@@ -334,8 +337,11 @@ class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_out_color, _grad_radii, _grad_depth):
         colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh = ctx.saved_tensors
+        nch = 6 if ctx.depth_sil else 3
         if grad_out_color is None:
-            grad_out_color = torch.zeros(3, ctx.state.H, ctx.state.W, device=means3D.device)
+            grad_out_color = torch.zeros(nch, ctx.state.H, ctx.state.W, device=means3D.device)
+        if tuple(grad_out_color.shape) != (nch, ctx.state.H, ctx.state.W):
+            raise RuntimeError("grad of the rendered image must be [%d,%d,%d]" % (nch, ctx.state.H, ctx.state.W))
         (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D) = rasterize_backward(
             ctx.raster_settings, ctx.near, ctx.state, ctx.backward_power, ctx.fused, means3D, colors_precomp,
             scales, rotations, cov3Ds_precomp, sh, radii, grad_out_color, ctx.sinks)
@@ -347,15 +353,17 @@ class _RasterizeGaussians(torch.autograd.Function):
                 g_scales if scales.numel() and "scales" not in sunk else None,
                 g_rots if rotations.numel() and "rotations" not in sunk else None,
                 g_cov3D if cov3Ds_precomp.numel() else None,
-                None, None, None, None, None)
+                None, None, None, None, None, None)
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                        raster_settings, backward_power=1, near=NEAR_HX, fused=True):
+                        raster_settings, backward_power=1, near=NEAR_HX, fused=True, depth_sil=False):
+    if depth_sil and int(backward_power) != 1:
+        raise RuntimeError("render_depth_sil supports backward_power == 1 only")
     sinks = _collect_sinks(means3D=means3D, colors_precomp=colors_precomp, opacities=opacities, scales=scales,
                            rotations=rotations)
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                                     cov3Ds_precomp, raster_settings, backward_power, near, fused, sinks)
+                                     cov3Ds_precomp, raster_settings, backward_power, near, fused, sinks, bool(depth_sil))
 
 
 class GaussianRasterizer(nn.Module):
@@ -386,6 +394,18 @@ class GaussianRasterizer(nn.Module):
 
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
                 cov3D_precomp=None):
+        """Same call as the reference (HX/.../__init__.py:170-204)."""
+        return self._render(means3D, means2D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp, False)
+
+    def render_rgbd_sil(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                        cov3D_precomp=None):
+        """Extension, same arguments as forward(): the returned image has SIX planes -- planes 0..2 the
+        colours, planes 3..5 exactly what a second pass with colors_precomp = get_depth_and_silhouette(means3D, w2c) =
+        (z, 1, z*z) renders (utils/slam_helpers.py:124-139, scripts/splatam.py:257-259) -- from ONE preprocess / sort /
+        alpha evaluation; the gradient of planes 3..5 reaches means3D through z.  backward_power must be 1."""
+        return self._render(means3D, means2D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp, True)
+
+    def _render(self, means3D, means2D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp, depth_sil):
         raster_settings = self.raster_settings
         if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
             raise Exception('Please provide excatly one of either SHs or precomputed colors!')
@@ -405,4 +425,4 @@ class GaussianRasterizer(nn.Module):
             cov3D_precomp = empty
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
                                    cov3D_precomp, raster_settings, self.backward_power, self.NEAR_PLANE,
-                                   self.FUSED_BACKWARD)
+                                   self.FUSED_BACKWARD, depth_sil)
