@@ -143,6 +143,9 @@ extern "C" int splat_peer_allreduce_sum(const uint64_t* buffers, const uint64_t*
   const size_t per = (a.n4 + world - 1) / world;
   if (multicast_buffer) {
     if (multicast_buffer & 15) return fail(SPLAT_ERR_BAD_ARG, "misaligned multicast address");
+    // (A hybrid split -- part of each slice through the switch, the rest through peer loads/stores in the same
+    // launch -- was swept at N=8: 0.184 ms at 90/10 rising to 0.234 ms at 35/65 vs 0.178 ms all in-switch: both
+    // halves contend for the same links.)
     int mblocks = (int)std::min<size_t>((per + 512 * 4 - 1) / (512 * 4), (size_t)148 * 2);
     if (mblocks < 1) mblocks = 1;
     multimem_reduce_kernel<<<mblocks, 512, 0, st>>>(reinterpret_cast<float4*>(multicast_buffer), rank, world, a.n4);
