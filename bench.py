@@ -68,32 +68,78 @@ def parse():
 
 # ------------------------------------------------------------------------------------------------
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    """SM clock and throttle reasons DURING the timed region (B200_PROFILING.md's clocks line).  Sampled in-process
+    through NVML (nvidia_ml_py -- the library nvidia-smi itself sits on) from a thread, every 40 ms: a separate
+    `nvidia-smi -lms` process polling at 25-50 ms was seen to stretch some timed regions by 10-15% (host-side launch
+    stalls while it holds driver locks).  Falls back to one `nvidia-smi` loop at 200 ms if NVML cannot be loaded."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    PERIOD = 0.04
 
     def __init__(self, index):
-        self.rows = []        # (arrival time, csv line)
-        self.proc = None
+        self.rows = []        # (time, sm_mhz, max_mhz, set of reasons)
         self.index = index
         self.t0 = self.t1 = None
+        self._stop = threading.Event()
+        self.thread = None
+        self.proc = None
+        self.mode = None
 
     def start(self):
-        """Started BEFORE the warm-up: the fork and nvidia-smi's NVML start-up (which takes driver locks and can
-        stall kernel launches for milliseconds) stay out of the timed region; the loop then samples every 25 ms."""
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # NVML indexes physical devices; honour CUDA_VISIBLE_DEVICES when it is a plain list of indices
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = self.index
+            if vis:
+                ids = [v.strip() for v in vis.split(",") if v.strip()]
+                if self.index < len(ids) and ids[self.index].isdigit():
+                    phys = int(ids[self.index])
+            h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            names = (("hw_slowdown", pynvml.nvmlClocksEventReasonHwSlowdown),
+                     ("hw_thermal_slowdown", pynvml.nvmlClocksEventReasonHwThermalSlowdown),
+                     ("sw_thermal_slowdown", pynvml.nvmlClocksEventReasonSwThermalSlowdown),
+                     ("sw_power_cap", pynvml.nvmlClocksEventReasonSwPowerCap))
+
+            def loop():
+                while not self._stop.is_set():
+                    try:
+                        sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                        bits = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                        self.rows.append((time.time(), float(sm), float(mx), {n for n, b in names if bits & b}))
+                    except Exception:
+                        pass
+                    self._stop.wait(self.PERIOD)
+            self.thread = threading.Thread(target=loop, daemon=True)
+            self.thread.start()
+            self.mode = "nvml"
+            return
+        except Exception:
+            pass
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+            self.mode = "nvidia-smi"
         except Exception:
             self.proc = None
 
     def _read(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in self.proc.stdout:
-            self.rows.append((time.time(), line.strip()))
+            f = [x.strip() for x in line.strip().split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                self.rows.append((time.time(), float(f[0]), float(f[1]),
+                                  {n for n, v in zip(names, f[3:7]) if v.lower().startswith("active")}))
+            except ValueError:
+                continue
 
     def mark_start(self):
         self.t0 = time.time()
@@ -102,31 +148,23 @@ class ClockSampler:
         self.t1 = time.time()
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        t0, t1 = self.t0 or 0.0, self.t1 or float("inf")
-        rows = [r for t, r in self.rows if t0 <= t <= t1 + 0.03]   # samples taken during the timed region
-        for r in rows:
-            f = [x.strip() for x in r.split(",")]
-            if len(f) < 7:
-                continue
+        self._stop.set()
+        if self.proc is not None:
+            self.proc.terminate()
             try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
-            except ValueError:
-                continue
-            for n, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        if self.mode is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["clock sampler unavailable"], "samples": 0}
+        t0, t1 = self.t0 or 0.0, self.t1 or float("inf")
+        rows = [r for r in self.rows if t0 <= r[0] <= t1 + 0.03]   # samples taken during the timed region
+        sm = sorted(r[1] for r in rows)
+        reasons = set()
+        for r in rows:
+            reasons |= r[3]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max((r[2] for r in rows), default=None),
+                "reasons": sorted(reasons), "samples": len(sm), "source": self.mode}
 
 
 def build_workload(name, device):

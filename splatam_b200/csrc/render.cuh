@@ -1,6 +1,6 @@
 // render.cuh -- pieces shared by the forward and backward blend kernels.
 //
-// Tile = 16x16 pixels, CTA = 256 threads = 8 warps (same tile semantics as the reference,
+// Tile = 16x16 pixels, covered by 8 warps in CTA_PARTS CTAs of CTA_WARPS warps (same tile semantics as the reference,
 // HX/cuda_rasterizer/config.h:15-17, so tile-rect culling is identical), but the thread->pixel
 // map is ours: warp w owns the 8x4 sub-tile (w&1, w>>1) so that a warp can reject a whole
 // Gaussian whose footprint misses its 32 pixels with ONE lane-parallel test + ballot.
@@ -10,13 +10,20 @@
 namespace splat {
 
 // Instance ring shared by both blend kernels: RING_NS stages of RING_CH records (48 B each), filled by
-// the TMA unit and consumed by the CTA's 8 warps (one 8x4 sub-tile each).  There is no producer
+// the TMA unit and consumed by the CTA's CTA_WARPS warps (one 8x4 sub-tile each).  There is no producer
 // warp: a stage is released through a shared-memory counter, and the warp whose release is the
-// eighth issues the refill of that stage itself (one elected lane, ~10 instructions per 6 KB) -- a
+// last issues the refill of that stage itself (one elected lane, ~10 instructions per 6 KB) -- a
 // polling producer lane cost 6.6% of the backward kernel's issue slots (profiles/r01c).
 #define RING_CH 128
-#define RING_NS 4
-#define RING_THREADS 256
+#ifndef RING_NS
+#define RING_NS 3
+#endif
+#ifndef CTA_WARPS
+#define CTA_WARPS 4            // warps (8x4 sub-tiles) per CTA: 8 = one CTA per 16x16 tile, 4 = two CTAs per tile (measured:
+                               // 4 warps + 3 ring stages beat 8 + 4 by ~1.5% in both blend kernels: finer scheduling grain)
+#endif
+#define CTA_PARTS (8 / CTA_WARPS)
+#define RING_THREADS (CTA_WARPS * 32)
 
 struct SubTile {
   int px, py;        // this lane's pixel
@@ -24,8 +31,8 @@ struct SubTile {
   float fy0, fy1;
 };
 
-__device__ __forceinline__ SubTile make_subtile(int tile_x, int tile_y) {
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+__device__ __forceinline__ SubTile make_subtile(int tile_x, int tile_y, int part = 0) {
+  const int lane = threadIdx.x & 31, wid = (threadIdx.x >> 5) + part * CTA_WARPS;
   SubTile s;
   const int sx0 = tile_x * TILE_X + (wid & 1) * 8;
   const int sy0 = tile_y * TILE_Y + (wid >> 1) * 4;

@@ -42,7 +42,7 @@ template <> struct BwdTraits<2> { static const int VALS = 11, GROUP = 2, STRIDE 
 #define TR_STRIDE 36                        // words per transposed row (32 lanes + 4 pad)
 #define TR_ROWS 27
 #define TR_WARP_BYTES (TR_ROWS * TR_STRIDE * 4)
-#define BWD_SMEM (RING_NS * RING_CH * INST_BYTES + 8 * TR_WARP_BYTES)
+#define BWD_SMEM (RING_NS * RING_CH * INST_BYTES + CTA_WARPS * TR_WARP_BYTES)
 
 __device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
   float2 r;
@@ -70,19 +70,19 @@ __device__ __forceinline__ float row_sum32(uint32_t addr) {
 }
 
 template <bool CULL, int MODE>
-__global__ void __launch_bounds__(RING_THREADS, MODE == 2 ? 2 : 3) render_bwd_kernel(const RenderBwdArgs a) {
+__global__ void __launch_bounds__(RING_THREADS, (MODE == 2 ? 2 : 3) * CTA_PARTS) render_bwd_kernel(const RenderBwdArgs a) {
   constexpr int VALS = BwdTraits<MODE>::VALS, GROUP = BwdTraits<MODE>::GROUP, STRIDE = BwdTraits<MODE>::STRIDE;
   constexpr int NV = VALS * GROUP;
   extern __shared__ __align__(128) unsigned char smem_dyn[];
   __shared__ __align__(8) uint64_t s_full[RING_NS];
   __shared__ int s_rel[RING_NS];
-  __shared__ int s_max[8];
+  __shared__ int s_max[CTA_WARPS];
 
-  const int tile = (int)a.order[blockIdx.x];
+  const int tile = (int)a.order[blockIdx.x / CTA_PARTS], part = blockIdx.x % CTA_PARTS;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const uint2 range = a.ranges[tile];
   const int tile_x = tile % a.gx, tile_y = tile / a.gx;
-  const SubTile st = make_subtile(tile_x, tile_y);
+  const SubTile st = make_subtile(tile_x, tile_y, part);
   const bool inside = st.px < a.W && st.py < a.H;
   const int pix = st.py * a.W + st.px;
   const int last = inside ? (int)a.n_contrib[pix] : 0;
@@ -97,7 +97,7 @@ __global__ void __launch_bounds__(RING_THREADS, MODE == 2 ? 2 : 3) render_bwd_ke
   __syncthreads();
   int hi = 0;  // list positions >= max(n_contrib) over the tile are never touched by anyone
 #pragma unroll
-  for (int w = 0; w < 8; ++w) hi = max(hi, s_max[w]);
+  for (int w = 0; w < CTA_WARPS; ++w) hi = max(hi, s_max[w]);
   const int nch = (hi + RING_CH - 1) / RING_CH;
 
   // chunk c = list positions [max(0, hi-(c+1)*RING_CH), hi - c*RING_CH), streamed into stage c % RING_NS
@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(RING_THREADS, MODE == 2 ? 2 : 3) render_bwd_ke
       }
     }
     __syncwarp();
-    if (lane == 0 && ring_release(&s_rel[s], 8) && c + RING_NS < nch) fill(c + RING_NS);
+    if (lane == 0 && ring_release(&s_rel[s], CTA_WARPS) && c + RING_NS < nch) fill(c + RING_NS);
   }
 }
 
@@ -268,13 +268,13 @@ int launch_render_bwd(const RenderBwdArgs& a, int T, int mode, cudaStream_t st) 
     attr_set = true;
   }
   if (mode == 2) {
-    render_bwd_kernel<true, 2><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
+    render_bwd_kernel<true, 2><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);
   } else if (mode == 0) {
-    if (g_disable_cull) render_bwd_kernel<false, 0><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
-    else render_bwd_kernel<true, 0><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
+    if (g_disable_cull) render_bwd_kernel<false, 0><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);
+    else render_bwd_kernel<true, 0><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);
   } else {
-    if (g_disable_cull) render_bwd_kernel<false, 1><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
-    else render_bwd_kernel<true, 1><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
+    if (g_disable_cull) render_bwd_kernel<false, 1><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);
+    else render_bwd_kernel<true, 1><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);
   }
   SPLAT_LAUNCH_CHECK("render_bwd_kernel");
   return SPLAT_OK;

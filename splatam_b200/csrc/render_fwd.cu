@@ -3,10 +3,10 @@
 //
 // Differences in HOW (results identical):
 //  * the tile's sorted instance records (48 B each, written by the tile sort in list order) are ONE
-//    contiguous byte range, streamed into a 4-stage shared-memory ring by the TMA unit
-//    (cp.async.bulk + mbarrier complete_tx).  The 8 warps never meet at a CTA barrier: each waits
+//    contiguous byte range, streamed into a RING_NS-stage shared-memory ring by the TMA unit
+//    (cp.async.bulk + mbarrier complete_tx).  The warps never meet at a CTA barrier: each waits
 //    on the stage's "full" mbarrier and releases the stage through a counter; the warp whose
-//    release is the eighth issues the refill.  Warps drift apart by up to 4 stages instead of
+//    release is the last issues the refill.  Warps drift apart by up to RING_NS stages instead of
 //    idling at __syncthreads (the reference re-syncs the whole CTA every 256 Gaussians,
 //    forward.cu:311-334);
 //  * per-warp 8x4 sub-tiles with an exact conservative footprint test (render.cuh): a warp only
@@ -14,7 +14,7 @@
 //    two hits at a time so the two exponentials overlap;
 //  * colour and depth travel with the record (the reference re-reads colour from global memory per
 //    pixel, forward.cu:361);
-//  * warp-level early termination, and the ring stops being refilled once all 8 warps are done.
+//  * warp-level early termination, and the ring stops being refilled once all warps of the CTA are done.
 // Per-pixel arithmetic keeps the reference's expression order and precise expf so the discrete
 // tests (power>0, alpha<1/255, T<1e-4, median crossing) take the same branches.
 #include "render.cuh"
@@ -35,7 +35,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
   __shared__ int s_ndone;
   __shared__ int s_stop;
 
-  const int tile = (int)a.order[blockIdx.x];
+  const int tile = (int)a.order[blockIdx.x / CTA_PARTS], part = blockIdx.x % CTA_PARTS;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const uint2 range = a.ranges[tile];
   const int n = (int)(range.y - range.x);
@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
 
   // ------------------------------------------------------------------------------ consumer warps
   const int tile_x = tile % a.gx, tile_y = tile / a.gx;
-  const SubTile st = make_subtile(tile_x, tile_y);
+  const SubTile st = make_subtile(tile_x, tile_y, part);
   const bool inside = st.px < a.W && st.py < a.H;
   const float pxf = (float)st.px, pyf = (float)st.py;
   const float tile_cx = tile_x * TILE_X + 7.5f, tile_cy = tile_y * TILE_Y + 7.5f;
@@ -166,8 +166,8 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
       }
     }
     __syncwarp();
-    if (lane == 0 && ring_release(&s_rel[s], 8) && c + RING_NS < nch) {
-      if (*(volatile int*)&s_ndone == 8) {  // every pixel of the tile has terminated: stop streaming
+    if (lane == 0 && ring_release(&s_rel[s], CTA_WARPS) && c + RING_NS < nch) {
+      if (*(volatile int*)&s_ndone == CTA_WARPS) {  // every pixel of the tile has terminated: stop streaming
         atomicMin(&s_stop, c + RING_NS);  // stages already in flight drain; every warp leaves at this chunk
         __threadfence_block();
         mbar_arrive(&s_full[s]);
@@ -201,10 +201,10 @@ int g_disable_cull = 0;
 int launch_render_fwd(const RenderFwdArgs& a, int T, cudaStream_t st) {
   ProfScope prof_(K_RENDER_FWD, st);
   if (T <= 0) return SPLAT_OK;
-  if (a.blended) render_fwd_kernel<false, true, false><<<T, RING_THREADS, 0, st>>>(a);
-  else if (a.depth_sil) render_fwd_kernel<true, false, true><<<T, RING_THREADS, 0, st>>>(a);
-  else if (g_disable_cull) render_fwd_kernel<false, false, false><<<T, RING_THREADS, 0, st>>>(a);
-  else render_fwd_kernel<true, false, false><<<T, RING_THREADS, 0, st>>>(a);
+  if (a.blended) render_fwd_kernel<false, true, false><<<T * CTA_PARTS, RING_THREADS, 0, st>>>(a);
+  else if (a.depth_sil) render_fwd_kernel<true, false, true><<<T * CTA_PARTS, RING_THREADS, 0, st>>>(a);
+  else if (g_disable_cull) render_fwd_kernel<false, false, false><<<T * CTA_PARTS, RING_THREADS, 0, st>>>(a);
+  else render_fwd_kernel<true, false, false><<<T * CTA_PARTS, RING_THREADS, 0, st>>>(a);
   SPLAT_LAUNCH_CHECK("render_fwd_kernel");
   return SPLAT_OK;
 }
