@@ -70,7 +70,7 @@ __device__ __forceinline__ float row_sum32(uint32_t addr) {
 }
 
 template <bool CULL, int MODE>
-__global__ void __launch_bounds__(RING_THREADS, (MODE == 2 ? 2 : 3) * CTA_PARTS) render_bwd_kernel(const RenderBwdArgs a) {
+__global__ void __launch_bounds__(RING_THREADS, 3 * CTA_PARTS) render_bwd_kernel(const RenderBwdArgs a) {
   constexpr int VALS = BwdTraits<MODE>::VALS, GROUP = BwdTraits<MODE>::GROUP, STRIDE = BwdTraits<MODE>::STRIDE;
   constexpr int NV = VALS * GROUP;
   extern __shared__ __align__(128) unsigned char smem_dyn[];
