@@ -390,6 +390,22 @@ def test_fused_depth_sil_vs_two_reference_passes(case):
     _check_grads(ours, ref, ref2=ref2)
 
 
+@pytest.mark.parametrize("variant", ["dg", "hx"])
+def test_scale_modifier_and_background_vs_reference_extension(variant):
+    """Settings fields SplaTAM leaves at their defaults: scale_modifier != 1 (forward.cu:122-126, backward.cu:436-441)
+    and a non-black background (forward.cu:388, backward.cu:655-657 -- the bg term of dL/dalpha)."""
+    rs, sc, dL = build_case("cloud_small", "cuda")
+    rs = rs._replace(scale_modifier=0.7, bg=torch.tensor([0.2, 0.5, 0.9], device="cuda"))
+    ours = run_ours(variant, rs, sc, dL)
+    ref = run_ref(variant, rs, sc, dL)
+    assert torch.equal(ours["radii"], ref["radii"])
+    assert torch.equal(ours["views"]["point_list"], ref["point_list"])
+    assert torch.equal(ours["views"]["n_contrib"].flatten(), ref["n_contrib"])
+    assert rel_err(ours["color"], ref["color"], 1e-6) <= FWD_TOL
+    assert rel_err(ours["depth"], ref["depth"], 1e-6) <= FWD_TOL
+    _check_grads(ours["grads"], ref["grads"], ref2=[run_ref(variant, rs, sc, dL)["grads"] for _ in range(4)])
+
+
 def test_mark_visible_vs_reference_extension():
     import hessian_diff_gaussian_rasterization_w_depth as hx
     import diff_gaussian_rasterization as dg
