@@ -312,7 +312,7 @@ class RefCudaRunner(Runner):
 
 
 # ------------------------------------------------------------------------------------------------
-def cpu_oracle_sample(cam, sc, cams, dL, power, crop=(192, 112)):
+def cpu_oracle_sample(cam, sc, cams, dL, power, crop=(1200, 672)):
     """CPU oracle (port) on a bounded centre crop of the workload.  Returns (value iters/s
     extrapolated to the full image, cores, sample description)."""
     from oracle import raster_oracle as O
