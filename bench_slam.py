@@ -1,0 +1,207 @@
+#!/usr/bin/env python
+"""bench_slam.py -- one full SplaTAM optimisation iteration (get_loss + backward), SURVEY.md 8f-1..3.
+
+What scripts/splatam.py runs 40-200 times per tracked frame and 30-60 times per mapped frame:
+    transform_to_frame -> rendervars -> RGB render -> depth+silhouette render -> masked L1 (+SSIM) loss -> backward
+Arms (same seeded scene, same step schedule, CUDA events around K steps after W warm-ups, inputs resident in HBM):
+  --impl ours        splatam_b200.slam.get_loss: fused builder kernel -> ONE six-plane render -> fused loss kernel ->
+                     rasterizer backward -> builder backward (pose gradient reduced in-kernel)
+  --impl dropin      the reference's torch glue (oracle/slam_oracle.py restates it) around OUR 3-channel drop-in
+                     rasterizer, two passes: what an unmodified scripts/splatam.py gets from this repo
+  --impl reference   the same torch glue around the UNMODIFIED reference extension (oracle/_ref, --variant dg|hx)
+--mode tracking: C2 shape, 1200x680, 300k isotropic Gaussians, pose-only gradients (sil_thres 0.99, summed L1)
+--mode mapping : C3 shape, 1200x680, 1M Gaussians, Gaussian gradients (0.8 L1 + 0.2 (1-SSIM) colour, mean L1 depth)
+The optimizer step (torch Adam) is outside the timed iteration in every arm.  One JSON line on stdout.
+"""
+import argparse
+import json
+import math
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+import bench  # noqa: E402  (ClockSampler)
+
+
+def rot_to_quat(R):
+    """(w,x,y,z) of a rotation matrix with positive trace (small camera rotations)."""
+    w = math.sqrt(max(1e-12, 1.0 + R[0, 0] + R[1, 1] + R[2, 2])) / 2.0
+    return torch.tensor([w, (R[2, 1] - R[1, 2]) / (4 * w), (R[0, 2] - R[2, 0]) / (4 * w), (R[1, 0] - R[0, 1]) / (4 * w)])
+
+
+def build(mode, device, n_frames=24):
+    from splatam_b200 import synth
+    cam = synth.REPLICA
+    P, layers = (300_000, 1) if mode == "tracking" else (1_000_000, 3)
+    sc = synth.surface_scene(P, cam["w"], cam["h"], cam["fx"], cam["fy"], cam["cx"], cam["cy"], seed=2, layers=layers)
+    rs = synth.make_settings(device=device, **cam)            # camera stays at the first frame's w2c = I
+    rots, trans = [], []
+    for k in range(n_frames):                                 # relative poses of the keyframe window live in params
+        w2c = synth.arc_pose(k, n_frames)
+        rots.append(rot_to_quat(w2c[:3, :3]) * 1.1)
+        trans.append(w2c[:3, 3])
+    params = {
+        "means3D": sc["means3D"], "rgb_colors": sc["colors_precomp"],
+        "unnorm_rotations": sc["rotations"],
+        "logit_opacities": torch.logit(sc["opacities"].clamp(1e-4, 1 - 1e-4)),
+        "log_scales": torch.log(sc["scales"][:, :1]),
+        "cam_unnorm_rots": torch.stack(rots, 1).unsqueeze(0), "cam_trans": torch.stack(trans, 1).unsqueeze(0),
+    }
+    params = {k: v.float().contiguous().to(device).requires_grad_(True) for k, v in params.items()}
+    return cam, rs, params
+
+
+def make_targets(params, rs, n_frames, device):
+    """Ground-truth colour/depth per keyframe: our own fused render at a pose perturbed by (0.5 deg, 5 mm), SURVEY 8d C2."""
+    from splatam_b200 import slam
+    from diff_gaussian_rasterization import GaussianRasterizer
+    g = torch.Generator().manual_seed(5)
+    out = []
+    with torch.no_grad():
+        pert = {k: v.detach().clone() for k, v in params.items()}
+        pert["cam_unnorm_rots"] += 0.004 * torch.randn(pert["cam_unnorm_rots"].shape, generator=g).to(device)
+        pert["cam_trans"] += 0.005 * torch.randn(pert["cam_trans"].shape, generator=g).to(device)
+        for k in range(n_frames):
+            rv = slam.build_rendervar(pert, k, False, False)
+            img, _, _ = GaussianRasterizer(raster_settings=rs).render_rgbd_sil(**rv)
+            depth = img[3:4].clone()
+            depth[img[4:5] < 0.5] = 0.0                       # no surface -> invalid depth
+            out.append({"cam": rs, "im": img[:3].clamp(0, 1).contiguous(), "depth": depth.contiguous(),
+                        "w2c": torch.eye(4, device=device)})
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--mode", default="tracking", choices=["tracking", "mapping"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "dropin", "reference"])
+    ap.add_argument("--variant", default="dg", choices=["dg", "hx"])
+    ap.add_argument("--steps", type=int, default=96)
+    ap.add_argument("--warmup", type=int, default=8)
+    args = ap.parse_args()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    assert torch.cuda.is_available(), "bench_slam.py needs a CUDA device"
+    device = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    nf = 24
+    cam, rs, params = build(args.mode, device, nf)
+    targets = make_targets(params, rs, nf, device)
+    tracking = args.mode == "tracking"
+    P = params["means3D"].shape[0]
+    variables = {"max_2D_radius": torch.zeros(P, device=device)}
+    wts = dict(im=0.5, depth=1.0)                             # configs/replica/splatam.py:67-70, :88-91
+    sil_thres = 0.99 if tracking else 0.5
+
+    from splatam_b200 import slam
+    from splatam_b200._lib import lib
+    if args.impl == "ours":
+        def step(kf):
+            loss, _, wl = slam.get_loss(params, targets[kf], variables, kf, wts, tracking, sil_thres, True, False,
+                                        tracking=tracking, mapping=not tracking)
+            loss.backward()
+            return loss
+    else:
+        from oracle import slam_oracle as SO
+        if args.impl == "dropin":
+            from diff_gaussian_rasterization import GaussianRasterizer as R
+            Renderer = lambda raster_settings: R(raster_settings)   # noqa: E731
+        else:
+            from oracle import ref_ext
+            ref_ext.load(args.variant)
+            Renderer = ref_ext.renderer_class(args.variant)
+
+        def step(kf):   # scripts/splatam.py:226-353 (get_loss) with the restated glue
+            cur = targets[kf]
+            gg, cg = (False, True) if tracking else (True, False)
+            tg = SO.transform_to_frame(params, kf, gg, cg)
+            rv = SO.transformed_params2rendervar(params, tg)
+            rv["means2D"] = torch.zeros_like(params["means3D"], requires_grad=True) + 0
+            rv["means2D"].retain_grad()
+            im, radius, _ = Renderer(cur["cam"])(**rv)
+            variables["means2D"] = rv["means2D"]
+            rv2 = dict(rv)
+            rv2["colors_precomp"] = SO.get_depth_and_silhouette(tg["means3D"], cur["w2c"])
+            rv2["means2D"] = torch.zeros_like(params["means3D"], requires_grad=True) + 0
+            ds, _, _ = Renderer(cur["cam"])(**rv2)
+            loss, wl = SO.image_loss(im, ds, cur["im"], cur["depth"], wts, tracking, sil_thres, True, False, tracking)
+            seen = radius > 0
+            variables["max_2D_radius"][seen] = torch.max(radius[seen], variables["max_2D_radius"][seen])
+            variables["seen"] = seen
+            loss.backward()
+            return loss
+
+    def zero():
+        for v in params.values():
+            v.grad = None
+
+    sampler = bench.ClockSampler(0)
+    sampler.start()
+    for i in range(args.warmup):
+        zero()
+        step(i % nf)
+    torch.cuda.synchronize()
+    l0 = lib.splat_kernel_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.mark_start()
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(args.steps):
+        zero()
+        loss = step((7 * i) % nf)
+    e1.record()
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    sampler.mark_end()
+    ms = e0.elapsed_time(e1)
+    launches = lib.splat_kernel_launch_count() - l0
+    out = {"metric": "SplaTAM %s iterations/sec (get_loss + backward: builder, RGB + depth + silhouette render, loss)"
+                     % args.mode,
+           "unit": "iters/s", "value": args.steps / (ms * 1e-3), "ms_per_step": ms / args.steps,
+           "wall_ms_per_step": wall * 1e3 / args.steps, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+           "higher_is_better": True, "dtype": "f32", "data": "synthetic", "impl": args.impl,
+           "config": {"workload": "replica_1200x680_%s_%s" % ("300k" if tracking else "1M", args.mode),
+                      "image": [cam["w"], cam["h"]], "gaussians": P, "keyframes": nf,
+                      "variant": args.variant if args.impl == "reference" else "dg",
+                      "loss": "tracking: masked summed L1, sil_thres 0.99" if tracking else
+                              "mapping: 0.8 L1 + 0.2 (1-SSIM 11x11) colour, masked mean L1 depth"},
+           "gpu_launches": launches, "last_loss": float(loss.detach()), "clocks": sampler.stop()}
+    if args.impl == "ours":   # per-kernel event times from a second pass (kept out of the timed region)
+        import ctypes as C
+        lib.splat_profile_enable(1)
+        for i in range(args.steps):
+            zero()
+            step((7 * i) % nf)
+        n = 16
+        ms_sum = (C.c_float * n)(); cnt = (C.c_int32 * n)()
+        lib.splat_profile_read(ms_sum, cnt, n)
+        lib.splat_profile_enable(0)
+        names = [lib.splat_profile_kernel_name(k).decode() for k in range(n)]
+        out["kernel_ms_per_step"] = {names[k]: round(ms_sum[k] / args.steps, 5) for k in range(n) if cnt[k]}
+        N = cam["w"] * cam["h"]
+        sd = 1
+        # algorithmic HBM bytes of the glue kernels
+        rv_f = (12 + 16 + 4 + 4 * sd) + (12 + 16 + 4 + 12)
+        rv_b = (24 if tracking else 12 + 12 + 16 + 16 + 16) + (4 + 4 + 4) + (12 + 4 + 4 * sd)
+        loss_b = (40 + 24) if tracking else (6 * 4 + 9 * 4) + (9 * 4 + 6 * 4 + 6 * 4) + 16 + 12
+        peaks, src = bench.measured_peaks()
+        roof = {}
+        for name, byt in (("rendervar_fwd", rv_f * P), ("rendervar_bwd", rv_b * P), ("slam_loss", loss_b * N)):
+            t = out["kernel_ms_per_step"].get(name)
+            if t:
+                roof[name] = {"bound": "hbm", "algorithmic_bytes": byt, "achieved": byt / (t * 1e-3) / 1e9,
+                              "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": byt / (t * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                              "kernel_ms": t}
+        out["roofline_glue"] = roof
+    real_stdout.write(json.dumps(out) + "\n")
+    real_stdout.flush()
+
+
+if __name__ == "__main__":
+    main()

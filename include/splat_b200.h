@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define SPLAT_ABI_VERSION 3
+#define SPLAT_ABI_VERSION 4
 
 /* Error codes.  Positive values >= 1000 are 1000 + cudaError_t of a failed runtime call. */
 enum {
@@ -151,6 +151,62 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R,
 /* ---- markVisible (HX/cuda_rasterizer/rasterizer_impl.cu:54-66,141-153) ---------------------- */
 int splat_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
                        const float* projmatrix, float near_plane, uint8_t* present, void* stream);
+
+/* ---- SplaTAM glue around the rasterizer (ABI v4) -------------------------
+ * The reference runs these steps as ~45 small PyTorch kernels + autograd nodes per optimisation
+ * iteration; here each is one HBM-bound kernel (plus a one-block finalize).  All reductions are
+ * two-stage and deterministic.
+ *
+ * splat_rendervar_forward  <-  transform_to_frame + transformed_params2rendervar
+ *      (utils/slam_helpers.py:253-304, :123-139; build_rotation utils/slam_external.py:25-42):
+ *      out_means3D = R(q) p + t with q = normalize(cam_unnorm_rots[0,:,time_idx]), t = cam_trans[0,:,time_idx];
+ *      out_rotations = normalize(unnorm_rotations)                           (scale_dim == 1, isotropic)
+ *                    = normalize(quat_mult(q, normalize(unnorm_rotations)))  (scale_dim == 3);
+ *      out_opacities = sigmoid(logit_opacities); out_scales[P,3] = exp(log_scales) (tiled when scale_dim == 1).
+ *      colors_precomp is params['rgb_colors'] itself (no kernel).  cam_* are the full [1,4,F] / [1,3,F] tensors.
+ * splat_rendervar_backward <-  the autograd graph of the above.  dL_d{means3D_cam, rotations, opacities, scales}
+ *      are the rasterizer's gradients (any may be NULL == zero).  gaussians_grad / camera_grad are
+ *      transform_to_frame's flags: with gaussians_grad the four Gaussian-side gradients are written
+ *      ([P,3], [P,4], [P,1], [P,scale_dim]); with camera_grad the pose gradient -- the sum over ALL Gaussians of
+ *      dL/dp' and dL/dp' (x) p, chained through build_rotation and both normalisations -- is written into column
+ *      time_idx of dL_dcam_unnorm_rots [1,4,F] / dL_dcam_trans [1,3,F] (other columns untouched).
+ *      NOTE the reference detaches means3D AND unnorm_rotations when gaussians_grad is false, but opacity,
+ *      scale and colour gradients still flow (slam_helpers.py:282-288 vs :133-136): dL_dlogit_opacities and
+ *      dL_dlog_scales are written whenever their pointers are non-NULL. */
+int splat_rendervar_forward(int32_t P, int32_t scale_dim,
+                            const float* means3D, const float* unnorm_rotations, const float* logit_opacities,
+                            const float* log_scales, const float* cam_unnorm_rots, const float* cam_trans,
+                            int32_t n_frames, int32_t time_idx,
+                            float* out_means3D, float* out_rotations, float* out_opacities, float* out_scales,
+                            void* stream);
+size_t splat_rendervar_scratch_bytes(int32_t P);
+int splat_rendervar_backward(int32_t P, int32_t scale_dim,
+                             const float* means3D, const float* unnorm_rotations, const float* logit_opacities,
+                             const float* log_scales, const float* cam_unnorm_rots, const float* cam_trans,
+                             int32_t n_frames, int32_t time_idx,
+                             const float* dL_dmeans3D_cam, const float* dL_drotations, const float* dL_dopacities,
+                             const float* dL_dscales, int32_t gaussians_grad, int32_t camera_grad,
+                             float* dL_dmeans3D, float* dL_dunnorm_rotations, float* dL_dlogit_opacities,
+                             float* dL_dlog_scales, float* dL_dcam_unnorm_rots, float* dL_dcam_trans,
+                             void* scratch, size_t scratch_bytes, void* stream);
+
+/* splat_slam_loss  <-  the image-space part of get_loss (scripts/splatam.py:262-296,342-346) with
+ *      use_l1 = True and ignore_outlier_depth_loss = False (every shipped config): loss AND its gradient
+ *      w.r.t. the two rendered images in one call.
+ *      im [3,H,W] / depth_sil [3,H,W] = (depth, silhouette, depth^2) are the two Renderer outputs (or planes
+ *      0-2 / 3-5 of the fused render).  mask = gt_depth > 0 & !isnan(depth) & !isnan(depth^2 - depth*depth)
+ *      [& silhouette > sil_thres when tracking && use_sil_for_loss].
+ *      tracking != 0: losses = (w_im * sum_mask |gt_im - im|, w_depth * sum_mask |gt_depth - depth|, total, count)
+ *      tracking == 0: losses = (w_im * (0.8 mean|im - gt_im| + 0.2 (1 - SSIM_11x11(im, gt_im))),
+ *                               w_depth * mean_mask |gt_depth - depth|, total, count)
+ *      (calc_ssim, utils/slam_external.py:54-97).  `losses` is a device float[4].  dL_dim / dL_ddepth_sil are fully
+ *      written (planes 1 and 2 of dL_ddepth_sil are zero: silhouette only enters the mask, uncertainty is detached). */
+size_t splat_slam_loss_scratch_bytes(int32_t width, int32_t height, int32_t tracking);
+int splat_slam_loss(int32_t width, int32_t height, int32_t tracking, int32_t use_sil_for_loss, float sil_thres,
+                    float w_im, float w_depth,
+                    const float* im, const float* depth_sil, const float* gt_im, const float* gt_depth,
+                    float* losses, float* dL_dim, float* dL_ddepth_sil,
+                    void* scratch, size_t scratch_bytes, void* stream);
 
 /* ---- multi-GPU exchange (new; the reference is single-GPU, configs/replica/splatam.py:8) -------
  * Sum of one flat float32 bucket over the `world` ranks of one NVSwitch node, in place, on `stream`.

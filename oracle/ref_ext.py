@@ -97,3 +97,38 @@ def binning_point_list(fwd):
     base = buf.data_ptr()
     o0 = (base + 127) // 128 * 128 - base
     return buf[o0:o0 + 4 * R].view(torch.int32)
+
+
+class _RefRasterize(torch.autograd.Function):
+    """autograd edge around the reference extension's two pybind calls -- what the reference's own
+    `_RasterizeGaussians` does (HX/hessian_diff_gaussian_rasterization_w_depth/__init__.py:44-138), restated on
+    the wrappers above so that the reference's SplaTAM iteration (torch glue + two renders) can be run and timed
+    on the GPU box, where /root/reference does not exist."""
+    @staticmethod
+    def forward(ctx, variant, rs, means3D, means2D, colors_precomp, opacities, scales, rotations):
+        f = forward(variant, rs, means3D.contiguous(), colors_precomp.contiguous(), opacities.contiguous(),
+                    scales.contiguous(), rotations.contiguous())
+        ctx.f = f
+        ctx.mark_non_differentiable(f["radii"], f["depth"])
+        return f["color"], f["radii"], f["depth"]
+
+    @staticmethod
+    def backward(ctx, g_color, _r, _d):
+        g = backward(ctx.f, g_color.contiguous(), 1)
+        ctx.f = None
+        return None, None, g["means3D"], g["means2D"], g["colors"], g["opacities"], g["scales"], g["rotations"]
+
+
+class RefRenderer:
+    """`Renderer(raster_settings=cam)(**rendervar)` of scripts/splatam.py:255 on the unmodified reference extension."""
+    variant = "dg"   # scripts/splatam.py:37 imports diff_gaussian_rasterization
+
+    def __init__(self, raster_settings):
+        self.rs = raster_settings
+
+    def __call__(self, means3D, means2D, opacities, colors_precomp, scales, rotations):
+        return _RefRasterize.apply(self.variant, self.rs, means3D, means2D, colors_precomp, opacities, scales, rotations)
+
+
+def renderer_class(variant):
+    return type("RefRenderer_%s" % variant, (RefRenderer,), {"variant": variant})

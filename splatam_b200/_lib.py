@@ -49,6 +49,15 @@ _SIGNATURES = {
     "splat_state_point_list": (_P, [_P, C.c_int32, C.c_int32, C.c_int64]),
     "splat_state_gaussian_records": (_P, [_P, C.c_int32]),
     "splat_state_instance_records": (_P, [_P, C.c_int32, C.c_int32, C.c_int64]),
+    "splat_rendervar_forward": (C.c_int, [C.c_int32, C.c_int32, _P, _P, _P, _P, _P, _P, C.c_int32, C.c_int32,
+                                          _P, _P, _P, _P, _P]),
+    "splat_rendervar_scratch_bytes": (C.c_size_t, [C.c_int32]),
+    "splat_rendervar_backward": (C.c_int, [C.c_int32, C.c_int32, _P, _P, _P, _P, _P, _P, C.c_int32, C.c_int32,
+                                           _P, _P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P, _P, _P, _P,
+                                           _P, C.c_size_t, _P]),
+    "splat_slam_loss_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
+    "splat_slam_loss": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_float,
+                                  _P, _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "splat_peer_allreduce_sum": (C.c_int, [_P, _P, C.c_uint64, C.c_int32, C.c_int32, C.c_uint32, C.c_int64, _P]),
     "splat_profile_enable": (C.c_int, [C.c_int]),
     "splat_profile_read": (C.c_int, [_P, _P, C.c_int32]),
@@ -75,7 +84,7 @@ def _load():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing: intended
         fn.restype = res
         fn.argtypes = args
-    if lib.splat_abi_version() != 3:
+    if lib.splat_abi_version() != 4:
         raise ImportError("libsplat_b200.so ABI version mismatch")
     return lib
 

@@ -1,5 +1,6 @@
 // api.cu -- the extern "C" boundary declared in include/splat_b200.h.
 // Argument validation, state carving and kernel sequencing only; no device allocation.
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -334,8 +335,107 @@ int splat_profile_read_gaps(float* gap_ms_sum, int32_t n) {
 }
 const char* splat_profile_kernel_name(int k) {
   static const char* names[K_COUNT] = {"preprocess_fwd", "tile_scan", "scatter", "tile_sort", "render_fwd",
-                                       "render_bwd", "preprocess_bwd", "hessian_finalize", "emit_records"};
+                                       "render_bwd", "preprocess_bwd", "hessian_finalize", "emit_records",
+                                       "rendervar_fwd", "rendervar_bwd", "slam_loss"};
   return (k >= 0 && k < K_COUNT) ? names[k] : "";
+}
+
+// ---- SplaTAM glue -------------------------------------------------------------
+static int check_rv(int32_t P, int32_t scale_dim, const float* means3D, const float* unnorm_rotations,
+                    const float* logit_opacities, const float* log_scales, const float* cam_unnorm_rots,
+                    const float* cam_trans, int32_t n_frames, int32_t time_idx) {
+  if (P < 0) return fail(SPLAT_ERR_BAD_ARG, "P < 0");
+  if (scale_dim != 1 && scale_dim != 3) return fail(SPLAT_ERR_BAD_ARG, "log_scales must have 1 or 3 columns, got %d", scale_dim);
+  if (!cam_unnorm_rots || !cam_trans) return fail(SPLAT_ERR_BAD_ARG, "cam_unnorm_rots/cam_trans must be non-NULL");
+  if (n_frames <= 0 || time_idx < 0 || time_idx >= n_frames)
+    return fail(SPLAT_ERR_BAD_ARG, "time_idx %d out of range for %d frames", time_idx, n_frames);
+  if (P > 0 && (!means3D || !unnorm_rotations || !logit_opacities || !log_scales))
+    return fail(SPLAT_ERR_BAD_ARG, "means3D/unnorm_rotations/logit_opacities/log_scales must be non-NULL");
+  if ((uintptr_t)unnorm_rotations & 15) return fail(SPLAT_ERR_BAD_ARG, "unnorm_rotations must be 16-byte aligned");
+  return SPLAT_OK;
+}
+
+int splat_rendervar_forward(int32_t P, int32_t scale_dim, const float* means3D, const float* unnorm_rotations,
+                            const float* logit_opacities, const float* log_scales, const float* cam_unnorm_rots,
+                            const float* cam_trans, int32_t n_frames, int32_t time_idx, float* out_means3D,
+                            float* out_rotations, float* out_opacities, float* out_scales, void* stream) {
+  if (int rc = check_rv(P, scale_dim, means3D, unnorm_rotations, logit_opacities, log_scales, cam_unnorm_rots,
+                        cam_trans, n_frames, time_idx)) return rc;
+  if (P > 0 && (!out_means3D || !out_rotations || !out_opacities || !out_scales))
+    return fail(SPLAT_ERR_BAD_ARG, "rendervar outputs must be non-NULL");
+  if ((uintptr_t)out_rotations & 15) return fail(SPLAT_ERR_BAD_ARG, "out_rotations must be 16-byte aligned");
+  RvArgs a = {};
+  a.P = P; a.aniso = scale_dim == 3; a.n_frames = n_frames; a.t = time_idx;
+  a.means = means3D; a.unnorm_rots = unnorm_rotations; a.logit_op = logit_opacities; a.log_scales = log_scales;
+  a.cam_rots = cam_unnorm_rots; a.cam_trans = cam_trans;
+  a.o_means = out_means3D; a.o_rots = out_rotations; a.o_op = out_opacities; a.o_scales = out_scales;
+  return launch_rendervar_fwd(a, (cudaStream_t)stream);
+}
+
+size_t splat_rendervar_scratch_bytes(int32_t P) { return align_up((size_t)rendervar_bwd_blocks(P) * 16 * sizeof(float)); }
+
+int splat_rendervar_backward(int32_t P, int32_t scale_dim, const float* means3D, const float* unnorm_rotations,
+                             const float* logit_opacities, const float* log_scales, const float* cam_unnorm_rots,
+                             const float* cam_trans, int32_t n_frames, int32_t time_idx,
+                             const float* dL_dmeans3D_cam, const float* dL_drotations, const float* dL_dopacities,
+                             const float* dL_dscales, int32_t gaussians_grad, int32_t camera_grad,
+                             float* dL_dmeans3D, float* dL_dunnorm_rotations, float* dL_dlogit_opacities,
+                             float* dL_dlog_scales, float* dL_dcam_unnorm_rots, float* dL_dcam_trans,
+                             void* scratch, size_t scratch_bytes, void* stream) {
+  if (int rc = check_rv(P, scale_dim, means3D, unnorm_rotations, logit_opacities, log_scales, cam_unnorm_rots,
+                        cam_trans, n_frames, time_idx)) return rc;
+  if (gaussians_grad && P > 0 && (!dL_dmeans3D || !dL_dunnorm_rotations))
+    return fail(SPLAT_ERR_BAD_ARG, "gaussians_grad needs dL_dmeans3D and dL_dunnorm_rotations");
+  if (camera_grad && (!dL_dcam_unnorm_rots || !dL_dcam_trans))
+    return fail(SPLAT_ERR_BAD_ARG, "camera_grad needs dL_dcam_unnorm_rots and dL_dcam_trans");
+  if (camera_grad && (!scratch || scratch_bytes < splat_rendervar_scratch_bytes(P)))
+    return fail(SPLAT_ERR_SCRATCH_TOO_SMALL, "rendervar scratch needs %zu bytes", splat_rendervar_scratch_bytes(P));
+  if (((uintptr_t)dL_drotations & 15) || ((uintptr_t)dL_dunnorm_rotations & 15))
+    return fail(SPLAT_ERR_BAD_ARG, "rotation gradients must be 16-byte aligned");
+  RvArgs a = {};
+  a.P = P; a.aniso = scale_dim == 3; a.n_frames = n_frames; a.t = time_idx;
+  a.means = means3D; a.unnorm_rots = unnorm_rotations; a.logit_op = logit_opacities; a.log_scales = log_scales;
+  a.cam_rots = cam_unnorm_rots; a.cam_trans = cam_trans;
+  a.g_means = dL_dmeans3D_cam; a.g_rots = dL_drotations; a.g_op = dL_dopacities; a.g_scales = dL_dscales;
+  a.d_means = dL_dmeans3D; a.d_unnorm_rots = dL_dunnorm_rotations; a.d_logit = dL_dlogit_opacities;
+  a.d_logscales = dL_dlog_scales; a.d_cam_rots = dL_dcam_unnorm_rots; a.d_cam_trans = dL_dcam_trans;
+  return launch_rendervar_bwd(a, gaussians_grad != 0, camera_grad != 0, (float*)scratch, (cudaStream_t)stream);
+}
+
+// scratch = [partials: blocks x 4 floats][stats: 4 floats (256 B)][mapping only: 9 derivative planes]
+static size_t loss_partial_bytes(int32_t W, int32_t H) {
+  const int nb_t = slam_loss_blocks(W, H, 1), nb_m = slam_loss_blocks(W, H, 0);
+  return align_up((size_t)(nb_t > nb_m ? nb_t : nb_m) * 4 * sizeof(float));
+}
+size_t splat_slam_loss_scratch_bytes(int32_t W, int32_t H, int32_t tracking) {
+  if (W <= 0 || H <= 0) return 0;
+  return loss_partial_bytes(W, H) + 256 + (tracking ? 0 : align_up((size_t)9 * W * H * sizeof(float)));
+}
+
+int splat_slam_loss(int32_t W, int32_t H, int32_t tracking, int32_t use_sil_for_loss, float sil_thres, float w_im,
+                    float w_depth, const float* im, const float* depth_sil, const float* gt_im, const float* gt_depth,
+                    float* losses, float* dL_dim, float* dL_ddepth_sil, void* scratch, size_t scratch_bytes,
+                    void* stream) {
+  if (W <= 0 || H <= 0) return fail(SPLAT_ERR_BAD_ARG, "bad image size %dx%d", W, H);
+  if (!im || !depth_sil || !gt_im || !gt_depth || !losses || !dL_dim || !dL_ddepth_sil)
+    return fail(SPLAT_ERR_BAD_ARG, "image / loss / gradient pointers must be non-NULL");
+  if (!scratch || scratch_bytes < splat_slam_loss_scratch_bytes(W, H, tracking))
+    return fail(SPLAT_ERR_SCRATCH_TOO_SMALL, "loss scratch needs %zu bytes", splat_slam_loss_scratch_bytes(W, H, tracking));
+  LossArgs a = {};
+  a.W = W; a.H = H; a.tracking = tracking != 0; a.use_sil = (tracking != 0) && (use_sil_for_loss != 0);
+  a.sil_thres = sil_thres; a.w_im = w_im; a.w_depth = w_depth;
+  {  // gaussian(11, 1.5) exactly as the reference builds it: float32 tensor of exp(...) divided by its float32 sum
+    float g[11], sum = 0.f;
+    for (int x = 0; x < 11; ++x) { g[x] = (float)exp(-(double)((x - 5) * (x - 5)) / (2.0 * 1.5 * 1.5)); sum += g[x]; }
+    for (int x = 0; x < 11; ++x) a.gauss[x] = g[x] / sum;
+  }
+  a.im = im; a.depth_sil = depth_sil; a.gt_im = gt_im; a.gt_depth = gt_depth;
+  a.losses = losses; a.g_im = dL_dim; a.g_depth_sil = dL_ddepth_sil;
+  char* c = (char*)scratch;
+  float* partial = (float*)c; c += loss_partial_bytes(W, H);
+  float* stats = (float*)c;   c += 256;
+  a.dmaps = tracking ? nullptr : (float*)c;
+  return launch_slam_loss(a, partial, stats, (cudaStream_t)stream);
 }
 
 int splat_abi_version(void) { return SPLAT_ABI_VERSION; }

@@ -59,6 +59,31 @@ struct RenderBwdArgs {
   float* acc;   // MODE 0: [P,12] raw sums.  MODE 1: [P,20] moment accumulator.  Pre-zeroed.
 };
 
+// SplaTAM glue (slam_ops.cu).  Render-variable builder: forward outputs o_*, backward inputs g_* (any may be NULL ==
+// zero), Gaussian-side gradients d_* and the pose gradient columns d_cam_*[:, :, t].
+struct RvArgs {
+  int P, aniso, n_frames, t;
+  const float* means; const float* unnorm_rots; const float* logit_op; const float* log_scales;
+  const float* cam_rots; const float* cam_trans;       // [1,4,F], [1,3,F]
+  float* o_means; float* o_rots; float* o_op; float* o_scales;
+  const float* g_means; const float* g_rots; const float* g_op; const float* g_scales;
+  float* d_means; float* d_unnorm_rots; float* d_logit; float* d_logscales;
+  float* d_cam_rots; float* d_cam_trans;
+};
+struct LossArgs {
+  int W, H, tracking, use_sil;
+  float sil_thres, w_im, w_depth;
+  float gauss[11];                                      // utils/slam_external.py:54-56
+  const float* im; const float* depth_sil; const float* gt_im; const float* gt_depth;
+  float* losses; float* g_im; float* g_depth_sil;
+  float* dmaps;                                         // [3 maps][3 ch][H][W] mapping loss only
+};
+int rendervar_bwd_blocks(int P);
+int launch_rendervar_fwd(const RvArgs& a, cudaStream_t st);
+int launch_rendervar_bwd(const RvArgs& a, bool gg, bool cg, float* partial, cudaStream_t st);
+int slam_loss_blocks(int W, int H, int tracking);
+int launch_slam_loss(const LossArgs& a, float* partial, float* stats, cudaStream_t st);
+
 int launch_preprocess_fwd(const PreFwdArgs& a, cudaStream_t st);
 int launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t st);
 int launch_hessian_finalize(const HessArgs& a, cudaStream_t st);

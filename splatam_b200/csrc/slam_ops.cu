@@ -1,0 +1,486 @@
+// slam_ops.cu -- the per-iteration glue SplaTAM runs in PyTorch on either side of the rasterizer
+// (SURVEY.md 8f-2 / 8f-3), as five HBM-bound kernels:
+//   rendervar_fwd / rendervar_bwd (+ pose_finalize)  <-  transform_to_frame + transformed_params2rendervar
+//        (utils/slam_helpers.py:253-304, :123-139; build_rotation utils/slam_external.py:25-42) and the
+//        autograd graph torch builds for them (cat, matmul, normalize, quat_mult, sigmoid, exp, tile);
+//        the camera-pose gradient (sum over all Gaussians of dL/dp' and dL/dp' (x) p) is reduced in-kernel;
+//   track_loss                                        <-  get_loss(tracking=True), scripts/splatam.py:262-285
+//   map_loss_fwd / map_loss_bwd (+ loss_finalize)     <-  get_loss(mapping=True): masked L1 depth mean +
+//        0.8 L1 + 0.2 (1 - SSIM) colour (scripts/splatam.py:279-296, utils/slam_external.py:54-97), producing
+//        dL/d(im, depth_sil) directly -- what torch autograd computes through five 11x11 convolutions.
+// All reductions are two-stage and deterministic (per-block partials, then one block).
+#include "kernels.cuh"
+
+namespace splat {
+
+// ------------------------------------------------------------------------------------------------ pose
+struct Pose {
+  float q1[4];   // F.normalize(cam_unnorm_rots[..., t])  (eps 1e-12)        slam_helpers.py:268
+  float q2[4];   // q1 / |q1|                                                 slam_external.py:26-27
+  float n0, n1;  // |u|, |q1|
+  float R[9];    // row-major rotation of q2                                  slam_external.py:33-41
+  float t[3];
+};
+
+__device__ __forceinline__ Pose load_pose(const float* cam_rots, const float* cam_trans, int F, int t) {
+  Pose p;
+  float u[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) u[k] = cam_rots[k * F + t];
+  p.n0 = sqrtf(u[0] * u[0] + u[1] * u[1] + u[2] * u[2] + u[3] * u[3]);
+  const float d0 = fmaxf(p.n0, 1e-12f);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) p.q1[k] = u[k] / d0;
+  p.n1 = sqrtf(p.q1[0] * p.q1[0] + p.q1[1] * p.q1[1] + p.q1[2] * p.q1[2] + p.q1[3] * p.q1[3]);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) p.q2[k] = p.q1[k] / p.n1;
+  const float r = p.q2[0], x = p.q2[1], y = p.q2[2], z = p.q2[3];
+  p.R[0] = 1.f - 2.f * (y * y + z * z); p.R[1] = 2.f * (x * y - r * z);       p.R[2] = 2.f * (x * z + r * y);
+  p.R[3] = 2.f * (x * y + r * z);       p.R[4] = 1.f - 2.f * (x * x + z * z); p.R[5] = 2.f * (y * z - r * x);
+  p.R[6] = 2.f * (x * z - r * y);       p.R[7] = 2.f * (y * z + r * x);       p.R[8] = 1.f - 2.f * (x * x + y * y);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) p.t[k] = cam_trans[k * F + t];
+  return p;
+}
+
+// F.normalize of a 4-vector: v / max(|v|, 1e-12); returns |v|
+__device__ __forceinline__ float normalize4(const float4 v, float4& o) {
+  const float n = sqrtf(v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w);
+  const float d = fmaxf(n, 1e-12f);
+  o = make_float4(v.x / d, v.y / d, v.z / d, v.w / d);
+  return n;
+}
+// backward of o = v / max(|v|, eps) given o, |v|
+__device__ __forceinline__ float4 normalize4_bwd(const float4 o, const float n, const float4 g) {
+  if (n < 1e-12f) return make_float4(g.x / 1e-12f, g.y / 1e-12f, g.z / 1e-12f, g.w / 1e-12f);
+  const float dot = o.x * g.x + o.y * g.y + o.z * g.z + o.w * g.w;
+  const float inv = 1.f / n;
+  return make_float4((g.x - o.x * dot) * inv, (g.y - o.y * dot) * inv, (g.z - o.z * dot) * inv, (g.w - o.w * dot) * inv);
+}
+// m = c (x) n, Hamilton product in (w,x,y,z) order (slam_helpers.py:21-28)
+__device__ __forceinline__ float4 quat_mul(const float* c, const float4 n) {
+  return make_float4(c[0] * n.x - c[1] * n.y - c[2] * n.z - c[3] * n.w,
+                     c[0] * n.y + c[1] * n.x + c[2] * n.w - c[3] * n.z,
+                     c[0] * n.z - c[1] * n.w + c[2] * n.x + c[3] * n.y,
+                     c[0] * n.w + c[1] * n.z - c[2] * n.y + c[3] * n.x);
+}
+
+// ------------------------------------------------------------------------------------------------ builder fwd
+__global__ void __launch_bounds__(256) rendervar_fwd_kernel(const RvArgs a) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= a.P) return;
+  const Pose ps = load_pose(a.cam_rots, a.cam_trans, a.n_frames, a.t);
+  const float px = a.means[3 * i], py = a.means[3 * i + 1], pz = a.means[3 * i + 2];
+  const float4 q = reinterpret_cast<const float4*>(a.unnorm_rots)[i];
+  const float lo = a.logit_op[i];
+  float ls[3];
+  if (a.aniso) { ls[0] = a.log_scales[3 * i]; ls[1] = a.log_scales[3 * i + 1]; ls[2] = a.log_scales[3 * i + 2]; }
+  else { ls[0] = ls[1] = ls[2] = a.log_scales[i]; }
+  a.o_means[3 * i + 0] = ps.R[0] * px + ps.R[1] * py + ps.R[2] * pz + ps.t[0];
+  a.o_means[3 * i + 1] = ps.R[3] * px + ps.R[4] * py + ps.R[5] * pz + ps.t[1];
+  a.o_means[3 * i + 2] = ps.R[6] * px + ps.R[7] * py + ps.R[8] * pz + ps.t[2];
+  float4 n, o;
+  normalize4(q, n);
+  if (a.aniso) { normalize4(quat_mul(ps.q1, n), o); } else { o = n; }
+  reinterpret_cast<float4*>(a.o_rots)[i] = o;
+  a.o_op[i] = 1.f / (1.f + expf(-lo));
+#pragma unroll
+  for (int k = 0; k < 3; ++k) a.o_scales[3 * i + k] = expf(ls[k]);
+}
+
+// ------------------------------------------------------------------------------------------------ builder bwd
+#define RV_SUMS 16   // 0..2 sum dL/dp' | 3..11 sum dL/dp' (x) p (row-major) | 12..15 sum dL/dq1 through quat_mult
+
+template <bool GG, bool CG, bool ANISO>
+__global__ void __launch_bounds__(256) rendervar_bwd_kernel(const RvArgs a, float* __restrict__ partial) {
+  const Pose ps = load_pose(a.cam_rots, a.cam_trans, a.n_frames, a.t);
+  float s[RV_SUMS];
+#pragma unroll
+  for (int k = 0; k < RV_SUMS; ++k) s[k] = 0.f;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < a.P; i += gridDim.x * 256) {
+    float gx = 0.f, gy = 0.f, gz = 0.f;
+    if (a.g_means) { gx = a.g_means[3 * i]; gy = a.g_means[3 * i + 1]; gz = a.g_means[3 * i + 2]; }
+    if (CG) {
+      const float px = a.means[3 * i], py = a.means[3 * i + 1], pz = a.means[3 * i + 2];
+      s[0] += gx; s[1] += gy; s[2] += gz;
+      s[3] += gx * px; s[4] += gx * py; s[5] += gx * pz;
+      s[6] += gy * px; s[7] += gy * py; s[8] += gy * pz;
+      s[9] += gz * px; s[10] += gz * py; s[11] += gz * pz;
+    }
+    if (GG) {
+      a.d_means[3 * i + 0] = ps.R[0] * gx + ps.R[3] * gy + ps.R[6] * gz;
+      a.d_means[3 * i + 1] = ps.R[1] * gx + ps.R[4] * gy + ps.R[7] * gz;
+      a.d_means[3 * i + 2] = ps.R[2] * gx + ps.R[5] * gy + ps.R[8] * gz;
+    }
+    if (a.d_logit) {   // opacity / scale gradients flow even when gaussians_grad is false (slam_helpers.py:133-136)
+      const float sg = 1.f / (1.f + expf(-a.logit_op[i]));
+      a.d_logit[i] = a.g_op ? a.g_op[i] * sg * (1.f - sg) : 0.f;
+    }
+    if (a.d_logscales) {
+      float g3[3] = {0.f, 0.f, 0.f};
+      if (a.g_scales) { g3[0] = a.g_scales[3 * i]; g3[1] = a.g_scales[3 * i + 1]; g3[2] = a.g_scales[3 * i + 2]; }
+      if (ANISO) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) a.d_logscales[3 * i + k] = g3[k] * expf(a.log_scales[3 * i + k]);
+      } else {
+        a.d_logscales[i] = (g3[0] + g3[1] + g3[2]) * expf(a.log_scales[i]);
+      }
+    }
+    if (GG || (CG && ANISO)) {
+      const float4 q = reinterpret_cast<const float4*>(a.unnorm_rots)[i];
+      float4 g = a.g_rots ? reinterpret_cast<const float4*>(a.g_rots)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 n;
+      const float nq = normalize4(q, n);
+      if (ANISO) {
+        const float4 m = quat_mul(ps.q1, n);
+        float4 o;
+        const float nm = normalize4(m, o);
+        const float4 dm = normalize4_bwd(o, nm, g);
+        const float* c = ps.q1;
+        if (CG) {
+          s[12] += n.x * dm.x + n.y * dm.y + n.z * dm.z + n.w * dm.w;
+          s[13] += -n.y * dm.x + n.x * dm.y - n.w * dm.z + n.z * dm.w;
+          s[14] += -n.z * dm.x + n.w * dm.y + n.x * dm.z - n.y * dm.w;
+          s[15] += -n.w * dm.x - n.z * dm.y + n.y * dm.z + n.x * dm.w;
+        }
+        g = make_float4(c[0] * dm.x + c[1] * dm.y + c[2] * dm.z + c[3] * dm.w,
+                        -c[1] * dm.x + c[0] * dm.y + c[3] * dm.z - c[2] * dm.w,
+                        -c[2] * dm.x - c[3] * dm.y + c[0] * dm.z + c[1] * dm.w,
+                        -c[3] * dm.x + c[2] * dm.y - c[1] * dm.z + c[0] * dm.w);
+      }
+      if (GG) reinterpret_cast<float4*>(a.d_unnorm_rots)[i] = normalize4_bwd(n, nq, g);
+    }
+  }
+  if (CG) {
+    __shared__ float red[8][RV_SUMS];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < RV_SUMS; ++k) {
+      float v = s[k];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) red[w][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < RV_SUMS) {
+      float v = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v += red[j][threadIdx.x];
+      partial[blockIdx.x * RV_SUMS + threadIdx.x] = v;
+    }
+  }
+}
+
+// One block: sums the per-block partials (double), then runs the 7-scalar chain
+// dR, dt, dq1 -> cam_unnorm_rots[:, :, t], cam_trans[:, :, t].
+__global__ void __launch_bounds__(512) pose_finalize_kernel(const RvArgs a, const float* __restrict__ partial, int nblk) {
+  __shared__ double S[RV_SUMS];
+  const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;   // 16 warps, one per sum
+  double v = 0.0;
+  for (int b = lane; b < nblk; b += 32) v += (double)partial[b * RV_SUMS + k];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if (lane == 0) S[k] = v;
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  const Pose ps = load_pose(a.cam_rots, a.cam_trans, a.n_frames, a.t);
+  const double r = ps.q2[0], x = ps.q2[1], y = ps.q2[2], z = ps.q2[3];
+  const double* G = &S[3];   // G[3*row+col] = dL/dR[row][col]
+  double d2[4];
+  d2[0] = 2.0 * (-z * G[1] + y * G[2] + z * G[3] - x * G[5] - y * G[6] + x * G[7]);
+  d2[1] = 2.0 * (y * G[1] + z * G[2] + y * G[3] - 2.0 * x * G[4] - r * G[5] + z * G[6] + r * G[7] - 2.0 * x * G[8]);
+  d2[2] = 2.0 * (-2.0 * y * G[0] + x * G[1] + r * G[2] + x * G[3] + z * G[5] - r * G[6] + z * G[7] - 2.0 * y * G[8]);
+  d2[3] = 2.0 * (-2.0 * z * G[0] - r * G[1] + x * G[2] + r * G[3] - 2.0 * z * G[4] + y * G[5] + x * G[6] + y * G[7]);
+  // q2 = q1 / |q1|
+  double dot = 0.0;
+  for (int j = 0; j < 4; ++j) dot += (double)ps.q2[j] * d2[j];
+  double d1[4];
+  for (int j = 0; j < 4; ++j) d1[j] = (d2[j] - (double)ps.q2[j] * dot) / (double)ps.n1 + S[12 + j];
+  // q1 = u / max(|u|, eps)
+  double du[4];
+  if (ps.n0 < 1e-12f) {
+    for (int j = 0; j < 4; ++j) du[j] = d1[j] / 1e-12;
+  } else {
+    dot = 0.0;
+    for (int j = 0; j < 4; ++j) dot += (double)ps.q1[j] * d1[j];
+    for (int j = 0; j < 4; ++j) du[j] = (d1[j] - (double)ps.q1[j] * dot) / (double)ps.n0;
+  }
+  for (int j = 0; j < 4; ++j) a.d_cam_rots[j * a.n_frames + a.t] = (float)du[j];
+  for (int j = 0; j < 3; ++j) a.d_cam_trans[j * a.n_frames + a.t] = (float)S[j];
+}
+
+int rendervar_bwd_blocks(int P) {
+  int nb = (P + 255) / 256;
+  return nb < 1 ? 1 : (nb > 148 * 8 ? 148 * 8 : nb);
+}
+
+int launch_rendervar_fwd(const RvArgs& a, cudaStream_t st) {
+  ProfScope prof_(K_RV_FWD, st);
+  if (a.P <= 0) return SPLAT_OK;
+  rendervar_fwd_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+  SPLAT_LAUNCH_CHECK("rendervar_fwd_kernel");
+  return SPLAT_OK;
+}
+
+int launch_rendervar_bwd(const RvArgs& a, bool gg, bool cg, float* partial, cudaStream_t st) {
+  ProfScope prof_(K_RV_BWD, st);
+  if (!gg && !cg && !a.d_logit && !a.d_logscales) return SPLAT_OK;
+  const int nb = rendervar_bwd_blocks(a.P);
+  if (a.P > 0) {
+#define RV_CASE(G, C, A) rendervar_bwd_kernel<G, C, A><<<nb, 256, 0, st>>>(a, partial)
+    const int key = (gg ? 4 : 0) | (cg ? 2 : 0) | (a.aniso ? 1 : 0);
+    switch (key) {
+      case 0: RV_CASE(false, false, false); break;
+      case 1: RV_CASE(false, false, true); break;
+      case 2: RV_CASE(false, true, false); break;
+      case 3: RV_CASE(false, true, true); break;
+      case 4: RV_CASE(true, false, false); break;
+      case 5: RV_CASE(true, false, true); break;
+      case 6: RV_CASE(true, true, false); break;
+      default: RV_CASE(true, true, true); break;
+    }
+#undef RV_CASE
+    SPLAT_LAUNCH_CHECK("rendervar_bwd_kernel");
+  }
+  if (cg) {
+    pose_finalize_kernel<<<1, 512, 0, st>>>(a, partial, a.P > 0 ? nb : 0);
+    SPLAT_LAUNCH_CHECK("pose_finalize_kernel");
+  }
+  return SPLAT_OK;
+}
+
+// ================================================================================================ losses
+#define LOSS_SUMS 4   // tracking: (sum |dim|, sum |ddepth|, mask count, -)   mapping: (ssim sum, L1 sum, depth sum, count)
+
+__device__ __forceinline__ float sgn(float v) { return (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f); }
+
+__device__ __forceinline__ void block_partials(float (&s)[LOSS_SUMS], float* __restrict__ partial, int block_id) {
+  __shared__ float red[8][LOSS_SUMS];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < LOSS_SUMS; ++k) {
+    float v = s[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) red[w][k] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < LOSS_SUMS) {
+    float v = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v += red[j][threadIdx.x];
+    partial[block_id * LOSS_SUMS + threadIdx.x] = v;
+  }
+}
+
+// mask of scripts/splatam.py:268-280 (ignore_outlier_depth_loss == False)
+__device__ __forceinline__ bool loss_mask(float gt_d, float d, float d2, float sil, bool use_sil, float thres) {
+  const float unc = d2 - d * d;
+  bool m = (gt_d > 0.f) && !isnan(d) && !isnan(unc);
+  if (use_sil) m = m && (sil > thres);
+  return m;
+}
+
+// get_loss(tracking=True): sums over the mask, gradient written in the same pass.
+__global__ void __launch_bounds__(256) track_loss_kernel(const LossArgs a, float* __restrict__ partial) {
+  const int N = a.W * a.H;
+  float s[LOSS_SUMS] = {0.f, 0.f, 0.f, 0.f};
+  for (int p = blockIdx.x * 256 + threadIdx.x; p < N; p += gridDim.x * 256) {
+    const float d = a.depth_sil[p], sil = a.depth_sil[N + p], d2 = a.depth_sil[2 * N + p];
+    const float gd = a.gt_depth[p];
+    const bool m = loss_mask(gd, d, d2, sil, a.use_sil, a.sil_thres);
+    const bool cm = a.use_sil ? m : true;   // colour mask only when use_sil_for_loss (splatam.py:288-293)
+    const float dd = gd - d;
+    s[1] += m ? fabsf(dd) : 0.f;
+    s[2] += m ? 1.f : 0.f;
+    a.g_depth_sil[p] = m ? -a.w_depth * sgn(dd) : 0.f;
+    a.g_depth_sil[N + p] = 0.f;
+    a.g_depth_sil[2 * N + p] = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float di = a.gt_im[c * N + p] - a.im[c * N + p];
+      s[0] += cm ? fabsf(di) : 0.f;
+      a.g_im[c * N + p] = cm ? -a.w_im * sgn(di) : 0.f;
+    }
+  }
+  block_partials(s, partial, blockIdx.x);
+}
+
+// ---- mapping loss: 11x11 Gaussian-window SSIM, separable, 32x32 output tile per CTA and channel
+#define ST 32
+#define SHALO 5
+#define SW (ST + 2 * SHALO)   // 42
+
+__global__ void __launch_bounds__(256) map_loss_fwd_kernel(const LossArgs a, float* __restrict__ partial) {
+  __shared__ float sx[SW][SW + 1], sy[SW][SW + 1];
+  __shared__ float hz[5][SW][ST + 1];
+  const int W = a.W, H = a.H, N = W * H, c = blockIdx.z;
+  const int x0 = blockIdx.x * ST, y0 = blockIdx.y * ST;
+  const float* X = a.im + (size_t)c * N;
+  const float* Y = a.gt_im + (size_t)c * N;
+  for (int k = threadIdx.x; k < SW * SW; k += 256) {
+    const int ly = k / SW, lx = k - ly * SW, gx = x0 + lx - SHALO, gy = y0 + ly - SHALO;
+    const bool in = gx >= 0 && gx < W && gy >= 0 && gy < H;
+    sx[ly][lx] = in ? X[gy * W + gx] : 0.f;
+    sy[ly][lx] = in ? Y[gy * W + gx] : 0.f;
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < SW * ST; k += 256) {
+    const int ly = k / ST, lx = k - ly * ST;
+    float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+    for (int j = 0; j < 11; ++j) {
+      const float g = a.gauss[j], u = sx[ly][lx + j], v = sy[ly][lx + j];
+      m1 += g * u; m2 += g * v; e11 += g * (u * u); e22 += g * (v * v); e12 += g * (u * v);
+    }
+    hz[0][ly][lx] = m1; hz[1][ly][lx] = m2; hz[2][ly][lx] = e11; hz[3][ly][lx] = e22; hz[4][ly][lx] = e12;
+  }
+  __syncthreads();
+  float s[LOSS_SUMS] = {0.f, 0.f, 0.f, 0.f};
+  const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+  for (int k = threadIdx.x; k < ST * ST; k += 256) {
+    const int ly = k / ST, lx = k - ly * ST, gx = x0 + lx, gy = y0 + ly;
+    if (gx >= W || gy >= H) continue;
+    float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+    for (int j = 0; j < 11; ++j) {
+      const float g = a.gauss[j];
+      m1 += g * hz[0][ly + j][lx]; m2 += g * hz[1][ly + j][lx]; e11 += g * hz[2][ly + j][lx];
+      e22 += g * hz[3][ly + j][lx]; e12 += g * hz[4][ly + j][lx];
+    }
+    const float s1 = e11 - m1 * m1, s2 = e22 - m2 * m2, s12 = e12 - m1 * m2;
+    const float A = 2.f * m1 * m2 + C1, B = 2.f * s12 + C2, Cc = m1 * m1 + m2 * m2 + C1, D = s1 + s2 + C2;
+    const float inv = 1.f / (Cc * D);
+    const float m = A * B * inv;
+    // partial derivatives of the map value w.r.t. the three window means that depend on the rendered image:
+    // conv(x) [with sigma1, sigma12 depending on it], conv(x*x), conv(x*y)
+    const float d_xy = 2.f * A * inv;
+    const float d_xx = -m / D;
+    const float d_mu = 2.f * m2 * B * inv - 2.f * m1 * m / Cc - m2 * d_xy - 2.f * m1 * d_xx;
+    const size_t p = (size_t)gy * W + gx;
+    a.dmaps[(size_t)(0 * 3 + c) * N + p] = d_mu;
+    a.dmaps[(size_t)(1 * 3 + c) * N + p] = d_xx;
+    a.dmaps[(size_t)(2 * 3 + c) * N + p] = d_xy;
+    s[0] += m;
+    s[1] += fabsf(sx[ly + SHALO][lx + SHALO] - sy[ly + SHALO][lx + SHALO]);
+    if (c == 0) {
+      const float d = a.depth_sil[p], sil = a.depth_sil[N + p], d2 = a.depth_sil[2 * N + p], gd = a.gt_depth[p];
+      const bool mk = loss_mask(gd, d, d2, sil, false, 0.f);
+      s[2] += mk ? fabsf(gd - d) : 0.f;
+      s[3] += mk ? 1.f : 0.f;
+    }
+  }
+  block_partials(s, partial, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x);
+}
+
+__global__ void __launch_bounds__(256) map_loss_bwd_kernel(const LossArgs a, const float* __restrict__ stats) {
+  __shared__ float sm[3][SW][SW + 1];
+  __shared__ float hz[3][SW][ST + 1];
+  const int W = a.W, H = a.H, N = W * H, c = blockIdx.z;
+  const int x0 = blockIdx.x * ST, y0 = blockIdx.y * ST;
+  for (int k = threadIdx.x; k < SW * SW; k += 256) {
+    const int ly = k / SW, lx = k - ly * SW, gx = x0 + lx - SHALO, gy = y0 + ly - SHALO;
+    const bool in = gx >= 0 && gx < W && gy >= 0 && gy < H;
+#pragma unroll
+    for (int q = 0; q < 3; ++q) sm[q][ly][lx] = in ? a.dmaps[(size_t)(q * 3 + c) * N + (size_t)gy * W + gx] : 0.f;
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < SW * ST; k += 256) {
+    const int ly = k / ST, lx = k - ly * ST;
+    float h0 = 0.f, h1 = 0.f, h2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < 11; ++j) {
+      const float g = a.gauss[j];
+      h0 += g * sm[0][ly][lx + j]; h1 += g * sm[1][ly][lx + j]; h2 += g * sm[2][ly][lx + j];
+    }
+    hz[0][ly][lx] = h0; hz[1][ly][lx] = h1; hz[2][ly][lx] = h2;
+  }
+  __syncthreads();
+  const float inv3N = 1.f / (3.f * (float)N);
+  const float inv_cnt = 1.f / stats[3];
+  for (int k = threadIdx.x; k < ST * ST; k += 256) {
+    const int ly = k / ST, lx = k - ly * ST, gx = x0 + lx, gy = y0 + ly;
+    if (gx >= W || gy >= H) continue;
+    float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < 11; ++j) {
+      const float g = a.gauss[j];
+      v0 += g * hz[0][ly + j][lx]; v1 += g * hz[1][ly + j][lx]; v2 += g * hz[2][ly + j][lx];
+    }
+    const size_t p = (size_t)gy * W + gx;
+    const float x = a.im[(size_t)c * N + p], y = a.gt_im[(size_t)c * N + p];
+    const float dssim = v0 + 2.f * x * v1 + y * v2;
+    a.g_im[(size_t)c * N + p] = a.w_im * inv3N * (0.8f * sgn(x - y) - 0.2f * dssim);
+    if (c == 0) {
+      const float d = a.depth_sil[p], sil = a.depth_sil[N + p], d2 = a.depth_sil[2 * N + p], gd = a.gt_depth[p];
+      const bool mk = loss_mask(gd, d, d2, sil, false, 0.f);
+      a.g_depth_sil[p] = mk ? -a.w_depth * sgn(gd - d) * inv_cnt : 0.f;
+      a.g_depth_sil[N + p] = 0.f;
+      a.g_depth_sil[2 * N + p] = 0.f;
+    }
+  }
+}
+
+// One block: partials -> stats[0..3] (raw sums, double accumulation) and the weighted losses
+// losses = (w_im * im, w_depth * depth, total, mask count)   (scripts/splatam.py:342-346)
+__global__ void __launch_bounds__(256) loss_finalize_kernel(const LossArgs a, const float* __restrict__ partial, int nblk,
+                                                            float* __restrict__ stats) {
+  __shared__ double S[8][LOSS_SUMS];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  double v[LOSS_SUMS] = {0.0, 0.0, 0.0, 0.0};
+  for (int b = threadIdx.x; b < nblk; b += 256)
+#pragma unroll
+    for (int k = 0; k < LOSS_SUMS; ++k) v[k] += (double)partial[b * LOSS_SUMS + k];
+#pragma unroll
+  for (int k = 0; k < LOSS_SUMS; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+    if (lane == 0) S[w][k] = v[k];
+  }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  double t[LOSS_SUMS];
+  for (int k = 0; k < LOSS_SUMS; ++k) { t[k] = 0.0; for (int j = 0; j < 8; ++j) t[k] += S[j][k]; stats[k] = (float)t[k]; }
+  double l_im, l_d, cnt;
+  if (a.tracking) {
+    l_im = t[0]; l_d = t[1]; cnt = t[2];
+  } else {
+    const double n3 = 3.0 * (double)a.W * (double)a.H;
+    l_im = 0.8 * (t[1] / n3) + 0.2 * (1.0 - t[0] / n3);
+    l_d = t[2] / t[3];   // mean over an empty mask is NaN in torch as well
+    cnt = t[3];
+  }
+  const float wi = a.w_im * (float)l_im, wd = a.w_depth * (float)l_d;
+  a.losses[0] = wi; a.losses[1] = wd; a.losses[2] = wi + wd; a.losses[3] = (float)cnt;
+}
+
+int slam_loss_blocks(int W, int H, int tracking) {
+  if (tracking) {
+    int nb = (W * H + 255) / 256;
+    return nb > 148 * 8 ? 148 * 8 : (nb < 1 ? 1 : nb);
+  }
+  return ((W + ST - 1) / ST) * ((H + ST - 1) / ST) * 3;
+}
+
+int launch_slam_loss(const LossArgs& a, float* partial, float* stats, cudaStream_t st) {
+  const int nb = slam_loss_blocks(a.W, a.H, a.tracking);
+  if (a.tracking) {
+    ProfScope prof_(K_LOSS, st);
+    track_loss_kernel<<<nb, 256, 0, st>>>(a, partial);
+    SPLAT_LAUNCH_CHECK("track_loss_kernel");
+    loss_finalize_kernel<<<1, 256, 0, st>>>(a, partial, nb, stats);
+    SPLAT_LAUNCH_CHECK("loss_finalize_kernel");
+    return SPLAT_OK;
+  }
+  ProfScope prof_(K_LOSS, st);
+  dim3 grid((a.W + ST - 1) / ST, (a.H + ST - 1) / ST, 3);
+  map_loss_fwd_kernel<<<grid, 256, 0, st>>>(a, partial);
+  SPLAT_LAUNCH_CHECK("map_loss_fwd_kernel");
+  loss_finalize_kernel<<<1, 256, 0, st>>>(a, partial, nb, stats);
+  SPLAT_LAUNCH_CHECK("loss_finalize_kernel");
+  map_loss_bwd_kernel<<<grid, 256, 0, st>>>(a, stats);
+  SPLAT_LAUNCH_CHECK("map_loss_bwd_kernel");
+  return SPLAT_OK;
+}
+
+}  // namespace splat

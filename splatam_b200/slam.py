@@ -1,0 +1,229 @@
+"""Host-side mirror of the SplaTAM glue on either side of the rasterizer, on top of
+libsplat_b200's `splat_rendervar_*` and `splat_slam_loss` entry points.  Same function names, argument meaning
+and return values as the reference:
+
+  transform_to_frame + transformed_params2rendervar  (utils/slam_helpers.py:253-304, :123-139)  -> build_rendervar
+  get_loss                                           (scripts/splatam.py:220-353)              -> get_loss
+
+`get_loss` here = fused builder -> ONE six-plane render (GaussianRasterizer.render_rgbd_sil) -> fused loss that hands
+dL/d(render) straight to the rasterizer's backward; the reference runs ~45 small torch kernels, two rasterizer passes and
+a second autograd sweep for the same quantities.  Patch point: `from splatam_b200.slam import get_loss` in
+scripts/splatam.py.  PyTorch is plumbing only (memory, streams, autograd edges); no CPU fallback.
+
+Restrictions (raise, never silently differ): use_l1=True and ignore_outlier_depth_loss=False (every shipped config,
+configs/*/splatam.py) and no matplotlib visualisation.  curr_data['w2c'] must be the camera's view matrix (it is:
+both are first_frame_w2c, scripts/splatam.py:189-200) because the fused render takes depth from the view matrix.
+"""
+import ctypes as C
+
+import torch
+
+from ._lib import check, lib
+from .rasterizer import _f32, _on_device
+
+
+def _vp(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+# ------------------------------------------------------------------------------------------------ 8f-2
+class _BuildRendervar(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, unnorm_rotations, logit_opacities, log_scales, cam_unnorm_rots, cam_trans, time_idx,
+                gaussians_grad, camera_grad):
+        means3D = _f32(means3D, "means3D")
+        unnorm_rotations = _f32(unnorm_rotations, "unnorm_rotations")
+        logit_opacities = _f32(logit_opacities, "logit_opacities")
+        log_scales = _f32(log_scales, "log_scales")
+        cam_unnorm_rots = _f32(cam_unnorm_rots, "cam_unnorm_rots")
+        cam_trans = _f32(cam_trans, "cam_trans")
+        P = means3D.shape[0]
+        sd = log_scales.shape[1]
+        F = cam_unnorm_rots.shape[-1]
+        if cam_unnorm_rots.numel() != 4 * F or cam_trans.numel() != 3 * F:
+            raise RuntimeError("cam_unnorm_rots / cam_trans must be [1,4,F] / [1,3,F]")
+        if unnorm_rotations.data_ptr() % 16:
+            unnorm_rotations = unnorm_rotations.clone()
+        dev = means3D.device
+        with _on_device(dev):
+            flat = torch.empty(P * 11, dtype=torch.float32, device=dev)     # [rotations 4 | means 3 | scales 3 | opacity 1]
+            rots = flat[:4 * P].view(P, 4)
+            means = flat[4 * P:7 * P].view(P, 3)
+            scales = flat[7 * P:10 * P].view(P, 3)
+            opac = flat[10 * P:].view(P, 1)
+            check(lib.splat_rendervar_forward(P, sd, _vp(means3D), _vp(unnorm_rotations), _vp(logit_opacities),
+                                              _vp(log_scales), _vp(cam_unnorm_rots), _vp(cam_trans), F, int(time_idx),
+                                              _vp(means), _vp(rots), _vp(opac), _vp(scales), _stream()))
+        ctx.save_for_backward(means3D, unnorm_rotations, logit_opacities, log_scales, cam_unnorm_rots, cam_trans)
+        ctx.cfg = (P, sd, F, int(time_idx), bool(gaussians_grad), bool(camera_grad))
+        ctx.set_materialize_grads(False)
+        return means, rots, opac, scales
+
+    @staticmethod
+    def backward(ctx, g_means, g_rots, g_op, g_scales):
+        means3D, unnorm_rotations, logit_opacities, log_scales, cam_unnorm_rots, cam_trans = ctx.saved_tensors
+        P, sd, F, t, gg, cg = ctx.cfg
+        need = ctx.needs_input_grad
+        gg = gg and (need[0] or need[1])
+        cg = cg and (need[4] or need[5])
+        dev = means3D.device
+        g_means, g_rots, g_op, g_scales = [None if g is None else _f32(g, "grad") for g in (g_means, g_rots, g_op, g_scales)]
+        if g_rots is not None and g_rots.data_ptr() % 16:
+            g_rots = g_rots.clone()
+        with _on_device(dev):
+            n = P * ((7 if gg else 0) + (1 if need[2] else 0) + (sd if need[3] else 0))
+            flat = torch.empty(max(n, 1), dtype=torch.float32, device=dev)
+            off = 0
+            d_rots = d_means = d_logit = d_ls = None
+            if gg:
+                d_rots = flat[:4 * P].view(P, 4)
+                d_means = flat[4 * P:7 * P].view(P, 3)
+                off = 7 * P
+            if need[2]:
+                d_logit = flat[off:off + P].view(P, 1)
+                off += P
+            if need[3]:
+                d_ls = flat[off:off + P * sd].view(P, sd)
+            d_cr = d_ct = scratch = None
+            nscr = 0
+            if cg:
+                pose = torch.zeros(7 * F, dtype=torch.float32, device=dev)
+                d_cr, d_ct = pose[:4 * F].view(1, 4, F), pose[4 * F:].view(1, 3, F)
+                nscr = lib.splat_rendervar_scratch_bytes(P)
+                scratch = torch.empty(nscr, dtype=torch.uint8, device=dev)
+            check(lib.splat_rendervar_backward(P, sd, _vp(means3D), _vp(unnorm_rotations), _vp(logit_opacities),
+                                               _vp(log_scales), _vp(cam_unnorm_rots), _vp(cam_trans), F, t,
+                                               _vp(g_means), _vp(g_rots), _vp(g_op), _vp(g_scales), int(gg), int(cg),
+                                               _vp(d_means), _vp(d_rots), _vp(d_logit), _vp(d_ls), _vp(d_cr), _vp(d_ct),
+                                               _vp(scratch), nscr, _stream()))
+        return (d_means if need[0] else None, d_rots if need[1] else None, d_logit, d_ls,
+                d_cr if need[4] else None, d_ct if need[5] else None, None, None, None)
+
+
+def build_rendervar(params, time_idx, gaussians_grad, camera_grad):
+    """transform_to_frame + transformed_params2rendervar in one kernel (utils/slam_helpers.py:253-304, :123-139).
+    Returns the reference's rendervar dict (means3D, colors_precomp, rotations, opacities, scales, means2D)."""
+    means, rots, opac, scales = _BuildRendervar.apply(
+        params['means3D'], params['unnorm_rotations'], params['logit_opacities'], params['log_scales'],
+        params['cam_unnorm_rots'], params['cam_trans'], time_idx, gaussians_grad, camera_grad)
+    return {'means3D': means, 'colors_precomp': params['rgb_colors'], 'rotations': rots, 'opacities': opac,
+            'scales': scales,
+            # a leaf that only ever receives a gradient (the reference adds `+ 0` and calls retain_grad(), :135)
+            'means2D': torch.zeros_like(params['means3D'], requires_grad=True)}
+
+
+# ------------------------------------------------------------------------------------------------ 8f-3
+def _loss_call(dev, H, W, tracking, use_sil, sil_thres, w_im, w_depth, im, depth_sil, gt_im, gt_depth, g_im, g_ds):
+    losses = torch.empty(4, dtype=torch.float32, device=dev)
+    nscr = lib.splat_slam_loss_scratch_bytes(W, H, int(tracking))
+    scratch = torch.empty(nscr, dtype=torch.uint8, device=dev)
+    check(lib.splat_slam_loss(W, H, int(tracking), int(use_sil), float(sil_thres), float(w_im), float(w_depth),
+                              _vp(im), _vp(depth_sil), _vp(gt_im), _vp(gt_depth), _vp(losses), _vp(g_im), _vp(g_ds),
+                              _vp(scratch), nscr, _stream()))
+    return losses
+
+
+def _check_images(render, nplanes, gt_im, gt_depth):
+    render = _f32(render, "rendered image")
+    gt_im = _f32(gt_im, "curr_data['im']")
+    gt_depth = _f32(gt_depth, "curr_data['depth']")
+    H, W = render.shape[-2], render.shape[-1]
+    if render.shape[0] != nplanes or gt_im.numel() != 3 * H * W or gt_depth.numel() != H * W:
+        raise RuntimeError("image shapes do not match: render %s, im %s, depth %s"
+                           % (tuple(render.shape), tuple(gt_im.shape), tuple(gt_depth.shape)))
+    return render, gt_im, gt_depth, H, W
+
+
+class _ImageLoss6(torch.autograd.Function):
+    """Loss on the six-plane fused render: planes 0-2 = im, 3-5 = (depth, silhouette, depth^2)."""
+    @staticmethod
+    def forward(ctx, render, gt_im, gt_depth, tracking, use_sil, sil_thres, w_im, w_depth):
+        render, gt_im, gt_depth, H, W = _check_images(render, 6, gt_im, gt_depth)
+        dev = render.device
+        with _on_device(dev):
+            grad = torch.empty_like(render)
+            losses = _loss_call(dev, H, W, tracking, use_sil, sil_thres, w_im, w_depth, render[:3], render[3:], gt_im,
+                                gt_depth, grad[:3], grad[3:])
+        ctx.grad = grad
+        ctx.mark_non_differentiable(losses)
+        return losses[2], losses
+
+    @staticmethod
+    def backward(ctx, g_loss, _g_losses):
+        grad, ctx.grad = ctx.grad, None
+        return grad.mul_(g_loss), None, None, None, None, None, None, None
+
+
+class _ImageLoss33(torch.autograd.Function):
+    """Loss on the two images of the reference flow: im [3,H,W] and depth_sil [3,H,W] (two Renderer passes)."""
+    @staticmethod
+    def forward(ctx, im, depth_sil, gt_im, gt_depth, tracking, use_sil, sil_thres, w_im, w_depth):
+        im, gt_im, gt_depth, H, W = _check_images(im, 3, gt_im, gt_depth)
+        depth_sil = _f32(depth_sil, "depth_sil")
+        if tuple(depth_sil.shape) != (3, H, W):
+            raise RuntimeError("depth_sil must be [3,%d,%d]" % (H, W))
+        dev = im.device
+        with _on_device(dev):
+            grad = torch.empty(6, H, W, dtype=torch.float32, device=dev)
+            losses = _loss_call(dev, H, W, tracking, use_sil, sil_thres, w_im, w_depth, im, depth_sil, gt_im, gt_depth,
+                                grad[:3], grad[3:])
+        ctx.grad = grad
+        ctx.mark_non_differentiable(losses)
+        return losses[2], losses
+
+    @staticmethod
+    def backward(ctx, g_loss, _g_losses):
+        grad, ctx.grad = ctx.grad, None
+        grad.mul_(g_loss)
+        return grad[:3], grad[3:], None, None, None, None, None, None, None
+
+
+def image_loss(im, depth_sil, gt_im, gt_depth, loss_weights, use_sil_for_loss, sil_thres, tracking):
+    """Image-space part of get_loss (scripts/splatam.py:262-296,342-346).  `im` may be the six-plane fused render with
+    depth_sil=None.  Returns (loss, {'im':, 'depth':, 'loss':}) as device scalars; loss.backward() delivers the
+    gradient the kernel already formed (scaled by the incoming gradient)."""
+    args = (bool(tracking), bool(use_sil_for_loss), float(sil_thres), float(loss_weights['im']),
+            float(loss_weights['depth']))
+    if depth_sil is None:
+        loss, losses = _ImageLoss6.apply(im, gt_im, gt_depth, *args)
+    else:
+        loss, losses = _ImageLoss33.apply(im, depth_sil, gt_im, gt_depth, *args)
+    return loss, {'im': losses[0], 'depth': losses[1], 'loss': loss}
+
+
+def _default_renderer():
+    from diff_gaussian_rasterization import GaussianRasterizer   # what scripts/splatam.py:37 imports
+    return GaussianRasterizer
+
+
+def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_for_loss,
+             sil_thres, use_l1, ignore_outlier_depth_loss, tracking=False,
+             mapping=False, do_ba=False, plot_dir=None, visualize_tracking_loss=False, tracking_iteration=None,
+             Renderer=None):
+    """Same signature and return value as the reference's get_loss (scripts/splatam.py:220-353)."""
+    if not use_l1 or ignore_outlier_depth_loss:
+        raise NotImplementedError("fused get_loss covers use_l1=True, ignore_outlier_depth_loss=False (all shipped configs)")
+    if visualize_tracking_loss:
+        raise NotImplementedError("visualize_tracking_loss needs matplotlib/cv2 windows: unavailable on this box")
+    if tracking:
+        gg, cg = False, True
+    elif mapping and do_ba:
+        gg, cg = True, True
+    else:
+        gg, cg = True, False
+    rendervar = build_rendervar(params, iter_time_idx, gaussians_grad=gg, camera_grad=cg)
+    Renderer = Renderer or _default_renderer()
+    out, radius, _ = Renderer(raster_settings=curr_data['cam']).render_rgbd_sil(**rendervar)
+    variables['means2D'] = rendervar['means2D']
+    loss, weighted_losses = image_loss(out, None, curr_data['im'], curr_data['depth'], loss_weights,
+                                       use_sil_for_loss, sil_thres, tracking)
+    # == `seen = radius > 0; max_2D_radius[seen] = max(radius[seen], max_2D_radius[seen])` (:348-350) without the
+    # boolean-index host synchronisation: radius is 0 where not seen and max_2D_radius >= 0
+    m2r = variables['max_2D_radius']
+    torch.maximum(m2r, radius.to(m2r.dtype), out=m2r)
+    variables['seen'] = radius > 0
+    return loss, variables, weighted_losses

@@ -34,7 +34,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_abi_version_and_error_strings():
     from splatam_b200._lib import lib
-    assert lib.splat_abi_version() == 3
+    assert lib.splat_abi_version() == 4
     assert lib.splat_strerror(0) == b"ok"
     assert lib.splat_strerror(1) == b"bad argument"
     assert lib.splat_strerror(2) == b"scratch buffer too small"
@@ -75,6 +75,51 @@ def test_argument_validation_happens_before_any_cuda_call():
     rc = lib.splat_mark_visible(-1, null, null, null, 0.2, null, null)
     assert rc == 1
     assert lib.splat_mark_visible(0, null, null, null, 0.2, null, null) == 0   # P == 0 short-circuits
+
+
+def test_slam_glue_entry_points_validate_before_cuda():
+    """splat_rendervar_* / splat_slam_loss (ABI v4): sizes and argument checks need no GPU."""
+    from splatam_b200._lib import lib
+    null = C.c_void_p(0)
+    one = C.c_void_p(256)   # any non-NULL, 16-byte aligned address: validation fails before it is dereferenced
+    assert lib.splat_rendervar_scratch_bytes(0) >= 64 and lib.splat_rendervar_scratch_bytes(0) % 256 == 0
+    assert lib.splat_rendervar_scratch_bytes(10_000_000) <= 148 * 8 * 64 + 256
+    rc = lib.splat_rendervar_forward(10, 2, one, one, one, one, one, one, 5, 0, one, one, one, one, null)
+    assert rc == 1 and b"1 or 3 columns" in lib.splat_last_error()
+    rc = lib.splat_rendervar_forward(10, 1, one, one, one, one, one, one, 5, 5, one, one, one, one, null)
+    assert rc == 1 and b"time_idx" in lib.splat_last_error()
+    rc = lib.splat_rendervar_forward(10, 1, one, one, one, one, null, one, 5, 0, one, one, one, one, null)
+    assert rc == 1 and b"cam_" in lib.splat_last_error()
+    rc = lib.splat_rendervar_backward(10, 3, one, one, one, one, one, one, 5, 1, null, null, null, null, 1, 0,
+                                      null, null, null, null, null, null, null, 0, null)
+    assert rc == 1 and b"gaussians_grad" in lib.splat_last_error()
+    rc = lib.splat_rendervar_backward(10, 3, one, one, one, one, one, one, 5, 1, null, null, null, null, 0, 1,
+                                      null, null, null, null, one, one, null, 0, null)
+    assert rc == 2 and b"scratch" in lib.splat_last_error()
+    t, m = lib.splat_slam_loss_scratch_bytes(1200, 680, 1), lib.splat_slam_loss_scratch_bytes(1200, 680, 0)
+    assert t % 256 == 0 and m % 256 == 0 and m - t >= 9 * 4 * 1200 * 680
+    assert lib.splat_slam_loss_scratch_bytes(0, 680, 1) == 0
+    rc = lib.splat_slam_loss(0, 4, 1, 1, 0.99, 0.5, 1.0, one, one, one, one, one, one, one, one, 1 << 20, null)
+    assert rc == 1 and b"image size" in lib.splat_last_error()
+    rc = lib.splat_slam_loss(64, 64, 1, 1, 0.99, 0.5, 1.0, one, one, one, null, one, one, one, one, 1 << 20, null)
+    assert rc == 1
+    rc = lib.splat_slam_loss(64, 64, 0, 0, 0.5, 0.5, 1.0, one, one, one, one, one, one, one, one, 1024, null)
+    assert rc == 2 and b"scratch" in lib.splat_last_error()
+
+
+def test_slam_module_mirrors_reference_signatures():
+    """splatam_b200.slam.get_loss keeps the parameter list of scripts/splatam.py:220-222 (plus a trailing Renderer=)."""
+    from splatam_b200 import slam
+    names = list(inspect.signature(slam.get_loss).parameters)
+    assert names[:15] == ["params", "curr_data", "variables", "iter_time_idx", "loss_weights", "use_sil_for_loss",
+                          "sil_thres", "use_l1", "ignore_outlier_depth_loss", "tracking", "mapping", "do_ba",
+                          "plot_dir", "visualize_tracking_loss", "tracking_iteration"]
+    with pytest.raises(NotImplementedError):
+        slam.get_loss({}, {}, {}, 0, {}, True, 0.99, True, True, tracking=True)
+    with pytest.raises(NotImplementedError):
+        slam.get_loss({}, {}, {}, 0, {}, True, 0.99, False, False, tracking=True)
+    assert list(inspect.signature(slam.build_rendervar).parameters) == ["params", "time_idx", "gaussians_grad",
+                                                                          "camera_grad"]
 
 
 @pytest.mark.parametrize("pkg,near,has_power", [("diff_gaussian_rasterization", 0.2, False),

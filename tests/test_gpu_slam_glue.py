@@ -1,0 +1,213 @@
+"""GPU parity of the fused SplaTAM glue through the C ABI:
+  * render-variable builder fwd + bwd (incl. the in-kernel pose-gradient reduction) vs the golden fixtures produced by
+    the reference's own utils/slam_helpers.py, and vs the torch oracle at full size (1M Gaussians);
+  * tracking / mapping image loss + gradient vs the golden fixtures produced by the reference's own get_loss, and vs
+    the torch oracle at 1200x680;
+  * fused get_loss (builder -> six-plane render -> loss -> backward) vs the reference flow (oracle glue, two
+    three-channel renders) on pose and Gaussian gradients.
+Tolerances: forward 1e-5 relative to the array's max; gradients 1e-3 (BASELINE.json)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from util import GOLDEN_DIR
+from oracle import slam_oracle as SO
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _close(a, b, tol, what="", atol=0.0):
+    a, b = torch.as_tensor(a).double().cpu(), torch.as_tensor(b).double().cpu()
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    scale = float(b.abs().max()) + 1e-30
+    err = float((a - b).abs().max())
+    assert err <= tol * scale + atol, "%s: max abs err %.3g vs scale %.3g (tol %.1g)" % (what, err, scale, tol)
+
+
+def _params(case, n_frames=5, dev=DEV, P=None):
+    p = SO.random_params(P or case["P"], n_frames, case["iso"], case["seed"])
+    return {k: v.to(dev).requires_grad_(True) for k, v in p.items()}
+
+
+@pytest.mark.parametrize("case", SO.RV_CASES, ids=lambda c: c["name"])
+def test_rendervar_vs_reference_python_golden(case):
+    from splatam_b200 import slam
+    gold = np.load(os.path.join(GOLDEN_DIR, "slam_glue_rv_%s.npz" % case["name"]))
+    params = _params(case)
+    rv = slam.build_rendervar(params, 3, case["gg"], case["cg"])
+    ds = SO.get_depth_and_silhouette(rv["means3D"], torch.from_numpy(gold["w2c"]).to(DEV))
+    g = torch.Generator().manual_seed(100 + case["seed"])
+    seeds = {k: torch.randn(rv[k].shape, generator=g).to(DEV) for k in ("means3D", "rotations", "opacities", "scales")}
+    seeds["depth_sil"] = torch.randn(ds.shape, generator=g).to(DEV)
+    scalar = sum((rv[k] * seeds[k]).sum() for k in seeds if k != "depth_sil") + (ds * seeds["depth_sil"]).sum()
+    scalar.backward()
+    for k in ("means3D", "rotations", "opacities", "scales"):
+        _close(rv[k].detach(), gold["rv_" + k], 1e-5, "rv " + k)
+    assert rv["colors_precomp"] is params["rgb_colors"]
+    for k, v in params.items():
+        if k == "rgb_colors":
+            continue
+        got = v.grad if v.grad is not None else torch.zeros_like(v)
+        _close(got, gold["g_" + k], 1e-4, "grad " + k)
+
+
+@pytest.mark.parametrize("iso,gg,cg", [(True, False, True), (True, True, False), (False, True, True)])
+def test_rendervar_full_size_vs_oracle(iso, gg, cg):
+    """1M Gaussians: kernel vs the torch oracle run on the GPU (same ops as the reference, torch autograd)."""
+    from splatam_b200 import slam
+    case = dict(P=1_000_003, iso=iso, seed=21)
+    pa = _params(case, n_frames=7)
+    pb = {k: v.detach().clone().requires_grad_(True) for k, v in pa.items()}
+    ra = slam.build_rendervar(pa, 4, gg, cg)
+    rb = SO.build_rendervar(pb, 4, gg, cg)
+    g = torch.Generator().manual_seed(5)
+    tot_a = tot_b = 0.0
+    for k in ("means3D", "rotations", "opacities", "scales"):
+        _close(ra[k].detach(), rb[k].detach(), 1e-5, k)
+        w = torch.randn(ra[k].shape, generator=g).to(DEV)
+        tot_a = tot_a + (ra[k] * w).sum()
+        tot_b = tot_b + (rb[k] * w).sum()
+    tot_a.backward()
+    tot_b.backward()
+    for k in pa:
+        if k == "rgb_colors":
+            continue
+        ga = pa[k].grad if pa[k].grad is not None else torch.zeros_like(pa[k])
+        gb = pb[k].grad if pb[k].grad is not None else torch.zeros_like(pb[k])
+        # the pose gradient is a sum of 1M terms: torch reduces it in float32 in another order
+        _close(ga, gb, 1e-3 if k.startswith("cam_") else 1e-4, "grad " + k)
+    # deterministic (two-stage reduction, no atomics)
+    pc = {k: v.detach().clone().requires_grad_(True) for k, v in pa.items()}
+    rc = slam.build_rendervar(pc, 4, gg, cg)
+    g = torch.Generator().manual_seed(5)
+    tot_c = 0.0
+    for k in ("means3D", "rotations", "opacities", "scales"):
+        tot_c = tot_c + (rc[k] * torch.randn(rc[k].shape, generator=g).to(DEV)).sum()
+    tot_c.backward()
+    for k in pa:
+        if pa[k].grad is not None:
+            assert torch.equal(pa[k].grad, pc[k].grad), k
+
+
+def test_rendervar_empty_and_single():
+    from splatam_b200 import slam
+    for P in (0, 1):
+        pa = _params(dict(P=P, iso=True, seed=3), P=P)
+        rv = slam.build_rendervar(pa, 0, True, True)
+        assert rv["means3D"].shape == (P, 3) and rv["scales"].shape == (P, 3)
+        (rv["means3D"].sum() + rv["opacities"].sum()).backward()
+        assert pa["cam_trans"].grad is not None and pa["cam_trans"].grad.shape == pa["cam_trans"].shape
+        if P == 0:
+            assert float(pa["cam_trans"].grad.abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("case", SO.LOSS_CASES, ids=lambda c: c["name"])
+@pytest.mark.parametrize("six", [True, False], ids=["fused6", "two3"])
+def test_image_loss_vs_reference_get_loss_golden(case, six):
+    from splatam_b200 import slam
+    gold = np.load(os.path.join(GOLDEN_DIR, "slam_glue_loss_%s.npz" % case["name"]))
+    im, ds, gt_im, gt_d = [t.to(DEV) for t in SO.images(case["h"], case["w_"], case["seed"])]
+    if six:
+        r6 = torch.cat([im, ds], 0).requires_grad_(True)
+        loss, wl = slam.image_loss(r6, None, gt_im, gt_d, case["w"], case["use_sil"], case["sil_thres"], case["tracking"])
+        loss.backward()
+        g_im, g_ds = r6.grad[:3], r6.grad[3:]
+    else:
+        im.requires_grad_(True)
+        ds.requires_grad_(True)
+        loss, wl = slam.image_loss(im, ds, gt_im, gt_d, case["w"], case["use_sil"], case["sil_thres"], case["tracking"])
+        (loss * 1.0).backward()
+        g_im, g_ds = im.grad, ds.grad
+    _close(loss.detach(), gold["loss"], 1e-5, "loss")
+    _close(wl["im"], gold["l_im"], 1e-5, "im loss")
+    _close(wl["depth"], gold["l_depth"], 1e-5, "depth loss")
+    _close(g_im, gold["g_im"], 1e-3, "dL/dim")
+    _close(g_ds, gold["g_depth_sil"], 1e-3, "dL/ddepth_sil")
+
+
+@pytest.mark.parametrize("tracking", [True, False], ids=["tracking", "mapping"])
+def test_image_loss_full_size_vs_oracle(tracking):
+    from splatam_b200 import slam
+    h, w = 680, 1200
+    im, ds, gt_im, gt_d = [t.to(DEV) for t in SO.images(h, w, 9)]
+    wts = dict(im=0.5, depth=1.0)
+    r6 = torch.cat([im, ds], 0).requires_grad_(True)
+    loss, wl = slam.image_loss(r6, None, gt_im, gt_d, wts, tracking, 0.99, tracking)
+    (loss * 3.0).backward()           # a non-unit incoming gradient must scale the stored one
+    im_o, ds_o = im.clone().requires_grad_(True), ds.clone().requires_grad_(True)
+    loss_o, wl_o = SO.image_loss(im_o, ds_o, gt_im, gt_d, wts, tracking, 0.99, True, False, tracking)
+    (loss_o * 3.0).backward()
+    _close(loss.detach(), loss_o.detach(), 2e-5, "loss")
+    _close(wl["im"], wl_o["im"].detach(), 2e-5)
+    _close(wl["depth"], wl_o["depth"].detach(), 2e-5)
+    _close(r6.grad[:3], im_o.grad, 1e-3, "dL/dim")
+    _close(r6.grad[3:], ds_o.grad, 1e-3, "dL/ddepth_sil")
+    assert float(r6.grad[4:].abs().max()) == 0.0
+
+
+def _slam_scene(P, tracking, seed=4):
+    from splatam_b200 import synth
+    cam = dict(w=160, h=96, fx=80.0, fy=80.0, cx=79.5, cy=47.5)
+    w2c0 = torch.eye(4)
+    rs = synth.make_settings(device=DEV, w2c=w2c0, **cam)
+    sc = synth.surface_scene(P, cam["w"], cam["h"], cam["fx"], cam["fy"], cam["cx"], cam["cy"], seed=seed)
+    g = torch.Generator().manual_seed(seed)
+    nf = 3
+    rots = torch.tensor([1.0, 0, 0, 0]).view(1, 4, 1).repeat(1, 1, nf) + 0.01 * torch.randn(1, 4, nf, generator=g)
+    params = {
+        "means3D": sc["means3D"], "rgb_colors": sc["colors_precomp"],
+        "unnorm_rotations": sc["rotations"] * 1.7,
+        "logit_opacities": torch.logit(sc["opacities"].clamp(1e-4, 1 - 1e-4)),
+        "log_scales": torch.log(sc["scales"][:, :1]),
+        "cam_unnorm_rots": rots, "cam_trans": 0.01 * torch.randn(1, 3, nf, generator=g),
+    }
+    params = {k: v.contiguous().to(DEV) for k, v in params.items()}
+    gt_im = torch.rand(3, cam["h"], cam["w"], generator=g).to(DEV)
+    gt_d = (2.5 + 0.5 * torch.rand(1, cam["h"], cam["w"], generator=g)).to(DEV)
+    gt_d[0, :5] = 0.0
+    curr = {"cam": rs, "im": gt_im, "depth": gt_d, "w2c": w2c0.to(DEV)}
+    return params, curr
+
+
+@pytest.mark.parametrize("mode", ["tracking", "mapping", "ba"])
+def test_fused_get_loss_vs_reference_flow(mode):
+    """Whole iteration: fused get_loss vs (oracle builder -> two 3-channel renders -> oracle loss -> torch autograd)."""
+    from splatam_b200 import slam
+    from diff_gaussian_rasterization import GaussianRasterizer as Renderer
+    tracking = mode == "tracking"
+    base, curr = _slam_scene(6000, tracking)
+    wts = dict(im=0.5, depth=1.0)
+    sil_thres = 0.99 if tracking else 0.5
+    # ---- fused
+    pa = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+    va = {"max_2D_radius": torch.zeros(6000, device=DEV)}
+    loss_a, va, wl_a = slam.get_loss(pa, curr, va, 1, wts, tracking, sil_thres, True, False, tracking=tracking,
+                                     mapping=not tracking, do_ba=mode == "ba")
+    loss_a.backward()
+    # ---- reference flow (scripts/splatam.py:226-296 with the oracle's glue)
+    pb = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+    gg, cg = (False, True) if tracking else ((True, True) if mode == "ba" else (True, False))
+    tg = SO.transform_to_frame(pb, 1, gg, cg)
+    rv = SO.transformed_params2rendervar(pb, tg)
+    m2d = torch.zeros_like(pb["means3D"], requires_grad=True)
+    im, radius, _ = Renderer(raster_settings=curr["cam"])(means2D=m2d, **rv)
+    rv2 = dict(rv)
+    rv2["colors_precomp"] = SO.get_depth_and_silhouette(tg["means3D"], curr["w2c"])
+    ds, _, _ = Renderer(raster_settings=curr["cam"])(means2D=torch.zeros_like(m2d, requires_grad=True), **rv2)
+    loss_b, wl_b = SO.image_loss(im, ds, curr["im"], curr["depth"], wts, tracking, sil_thres, True, False, tracking)
+    loss_b.backward()
+    _close(loss_a.detach(), loss_b.detach(), 1e-4, "loss")
+    _close(wl_a["im"], wl_b["im"].detach(), 1e-4, "im")
+    _close(wl_a["depth"], wl_b["depth"].detach(), 1e-4, "depth")
+    assert torch.equal(va["seen"], radius > 0)
+    assert torch.equal(va["max_2D_radius"], radius.float())
+    for k in pa:
+        ga = pa[k].grad if pa[k].grad is not None else torch.zeros_like(pa[k])
+        gb = pb[k].grad if pb[k].grad is not None else torch.zeros_like(pb[k])
+        # isotropic Gaussians: the rotation gradient is numerically zero in both flows (1e-11 of rounding noise)
+        _close(ga, gb, 2e-3, "grad " + k, atol=1e-8 if k == "unnorm_rotations" else 0.0)
+        if k.startswith("cam_"):
+            assert (float(ga.abs().max()) > 0) == cg, k
