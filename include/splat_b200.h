@@ -127,14 +127,19 @@ int splat_forward_render(const SplatCamera* cam, int32_t P,
  * `scratch` is a 16-byte aligned device buffer of at least splat_backward_scratch_bytes(P, power)
  * bytes (the packed per-Gaussian accumulator rows the blend-backward kernel reduces into); the
  * call zeroes it itself.  colors_precomp is accepted for signature parity with the reference
- * (HX/rasterize_points.h:43-65) but the colours of the forward call are used. */
+ * (HX/rasterize_points.h:43-65) but the colours of the forward call are used.
+ * out_color (optional) only CONDITIONS the power-1 blend backward: dL/dalpha of a pair is invariant under a constant
+ * shift of all feature vectors of a pixel (sum of blend weights + final T == 1), so the kernel measures features
+ * relative to the pixel's rendered value, which keeps its one running suffix sum small where neighbouring splats
+ * have similar colours.  Any finite values give the same result up to float rounding; NULL means no shift. */
 size_t splat_backward_scratch_bytes(int32_t P, int32_t power);
 int splat_backward(const SplatCamera* cam, int32_t P, int64_t R,
                    const float* means3D, const float* scales, const float* rotations,
                    const float* cov3D_precomp, const float* shs, int32_t M,
                    const float* colors_precomp, const int32_t* radii,
                    const void* geom_state, const void* image_state, const void* binning_state,
-                   const float* dL_dout_color,          /* [3,H,W] */
+                   const float* dL_dout_color,          /* [3,H,W] ([6,H,W] with depth_sil) */
+                   const float* out_color,              /* the forward's rendered image, same shape, or NULL (see below) */
                    int32_t power, int32_t fused,
                    float* dL_dmeans3D,  /* [P,3] */
                    float* dL_dmeans2D,  /* [P,3] (z always 0) */

@@ -39,7 +39,7 @@ _SIGNATURES = {
                                          _P, _P, _P, _P, _P, _P]),
     "splat_forward_render": (C.c_int, [C.POINTER(SplatCamera), C.c_int32, _P, _P, _P, _P, _P, C.c_int64, _P, _P, _P]),
     "splat_backward": (C.c_int, [C.POINTER(SplatCamera), C.c_int32, C.c_int64, _P, _P, _P, _P, _P, C.c_int32,
-                                 _P, _P, _P, _P, _P, _P, C.c_int32, C.c_int32,
+                                 _P, _P, _P, _P, _P, _P, _P, C.c_int32, C.c_int32,
                                  _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "splat_backward_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "splat_mark_visible": (C.c_int, [C.c_int32, _P, _P, _P, C.c_float, _P, _P]),

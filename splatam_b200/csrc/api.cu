@@ -151,7 +151,7 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
                    const float* rotations, const float* cov3D_precomp, const float* shs, int32_t M,
                    const float* colors_precomp, const int32_t* radii, const void* geom_state,
                    const void* image_state, const void* binning_state, const float* dL_dout_color,
-                   int32_t power, int32_t fused, float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors,
+                   const float* out_color, int32_t power, int32_t fused, float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors,
                    float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
                    float* dL_dconic, float* dL_dsh, void* scratch, size_t scratch_bytes, void* stream) {
   read_env_once();
@@ -190,7 +190,7 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
 
   RenderBwdArgs r;
   r.W = W; r.H = H; r.gx = gx; r.order = iv.tile_order; r.ranges = iv.ranges; r.inst = bv.inst; r.bg = cam->bg;
-  r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.dL_dpix = dL_dout_color;
+  r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.dL_dpix = dL_dout_color; r.out_color = out_color;
   r.acc = acc;
   if (!hess) {
     if (R > 0) if (int rc = launch_render_bwd(r, T, cam->depth_sil ? 2 : 0, st)) return rc;

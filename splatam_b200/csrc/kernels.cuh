@@ -56,6 +56,7 @@ struct RenderBwdArgs {
   const uint32_t* order;
   const uint2* ranges; const float4* inst; const float* bg;
   const float* final_T; const uint32_t* n_contrib; const float* dL_dpix;
+  const float* out_color;   // optional: the forward's image, reference level of the per-pixel feature sums (MODE 0/2)
   float* acc;   // MODE 0: [P,12] raw sums.  MODE 1: [P,20] moment accumulator.  Pre-zeroed.
 };
 

@@ -280,7 +280,7 @@ def _plan_backward(st, dev, power, fused, means3D, colors_precomp, scales, rotat
 
 
 def rasterize_backward(rs, near, st, power, fused, means3D, colors_precomp, scales, rotations,
-                       cov3D_precomp, sh, radii, grad_out_color, sinks=None):
+                       cov3D_precomp, sh, radii, grad_out_color, sinks=None, out_color=None):
     dev = means3D.device
     P = st.P
     with _on_device(dev):
@@ -294,7 +294,7 @@ def rasterize_backward(rs, near, st, power, fused, means3D, colors_precomp, scal
         stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         grad = _f32(grad_out_color, "grad_out_color")
         check(lib.splat_backward(C.byref(st.cam), P, st.capacity, *plan["head"], _ptr(st.geom), _ptr(st.image),
-                                 _ptr(st.binning), _ptr(grad), *plan["tail"], stream))
+                                 _ptr(st.binning), _ptr(grad), _ptr(out_color), *plan["tail"], stream))
     return plan["result"]
 
 
@@ -327,6 +327,10 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.near = near
         ctx.fused = fused
         ctx.sinks = sinks
+        # the rendered image conditions the blend backward's sums (splat_backward's optional out_color).  A detached
+        # alias, not save_for_backward: a later in-place edit of the image by the caller is harmless (any values
+        # are valid reference levels) and must not trip autograd's version check.
+        ctx.out_color = color.detach() if bwd is not None else None
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh)
         # radii and depth are not differentiable in the reference (only grad_out_color is read,
         # HX/.../__init__.py:91-123): do not let autograd materialise zero gradients for them every backward
@@ -344,7 +348,8 @@ class _RasterizeGaussians(torch.autograd.Function):
             raise RuntimeError("grad of the rendered image must be [%d,%d,%d]" % (nch, ctx.state.H, ctx.state.W))
         (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D) = rasterize_backward(
             ctx.raster_settings, ctx.near, ctx.state, ctx.backward_power, ctx.fused, means3D, colors_precomp,
-            scales, rotations, cov3Ds_precomp, sh, radii, grad_out_color, ctx.sinks)
+            scales, rotations, cov3Ds_precomp, sh, radii, grad_out_color, ctx.sinks, ctx.out_color)
+        ctx.out_color = None
         sunk = ctx.sinks or {}
         return (g_means3D if "means3D" not in sunk else None, g_means2D,
                 g_sh if sh.numel() else None,
