@@ -82,6 +82,11 @@ def main():
     ap.add_argument("--mode", default="tracking", choices=["tracking", "mapping"])
     ap.add_argument("--impl", default="ours", choices=["ours", "dropin", "reference"])
     ap.add_argument("--variant", default="dg", choices=["dg", "hx"])
+    ap.add_argument("--pose-only", action="store_true",
+                    help="ours, tracking: skip the Gaussian-side gradients the reference computes and discards")
+    ap.add_argument("--optimizer", default="none", choices=["none", "torch", "fused"],
+                    help="include the per-iteration optimizer step + zero_grad in the timed iteration: torch = "
+                         "torch.optim.Adam as the reference builds it, fused = splatam_b200.slam.FusedAdam (ours only)")
     ap.add_argument("--steps", type=int, default=96)
     ap.add_argument("--warmup", type=int, default=8)
     args = ap.parse_args()
@@ -104,7 +109,8 @@ def main():
     if args.impl == "ours":
         def step(kf):
             loss, _, wl = slam.get_loss(params, targets[kf], variables, kf, wts, tracking, sil_thres, True, False,
-                                        tracking=tracking, mapping=not tracking)
+                                        tracking=tracking, mapping=not tracking,
+                                        tracking_pose_only=args.pose_only)
             loss.backward()
             return loss
     else:
@@ -137,7 +143,27 @@ def main():
             loss.backward()
             return loss
 
+    opt = None
+    if args.optimizer != "none":   # initialize_optimizer (scripts/splatam.py:166-172) with the config's learning rates
+        lrs = (dict(means3D=0.0, rgb_colors=0.0, unnorm_rotations=0.0, logit_opacities=0.0, log_scales=0.0,
+                    cam_unnorm_rots=0.0004, cam_trans=0.002) if tracking else
+               dict(means3D=0.0001, rgb_colors=0.0025, unnorm_rotations=0.001, logit_opacities=0.05, log_scales=0.001,
+                    cam_unnorm_rots=0.0, cam_trans=0.0))     # configs/replica/splatam.py:71-79, :92-100
+        Adam = slam.FusedAdam if args.optimizer == "fused" else torch.optim.Adam
+        groups = [{'params': [v], 'name': k, 'lr': lrs[k]} for k, v in params.items()]
+        opt = Adam(groups) if tracking else Adam(groups, lr=0.0, eps=1e-15)
+        inner = step
+
+        def step(kf):   # scripts/splatam.py:724-725 / :889-890
+            loss = inner(kf)
+            with torch.no_grad():
+                opt.step()
+            return loss
+
     def zero():
+        if opt is not None:
+            opt.zero_grad(set_to_none=True)
+            return
         for v in params.values():
             v.grad = None
 
@@ -166,6 +192,7 @@ def main():
            "unit": "iters/s", "value": args.steps / (ms * 1e-3), "ms_per_step": ms / args.steps,
            "wall_ms_per_step": wall * 1e3 / args.steps, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
            "higher_is_better": True, "dtype": "f32", "data": "synthetic", "impl": args.impl,
+           "pose_only": bool(args.pose_only), "optimizer_in_timed_step": args.optimizer,
            "config": {"workload": "replica_1200x680_%s_%s" % ("300k" if tracking else "1M", args.mode),
                       "image": [cam["w"], cam["h"]], "gaussians": P, "keyframes": nf,
                       "variant": args.variant if args.impl == "reference" else "dg",

@@ -213,6 +213,21 @@ int splat_slam_loss(int32_t width, int32_t height, int32_t tracking, int32_t use
                     float* losses, float* dL_dim, float* dL_ddepth_sil,
                     void* scratch, size_t scratch_bytes, void* stream);
 
+/* splat_adam_step  <-  the per-iteration optimizer.step() of SplaTAM (scripts/splatam.py:724-725, :889-890):
+ *      torch.optim.Adam over one param group per tensor (scripts/splatam.py:166-172; betas (0.9, 0.999), eps 1e-8 while
+ *      tracking / 1e-15 while mapping, no weight decay, no amsgrad), all tensors in ONE launch.  Arithmetic as torch/optim/adam.py::_single_tensor_adam:
+ *        exp_avg += (1 - beta1) (grad - exp_avg);  exp_avg_sq = beta2 exp_avg_sq + (1 - beta2) grad^2;
+ *        param  -= (lr / bias_correction1) * exp_avg / (sqrt(exp_avg_sq) / bias_correction2_sqrt + eps)
+ *      with bias_correction1 = 1 - beta1^step and bias_correction2_sqrt = sqrt(1 - beta2^step) computed by the
+ *      caller per tensor (a tensor without a gradient this step is simply left out, as torch does).
+ *      `tensors` is a HOST array of `count` <= 16 descriptors (copied into the launch). */
+typedef struct SplatAdamTensor {
+  float* param; const float* grad; float* exp_avg; float* exp_avg_sq;   /* device, n floats each */
+  int64_t n;
+  float lr, bias_correction1, bias_correction2_sqrt;
+} SplatAdamTensor;
+int splat_adam_step(const SplatAdamTensor* tensors, int32_t count, double beta1, double beta2, double eps, void* stream);
+
 /* ---- multi-GPU exchange (new; the reference is single-GPU, configs/replica/splatam.py:8) -------
  * Sum of one flat float32 bucket over the `world` ranks of one NVSwitch node, in place, on `stream`.
  * buffers[j] / flag_pads[j] are the device addresses, valid in THIS process, of rank j's bucket and of

@@ -161,9 +161,11 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
   if (P == 0) return SPLAT_OK;
   if (!means3D || !radii || !geom_state || !image_state || !binning_state || !dL_dout_color)
     return fail(SPLAT_ERR_BAD_ARG, "NULL input buffer");
-  if (!dL_dmeans3D || !dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dscales || !dL_drotations ||
-      !dL_dcov3D || !dL_dconic)
-    return fail(SPLAT_ERR_BAD_ARG, "NULL gradient buffer");
+  if (!dL_dmeans3D) return fail(SPLAT_ERR_BAD_ARG, "dL_dmeans3D must be non-NULL");
+  const bool all_out = dL_dmeans2D && dL_dcolors && dL_dopacity && dL_dscales && dL_drotations && dL_dcov3D && dL_dconic;
+  if (!all_out && (fused && power != 1))
+    return fail(SPLAT_ERR_BAD_ARG, "the power-2 backward writes every gradient array: NULL gradient buffer");
+  if (!all_out && shs) return fail(SPLAT_ERR_BAD_ARG, "the SH backward needs every gradient array");
   if (shs && !dL_dsh) return fail(SPLAT_ERR_BAD_ARG, "dL_dsh required with SHs");
   const bool sr = scales && rotations;
   if (!sr && !cov3D_precomp) return fail(SPLAT_ERR_BAD_ARG, "need scales+rotations or cov3D_precomp");
@@ -193,7 +195,9 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.dL_dpix = dL_dout_color; r.out_color = out_color;
   r.acc = acc;
   if (!hess) {
-    if (R > 0) if (int rc = launch_render_bwd(r, T, cam->depth_sil ? 2 : 0, st)) return rc;
+    // callers that need neither colour nor opacity gradients (pose-only tracking) get the blend backward without those sums
+    const int mode = cam->depth_sil ? ((!dL_dcolors && !dL_dopacity) ? 3 : 2) : 0;
+    if (R > 0) if (int rc = launch_render_bwd(r, T, mode, st)) return rc;
     PreBwdArgs b;
     b.depth_sil = cam->depth_sil ? 1 : 0;
     b.P = P; b.M = M; b.sh_degree = cam->sh_degree; b.tanx = cam->tanfovx; b.tany = cam->tanfovy;
@@ -336,7 +340,7 @@ int splat_profile_read_gaps(float* gap_ms_sum, int32_t n) {
 const char* splat_profile_kernel_name(int k) {
   static const char* names[K_COUNT] = {"preprocess_fwd", "tile_scan", "scatter", "tile_sort", "render_fwd",
                                        "render_bwd", "preprocess_bwd", "hessian_finalize", "emit_records",
-                                       "rendervar_fwd", "rendervar_bwd", "slam_loss"};
+                                       "rendervar_fwd", "rendervar_bwd", "slam_loss", "adam"};
   return (k >= 0 && k < K_COUNT) ? names[k] : "";
 }
 
@@ -436,6 +440,28 @@ int splat_slam_loss(int32_t W, int32_t H, int32_t tracking, int32_t use_sil_for_
   float* stats = (float*)c;   c += 256;
   a.dmaps = tracking ? nullptr : (float*)c;
   return launch_slam_loss(a, partial, stats, (cudaStream_t)stream);
+}
+
+int splat_adam_step(const SplatAdamTensor* tensors, int32_t count, double beta1, double beta2, double eps, void* stream) {
+  if (count < 0 || count > ADAM_MAX_TENSORS) return fail(SPLAT_ERR_BAD_ARG, "count must be 0..%d", ADAM_MAX_TENSORS);
+  if (count == 0) return SPLAT_OK;
+  if (!tensors) return fail(SPLAT_ERR_BAD_ARG, "tensors is NULL");
+  AdamArgs a = {};
+  // (1 - beta) is formed in double like torch's Python scalars: 1 - 0.999f is off by 1.3e-5 relative
+  a.count = 0; a.beta2 = (float)beta2; a.w1 = (float)(1.0 - beta1); a.w2 = (float)(1.0 - beta2); a.eps = (float)eps;
+  for (int i = 0; i < count; ++i) {
+    const SplatAdamTensor& t = tensors[i];
+    if (t.n < 0) return fail(SPLAT_ERR_BAD_ARG, "tensor %d: n < 0", i);
+    if (t.n == 0) continue;
+    if (!t.param || !t.grad || !t.exp_avg || !t.exp_avg_sq) return fail(SPLAT_ERR_BAD_ARG, "tensor %d: NULL pointer", i);
+    if (!(t.bias_correction1 > 0.f) || !(t.bias_correction2_sqrt > 0.f))
+      return fail(SPLAT_ERR_BAD_ARG, "tensor %d: bias corrections must be > 0 (step >= 1)", i);
+    SplatAdamTensorK& k = a.t[a.count++];
+    k.param = t.param; k.grad = t.grad; k.exp_avg = t.exp_avg; k.exp_avg_sq = t.exp_avg_sq; k.n = t.n;
+    k.lr = t.lr; k.bias_correction1 = t.bias_correction1; k.bias_correction2_sqrt = t.bias_correction2_sqrt;
+    k.vec = (((uintptr_t)t.param | (uintptr_t)t.grad | (uintptr_t)t.exp_avg | (uintptr_t)t.exp_avg_sq) & 15) == 0;
+  }
+  return launch_adam(a, (cudaStream_t)stream);
 }
 
 int splat_abi_version(void) { return SPLAT_ABI_VERSION; }

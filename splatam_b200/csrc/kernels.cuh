@@ -79,6 +79,19 @@ struct LossArgs {
   float* losses; float* g_im; float* g_depth_sil;
   float* dmaps;                                         // [3 maps][3 ch][H][W] mapping loss only
 };
+struct SplatAdamTensorDev {   // == SplatAdamTensor of the C ABI + a vector-access flag
+  float* param; const float* grad; float* exp_avg; float* exp_avg_sq;
+  int64_t n; float lr, bias_correction1, bias_correction2_sqrt; int vec;
+};
+typedef SplatAdamTensorDev SplatAdamTensorK;
+#define ADAM_MAX_TENSORS 16
+struct AdamArgs {
+  int count;
+  float beta2, w1, w2, eps;   // w = 1 - beta, rounded from double
+  int blocks[ADAM_MAX_TENSORS];
+  SplatAdamTensorK t[ADAM_MAX_TENSORS];
+};
+int launch_adam(AdamArgs& a, cudaStream_t st);
 int rendervar_bwd_blocks(int P);
 int launch_rendervar_fwd(const RvArgs& a, cudaStream_t st);
 int launch_rendervar_bwd(const RvArgs& a, bool gg, bool cg, float* partial, cudaStream_t st);

@@ -373,7 +373,9 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
       if (!a.cov3D_pre) cov3d_from_scale_rot(s, a.mod, q, cov3D);
     }
     GaussChain g;
-    chain_setup(g, mean, cov3D, has_scale, s, a.mod, q, a.fx, a.fy, a.tanx, a.tany, a.V, a.Pm);
+    // the cov3D -> scale / rotation leg is skipped when the caller wants neither gradient (pose-only tracking)
+    const bool scale_leg = has_scale && (a.dL_dscales != nullptr || a.dL_drots != nullptr);
+    chain_setup(g, mean, cov3D, scale_leg, s, a.mod, q, a.fx, a.fy, a.tanx, a.tany, a.V, a.Pm);
     chain_apply(g, dcon.x, dcon.y, dcon.w, dm2x, dm2y, dmean, dcov, dscale, drot);
     if (a.depth_sil) {
       // fused depth/silhouette channels: features (z, 1, z*z) with z = view depth = V[2]x + V[6]y + V[10]z + V[14]
@@ -414,17 +416,22 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
     float* dsh = a.dL_dsh + (size_t)idx * a.M * 3;
     for (int k = 0; k < a.M * 3; ++k) dsh[k] = 0.f;
   }
-  a.dL_dcolor[3 * idx] = dcol.x; a.dL_dcolor[3 * idx + 1] = dcol.y; a.dL_dcolor[3 * idx + 2] = dcol.z;
-  a.dL_dopacity[idx] = dop;
-  a.dL_dmean2D[3 * idx] = dm2x; a.dL_dmean2D[3 * idx + 1] = dm2y; a.dL_dmean2D[3 * idx + 2] = 0.f;
-  reinterpret_cast<float4*>(a.dL_dconic)[idx] = dcon;
+  // every gradient array except dL_dmeans is optional (NULL = the caller does not need it)
+  if (a.dL_dcolor) { a.dL_dcolor[3 * idx] = dcol.x; a.dL_dcolor[3 * idx + 1] = dcol.y; a.dL_dcolor[3 * idx + 2] = dcol.z; }
+  if (a.dL_dopacity) a.dL_dopacity[idx] = dop;
+  if (a.dL_dmean2D) { a.dL_dmean2D[3 * idx] = dm2x; a.dL_dmean2D[3 * idx + 1] = dm2y; a.dL_dmean2D[3 * idx + 2] = 0.f; }
+  if (a.dL_dconic) reinterpret_cast<float4*>(a.dL_dconic)[idx] = dcon;
 #pragma unroll
   for (int k = 0; k < 3; ++k) a.dL_dmeans[3 * idx + k] = dmean[k];
+  if (a.dL_dcov3D) {
 #pragma unroll
-  for (int k = 0; k < 6; ++k) a.dL_dcov3D[6 * idx + k] = dcov[k];
+    for (int k = 0; k < 6; ++k) a.dL_dcov3D[6 * idx + k] = dcov[k];
+  }
+  if (a.dL_dscales) {
 #pragma unroll
-  for (int k = 0; k < 3; ++k) a.dL_dscales[3 * idx + k] = dscale[k];
-  reinterpret_cast<float4*>(a.dL_drots)[idx] = make_float4(drot[0], drot[1], drot[2], drot[3]);
+    for (int k = 0; k < 3; ++k) a.dL_dscales[3 * idx + k] = dscale[k];
+  }
+  if (a.dL_drots) reinterpret_cast<float4*>(a.dL_drots)[idx] = make_float4(drot[0], drot[1], drot[2], drot[3]);
 }
 
 int launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t st) {
@@ -470,7 +477,9 @@ __global__ void __launch_bounds__(128) hessian_finalize_kernel(const HessArgs a)
       if (!a.cov3D_pre) cov3d_from_scale_rot(s, a.mod, q, cov3D);
     }
     GaussChain g;
-    chain_setup(g, mean, cov3D, has_scale, s, a.mod, q, a.fx, a.fy, a.tanx, a.tany, a.V, a.Pm);
+    // the cov3D -> scale / rotation leg is skipped when the caller wants neither gradient (pose-only tracking)
+    const bool scale_leg = has_scale && (a.dL_dscales != nullptr || a.dL_drots != nullptr);
+    chain_setup(g, mean, cov3D, scale_leg, s, a.mod, q, a.fx, a.fy, a.tanx, a.tany, a.V, a.Pm);
     float J[5][16];
 #pragma unroll
     for (int p = 0; p < 5; ++p)

@@ -22,6 +22,8 @@
 // MODE 2 (power == 1, fused RGB + depth + silhouette): six feature channels (r, g, b, z, 1, z*z) share the
 //   pair's alpha and T; row = MODE 0's nine sums + [9] alpha*T*dL/dpix[3] + [10] alpha*T*dL/dpix[5] (the z and z*z
 //   "colour" gradients, which preprocess_bwd turns into dL/dmean through z; the constant channel has no parameter).
+// MODE 3 = MODE 2 for callers that need no colour / opacity gradient (pose-only tracking: splat_backward with
+//   dL_dcolors == dL_dopacity == NULL): the four sums [0..2] and [8] are neither formed nor reduced; same row layout.
 // MODE 1 (power == 2), row = 20 floats: dcolor^2[3], dopacity^2, and the 15 second moments of
 //   v = (dconic.x, dconic.y, dconic.w, dmean2D.x, dmean2D.y); hessian_finalize turns the moments
 //   into sum_pairs (J_k . v)^2 per output k, which is what HX accumulates pair by pair
@@ -38,9 +40,10 @@ template <int MODE> struct BwdTraits;
 template <> struct BwdTraits<0> { static const int VALS = 9, GROUP = 3, STRIDE = 12; };
 template <> struct BwdTraits<1> { static const int VALS = 19, GROUP = 1, STRIDE = 20; };
 template <> struct BwdTraits<2> { static const int VALS = 11, GROUP = 2, STRIDE = 12; };
+template <> struct BwdTraits<3> { static const int VALS = 7, GROUP = 4, STRIDE = 12; };   // MODE 2 without rows 0-2 and 8
 
 #define TR_STRIDE 36                        // words per transposed row (32 lanes + 4 pad)
-#define TR_ROWS 27
+#define TR_ROWS 28
 #define TR_WARP_BYTES (TR_ROWS * TR_STRIDE * 4)
 #define BWD_SMEM (RING_NS * RING_CH * INST_BYTES + CTA_WARPS * TR_WARP_BYTES)
 
@@ -121,9 +124,10 @@ __global__ void __launch_bounds__(RING_THREADS, 3 * CTA_PARTS) render_bwd_kernel
   float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
   if (inside) { dp0 = a.dL_dpix[pix]; dp1 = a.dL_dpix[HW + pix]; dp2 = a.dL_dpix[2 * HW + pix]; }
   float dp3 = 0.f, dp4 = 0.f, dp5 = 0.f;
-  if (MODE == 2 && inside) { dp3 = a.dL_dpix[3 * HW + pix]; dp4 = a.dL_dpix[4 * HW + pix]; dp5 = a.dL_dpix[5 * HW + pix]; }
+  constexpr bool DS = (MODE == 2 || MODE == 3);
+  if (DS && inside) { dp3 = a.dL_dpix[3 * HW + pix]; dp4 = a.dL_dpix[4 * HW + pix]; dp5 = a.dL_dpix[5 * HW + pix]; }
   float bg_dot = __ldg(a.bg) * dp0 + __ldg(a.bg + 1) * dp1 + __ldg(a.bg + 2) * dp2;
-  if (MODE == 2) bg_dot += __ldg(a.bg) * dp3 + __ldg(a.bg + 1) * dp4 + __ldg(a.bg + 2) * dp5;
+  if (DS) bg_dot += __ldg(a.bg) * dp3 + __ldg(a.bg + 1) * dp4 + __ldg(a.bg + 2) * dp5;
   const float nTb = -T_final * bg_dot;
   float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
   // MODE 0/2: features are measured relative to a per-pixel reference level (the rendered value when the caller
@@ -132,7 +136,7 @@ __global__ void __launch_bounds__(RING_THREADS, 3 * CTA_PARTS) render_bwd_kernel
   float k0 = 0.f, k1 = 0.f, k2 = 0.f, k3 = 0.f, k4 = 0.f, k5 = 0.f;
   if (MODE != 1 && a.out_color != nullptr && inside) {
     k0 = a.out_color[pix] * dp0; k1 = a.out_color[HW + pix] * dp1; k2 = a.out_color[2 * HW + pix] * dp2;
-    if (MODE == 2) { k3 = a.out_color[3 * HW + pix] * dp3; k4 = a.out_color[4 * HW + pix] * dp4; k5 = a.out_color[5 * HW + pix] * dp5; }
+    if (DS) { k3 = a.out_color[3 * HW + pix] * dp3; k4 = a.out_color[4 * HW + pix] * dp4; k5 = a.out_color[5 * HW + pix] * dp5; }
   }
   const float c4 = dp4 - k4;
   float Rsum = T_final * (bg_dot - (((k0 + k1) + k2) + ((k3 + k4) + k5)));
@@ -211,7 +215,7 @@ __global__ void __launch_bounds__(RING_THREADS, 3 * CTA_PARTS) render_bwd_kernel
                   // (6 instead of 15 instructions per pair for 3 channels, 10 instead of 29 for the six of MODE 2).
                   // each channel's (c - ref) * dp is ONE fma (exact product, single rounding of the difference)
                   float sdot = (fmaf(col.x, dp0, -k0) + fmaf(col.y, dp1, -k1)) + fmaf(col.z, dp2, -k2);
-                  if (MODE == 2) {
+                  if (DS) {
                     const float z = q1.z;
                     sdot += (fmaf(z, dp3, -k3) + c4) + fmaf(z * z, dp5, -k5);
                   }
@@ -219,7 +223,12 @@ __global__ void __launch_bounds__(RING_THREADS, 3 * CTA_PARTS) render_bwd_kernel
                   Rsum = fmaf(w, sdot, Rsum);
                 }
                 const float c0 = w * dp0, c1 = w * dp1, c2 = w * dp2;
-                if (MODE == 0 || MODE == 2) {
+                if (MODE == 3) {
+                  float* o = &v[gsl * VALS];
+                  const float u = Gv * dLda, udx = u * dx, udy = u * dy;
+                  o[0] = udx; o[1] = udy; o[2] = udx * dx; o[3] = udx * dy; o[4] = udy * dy;
+                  o[5] = w * dp3; o[6] = w * dp5;
+                } else if (MODE == 0 || MODE == 2) {
                   float* o = &v[gsl * VALS];
                   const float u = Gv * dLda, udx = u * dx, udy = u * dy;
                   o[0] = c0; o[1] = c1; o[2] = c2;
@@ -264,7 +273,9 @@ __global__ void __launch_bounds__(RING_THREADS, 3 * CTA_PARTS) render_bwd_kernel
           float tot = 0.f;
           if (mine) tot = row_sum32(tr_ld);
           __syncwarp();
-          if (mine && tot != 0.f) red_add_f32(a.acc + (size_t)id * STRIDE + my_k, tot);
+          // MODE 3 keeps MODE 2's row layout: values 0-4 -> slots 3-7, values 5, 6 -> slots 9, 10
+          const int slot = (MODE == 3) ? (my_k < 5 ? my_k + 3 : my_k + 4) : my_k;
+          if (mine && tot != 0.f) red_add_f32(a.acc + (size_t)id * STRIDE + slot, tot);
         }
       }
     }
@@ -283,9 +294,12 @@ int launch_render_bwd(const RenderBwdArgs& a, int T, int mode, cudaStream_t st) 
     SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
     SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
     SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
+    SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
     attr_set = true;
   }
-  if (mode == 2) {
+  if (mode == 3) {
+    render_bwd_kernel<true, 3><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);
+  } else if (mode == 2) {
     render_bwd_kernel<true, 2><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);
   } else if (mode == 0) {
     if (g_disable_cull) render_bwd_kernel<false, 0><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);

@@ -67,9 +67,11 @@ __device__ __forceinline__ float4 quat_mul(const float* c, const float4 n) {
 
 // ------------------------------------------------------------------------------------------------ builder fwd
 __global__ void __launch_bounds__(256) rendervar_fwd_kernel(const RvArgs a) {
+  __shared__ Pose ps;   // R(q), t: built by one thread per CTA (two square roots + eight divides), broadcast from shared memory
+  if (threadIdx.x == 0) ps = load_pose(a.cam_rots, a.cam_trans, a.n_frames, a.t);
+  __syncthreads();
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i >= a.P) return;
-  const Pose ps = load_pose(a.cam_rots, a.cam_trans, a.n_frames, a.t);
   const float px = a.means[3 * i], py = a.means[3 * i + 1], pz = a.means[3 * i + 2];
   const float4 q = reinterpret_cast<const float4*>(a.unnorm_rots)[i];
   const float lo = a.logit_op[i];
@@ -93,7 +95,9 @@ __global__ void __launch_bounds__(256) rendervar_fwd_kernel(const RvArgs a) {
 
 template <bool GG, bool CG, bool ANISO>
 __global__ void __launch_bounds__(256) rendervar_bwd_kernel(const RvArgs a, float* __restrict__ partial) {
-  const Pose ps = load_pose(a.cam_rots, a.cam_trans, a.n_frames, a.t);
+  __shared__ Pose ps;
+  if (threadIdx.x == 0) ps = load_pose(a.cam_rots, a.cam_trans, a.n_frames, a.t);
+  __syncthreads();
   float s[RV_SUMS];
 #pragma unroll
   for (int k = 0; k < RV_SUMS; ++k) s[k] = 0.f;
@@ -306,110 +310,174 @@ __global__ void __launch_bounds__(256) track_loss_kernel(const LossArgs a, float
   block_partials(s, partial, blockIdx.x);
 }
 
-// ---- mapping loss: 11x11 Gaussian-window SSIM, separable, 32x32 output tile per CTA and channel
+// ---- mapping loss: 11x11 Gaussian-window SSIM, separable, 32x32 output tile per CTA and channel.
+// Both passes are register-blocked: a thread produces 4 adjacent outputs from 14 inputs (horizontal pass: four
+// 128-bit shared loads per image row segment; vertical pass: 14 conflict-free column loads per quantity), so an
+// output costs 3.5 shared-memory words per quantity instead of 11.
 #define ST 32
 #define SHALO 5
-#define SW (ST + 2 * SHALO)   // 42
+#define SW (ST + 2 * SHALO)   // 42 rows / columns incl. halo
+#define SWP 44                // padded input row: 16-byte aligned segments, columns up to 28 + 15
+#define HZP 36                // padded row of the horizontal-pass results
+
+__device__ __forceinline__ void lds16(const float* row, float (&u)[16]) {
+  const float4* r4 = reinterpret_cast<const float4*>(row);
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const float4 q = r4[t];
+    u[4 * t] = q.x; u[4 * t + 1] = q.y; u[4 * t + 2] = q.z; u[4 * t + 3] = q.w;
+  }
+}
 
 __global__ void __launch_bounds__(256) map_loss_fwd_kernel(const LossArgs a, float* __restrict__ partial) {
-  __shared__ float sx[SW][SW + 1], sy[SW][SW + 1];
-  __shared__ float hz[5][SW][ST + 1];
+  __shared__ __align__(16) float sx[SW][SWP], sy[SW][SWP];
+  __shared__ __align__(16) float hz[5][SW][HZP];
   const int W = a.W, H = a.H, N = W * H, c = blockIdx.z;
   const int x0 = blockIdx.x * ST, y0 = blockIdx.y * ST;
   const float* X = a.im + (size_t)c * N;
   const float* Y = a.gt_im + (size_t)c * N;
-  for (int k = threadIdx.x; k < SW * SW; k += 256) {
-    const int ly = k / SW, lx = k - ly * SW, gx = x0 + lx - SHALO, gy = y0 + ly - SHALO;
-    const bool in = gx >= 0 && gx < W && gy >= 0 && gy < H;
+  for (int k = threadIdx.x; k < SW * SWP; k += 256) {
+    const int ly = k / SWP, lx = k - ly * SWP, gx = x0 + lx - SHALO, gy = y0 + ly - SHALO;
+    const bool in = lx < SW && gx >= 0 && gx < W && gy >= 0 && gy < H;
     sx[ly][lx] = in ? X[gy * W + gx] : 0.f;
     sy[ly][lx] = in ? Y[gy * W + gx] : 0.f;
   }
   __syncthreads();
-  for (int k = threadIdx.x; k < SW * ST; k += 256) {
-    const int ly = k / ST, lx = k - ly * ST;
-    float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+  for (int k = threadIdx.x; k < SW * 8; k += 256) {
+    const int ly = k >> 3, lx0 = (k & 7) * 4;
+    float u[16], v[16];
+    lds16(&sx[ly][lx0], u);
+    lds16(&sy[ly][lx0], v);
+    float o[5][4];
 #pragma unroll
-    for (int j = 0; j < 11; ++j) {
-      const float g = a.gauss[j], u = sx[ly][lx + j], v = sy[ly][lx + j];
-      m1 += g * u; m2 += g * v; e11 += g * (u * u); e22 += g * (v * v); e12 += g * (u * v);
+    for (int q = 0; q < 5; ++q)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) o[q][i] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 14; ++j) {
+      const float uu = u[j] * u[j], vv = v[j] * v[j], uv = u[j] * v[j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int t = j - i;
+        if (t >= 0 && t < 11) {
+          const float g = a.gauss[t];
+          o[0][i] += g * u[j]; o[1][i] += g * v[j]; o[2][i] += g * uu; o[3][i] += g * vv; o[4][i] += g * uv;
+        }
+      }
     }
-    hz[0][ly][lx] = m1; hz[1][ly][lx] = m2; hz[2][ly][lx] = e11; hz[3][ly][lx] = e22; hz[4][ly][lx] = e12;
+#pragma unroll
+    for (int q = 0; q < 5; ++q)
+      *reinterpret_cast<float4*>(&hz[q][ly][lx0]) = make_float4(o[q][0], o[q][1], o[q][2], o[q][3]);
   }
   __syncthreads();
   float s[LOSS_SUMS] = {0.f, 0.f, 0.f, 0.f};
   const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
-  for (int k = threadIdx.x; k < ST * ST; k += 256) {
-    const int ly = k / ST, lx = k - ly * ST, gx = x0 + lx, gy = y0 + ly;
-    if (gx >= W || gy >= H) continue;
-    float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+  {
+    const int lx = threadIdx.x & 31, ly0 = (threadIdx.x >> 5) * 4;
+    float o[5][4];
 #pragma unroll
-    for (int j = 0; j < 11; ++j) {
-      const float g = a.gauss[j];
-      m1 += g * hz[0][ly + j][lx]; m2 += g * hz[1][ly + j][lx]; e11 += g * hz[2][ly + j][lx];
-      e22 += g * hz[3][ly + j][lx]; e12 += g * hz[4][ly + j][lx];
+    for (int q = 0; q < 5; ++q)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) o[q][i] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 14; ++j) {
+#pragma unroll
+      for (int q = 0; q < 5; ++q) {
+        const float h = hz[q][ly0 + j][lx];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int t = j - i;
+          if (t >= 0 && t < 11) o[q][i] += a.gauss[t] * h;
+        }
+      }
     }
-    const float s1 = e11 - m1 * m1, s2 = e22 - m2 * m2, s12 = e12 - m1 * m2;
-    const float A = 2.f * m1 * m2 + C1, B = 2.f * s12 + C2, Cc = m1 * m1 + m2 * m2 + C1, D = s1 + s2 + C2;
-    const float inv = 1.f / (Cc * D);
-    const float m = A * B * inv;
-    // partial derivatives of the map value w.r.t. the three window means that depend on the rendered image:
-    // conv(x) [with sigma1, sigma12 depending on it], conv(x*x), conv(x*y)
-    const float d_xy = 2.f * A * inv;
-    const float d_xx = -m / D;
-    const float d_mu = 2.f * m2 * B * inv - 2.f * m1 * m / Cc - m2 * d_xy - 2.f * m1 * d_xx;
-    const size_t p = (size_t)gy * W + gx;
-    a.dmaps[(size_t)(0 * 3 + c) * N + p] = d_mu;
-    a.dmaps[(size_t)(1 * 3 + c) * N + p] = d_xx;
-    a.dmaps[(size_t)(2 * 3 + c) * N + p] = d_xy;
-    s[0] += m;
-    s[1] += fabsf(sx[ly + SHALO][lx + SHALO] - sy[ly + SHALO][lx + SHALO]);
-    if (c == 0) {
-      const float d = a.depth_sil[p], sil = a.depth_sil[N + p], d2 = a.depth_sil[2 * N + p], gd = a.gt_depth[p];
-      const bool mk = loss_mask(gd, d, d2, sil, false, 0.f);
-      s[2] += mk ? fabsf(gd - d) : 0.f;
-      s[3] += mk ? 1.f : 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int ly = ly0 + i, gx = x0 + lx, gy = y0 + ly;
+      if (gx >= W || gy >= H) continue;
+      const float m1 = o[0][i], m2 = o[1][i], e11 = o[2][i], e22 = o[3][i], e12 = o[4][i];
+      const float s1 = e11 - m1 * m1, s2 = e22 - m2 * m2, s12 = e12 - m1 * m2;
+      const float A = 2.f * m1 * m2 + C1, B = 2.f * s12 + C2, Cc = m1 * m1 + m2 * m2 + C1, D = s1 + s2 + C2;
+      const float inv = 1.f / (Cc * D);
+      const float m = A * B * inv;
+      // partial derivatives of the map value w.r.t. the three window means that depend on the rendered image:
+      // conv(x) [with sigma1, sigma12 depending on it], conv(x*x), conv(x*y)
+      const float d_xy = 2.f * A * inv;
+      const float d_xx = -m / D;
+      const float d_mu = 2.f * m2 * B * inv - 2.f * m1 * m / Cc - m2 * d_xy - 2.f * m1 * d_xx;
+      const size_t p = (size_t)gy * W + gx;
+      a.dmaps[(size_t)(0 * 3 + c) * N + p] = d_mu;
+      a.dmaps[(size_t)(1 * 3 + c) * N + p] = d_xx;
+      a.dmaps[(size_t)(2 * 3 + c) * N + p] = d_xy;
+      s[0] += m;
+      s[1] += fabsf(sx[ly + SHALO][lx + SHALO] - sy[ly + SHALO][lx + SHALO]);
+      if (c == 0) {
+        const float d = a.depth_sil[p], sil = a.depth_sil[N + p], d2 = a.depth_sil[2 * N + p], gd = a.gt_depth[p];
+        const bool mk = loss_mask(gd, d, d2, sil, false, 0.f);
+        s[2] += mk ? fabsf(gd - d) : 0.f;
+        s[3] += mk ? 1.f : 0.f;
+      }
     }
   }
   block_partials(s, partial, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x);
 }
 
 __global__ void __launch_bounds__(256) map_loss_bwd_kernel(const LossArgs a, const float* __restrict__ stats) {
-  __shared__ float sm[3][SW][SW + 1];
-  __shared__ float hz[3][SW][ST + 1];
+  __shared__ __align__(16) float sm[3][SW][SWP];
+  __shared__ __align__(16) float hz[3][SW][HZP];
   const int W = a.W, H = a.H, N = W * H, c = blockIdx.z;
   const int x0 = blockIdx.x * ST, y0 = blockIdx.y * ST;
-  for (int k = threadIdx.x; k < SW * SW; k += 256) {
-    const int ly = k / SW, lx = k - ly * SW, gx = x0 + lx - SHALO, gy = y0 + ly - SHALO;
-    const bool in = gx >= 0 && gx < W && gy >= 0 && gy < H;
+  for (int k = threadIdx.x; k < SW * SWP; k += 256) {
+    const int ly = k / SWP, lx = k - ly * SWP, gx = x0 + lx - SHALO, gy = y0 + ly - SHALO;
+    const bool in = lx < SW && gx >= 0 && gx < W && gy >= 0 && gy < H;
 #pragma unroll
     for (int q = 0; q < 3; ++q) sm[q][ly][lx] = in ? a.dmaps[(size_t)(q * 3 + c) * N + (size_t)gy * W + gx] : 0.f;
   }
   __syncthreads();
-  for (int k = threadIdx.x; k < SW * ST; k += 256) {
-    const int ly = k / ST, lx = k - ly * ST;
-    float h0 = 0.f, h1 = 0.f, h2 = 0.f;
+  for (int k = threadIdx.x; k < SW * 8; k += 256) {
+    const int ly = k >> 3, lx0 = (k & 7) * 4;
 #pragma unroll
-    for (int j = 0; j < 11; ++j) {
-      const float g = a.gauss[j];
-      h0 += g * sm[0][ly][lx + j]; h1 += g * sm[1][ly][lx + j]; h2 += g * sm[2][ly][lx + j];
+    for (int q = 0; q < 3; ++q) {
+      float u[16];
+      lds16(&sm[q][ly][lx0], u);
+      float o[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int j = 0; j < 14; ++j)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int t = j - i;
+          if (t >= 0 && t < 11) o[i] += a.gauss[t] * u[j];
+        }
+      *reinterpret_cast<float4*>(&hz[q][ly][lx0]) = make_float4(o[0], o[1], o[2], o[3]);
     }
-    hz[0][ly][lx] = h0; hz[1][ly][lx] = h1; hz[2][ly][lx] = h2;
   }
   __syncthreads();
   const float inv3N = 1.f / (3.f * (float)N);
   const float inv_cnt = 1.f / stats[3];
-  for (int k = threadIdx.x; k < ST * ST; k += 256) {
-    const int ly = k / ST, lx = k - ly * ST, gx = x0 + lx, gy = y0 + ly;
-    if (gx >= W || gy >= H) continue;
-    float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+  const int lx = threadIdx.x & 31, ly0 = (threadIdx.x >> 5) * 4;
+  float o[3][4];
 #pragma unroll
-    for (int j = 0; j < 11; ++j) {
-      const float g = a.gauss[j];
-      v0 += g * hz[0][ly + j][lx]; v1 += g * hz[1][ly + j][lx]; v2 += g * hz[2][ly + j][lx];
+  for (int q = 0; q < 3; ++q)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) o[q][i] = 0.f;
+#pragma unroll
+  for (int j = 0; j < 14; ++j)
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+      const float h = hz[q][ly0 + j][lx];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int t = j - i;
+        if (t >= 0 && t < 11) o[q][i] += a.gauss[t] * h;
+      }
     }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int gx = x0 + lx, gy = y0 + ly0 + i;
+    if (gx >= W || gy >= H) continue;
     const size_t p = (size_t)gy * W + gx;
     const float x = a.im[(size_t)c * N + p], y = a.gt_im[(size_t)c * N + p];
-    const float dssim = v0 + 2.f * x * v1 + y * v2;
+    const float dssim = o[0][i] + 2.f * x * o[1][i] + y * o[2][i];
     a.g_im[(size_t)c * N + p] = a.w_im * inv3N * (0.8f * sgn(x - y) - 0.2f * dssim);
     if (c == 0) {
       const float d = a.depth_sil[p], sil = a.depth_sil[N + p], d2 = a.depth_sil[2 * N + p], gd = a.gt_depth[p];
@@ -480,6 +548,60 @@ int launch_slam_loss(const LossArgs& a, float* partial, float* stats, cudaStream
   SPLAT_LAUNCH_CHECK("loss_finalize_kernel");
   map_loss_bwd_kernel<<<grid, 256, 0, st>>>(a, stats);
   SPLAT_LAUNCH_CHECK("map_loss_bwd_kernel");
+  return SPLAT_OK;
+}
+
+// ================================================================================================ Adam
+// One launch for every parameter tensor of the optimizer (SplaTAM: 5 Gaussian tensors + 2 pose tensors,
+// scripts/splatam.py:166-172 builds one param group per tensor, each with its own lr): torch.optim.Adam's foreach path
+// runs ~8 multi-tensor kernels and several hundred microseconds of host code per step.  Arithmetic follows
+// torch/optim/adam.py::_single_tensor_adam (lerp, mul+addcmul, sqrt/bias2_sqrt + eps, addcdiv).
+// HBM roofline: 16 B read + 12 B written per element.
+__global__ void __launch_bounds__(256) adam_kernel(const AdamArgs a) {
+  int t = 0;
+  int b = (int)blockIdx.x;
+#pragma unroll 1
+  while (t < a.count - 1 && b >= a.blocks[t]) { b -= a.blocks[t]; ++t; }
+  const SplatAdamTensorK& T = a.t[t];
+  const float lr1 = T.lr / T.bias_correction1, inv_b2 = 1.f / T.bias_correction2_sqrt;
+  const float w1 = a.w1, w2 = a.w2;
+  const int64_t base = (int64_t)b * 1024 + threadIdx.x * 4;
+  if (base >= T.n) return;
+  if (T.vec && base + 4 <= T.n) {
+    const float4 g = *reinterpret_cast<const float4*>(T.grad + base);
+    float4 m = *reinterpret_cast<float4*>(T.exp_avg + base);
+    float4 v = *reinterpret_cast<float4*>(T.exp_avg_sq + base);
+    float4 p = *reinterpret_cast<float4*>(T.param + base);
+#define ADAM1(c)                                                        \
+    m.c = m.c + w1 * (g.c - m.c);                                       \
+    v.c = v.c * a.beta2 + w2 * (g.c * g.c);                             \
+    p.c = p.c - lr1 * (m.c / (sqrtf(v.c) * inv_b2 + a.eps));
+    ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
+#undef ADAM1
+    *reinterpret_cast<float4*>(T.exp_avg + base) = m;
+    *reinterpret_cast<float4*>(T.exp_avg_sq + base) = v;
+    *reinterpret_cast<float4*>(T.param + base) = p;
+  } else {
+    for (int64_t i = base; i < T.n && i < base + 4; ++i) {
+      const float g = T.grad[i];
+      const float m = T.exp_avg[i] + w1 * (g - T.exp_avg[i]);
+      const float v = T.exp_avg_sq[i] * a.beta2 + w2 * (g * g);
+      T.exp_avg[i] = m; T.exp_avg_sq[i] = v;
+      T.param[i] = T.param[i] - lr1 * (m / (sqrtf(v) * inv_b2 + a.eps));
+    }
+  }
+}
+
+int launch_adam(AdamArgs& a, cudaStream_t st) {
+  ProfScope prof_(K_ADAM, st);
+  int total = 0;
+  for (int i = 0; i < a.count; ++i) {
+    a.blocks[i] = (int)((a.t[i].n + 1023) / 1024);
+    total += a.blocks[i];
+  }
+  if (total == 0) return SPLAT_OK;
+  adam_kernel<<<total, 256, 0, st>>>(a);
+  SPLAT_LAUNCH_CHECK("adam_kernel");
   return SPLAT_OK;
 }
 

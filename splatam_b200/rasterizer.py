@@ -200,7 +200,7 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
             launched = True
         if bwd is not None:
             st.plan = _plan_backward(st, dev, bwd[0], bwd[1], means3D, colors_precomp, scales, rotations,
-                                     cov3D_precomp, sh, radii, bwd[2])
+                                     cov3D_precomp, sh, radii, bwd[2], bwd[3] if len(bwd) > 3 else frozenset())
         t_w = time.perf_counter()
         ev.synchronize()
         host_stats["wait_s"] += time.perf_counter() - t_w
@@ -240,7 +240,8 @@ def _collect_sinks(**named):
     return sinks or None
 
 
-def _plan_backward(st, dev, power, fused, means3D, colors_precomp, scales, rotations, cov3D_precomp, sh, radii, sinks):
+def _plan_backward(st, dev, power, fused, means3D, colors_precomp, scales, rotations, cov3D_precomp, sh, radii, sinks,
+                   skip=frozenset()):
     """Everything of the backward call that does not depend on dL/dcolour: the flat gradient/scratch allocation, the
     returned views and the packed C arguments.  rasterize_forward runs this BEFORE it blocks on the num_rendered
     read-back, so that after the wake-up the host only has to hand the backward launch to the (then busy) GPU."""
@@ -249,13 +250,19 @@ def _plan_backward(st, dev, power, fused, means3D, colors_precomp, scales, rotat
     hess = bool(fused) and int(power) != 1
     n_scratch = lib.splat_backward_scratch_bytes(P, 2 if hess else 1) // 4
     sinks = sinks if (sinks and P) else {}
+    # `skip`: gradient arrays nobody asked for (autograd's needs_input_grad) are neither allocated nor written
+    # (splat_backward takes NULL for them); only the plain power-1, non-SH backward supports that
+    if hess or M:
+        skip = frozenset()
+    if skip:
+        skip = skip | {"conic"}
     # one flat allocation: [scratch | rotations 4 | conic 4 | means3D 3 | means2D 3 | colors 3 | opacity 1 |
     # scales 3 | cov3D 6 | sh 3M]; float4-accessed arrays first so they stay 16-byte aligned for any P (torch
     # allocations are 512-byte aligned).  Arrays that have a sink are not carved at all.
     layout = (("rotations", 4, (P, 4)), ("conic", 4, None), ("means3D", 3, (P, 3)), ("means2D", 3, (P, 3)),
               ("colors_precomp", 3, (P, 3)), ("opacities", 1, (P, 1)), ("scales", 3, (P, 3)), ("cov3D", 6, (P, 6)),
               ("sh", 3 * M, (P, M, 3)))
-    total = n_scratch + sum(P * k for name, k, _ in layout if name not in sinks)
+    total = n_scratch + sum(P * k for name, k, _ in layout if name not in sinks and name not in skip)
     flat = torch.empty(total, dtype=torch.float32, device=dev)
     base = flat.data_ptr()
     ptrs, outs = {}, {}
@@ -264,31 +271,34 @@ def _plan_backward(st, dev, power, fused, means3D, colors_precomp, scales, rotat
         if name in sinks:
             ptrs[name] = sinks[name].data_ptr()
             continue
+        if name in skip:
+            ptrs[name] = 0
+            continue
         ptrs[name] = base + 4 * off if P * k else 0
         if shape is not None:
             outs[name] = flat[off:off + P * k].view(shape)
         off += P * k
-    result = (outs.get("means3D"), outs["means2D"], outs["sh"], outs.get("colors_precomp"), outs.get("opacities"),
-              outs.get("scales"), outs.get("rotations"), outs["cov3D"])
+    result = (outs.get("means3D"), outs.get("means2D"), outs.get("sh"), outs.get("colors_precomp"), outs.get("opacities"),
+              outs.get("scales"), outs.get("rotations"), outs.get("cov3D"))
     vp = C.c_void_p
     head = (_ptr(means3D), _ptr(scales), _ptr(rotations), _ptr(cov3D_precomp), _ptr(sh), M, _ptr(colors_precomp),
             _ptr(radii))
     tail = (int(power), int(bool(fused)), vp(ptrs["means3D"]), vp(ptrs["means2D"]), vp(ptrs["colors_precomp"]),
             vp(ptrs["opacities"]), vp(ptrs["scales"]), vp(ptrs["rotations"]), vp(ptrs["cov3D"]), vp(ptrs["conic"]),
             vp(ptrs["sh"]), vp(base), n_scratch * 4)
-    return dict(flat=flat, result=result, head=head, tail=tail, key=(int(power), bool(fused)))
+    return dict(flat=flat, result=result, head=head, tail=tail, key=(int(power), bool(fused), skip))
 
 
 def rasterize_backward(rs, near, st, power, fused, means3D, colors_precomp, scales, rotations,
-                       cov3D_precomp, sh, radii, grad_out_color, sinks=None, out_color=None):
+                       cov3D_precomp, sh, radii, grad_out_color, sinks=None, out_color=None, skip=frozenset()):
     dev = means3D.device
     P = st.P
     with _on_device(dev):
         plan = st.plan
         st.plan = None   # a plan's buffers are handed to autograd once
-        if plan is None or plan["key"] != (int(power), bool(fused)):
+        if plan is None or plan["key"][:2] != (int(power), bool(fused)):
             plan = _plan_backward(st, dev, power, fused, means3D, colors_precomp, scales, rotations, cov3D_precomp, sh,
-                                  radii, sinks)
+                                  radii, sinks, skip)
         if P == 0:
             return plan["result"]
         stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
@@ -316,7 +326,15 @@ class _RasterizeGaussians(torch.autograd.Function):
                         ("rotations", rotations), ("cov3D_precomp", cov3Ds_precomp)):
             if t.numel() and (t.dtype != torch.float32 or not t.is_cuda):
                 raise RuntimeError("%s must be a float32 CUDA tensor" % name)
-        bwd = (backward_power, fused, sinks) if any(ctx.needs_input_grad) else None
+        # inputs that do not require a gradient (e.g. everything but the means in pose-only tracking) are skipped by
+        # the backward kernels; means3D's gradient is always formed
+        need = ctx.needs_input_grad
+        skip = frozenset(n for n, i in (("means2D", 1), ("colors_precomp", 3), ("opacities", 4), ("scales", 5),
+                                        ("rotations", 6), ("cov3D", 7)) if not need[i])
+        if not {"colors_precomp", "opacities"} <= skip:
+            skip = skip - {"colors_precomp", "opacities"}   # the blend backward drops these sums only together
+        ctx.skip = skip
+        bwd = (backward_power, fused, sinks, skip) if any(need) else None
         color, radii, depth, st = rasterize_forward(raster_settings, near, means3D, colors_precomp, opacities,
                                                     scales, rotations, cov3Ds_precomp, sh, bwd, depth_sil)
         ctx.depth_sil = depth_sil
@@ -348,7 +366,7 @@ class _RasterizeGaussians(torch.autograd.Function):
             raise RuntimeError("grad of the rendered image must be [%d,%d,%d]" % (nch, ctx.state.H, ctx.state.W))
         (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D) = rasterize_backward(
             ctx.raster_settings, ctx.near, ctx.state, ctx.backward_power, ctx.fused, means3D, colors_precomp,
-            scales, rotations, cov3Ds_precomp, sh, radii, grad_out_color, ctx.sinks, ctx.out_color)
+            scales, rotations, cov3Ds_precomp, sh, radii, grad_out_color, ctx.sinks, ctx.out_color, ctx.skip)
         ctx.out_color = None
         sunk = ctx.sinks or {}
         return (g_means3D if "means3D" not in sunk else None, g_means2D,

@@ -18,6 +18,7 @@ import ctypes as C
 
 import torch
 
+from . import _lib
 from ._lib import check, lib
 from .rasterizer import _f32, _on_device
 
@@ -61,6 +62,21 @@ class _BuildRendervar(torch.autograd.Function):
         ctx.save_for_backward(means3D, unnorm_rotations, logit_opacities, log_scales, cam_unnorm_rots, cam_trans)
         ctx.cfg = (P, sd, F, int(time_idx), bool(gaussians_grad), bool(camera_grad))
         ctx.set_materialize_grads(False)
+        # an output is differentiable only if something it depends on wants a gradient: the rasterizer's backward
+        # skips the gradient arrays of inputs that do not (pose-only tracking: everything but the means)
+        need = ctx.needs_input_grad
+        cam = bool(camera_grad) and (need[4] or need[5])
+        dead = []
+        if not need[2]:
+            dead.append(opac)
+        if not need[3]:
+            dead.append(scales)
+        if not ((gaussians_grad and need[1]) or (sd == 3 and cam)):
+            dead.append(rots)
+        if not ((gaussians_grad and need[0]) or cam):
+            dead.append(means)
+        if dead:
+            ctx.mark_non_differentiable(*dead)
         return means, rots, opac, scales
 
     @staticmethod
@@ -104,16 +120,22 @@ class _BuildRendervar(torch.autograd.Function):
                 d_cr if need[4] else None, d_ct if need[5] else None, None, None, None)
 
 
-def build_rendervar(params, time_idx, gaussians_grad, camera_grad):
+def build_rendervar(params, time_idx, gaussians_grad, camera_grad, pose_only=False):
     """transform_to_frame + transformed_params2rendervar in one kernel (utils/slam_helpers.py:253-304, :123-139).
-    Returns the reference's rendervar dict (means3D, colors_precomp, rotations, opacities, scales, means2D)."""
+    Returns the reference's rendervar dict (means3D, colors_precomp, rotations, opacities, scales, means2D).
+
+    pose_only (opt-in, tracking): the reference lets colour / opacity / scale gradients flow during tracking although its
+    tracking optimizer has lr = 0 for them and is discarded after the frame (scripts/splatam.py:700,
+    configs/*/splatam.py `tracking.lrs`).  With pose_only those inputs are detached, so the backward kernels form the
+    pose gradient only; cam_unnorm_rots.grad / cam_trans.grad are unchanged, the Gaussian .grad fields stay None."""
+    det = (lambda t: t.detach()) if pose_only else (lambda t: t)
     means, rots, opac, scales = _BuildRendervar.apply(
-        params['means3D'], params['unnorm_rotations'], params['logit_opacities'], params['log_scales'],
+        params['means3D'], params['unnorm_rotations'], det(params['logit_opacities']), det(params['log_scales']),
         params['cam_unnorm_rots'], params['cam_trans'], time_idx, gaussians_grad, camera_grad)
-    return {'means3D': means, 'colors_precomp': params['rgb_colors'], 'rotations': rots, 'opacities': opac,
+    return {'means3D': means, 'colors_precomp': det(params['rgb_colors']), 'rotations': rots, 'opacities': opac,
             'scales': scales,
             # a leaf that only ever receives a gradient (the reference adds `+ 0` and calls retain_grad(), :135)
-            'means2D': torch.zeros_like(params['means3D'], requires_grad=True)}
+            'means2D': torch.zeros_like(params['means3D'], requires_grad=not pose_only)}
 
 
 # ------------------------------------------------------------------------------------------------ 8f-3
@@ -203,8 +225,10 @@ def _default_renderer():
 def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_for_loss,
              sil_thres, use_l1, ignore_outlier_depth_loss, tracking=False,
              mapping=False, do_ba=False, plot_dir=None, visualize_tracking_loss=False, tracking_iteration=None,
-             Renderer=None):
-    """Same signature and return value as the reference's get_loss (scripts/splatam.py:220-353)."""
+             Renderer=None, tracking_pose_only=False):
+    """Same signature and return value as the reference's get_loss (scripts/splatam.py:220-353).  Two trailing
+    extras: Renderer (rasterizer class, default the diff_gaussian_rasterization shim) and tracking_pose_only (see
+    build_rendervar: skip the Gaussian-side gradients the reference computes and discards while tracking)."""
     if not use_l1 or ignore_outlier_depth_loss:
         raise NotImplementedError("fused get_loss covers use_l1=True, ignore_outlier_depth_loss=False (all shipped configs)")
     if visualize_tracking_loss:
@@ -215,7 +239,8 @@ def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_
         gg, cg = True, True
     else:
         gg, cg = True, False
-    rendervar = build_rendervar(params, iter_time_idx, gaussians_grad=gg, camera_grad=cg)
+    rendervar = build_rendervar(params, iter_time_idx, gaussians_grad=gg, camera_grad=cg,
+                                pose_only=bool(tracking and tracking_pose_only))
     Renderer = Renderer or _default_renderer()
     out, radius, _ = Renderer(raster_settings=curr_data['cam']).render_rgbd_sil(**rendervar)
     variables['means2D'] = rendervar['means2D']
@@ -227,3 +252,60 @@ def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_
     torch.maximum(m2r, radius.to(m2r.dtype), out=m2r)
     variables['seen'] = radius > 0
     return loss, variables, weighted_losses
+
+
+# ------------------------------------------------------------------------------------------------ optimizer step
+class FusedAdam(torch.optim.Optimizer):
+    """`torch.optim.Adam(param_groups[, lr=0.0, eps=1e-15])` as SplaTAM builds it (initialize_optimizer,
+    scripts/splatam.py:166-172: one param group per tensor with its own lr) with the whole step in ONE kernel launch
+    (`splat_adam_step`) and ~40 us of host code; torch's foreach path costs 0.3-0.8 ms per iteration here, more than
+    the fused tracking iteration itself.  Same constructor arguments, same `param_groups` / `state[p]` layout
+    (`step`, `exp_avg`, `exp_avg_sq`), so the reference's optimizer surgery (cat_params_to_optimizer, remove_points,
+    update_params_and_optimizer: utils/slam_external.py:107-165) works on it unchanged.  weight_decay / amsgrad /
+    maximize are not supported (SplaTAM never sets them)."""
+
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0, amsgrad=False):
+        if weight_decay != 0 or amsgrad:
+            raise NotImplementedError("FusedAdam: weight_decay / amsgrad are not supported")
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=0, amsgrad=False))
+        self._desc = (_lib.SplatAdamTensor * 16)()
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        batches = {}
+        for group in self.param_groups:
+            key = (float(group['betas'][0]), float(group['betas'][1]), float(group['eps']))
+            lr = float(group['lr'])
+            for p in group['params']:
+                g = p.grad
+                if g is None:
+                    continue
+                if p.dtype != torch.float32 or not p.is_cuda or not p.is_contiguous():
+                    raise RuntimeError("FusedAdam needs contiguous float32 CUDA parameters")
+                state = self.state[p]
+                if len(state) == 0:
+                    state['step'] = torch.tensor(0.0)
+                    state['exp_avg'] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                    state['exp_avg_sq'] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                state['step'] += 1
+                t = float(state['step'])
+                if not g.is_contiguous():
+                    g = g.contiguous()
+                batches.setdefault((p.device, key), []).append(
+                    (p, g, state['exp_avg'], state['exp_avg_sq'], lr, 1.0 - key[0] ** t, (1.0 - key[1] ** t) ** 0.5))
+        for (dev, (b1, b2, eps)), items in batches.items():
+            with _on_device(dev):
+                stream = _stream()
+                for i0 in range(0, len(items), 16):
+                    chunk = items[i0:i0 + 16]
+                    d = self._desc
+                    for i, (p, g, m, v, lr, bc1, bc2s) in enumerate(chunk):
+                        e = d[i]
+                        e.param, e.grad, e.exp_avg, e.exp_avg_sq = p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr()
+                        e.n, e.lr, e.bias_correction1, e.bias_correction2_sqrt = p.numel(), lr, bc1, bc2s
+                    check(lib.splat_adam_step(d, len(chunk), b1, b2, eps, stream))
+        return loss

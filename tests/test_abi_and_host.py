@@ -107,6 +107,18 @@ def test_slam_glue_entry_points_validate_before_cuda():
     assert rc == 2 and b"scratch" in lib.splat_last_error()
 
 
+def test_adam_entry_point_validates_before_cuda():
+    from splatam_b200._lib import SplatAdamTensor, lib
+    d = (SplatAdamTensor * 16)()
+    assert lib.splat_adam_step(d, 0, 0.9, 0.999, 1e-8, None) == 0
+    assert lib.splat_adam_step(d, 17, 0.9, 0.999, 1e-8, None) == 1
+    assert lib.splat_adam_step(None, 1, 0.9, 0.999, 1e-8, None) == 1
+    d[0].n = 8
+    assert lib.splat_adam_step(d, 1, 0.9, 0.999, 1e-8, None) == 1 and b"NULL" in lib.splat_last_error()
+    d[0].param = d[0].grad = d[0].exp_avg = d[0].exp_avg_sq = 256
+    assert lib.splat_adam_step(d, 1, 0.9, 0.999, 1e-8, None) == 1 and b"bias" in lib.splat_last_error()
+
+
 def test_slam_module_mirrors_reference_signatures():
     """splatam_b200.slam.get_loss keeps the parameter list of scripts/splatam.py:220-222 (plus a trailing Renderer=)."""
     from splatam_b200 import slam
@@ -118,8 +130,8 @@ def test_slam_module_mirrors_reference_signatures():
         slam.get_loss({}, {}, {}, 0, {}, True, 0.99, True, True, tracking=True)
     with pytest.raises(NotImplementedError):
         slam.get_loss({}, {}, {}, 0, {}, True, 0.99, False, False, tracking=True)
-    assert list(inspect.signature(slam.build_rendervar).parameters) == ["params", "time_idx", "gaussians_grad",
-                                                                          "camera_grad"]
+    assert list(inspect.signature(slam.build_rendervar).parameters)[:4] == ["params", "time_idx", "gaussians_grad",
+                                                                              "camera_grad"]
 
 
 @pytest.mark.parametrize("pkg,near,has_power", [("diff_gaussian_rasterization", 0.2, False),

@@ -211,3 +211,92 @@ def test_fused_get_loss_vs_reference_flow(mode):
         _close(ga, gb, 2e-3, "grad " + k, atol=1e-8 if k == "unnorm_rotations" else 0.0)
         if k.startswith("cam_"):
             assert (float(ga.abs().max()) > 0) == cg, k
+
+
+def test_pose_only_tracking_matches_full_backward():
+    """tracking_pose_only skips the Gaussian-side gradients (blend-backward MODE 3, no colour / opacity sums, no scale /
+    rotation chain): the pose gradient and the loss must not move; the Gaussian .grad fields stay None."""
+    from splatam_b200 import slam
+    base, curr = _slam_scene(6000, True)
+    wts = dict(im=0.5, depth=1.0)
+    out = {}
+    for lite in (False, True):
+        p = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+        va = {"max_2D_radius": torch.zeros(6000, device=DEV)}
+        loss, va, wl = slam.get_loss(p, curr, va, 1, wts, True, 0.99, True, False, tracking=True,
+                                     tracking_pose_only=lite)
+        loss.backward()
+        out[lite] = (loss.detach(), p)
+    _close(out[True][0], out[False][0], 1e-7, "loss")
+    for k in ("cam_unnorm_rots", "cam_trans"):
+        assert float(out[False][1][k].grad.abs().max()) > 0
+        _close(out[True][1][k].grad, out[False][1][k].grad, 1e-4, "pose-only grad " + k)
+    for k in ("means3D", "rgb_colors", "unnorm_rotations", "logit_opacities", "log_scales"):
+        assert out[True][1][k].grad is None, k
+    assert out[False][1]["rgb_colors"].grad is not None and out[False][1]["logit_opacities"].grad is not None
+
+
+@pytest.mark.parametrize("six", [False, True], ids=["3ch", "6ch"])
+def test_rasterizer_backward_skips_unneeded_gradients(six):
+    """Only means3D requires a gradient: splat_backward gets NULL for every other array; dL/dmeans3D is unchanged."""
+    from diff_gaussian_rasterization import GaussianRasterizer
+    from util import build_case
+    rs, sc, dL = build_case("surface_small", "cuda")
+    if six:
+        g = torch.Generator().manual_seed(3)
+        dL = torch.cat([dL, torch.randn(3, rs.image_height, rs.image_width, generator=g).to(DEV) * 0.3], 0)
+    grads = {}
+    for only_means in (False, True):
+        leaves = {k: v.clone().requires_grad_(k == "means3D" or not only_means) for k, v in sc.items()}
+        m2d = torch.zeros_like(leaves["means3D"], requires_grad=not only_means)
+        r = GaussianRasterizer(rs)
+        img, radii, _ = (r.render_rgbd_sil if six else r.forward)(means2D=m2d, **leaves)
+        img.backward(dL)
+        grads[only_means] = leaves
+    _close(grads[True]["means3D"].grad, grads[False]["means3D"].grad, 1e-4, "dL/dmeans3D")
+    for k in ("scales", "rotations", "opacities", "colors_precomp"):
+        assert grads[True][k].grad is None and grads[False][k].grad is not None
+
+
+@pytest.mark.parametrize("eps,lr0", [(1e-15, 0.0), (1e-8, 1e-3)], ids=["mapping", "tracking"])
+def test_fused_adam_vs_torch_adam(eps, lr0):
+    """splat_adam_step / slam.FusedAdam against torch.optim.Adam built the way initialize_optimizer does
+    (scripts/splatam.py:166-172): ragged sizes (vector + scalar tails), a group without a gradient, several steps."""
+    from splatam_b200 import slam
+    g = torch.Generator().manual_seed(8)
+    shapes = {"means3D": (100003, 3), "rgb_colors": (100003, 3), "unnorm_rotations": (100003, 4),
+              "logit_opacities": (100003, 1), "log_scales": (100003, 1), "cam_unnorm_rots": (1, 4, 7), "cam_trans": (1, 3, 7)}
+    lrs = dict(means3D=0.0001, rgb_colors=0.0025, unnorm_rotations=0.001, logit_opacities=0.05, log_scales=0.001,
+               cam_unnorm_rots=0.0004, cam_trans=0.002)
+    init = {k: torch.randn(*s, generator=g).to(DEV) for k, s in shapes.items()}
+    pa = {k: v.clone().requires_grad_(True) for k, v in init.items()}
+    pb = {k: v.clone().requires_grad_(True) for k, v in init.items()}
+    mk = lambda cls, p: cls([{'params': [v], 'name': k, 'lr': lrs[k]} for k, v in p.items()], lr=lr0, eps=eps)
+    oa, ob = mk(slam.FusedAdam, pa), mk(torch.optim.Adam, pb)
+    for step in range(12):
+        for k in pa:
+            if k == "log_scales" and step % 3 == 0:      # no gradient this step: its state must not advance
+                pa[k].grad = pb[k].grad = None
+                continue
+            gr = torch.randn(*shapes[k], generator=g).to(DEV) * (10.0 ** (step % 4 - 2))
+            pa[k].grad, pb[k].grad = gr.clone(), gr.clone()
+        oa.step()
+        ob.step()
+    for k in pa:
+        _close(pa[k].detach(), pb[k].detach(), 2e-6, "param " + k)
+        sa, sb = oa.state[pa[k]], ob.state[pb[k]]
+        assert float(sa["step"]) == float(sb["step"])
+        _close(sa["exp_avg"], sb["exp_avg"], 2e-6, "exp_avg " + k)
+        _close(sa["exp_avg_sq"], sb["exp_avg_sq"], 2e-6, "exp_avg_sq " + k)
+    # the reference's optimizer surgery keeps working: cat_params_to_optimizer pattern (utils/slam_external.py:122-136)
+    grp = [x for x in oa.param_groups if x["name"] == "means3D"][0]
+    st = oa.state.get(grp["params"][0])
+    extra = torch.zeros(5, 3, device=DEV)
+    st["exp_avg"] = torch.cat((st["exp_avg"], torch.zeros_like(extra)), 0)
+    st["exp_avg_sq"] = torch.cat((st["exp_avg_sq"], torch.zeros_like(extra)), 0)
+    del oa.state[grp["params"][0]]
+    grp["params"][0] = torch.nn.Parameter(torch.cat((grp["params"][0], extra), 0).requires_grad_(True))
+    oa.state[grp["params"][0]] = st
+    grp["params"][0].grad = torch.ones_like(grp["params"][0])
+    oa.step()
+    assert float(oa.state[grp["params"][0]]["step"]) == 13.0 and bool(torch.isfinite(grp["params"][0]).all())
