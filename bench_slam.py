@@ -87,6 +87,10 @@ def main():
     ap.add_argument("--optimizer", default="none", choices=["none", "torch", "fused"],
                     help="include the per-iteration optimizer step + zero_grad in the timed iteration: torch = "
                          "torch.optim.Adam as the reference builds it, fused = splatam_b200.slam.FusedAdam (ours only)")
+    ap.add_argument("--graph", type=int, default=0, metavar="ITERS",
+                    help="ours + --optimizer fused: per frame, run ITERS iterations as 1 eager one + one CUDA-graph capture "
+                         "+ (ITERS-1) replays (slam.GraphedIteration); 40 = Replica tracking, 200 = TUM; capture cost is "
+                         "inside the timed region")
     ap.add_argument("--steps", type=int, default=96)
     ap.add_argument("--warmup", type=int, default=8)
     args = ap.parse_args()
@@ -178,9 +182,20 @@ def main():
     sampler.mark_start()
     t0 = time.perf_counter()
     e0.record()
-    for i in range(args.steps):
-        zero()
-        loss = step((7 * i) % nf)
+    if args.graph:
+        assert args.impl == "ours" and args.optimizer == "fused", "--graph needs --impl ours --optimizer fused"
+        frames = max(1, args.steps // args.graph)
+        args.steps = frames * args.graph
+        for f in range(frames):   # one tracked frame: same keyframe for all of its iterations (scripts/splatam.py:710-758)
+            kf = (7 * f) % nf
+            it = slam.GraphedIteration(lambda: step(kf), params, opt, warmup=1)
+            for _ in range(args.graph - 1):
+                loss = it.replay()
+            it.check()
+    else:
+        for i in range(args.steps):
+            zero()
+            loss = step((7 * i) % nf)
     e1.record()
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
@@ -192,7 +207,7 @@ def main():
            "unit": "iters/s", "value": args.steps / (ms * 1e-3), "ms_per_step": ms / args.steps,
            "wall_ms_per_step": wall * 1e3 / args.steps, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
            "higher_is_better": True, "dtype": "f32", "data": "synthetic", "impl": args.impl,
-           "pose_only": bool(args.pose_only), "optimizer_in_timed_step": args.optimizer,
+           "pose_only": bool(args.pose_only), "optimizer_in_timed_step": args.optimizer, "graph_iters_per_frame": args.graph,
            "config": {"workload": "replica_1200x680_%s_%s" % ("300k" if tracking else "1M", args.mode),
                       "image": [cam["w"], cam["h"]], "gaussians": P, "keyframes": nf,
                       "variant": args.variant if args.impl == "reference" else "dg",

@@ -219,14 +219,27 @@ int splat_slam_loss(int32_t width, int32_t height, int32_t tracking, int32_t use
  *        exp_avg += (1 - beta1) (grad - exp_avg);  exp_avg_sq = beta2 exp_avg_sq + (1 - beta2) grad^2;
  *        param  -= (lr / bias_correction1) * exp_avg / (sqrt(exp_avg_sq) / bias_correction2_sqrt + eps)
  *      with bias_correction1 = 1 - beta1^step and bias_correction2_sqrt = sqrt(1 - beta2^step) computed by the
- *      caller per tensor (a tensor without a gradient this step is simply left out, as torch does).
+ *      library from each tensor's `step` (a tensor without a gradient this step is simply left out, as torch does).
  *      `tensors` is a HOST array of `count` <= 16 descriptors (copied into the launch). */
 typedef struct SplatAdamTensor {
   float* param; const float* grad; float* exp_avg; float* exp_avg_sq;   /* device, n floats each */
   int64_t n;
-  float lr, bias_correction1, bias_correction2_sqrt;
+  float lr;
+  int32_t step;            /* number of THIS update for this tensor (>= 1): bias corrections use beta^step */
 } SplatAdamTensor;
-int splat_adam_step(const SplatAdamTensor* tensors, int32_t count, double beta1, double beta2, double eps, void* stream);
+/* replay_counter == NULL: bias corrections are formed on the host from `step`.  replay_counter != NULL (a device
+ * int32, zero-initialised by the caller) makes the call CUDA-graph capturable: a one-block prologue kernel forms the
+ * bias corrections for step + *replay_counter on the device (into replay_scratch, >= 32 device floats) and then
+ * increments the counter, so every replay of a captured step advances the optimizer by one step. */
+int splat_adam_step(const SplatAdamTensor* tensors, int32_t count, double beta1, double beta2, double eps,
+                    int32_t* replay_counter, float* replay_scratch, void* stream);
+
+/* Capture guard.  Inside a CUDA graph the host cannot read num_rendered to re-size binning_state (phase 2 then runs
+ * with a capacity fixed at capture time and simply exits if R exceeds it).  This one-thread kernel ORs
+ * (R > R_capacity) into flags[0] and keeps max(R) in flags[1] (device or mapped pinned uint32[2]) so that the host can
+ * tell, after any number of replays, whether every one of them rendered. */
+int splat_forward_guard(const void* image_state, int32_t width, int32_t height, int64_t R_capacity,
+                        uint32_t* flags, void* stream);
 
 /* ---- multi-GPU exchange (new; the reference is single-GPU, configs/replica/splatam.py:8) -------
  * Sum of one flat float32 bucket over the `world` ranks of one NVSwitch node, in place, on `stream`.

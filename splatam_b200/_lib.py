@@ -33,8 +33,7 @@ class SplatCamera(C.Structure):
 class SplatAdamTensor(C.Structure):
     """Mirror of `struct SplatAdamTensor` (include/splat_b200.h)."""
     _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
-                ("n", C.c_int64), ("lr", C.c_float), ("bias_correction1", C.c_float),
-                ("bias_correction2_sqrt", C.c_float)]
+                ("n", C.c_int64), ("lr", C.c_float), ("step", C.c_int32)]
 
 
 _P = C.c_void_p
@@ -65,7 +64,8 @@ _SIGNATURES = {
     "splat_slam_loss_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     "splat_slam_loss": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_float,
                                   _P, _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
-    "splat_adam_step": (C.c_int, [C.POINTER(SplatAdamTensor), C.c_int32, C.c_double, C.c_double, C.c_double, _P]),
+    "splat_adam_step": (C.c_int, [C.POINTER(SplatAdamTensor), C.c_int32, C.c_double, C.c_double, C.c_double, _P, _P, _P]),
+    "splat_forward_guard": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, _P, _P]),
     "splat_peer_allreduce_sum": (C.c_int, [_P, _P, C.c_uint64, C.c_int32, C.c_int32, C.c_uint32, C.c_int64, _P]),
     "splat_profile_enable": (C.c_int, [C.c_int]),
     "splat_profile_read": (C.c_int, [_P, _P, C.c_int32]),

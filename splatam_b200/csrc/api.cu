@@ -442,26 +442,39 @@ int splat_slam_loss(int32_t W, int32_t H, int32_t tracking, int32_t use_sil_for_
   return launch_slam_loss(a, partial, stats, (cudaStream_t)stream);
 }
 
-int splat_adam_step(const SplatAdamTensor* tensors, int32_t count, double beta1, double beta2, double eps, void* stream) {
+int splat_adam_step(const SplatAdamTensor* tensors, int32_t count, double beta1, double beta2, double eps,
+                    int32_t* replay_counter, float* replay_scratch, void* stream) {
   if (count < 0 || count > ADAM_MAX_TENSORS) return fail(SPLAT_ERR_BAD_ARG, "count must be 0..%d", ADAM_MAX_TENSORS);
   if (count == 0) return SPLAT_OK;
   if (!tensors) return fail(SPLAT_ERR_BAD_ARG, "tensors is NULL");
+  if (replay_counter && !replay_scratch) return fail(SPLAT_ERR_BAD_ARG, "replay_counter needs replay_scratch (32 device floats)");
   AdamArgs a = {};
   // (1 - beta) is formed in double like torch's Python scalars: 1 - 0.999f is off by 1.3e-5 relative
   a.count = 0; a.beta2 = (float)beta2; a.w1 = (float)(1.0 - beta1); a.w2 = (float)(1.0 - beta2); a.eps = (float)eps;
+  a.beta1d = beta1; a.beta2d = beta2;
+  a.replay_counter = replay_counter; a.dev_bias = replay_counter ? replay_scratch : nullptr;
   for (int i = 0; i < count; ++i) {
     const SplatAdamTensor& t = tensors[i];
     if (t.n < 0) return fail(SPLAT_ERR_BAD_ARG, "tensor %d: n < 0", i);
     if (t.n == 0) continue;
     if (!t.param || !t.grad || !t.exp_avg || !t.exp_avg_sq) return fail(SPLAT_ERR_BAD_ARG, "tensor %d: NULL pointer", i);
-    if (!(t.bias_correction1 > 0.f) || !(t.bias_correction2_sqrt > 0.f))
-      return fail(SPLAT_ERR_BAD_ARG, "tensor %d: bias corrections must be > 0 (step >= 1)", i);
+    if (t.step < 1) return fail(SPLAT_ERR_BAD_ARG, "tensor %d: step must be >= 1", i);
+    a.step[a.count] = t.step;
     SplatAdamTensorK& k = a.t[a.count++];
     k.param = t.param; k.grad = t.grad; k.exp_avg = t.exp_avg; k.exp_avg_sq = t.exp_avg_sq; k.n = t.n;
-    k.lr = t.lr; k.bias_correction1 = t.bias_correction1; k.bias_correction2_sqrt = t.bias_correction2_sqrt;
+    k.lr = t.lr;
+    k.bias_correction1 = (float)(1.0 - pow(beta1, (double)t.step));
+    k.bias_correction2_sqrt = (float)sqrt(1.0 - pow(beta2, (double)t.step));
     k.vec = (((uintptr_t)t.param | (uintptr_t)t.grad | (uintptr_t)t.exp_avg | (uintptr_t)t.exp_avg_sq) & 15) == 0;
   }
   return launch_adam(a, (cudaStream_t)stream);
+}
+
+int splat_forward_guard(const void* image_state, int32_t W, int32_t H, int64_t R_capacity, uint32_t* flags, void* stream) {
+  if (!image_state || !flags || W <= 0 || H <= 0 || R_capacity < 0) return fail(SPLAT_ERR_BAD_ARG, "bad guard arguments");
+  ImageView iv = image_view(const_cast<void*>(image_state), W, H);
+  return launch_forward_guard(iv.hdr, (uint32_t)(R_capacity > 0xffffffffll ? 0xffffffffll : R_capacity), flags,
+                              (cudaStream_t)stream);
 }
 
 int splat_abi_version(void) { return SPLAT_ABI_VERSION; }

@@ -88,10 +88,15 @@ typedef SplatAdamTensorDev SplatAdamTensorK;
 struct AdamArgs {
   int count;
   float beta2, w1, w2, eps;   // w = 1 - beta, rounded from double
+  double beta1d, beta2d;
+  int step[ADAM_MAX_TENSORS];
+  int* replay_counter;        // capturable mode: effective step = step[i] + *replay_counter (then incremented)
+  float* dev_bias;            // [2 * ADAM_MAX_TENSORS]: (bias_correction1, bias_correction2_sqrt) per tensor, device-formed
   int blocks[ADAM_MAX_TENSORS];
   SplatAdamTensorK t[ADAM_MAX_TENSORS];
 };
 int launch_adam(AdamArgs& a, cudaStream_t st);
+int launch_forward_guard(const ImageHeader* hdr, uint32_t Rcap, uint32_t* flags, cudaStream_t st);
 int rendervar_bwd_blocks(int P);
 int launch_rendervar_fwd(const RvArgs& a, cudaStream_t st);
 int launch_rendervar_bwd(const RvArgs& a, bool gg, bool cg, float* partial, cudaStream_t st);

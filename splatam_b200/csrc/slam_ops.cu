@@ -557,13 +557,34 @@ int launch_slam_loss(const LossArgs& a, float* partial, float* stats, cudaStream
 // runs ~8 multi-tensor kernels and several hundred microseconds of host code per step.  Arithmetic follows
 // torch/optim/adam.py::_single_tensor_adam (lerp, mul+addcmul, sqrt/bias2_sqrt + eps, addcdiv).
 // HBM roofline: 16 B read + 12 B written per element.
+// capturable mode: bias corrections for step[i] + *replay_counter, formed on the device in double; one block
+__global__ void adam_prep_kernel(const AdamArgs a) {
+  const int i = threadIdx.x;
+  const int replays = *a.replay_counter;
+  if (i < a.count) {
+    const double t = (double)(a.step[i] + replays);
+    a.dev_bias[2 * i] = (float)(1.0 - pow(a.beta1d, t));
+    a.dev_bias[2 * i + 1] = (float)sqrt(1.0 - pow(a.beta2d, t));
+  }
+  __syncthreads();
+  if (i == 0) *a.replay_counter = replays + 1;
+}
+
+__global__ void forward_guard_kernel(const ImageHeader* hdr, uint32_t Rcap, uint32_t* flags) {
+  const uint32_t R = hdr->num_rendered;
+  if (R > Rcap) flags[0] = 1u;
+  if (R > flags[1]) flags[1] = R;
+}
+
 __global__ void __launch_bounds__(256) adam_kernel(const AdamArgs a) {
   int t = 0;
   int b = (int)blockIdx.x;
 #pragma unroll 1
   while (t < a.count - 1 && b >= a.blocks[t]) { b -= a.blocks[t]; ++t; }
   const SplatAdamTensorK& T = a.t[t];
-  const float lr1 = T.lr / T.bias_correction1, inv_b2 = 1.f / T.bias_correction2_sqrt;
+  const float bc1 = a.dev_bias ? a.dev_bias[2 * t] : T.bias_correction1;
+  const float bc2s = a.dev_bias ? a.dev_bias[2 * t + 1] : T.bias_correction2_sqrt;
+  const float lr1 = T.lr / bc1, inv_b2 = 1.f / bc2s;
   const float w1 = a.w1, w2 = a.w2;
   const int64_t base = (int64_t)b * 1024 + threadIdx.x * 4;
   if (base >= T.n) return;
@@ -600,8 +621,18 @@ int launch_adam(AdamArgs& a, cudaStream_t st) {
     total += a.blocks[i];
   }
   if (total == 0) return SPLAT_OK;
+  if (a.replay_counter) {
+    adam_prep_kernel<<<1, 32, 0, st>>>(a);
+    SPLAT_LAUNCH_CHECK("adam_prep_kernel");
+  }
   adam_kernel<<<total, 256, 0, st>>>(a);
   SPLAT_LAUNCH_CHECK("adam_kernel");
+  return SPLAT_OK;
+}
+
+int launch_forward_guard(const ImageHeader* hdr, uint32_t Rcap, uint32_t* flags, cudaStream_t st) {
+  forward_guard_kernel<<<1, 1, 0, st>>>(hdr, Rcap, flags);
+  SPLAT_LAUNCH_CHECK("forward_guard_kernel");
   return SPLAT_OK;
 }
 

@@ -59,6 +59,18 @@ def _pinned_scalar(device):
     return cache[key]
 
 
+_guard = {}
+
+
+def capture_guard(device):
+    """Pinned uint32[2] per device: [0] = some captured forward exceeded its binning capacity, [1] = largest
+    num_rendered seen by a captured forward (written by splat_forward_guard; see slam.GraphedIteration)."""
+    key = torch.device(device).index
+    if key not in _guard:
+        _guard[key] = torch.zeros(2, dtype=torch.int32).pin_memory()
+    return _guard[key]
+
+
 def _f32(t, name):
     if t.dtype != torch.float32:
         raise RuntimeError("%s must be float32, got %s" % (name, t.dtype))
@@ -150,6 +162,7 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
                       depth_sil=False):
     """Runs both forward phases.  Returns (color, radii, depth, RasterState).  bwd = (power, fused, sinks) when a
     backward pass will follow: its buffers are then prepared here, ahead of the blocking read-back."""
+    global last_state
     if means3D.dim() != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     dev = means3D.device
@@ -182,8 +195,10 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
                                          _ptr(opacities), _ptr(cov3D_precomp), _ptr(sh), M,
                                          _ptr(colors_precomp), _ptr(st.geom), _ptr(st.image), _ptr(radii),
                                          C.c_void_p(pinned.data_ptr()), stream))
-        ev = torch.cuda.Event()
-        ev.record()
+        capturing = torch.cuda.is_current_stream_capturing()
+        if not capturing:
+            ev = torch.cuda.Event()
+            ev.record()
 
         def phase2(cap):
             st.capacity = cap
@@ -194,6 +209,20 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
 
         key = (dev.index, H, W)
         hint = _capacity_hint.get(key)
+        if capturing:
+            # CUDA-graph capture: no host wait for num_rendered.  Phase 2 runs with the capacity the warm-up iterations
+            # established; the guard kernel records (device side) whether a replay ever exceeds it.
+            if hint is None:
+                raise RuntimeError("run one un-captured forward at this image size before capturing a CUDA graph")
+            phase2(int(hint * _CAP_GROWTH) + _CAP_SLACK)
+            check(lib.splat_forward_guard(_ptr(st.image), W, H, st.capacity, C.c_void_p(capture_guard(dev).data_ptr()),
+                                          stream))
+            if bwd is not None:
+                st.plan = _plan_backward(st, dev, bwd[0], bwd[1], means3D, colors_precomp, scales, rotations,
+                                         cov3D_precomp, sh, radii, bwd[2], bwd[3] if len(bwd) > 3 else frozenset())
+            st.num_rendered = hint
+            last_state = st
+            return out_color, radii, out_depth, st
         launched = False
         if hint is not None:
             phase2(int(hint * _CAP_GROWTH) + _CAP_SLACK)
@@ -210,7 +239,6 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
         if not launched or R > st.capacity:
             phase2(max(R, 1))
         st.num_rendered = R
-    global last_state
     last_state = st
     return out_color, radii, out_depth, st
 

@@ -261,14 +261,33 @@ class FusedAdam(torch.optim.Optimizer):
     (`splat_adam_step`) and ~40 us of host code; torch's foreach path costs 0.3-0.8 ms per iteration here, more than
     the fused tracking iteration itself.  Same constructor arguments, same `param_groups` / `state[p]` layout
     (`step`, `exp_avg`, `exp_avg_sq`), so the reference's optimizer surgery (cat_params_to_optimizer, remove_points,
-    update_params_and_optimizer: utils/slam_external.py:107-165) works on it unchanged.  weight_decay / amsgrad /
-    maximize are not supported (SplaTAM never sets them)."""
+    update_params_and_optimizer: utils/slam_external.py:107-161) works on it unchanged.  weight_decay / amsgrad /
+    maximize are not supported (SplaTAM never sets them).
+
+    CUDA-graph capture: a step() issued while the stream is capturing uses a device-side replay counter for the
+    bias corrections, so each replay is one more optimizer step; `add_replays(n)` (called by GraphedIteration) brings
+    the host-side `state[p]['step']` up to date afterwards."""
 
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0, amsgrad=False):
         if weight_decay != 0 or amsgrad:
             raise NotImplementedError("FusedAdam: weight_decay / amsgrad are not supported")
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=0, amsgrad=False))
         self._desc = (_lib.SplatAdamTensor * 16)()
+        self._replay = {}        # device -> (int32 counter, float32 scratch), allocated outside any capture
+        self._captured = []      # state dicts whose step advanced inside the captured step
+
+    def _replay_buffers(self, dev):
+        if dev not in self._replay:
+            if torch.cuda.is_current_stream_capturing():
+                raise RuntimeError("FusedAdam: run one un-captured step() before capturing (allocates the replay counter)")
+            self._replay[dev] = (torch.zeros(1, dtype=torch.int32, device=dev), torch.zeros(32, dtype=torch.float32, device=dev))
+        return self._replay[dev]
+
+    def add_replays(self, n):
+        """After a captured step was replayed n times: the capture itself executed nothing, so the host-side step
+        counters (advanced once at capture time) move by n - 1."""
+        for st in self._captured:
+            st['step'] += n - 1
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -276,6 +295,9 @@ class FusedAdam(torch.optim.Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
+        capturing = torch.cuda.is_current_stream_capturing()
+        if capturing:
+            self._captured = []
         batches = {}
         for group in self.param_groups:
             key = (float(group['betas'][0]), float(group['betas'][1]), float(group['eps']))
@@ -292,20 +314,100 @@ class FusedAdam(torch.optim.Optimizer):
                     state['exp_avg'] = torch.zeros_like(p, memory_format=torch.preserve_format)
                     state['exp_avg_sq'] = torch.zeros_like(p, memory_format=torch.preserve_format)
                 state['step'] += 1
-                t = float(state['step'])
+                if capturing:
+                    self._captured.append(state)
                 if not g.is_contiguous():
                     g = g.contiguous()
-                batches.setdefault((p.device, key), []).append(
-                    (p, g, state['exp_avg'], state['exp_avg_sq'], lr, 1.0 - key[0] ** t, (1.0 - key[1] ** t) ** 0.5))
+                batches.setdefault((p.device, key), []).append((p, g, state['exp_avg'], state['exp_avg_sq'], lr,
+                                                                int(state['step'])))
         for (dev, (b1, b2, eps)), items in batches.items():
             with _on_device(dev):
+                counter, scratch = self._replay_buffers(dev)
                 stream = _stream()
                 for i0 in range(0, len(items), 16):
                     chunk = items[i0:i0 + 16]
+                    if capturing and len(items) > 16:
+                        raise RuntimeError("FusedAdam: at most 16 tensors per (device, betas, eps) inside a CUDA graph")
                     d = self._desc
-                    for i, (p, g, m, v, lr, bc1, bc2s) in enumerate(chunk):
+                    for i, (p, g, m, v, lr, t) in enumerate(chunk):
                         e = d[i]
                         e.param, e.grad, e.exp_avg, e.exp_avg_sq = p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr()
-                        e.n, e.lr, e.bias_correction1, e.bias_correction2_sqrt = p.numel(), lr, bc1, bc2s
-                    check(lib.splat_adam_step(d, len(chunk), b1, b2, eps, stream))
+                        e.n, e.lr, e.step = p.numel(), lr, t
+                    check(lib.splat_adam_step(d, len(chunk), b1, b2, eps, _vp(counter) if capturing else None,
+                                              _vp(scratch) if capturing else None, stream))
         return loss
+
+
+# ------------------------------------------------------------------------------------------------ CUDA-graph replay
+_GRAPH_POOL = {}
+
+
+class GraphedIteration:
+    """Captures ONE optimisation iteration -- `fn()` = get_loss + loss.backward() + FusedAdam.step(), no zero_grad --
+    into a CUDA graph and replays it: the 40-200 tracking iterations SplaTAM runs on one frame (scripts/splatam.py:
+    710-758) are launch- and host-bound once the kernels take 0.65 ms, and differ only in the values of the pose
+    parameters, which the captured optimizer step updates in place.
+
+    What makes the iteration capturable: the rasterizer's forward does not wait for num_rendered while capturing (the
+    binning capacity is fixed from the warm-up iterations; `splat_forward_guard` records on the device whether any
+    replay exceeded it -> `check()`), and FusedAdam keeps its step count on the device.  Everything `fn` allocates lives in
+    the graph's private pool; gradients are written (not accumulated) because capture starts with `.grad = None`.
+    `fn` must return a tensor or a tuple of tensors (e.g. the loss): the same objects are refreshed by every replay."""
+
+    def __init__(self, fn, params, optimizer=None, warmup=1):
+        from . import rasterizer
+        self.optimizer, self.replays = optimizer, 0
+        tensors = list(params.values()) if isinstance(params, dict) else list(params)
+        dev = tensors[0].device
+        self.device = dev
+        # Warm-up = ordinary eager iterations on the current stream (they count as optimisation iterations): they size
+        # the binning capacity for this frame and allocate optimizer state / replay counters.  (On a side stream the
+        # caching allocator would start from an empty per-stream pool: measured 4 ms of cudaMalloc per frame.)
+        for _ in range(max(1, warmup)):
+            for t in tensors:
+                t.grad = None
+            fn()
+        for t in tensors:
+            t.grad = None
+        rasterizer.capture_guard(dev).zero_()
+        # capture_begin / capture_end directly: torch.cuda.graph() would run gc.collect() + empty_cache() on entry
+        # (tens of milliseconds -- as much as the 40 iterations of a Replica frame) and give every graph a fresh private
+        # pool (cudaMalloc per capture); all GraphedIterations of a device share one pool and one capture stream.
+        if dev not in _GRAPH_POOL:
+            _GRAPH_POOL[dev] = (torch.cuda.graph_pool_handle(), torch.cuda.Stream(dev))
+        pool, side = _GRAPH_POOL[dev]
+        cur = torch.cuda.current_stream(dev)
+        side.wait_stream(cur)
+        self.graph = torch.cuda.CUDAGraph()
+        warn = torch.autograd.graph.set_warn_on_accumulate_grad_stream_mismatch
+        warn(False)   # the parameters' AccumulateGrad nodes were created by eager iterations on another stream: harmless here
+        try:
+            with torch.cuda.stream(side):
+                self.graph.capture_begin(pool=pool)
+                try:
+                    self.out = fn()
+                finally:
+                    self.graph.capture_end()
+        finally:
+            warn(True)
+        cur.wait_stream(side)
+
+    def replay(self):
+        self.graph.replay()
+        self.replays += 1
+        return self.out
+
+    __call__ = replay
+
+    def check(self):
+        """Synchronises; raises if any replay needed more binning capacity than the capture had (its results are then
+        undefined -- re-run those iterations un-captured); brings the optimizer's host-side step counts up to date."""
+        from . import rasterizer
+        torch.cuda.synchronize(self.device)
+        if self.optimizer is not None and self.replays:
+            self.optimizer.add_replays(self.replays)
+            self.replays = 0
+        flags = rasterizer.capture_guard(self.device)
+        if int(flags[0]) != 0:
+            raise RuntimeError("a replayed iteration rendered %d instances, more than the captured binning capacity"
+                               % int(flags[1]))

@@ -110,13 +110,15 @@ def test_slam_glue_entry_points_validate_before_cuda():
 def test_adam_entry_point_validates_before_cuda():
     from splatam_b200._lib import SplatAdamTensor, lib
     d = (SplatAdamTensor * 16)()
-    assert lib.splat_adam_step(d, 0, 0.9, 0.999, 1e-8, None) == 0
-    assert lib.splat_adam_step(d, 17, 0.9, 0.999, 1e-8, None) == 1
-    assert lib.splat_adam_step(None, 1, 0.9, 0.999, 1e-8, None) == 1
+    assert lib.splat_adam_step(d, 0, 0.9, 0.999, 1e-8, None, None, None) == 0
+    assert lib.splat_adam_step(d, 17, 0.9, 0.999, 1e-8, None, None, None) == 1
+    assert lib.splat_adam_step(None, 1, 0.9, 0.999, 1e-8, None, None, None) == 1
     d[0].n = 8
-    assert lib.splat_adam_step(d, 1, 0.9, 0.999, 1e-8, None) == 1 and b"NULL" in lib.splat_last_error()
+    assert lib.splat_adam_step(d, 1, 0.9, 0.999, 1e-8, None, None, None) == 1 and b"NULL" in lib.splat_last_error()
     d[0].param = d[0].grad = d[0].exp_avg = d[0].exp_avg_sq = 256
-    assert lib.splat_adam_step(d, 1, 0.9, 0.999, 1e-8, None) == 1 and b"bias" in lib.splat_last_error()
+    assert lib.splat_adam_step(d, 1, 0.9, 0.999, 1e-8, None, None, None) == 1 and b"step" in lib.splat_last_error()
+    assert lib.splat_adam_step(d, 1, 0.9, 0.999, 1e-8, C.c_void_p(256), None, None) == 1 and b"scratch" in lib.splat_last_error()
+    assert lib.splat_forward_guard(None, 64, 64, 10, C.c_void_p(256), None) == 1
 
 
 def test_slam_module_mirrors_reference_signatures():

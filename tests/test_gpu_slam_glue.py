@@ -300,3 +300,45 @@ def test_fused_adam_vs_torch_adam(eps, lr0):
     grp["params"][0].grad = torch.ones_like(grp["params"][0])
     oa.step()
     assert float(oa.state[grp["params"][0]]["step"]) == 13.0 and bool(torch.isfinite(grp["params"][0]).all())
+
+
+def test_graphed_tracking_iterations_match_eager():
+    """slam.GraphedIteration: 3 eager (warm-up) + 5 replayed tracking iterations (get_loss + backward + FusedAdam.step inside one
+    CUDA graph) land on the same pose, optimizer state and step count as 8 eager iterations."""
+    from splatam_b200 import slam
+    base, curr = _slam_scene(6000, True)
+    wts = dict(im=0.5, depth=1.0)
+    lrs = dict(means3D=0.0, rgb_colors=0.0, unnorm_rotations=0.0, logit_opacities=0.0, log_scales=0.0,
+               cam_unnorm_rots=0.0004, cam_trans=0.002)
+    res = {}
+    for graphed in (False, True):
+        p = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+        va = {"max_2D_radius": torch.zeros(6000, device=DEV)}
+        opt = slam.FusedAdam([{'params': [v], 'name': k, 'lr': lrs[k]} for k, v in p.items()])
+
+        def it():
+            loss, _, _ = slam.get_loss(p, curr, va, 1, wts, True, 0.99, True, False, tracking=True,
+                                       tracking_pose_only=True)
+            loss.backward()
+            opt.step()
+            return loss
+
+        if graphed:
+            g = slam.GraphedIteration(it, p, opt, warmup=3)
+            for _ in range(5):
+                loss = g.replay()
+            g.check()
+        else:
+            for _ in range(8):
+                opt.zero_grad(set_to_none=True)
+                loss = it()
+        torch.cuda.synchronize()
+        res[graphed] = (p, opt, float(loss))
+    (pe, oe, le), (pg, og, lg) = res[False], res[True]
+    assert abs(le - lg) <= 1e-4 * abs(le)
+    for k in ("cam_unnorm_rots", "cam_trans"):
+        assert float((pe[k] - base[k]).abs().max()) > 1e-4          # the pose did move
+        _close(pg[k].detach(), pe[k].detach(), 1e-5, "pose after 8 iterations " + k)
+        assert float(og.state[pg[k]]["step"]) == float(oe.state[pe[k]]["step"]) == 8.0
+        _close(og.state[pg[k]]["exp_avg"], oe.state[pe[k]]["exp_avg"], 1e-3, "exp_avg " + k)
+    assert torch.equal(pg["means3D"].detach(), base["means3D"])
