@@ -122,8 +122,12 @@ int splat_forward_render(const SplatCamera* cam, int32_t P,
  * term is raised to `power` before accumulation (HX/cuda_rasterizer/backward.cu:1093-1137);
  * power == 2 is the fork's diagonal Gauss-Newton ("Hessian") accumulation.
  * `R` is the R_capacity that was passed to splat_forward_render (it fixes the state layout).
- * All dL_* outputs are fully written by the call (no pre-zeroing needed).  dL_dconic is a
+ * Every dL_* output that is passed is fully written by the call (no pre-zeroing needed).  dL_dconic is a
  * [P,4] output (x,y,_,w as in the reference's [P,2,2]).  dL_dsh may be NULL when shs is.
+ * With power == 1 and no SHs every gradient array except dL_dmeans3D is OPTIONAL (NULL = not needed): it is then
+ * neither computed nor written, and with the fused depth/silhouette render a call without dL_dcolors and
+ * dL_dopacity skips those sums in the blend backward altogether (pose-only tracking, where the reference computes
+ * them for an optimizer with zero learning rates, configs/replica/splatam.py:71-79).
  * `scratch` is a 16-byte aligned device buffer of at least splat_backward_scratch_bytes(P, power)
  * bytes (the packed per-Gaussian accumulator rows the blend-backward kernel reduces into); the
  * call zeroes it itself.  colors_precomp is accepted for signature parity with the reference
