@@ -411,3 +411,30 @@ class GraphedIteration:
         if int(flags[0]) != 0:
             raise RuntimeError("a replayed iteration rendered %d instances, more than the captured binning capacity"
                                % int(flags[1]))
+
+
+class BestPose:
+    """The tracking loop's candidate-pose bookkeeping (scripts/splatam.py:701-704, :726-731, :761-764) without its
+    per-iteration host synchronisation: the reference evaluates `loss < current_min_loss` on the host (a blocking
+    read of a CUDA scalar every iteration); here the comparison and both conditional copies stay on the device
+    (three tiny kernels, capturable inside a GraphedIteration).  Call `update(loss, params)` right after
+    optimizer.step() -- like the reference it stores the pose AFTER the step whose pre-step loss was the minimum."""
+
+    def __init__(self, params, time_idx):
+        self.t = int(time_idx)
+        self.rot = params['cam_unnorm_rots'][..., self.t].detach().clone()
+        self.tran = params['cam_trans'][..., self.t].detach().clone()
+        self.min_loss = torch.full((), 1e20, dtype=torch.float32, device=self.rot.device)
+
+    @torch.no_grad()
+    def update(self, loss, params):
+        loss = loss.detach()
+        better = loss < self.min_loss
+        self.min_loss.copy_(torch.where(better, loss, self.min_loss))
+        self.rot.copy_(torch.where(better, params['cam_unnorm_rots'][..., self.t], self.rot))
+        self.tran.copy_(torch.where(better, params['cam_trans'][..., self.t], self.tran))
+
+    @torch.no_grad()
+    def write_back(self, params):
+        params['cam_unnorm_rots'][..., self.t] = self.rot
+        params['cam_trans'][..., self.t] = self.tran

@@ -315,12 +315,15 @@ def test_graphed_tracking_iterations_match_eager():
         p = {k: v.clone().requires_grad_(True) for k, v in base.items()}
         va = {"max_2D_radius": torch.zeros(6000, device=DEV)}
         opt = slam.FusedAdam([{'params': [v], 'name': k, 'lr': lrs[k]} for k, v in p.items()])
+        best = slam.BestPose(p, 1)
+        seen = []
 
         def it():
             loss, _, _ = slam.get_loss(p, curr, va, 1, wts, True, 0.99, True, False, tracking=True,
                                        tracking_pose_only=True)
             loss.backward()
             opt.step()
+            best.update(loss, p)
             return loss
 
         if graphed:
@@ -333,8 +336,12 @@ def test_graphed_tracking_iterations_match_eager():
                 opt.zero_grad(set_to_none=True)
                 loss = it()
         torch.cuda.synchronize()
-        res[graphed] = (p, opt, float(loss))
-    (pe, oe, le), (pg, og, lg) = res[False], res[True]
+        res[graphed] = (p, opt, float(loss), best)
+    (pe, oe, le, be), (pg, og, lg, bg) = res[False], res[True]
+    # device-side candidate-pose bookkeeping (scripts/splatam.py:726-731) agrees between the two runs
+    assert float(be.min_loss) < 1e19 and abs(float(be.min_loss) - float(bg.min_loss)) <= 1e-4 * float(be.min_loss)
+    _close(bg.rot, be.rot, 1e-5, "best rot")
+    _close(bg.tran, be.tran, 1e-4, "best tran")
     assert abs(le - lg) <= 1e-4 * abs(le)
     for k in ("cam_unnorm_rots", "cam_trans"):
         assert float((pe[k] - base[k]).abs().max()) > 1e-4          # the pose did move
