@@ -91,14 +91,27 @@ def main():
                     help="ours + --optimizer fused: per frame, run ITERS iterations as 1 eager one + one CUDA-graph capture "
                          "+ (ITERS-1) replays (slam.GraphedIteration); 40 = Replica tracking, 200 = TUM; capture cost is "
                          "inside the timed region")
+    ap.add_argument("--gpus", type=int, default=1,
+                    help="mapping, ours: keyframe-sharded over N ranks (launch under torchrun): every rank runs the fused "
+                         "iteration on its own keyframe, the raw-parameter gradient bucket is all-reduced (own NVLink kernel), "
+                         "FusedAdam steps on every replica; value = N * steps / time")
+    ap.add_argument("--collective", default="peer", choices=["peer", "nccl"])
     ap.add_argument("--steps", type=int, default=96)
     ap.add_argument("--warmup", type=int, default=8)
     args = ap.parse_args()
     real_stdout = os.fdopen(os.dup(1), "w")
     os.dup2(2, 1)
     assert torch.cuda.is_available(), "bench_slam.py needs a CUDA device"
-    device = torch.device("cuda", 0)
-    torch.cuda.set_device(0)
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        assert args.mode == "mapping" and args.impl == "ours" and args.optimizer == "fused" and args.gpus == world, \
+            "N > 1: --mode mapping --impl ours --optimizer fused --gpus WORLD_SIZE"
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
     nf = 24
     cam, rs, params = build(args.mode, device, nf)
     targets = make_targets(params, rs, nf, device)
@@ -110,6 +123,32 @@ def main():
 
     from splatam_b200 import slam
     from splatam_b200._lib import lib
+    bucket, sched, parallelism = None, None, "single GPU"
+    if world > 1:
+        # replicated raw parameters in one flat bucket; their gradients are written by the backward kernels straight
+        # into the (symmetric-memory) gradient bucket, summed over the ranks by ONE exchange, then FusedAdam steps
+        from splatam_b200 import mapping
+        raw = {k: params[k].detach() for k, _ in mapping.raw_layout(1)}
+        why = ""
+        if args.collective == "peer":
+            try:
+                bucket = mapping.GradBucket(raw, device, direct=True, peer_group=dist.group.WORLD, layout=mapping.raw_layout(1))
+            except Exception as e:  # noqa: BLE001
+                why, bucket = repr(e)[:160], None
+            ok = torch.tensor([0.0 if bucket is None else 1.0], device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if float(ok.item()) != 1.0:
+                sys.stderr.write("peer-memory all-reduce unavailable (%s); using NCCL\n" % why)
+                bucket = None
+        if bucket is None:
+            bucket = mapping.GradBucket(raw, device, direct=True, layout=mapping.raw_layout(1))
+            parallelism = "keyframe-sharded x%d + NCCL all-reduce of the raw-parameter gradient bucket" % world
+        else:
+            parallelism = "keyframe-sharded x%d + own %s all-reduce of the raw-parameter gradient bucket" % (
+                world, "in-switch (multimem)" if bucket.peer.multicast else "NVLink peer-memory")
+        leaves = bucket.leaves()
+        params = dict(leaves, cam_unnorm_rots=params["cam_unnorm_rots"], cam_trans=params["cam_trans"])
+        sched = mapping.keyframe_schedule(nf, max(args.steps, 8) + args.warmup, world, seed=11)
     if args.impl == "ours":
         def step(kf):
             loss, _, wl = slam.get_loss(params, targets[kf], variables, kf, wts, tracking, sil_thres, True, False,
@@ -160,23 +199,36 @@ def main():
 
         def step(kf):   # scripts/splatam.py:724-725 / :889-890
             loss = inner(kf)
+            if bucket is not None:
+                bucket.all_reduce()
             with torch.no_grad():
                 opt.step()
             return loss
 
     def zero():
+        if bucket is not None:     # the bucket views stay attached as .grad; every row is overwritten by the next backward
+            return
         if opt is not None:
             opt.zero_grad(set_to_none=True)
             return
         for v in params.values():
             v.grad = None
 
-    sampler = bench.ClockSampler(0)
-    sampler.start()
+    def kf_of(i):
+        return int(sched[i % sched.shape[0], rank]) if sched is not None else (7 * i) % nf
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = bench.ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     for i in range(args.warmup):
         zero()
-        step(i % nf)
-    torch.cuda.synchronize()
+        step(kf_of(i))
+    barrier()
     l0 = lib.splat_kernel_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler.mark_start()
@@ -195,25 +247,35 @@ def main():
     else:
         for i in range(args.steps):
             zero()
-            loss = step((7 * i) % nf)
+            loss = step(kf_of(args.warmup + i))
     e1.record()
-    torch.cuda.synchronize()
+    barrier()
     wall = time.perf_counter() - t0
     sampler.mark_end()
     ms = e0.elapsed_time(e1)
+    if dist is not None:    # max over ranks
+        t = torch.tensor([ms], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
     launches = lib.splat_kernel_launch_count() - l0
     out = {"metric": "SplaTAM %s iterations/sec (get_loss + backward: builder, RGB + depth + silhouette render, loss)"
                      % args.mode,
-           "unit": "iters/s", "value": args.steps / (ms * 1e-3), "ms_per_step": ms / args.steps,
-           "wall_ms_per_step": wall * 1e3 / args.steps, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
-           "higher_is_better": True, "dtype": "f32", "data": "synthetic", "impl": args.impl,
+           "unit": "iters/s", "value": world * args.steps / (ms * 1e-3), "ms_per_step": ms / args.steps,
+           "wall_ms_per_step": wall * 1e3 / args.steps, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+           "higher_is_better": True, "scaling": "weak", "dtype": "f32", "data": "synthetic", "impl": args.impl,
            "pose_only": bool(args.pose_only), "optimizer_in_timed_step": args.optimizer, "graph_iters_per_frame": args.graph,
            "config": {"workload": "replica_1200x680_%s_%s" % ("300k" if tracking else "1M", args.mode),
-                      "image": [cam["w"], cam["h"]], "gaussians": P, "keyframes": nf,
+                      "image": [cam["w"], cam["h"]], "gaussians": P, "keyframes": nf, "parallelism": parallelism,
                       "variant": args.variant if args.impl == "reference" else "dg",
                       "loss": "tracking: masked summed L1, sil_thres 0.99" if tracking else
                               "mapping: 0.8 L1 + 0.2 (1-SSIM 11x11) colour, masked mean L1 depth"},
-           "gpu_launches": launches, "last_loss": float(loss.detach()), "clocks": sampler.stop()}
+           "gpu_launches": launches, "last_loss": float(loss.detach()), "clocks": sampler.stop() if rank == 0 else None}
+    if world > 1:
+        if rank == 0:
+            real_stdout.write(json.dumps(out) + "\n")
+            real_stdout.flush()
+        dist.destroy_process_group()
+        return
     if args.impl == "ours":   # per-kernel event times from a second pass (kept out of the timed region)
         import ctypes as C
         lib.splat_profile_enable(1)

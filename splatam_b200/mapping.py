@@ -19,6 +19,12 @@ LAYOUT = (("rotations", 4), ("means3D", 3), ("colors_precomp", 3), ("opacities",
 FLOATS_PER_GAUSSIAN = sum(w for _, w in LAYOUT)
 
 
+def raw_layout(scale_dim=1):
+    """Bucket layout over SplaTAM's RAW Gaussian parameters (scripts/splatam.py:118-140) for the fused mapping iteration
+    (slam.get_loss): the builder's backward and the rasterizer write their gradients straight into these views."""
+    return (("unnorm_rotations", 4), ("means3D", 3), ("rgb_colors", 3), ("logit_opacities", 1), ("log_scales", int(scale_dim)))
+
+
 def keyframe_schedule(n_keyframes, steps, world, seed=0):
     """int64 [steps, world]: keyframe rendered by each rank at each step.  Identical on every rank
     (seeded, CPU generator) -- it replaces the reference's per-iteration `np.random.randint`
@@ -52,12 +58,14 @@ class GradBucket:
     every row.  Use it when a step is exactly one render per bucket (the mapping step); leave it off
     when several losses accumulate into the same leaves."""
 
-    def __init__(self, scene, device="cpu", direct=False, peer_group=None):
+    def __init__(self, scene, device="cpu", direct=False, peer_group=None, layout=LAYOUT):
         """peer_group: a torch.distributed process group whose ranks share one NVSwitch node.  The gradient buffer
         is then allocated in symmetric memory and `all_reduce` runs the library's own peer-memory two-shot kernel
         (csrc/allreduce.cu) on the current stream instead of NCCL."""
         self.direct = bool(direct)
         self.peer = None
+        self.layout = tuple(layout)
+        LAYOUT = self.layout   # noqa: N806  (the rest of the class reads the instance's layout)
         self.P = int(scene["means3D"].shape[0])
         for k, w in LAYOUT:
             if tuple(scene[k].shape) != (self.P, w):
@@ -71,7 +79,7 @@ class GradBucket:
             self.grads = torch.zeros_like(self.params)
         self.views, self.gviews = {}, {}
         off = 0
-        for k, w in LAYOUT:
+        for k, w in self.layout:
             n = self.P * w
             self.views[k] = self.params[off:off + n].view(self.P, w)
             self.gviews[k] = self.grads[off:off + n].view(self.P, w)

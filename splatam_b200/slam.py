@@ -20,7 +20,7 @@ import torch
 
 from . import _lib
 from ._lib import check, lib
-from .rasterizer import _f32, _on_device
+from .rasterizer import SINK_ATTR, _f32, _on_device
 
 
 def _vp(t):
@@ -36,6 +36,13 @@ class _BuildRendervar(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, unnorm_rotations, logit_opacities, log_scales, cam_unnorm_rots, cam_trans, time_idx,
                 gaussians_grad, camera_grad):
+        # gradient sinks (mapping.GradBucket(direct=True, layout=mapping.raw_layout())): the backward kernel writes a
+        # parameter's gradient straight into the flat exchange bucket and autograd receives None for it
+        ctx.sinks = tuple(getattr(t, SINK_ATTR, None) for t in (means3D, unnorm_rotations, logit_opacities, log_scales))
+        for sk, t in zip(ctx.sinks, (means3D, unnorm_rotations, logit_opacities, log_scales)):
+            if sk is not None and (sk.dtype != torch.float32 or not sk.is_contiguous() or sk.shape != t.shape
+                                   or sk.device != t.device or sk.data_ptr() % 16 and t.shape[1] == 4):
+                raise RuntimeError("gradient sink must be a contiguous float32 tensor of the parameter's shape")
         means3D = _f32(means3D, "means3D")
         unnorm_rotations = _f32(unnorm_rotations, "unnorm_rotations")
         logit_opacities = _f32(logit_opacities, "logit_opacities")
@@ -90,20 +97,32 @@ class _BuildRendervar(torch.autograd.Function):
         g_means, g_rots, g_op, g_scales = [None if g is None else _f32(g, "grad") for g in (g_means, g_rots, g_op, g_scales)]
         if g_rots is not None and g_rots.data_ptr() % 16:
             g_rots = g_rots.clone()
+        sk_m, sk_r, sk_o, sk_s = ctx.sinks
         with _on_device(dev):
-            n = P * ((7 if gg else 0) + (1 if need[2] else 0) + (sd if need[3] else 0))
+            own = lambda need_it, sk: need_it and sk is None     # noqa: E731
+            n = P * ((4 if own(gg, sk_r) else 0) + (3 if own(gg, sk_m) else 0) + (1 if own(need[2], sk_o) else 0)
+                     + (sd if own(need[3], sk_s) else 0))
             flat = torch.empty(max(n, 1), dtype=torch.float32, device=dev)
             off = 0
             d_rots = d_means = d_logit = d_ls = None
             if gg:
-                d_rots = flat[:4 * P].view(P, 4)
-                d_means = flat[4 * P:7 * P].view(P, 3)
-                off = 7 * P
+                d_rots = sk_r
+                if d_rots is None:
+                    d_rots = flat[:4 * P].view(P, 4)
+                    off = 4 * P
+                d_means = sk_m
+                if d_means is None:
+                    d_means = flat[off:off + 3 * P].view(P, 3)
+                    off += 3 * P
             if need[2]:
-                d_logit = flat[off:off + P].view(P, 1)
-                off += P
+                d_logit = sk_o
+                if d_logit is None:
+                    d_logit = flat[off:off + P].view(P, 1)
+                    off += P
             if need[3]:
-                d_ls = flat[off:off + P * sd].view(P, sd)
+                d_ls = sk_s
+                if d_ls is None:
+                    d_ls = flat[off:off + P * sd].view(P, sd)
             d_cr = d_ct = scratch = None
             nscr = 0
             if cg:
@@ -116,7 +135,8 @@ class _BuildRendervar(torch.autograd.Function):
                                                _vp(g_means), _vp(g_rots), _vp(g_op), _vp(g_scales), int(gg), int(cg),
                                                _vp(d_means), _vp(d_rots), _vp(d_logit), _vp(d_ls), _vp(d_cr), _vp(d_ct),
                                                _vp(scratch), nscr, _stream()))
-        return (d_means if need[0] else None, d_rots if need[1] else None, d_logit, d_ls,
+        return (d_means if need[0] and sk_m is None else None, d_rots if need[1] and sk_r is None else None,
+                d_logit if sk_o is None else None, d_ls if sk_s is None else None,
                 d_cr if need[4] else None, d_ct if need[5] else None, None, None, None)
 
 

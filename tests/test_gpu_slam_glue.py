@@ -349,3 +349,31 @@ def test_graphed_tracking_iterations_match_eager():
         assert float(og.state[pg[k]]["step"]) == float(oe.state[pe[k]]["step"]) == 8.0
         _close(og.state[pg[k]]["exp_avg"], oe.state[pe[k]]["exp_avg"], 1e-3, "exp_avg " + k)
     assert torch.equal(pg["means3D"].detach(), base["means3D"])
+
+
+def test_fused_mapping_iteration_writes_the_raw_parameter_bucket():
+    """mapping.GradBucket(direct=True, layout=raw_layout()): the builder's backward and the rasterizer write every raw
+    parameter's gradient straight into the flat exchange bucket; values equal the ordinary autograd gradients."""
+    from splatam_b200 import mapping, slam
+    base, curr = _slam_scene(6000, False)
+    wts = dict(im=0.5, depth=1.0)
+    pa = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+    va = {"max_2D_radius": torch.zeros(6000, device=DEV)}
+    loss_a, _, _ = slam.get_loss(pa, curr, va, 1, wts, False, 0.5, True, False, mapping=True)
+    loss_a.backward()
+    bk = mapping.GradBucket({k: base[k] for k, _ in mapping.raw_layout(1)}, DEV, direct=True, layout=mapping.raw_layout(1))
+    bk.grads.fill_(float("nan"))            # every row must be overwritten
+    pb = dict(bk.leaves(), cam_unnorm_rots=base["cam_unnorm_rots"].clone().requires_grad_(True),
+              cam_trans=base["cam_trans"].clone().requires_grad_(True))
+    vb = {"max_2D_radius": torch.zeros(6000, device=DEV)}
+    loss_b, _, _ = slam.get_loss(pb, curr, vb, 1, wts, False, 0.5, True, False, mapping=True)
+    loss_b.backward()
+    _close(loss_b.detach(), loss_a.detach(), 1e-6, "loss")
+    assert bool(torch.isfinite(bk.grads).all())
+    for k, _ in mapping.raw_layout(1):
+        assert pb[k].grad.data_ptr() == bk.gviews[k].data_ptr()
+        _close(bk.gviews[k], pa[k].grad, 1e-3, "bucket grad " + k, atol=1e-8 if k == "unnorm_rotations" else 0.0)
+    opt = slam.FusedAdam([{'params': [v], 'name': k, 'lr': 1e-3} for k, v in pb.items()], lr=0.0, eps=1e-15)
+    before = bk.params.clone()
+    opt.step()                               # steps the flat parameter buffer through the views
+    assert float((bk.params - before).abs().max()) > 0

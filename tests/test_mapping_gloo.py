@@ -135,3 +135,19 @@ def test_direct_bucket_marks_leaves_and_skips_the_fill():
     plain.grads.fill_(7.0)
     plain.zero_grad()
     assert float(plain.grads.abs().max()) == 0.0
+
+
+def test_raw_parameter_layout_bucket():
+    """layout=raw_layout(): SplaTAM's raw parameter names, float4 array first, log_scales [P,1] or [P,3]."""
+    from oracle import slam_oracle as SO
+    for iso in (True, False):
+        p = SO.random_params(101, 3, iso, 1)
+        sd = 1 if iso else 3
+        bk = mapping.GradBucket({k: p[k] for k, _ in mapping.raw_layout(sd)}, direct=True, layout=mapping.raw_layout(sd))
+        assert bk.params.numel() == 101 * (4 + 3 + 3 + 1 + sd)
+        lv = bk.leaves()
+        assert set(lv) == {"unnorm_rotations", "means3D", "rgb_colors", "logit_opacities", "log_scales"}
+        assert lv["unnorm_rotations"].data_ptr() == bk.params.data_ptr() and lv["log_scales"].shape == (101, sd)
+        assert torch.equal(bk.views["means3D"], p["means3D"])
+        (lv["means3D"].sum() + lv["log_scales"].sum() * 2).backward()   # autograd accumulates into the bucket views
+        assert float(bk.gviews["log_scales"].min()) == 2.0 and lv["means3D"].grad.data_ptr() == bk.gviews["means3D"].data_ptr()
