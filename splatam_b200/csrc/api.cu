@@ -423,6 +423,7 @@ int splat_slam_loss(int32_t W, int32_t H, int32_t tracking, int32_t use_sil_for_
   if (W <= 0 || H <= 0) return fail(SPLAT_ERR_BAD_ARG, "bad image size %dx%d", W, H);
   if (!im || !depth_sil || !gt_im || !gt_depth || !losses || !dL_dim || !dL_ddepth_sil)
     return fail(SPLAT_ERR_BAD_ARG, "image / loss / gradient pointers must be non-NULL");
+  if ((uintptr_t)scratch & 15) return fail(SPLAT_ERR_BAD_ARG, "loss scratch must be 16-byte aligned");
   if (!scratch || scratch_bytes < splat_slam_loss_scratch_bytes(W, H, tracking))
     return fail(SPLAT_ERR_SCRATCH_TOO_SMALL, "loss scratch needs %zu bytes", splat_slam_loss_scratch_bytes(W, H, tracking));
   LossArgs a = {};

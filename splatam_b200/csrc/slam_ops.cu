@@ -181,7 +181,12 @@ __global__ void __launch_bounds__(512) pose_finalize_kernel(const RvArgs a, cons
   __shared__ double S[RV_SUMS];
   const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;   // 16 warps, one per sum
   double v = 0.0;
-  for (int b = lane; b < nblk; b += 32) v += (double)partial[b * RV_SUMS + k];
+  float p4[4];
+  for (int b0 = lane; b0 < nblk; b0 += 128) {   // four independent loads in flight per lane (single block: latency-bound)
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { const int b = b0 + 32 * u; p4[u] = b < nblk ? partial[b * RV_SUMS + k] : 0.f; }
+    v += ((double)p4[0] + (double)p4[1]) + ((double)p4[2] + (double)p4[3]);
+  }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   if (lane == 0) S[k] = v;
@@ -215,7 +220,7 @@ __global__ void __launch_bounds__(512) pose_finalize_kernel(const RvArgs a, cons
 
 int rendervar_bwd_blocks(int P) {
   int nb = (P + 255) / 256;
-  return nb < 1 ? 1 : (nb > 148 * 8 ? 148 * 8 : nb);
+  return nb < 1 ? 1 : (nb > 148 * 4 ? 148 * 4 : nb);   // grid-stride loop; few partial rows for the finalize kernel
 }
 
 int launch_rendervar_fwd(const RvArgs& a, cudaStream_t st) {
@@ -496,9 +501,14 @@ __global__ void __launch_bounds__(256) loss_finalize_kernel(const LossArgs a, co
   __shared__ double S[8][LOSS_SUMS];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   double v[LOSS_SUMS] = {0.0, 0.0, 0.0, 0.0};
-  for (int b = threadIdx.x; b < nblk; b += 256)
+  const float4* p4 = reinterpret_cast<const float4*>(partial);   // one 16-byte row per block
+  for (int b0 = threadIdx.x; b0 < nblk; b0 += 1024) {            // four independent row loads in flight per thread
+    float4 r[4];
 #pragma unroll
-    for (int k = 0; k < LOSS_SUMS; ++k) v[k] += (double)partial[b * LOSS_SUMS + k];
+    for (int u = 0; u < 4; ++u) { const int b = b0 + 256 * u; r[u] = b < nblk ? p4[b] : make_float4(0.f, 0.f, 0.f, 0.f); }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { v[0] += (double)r[u].x; v[1] += (double)r[u].y; v[2] += (double)r[u].z; v[3] += (double)r[u].w; }
+  }
 #pragma unroll
   for (int k = 0; k < LOSS_SUMS; ++k) {
 #pragma unroll
