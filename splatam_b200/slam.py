@@ -285,8 +285,8 @@ class FusedAdam(torch.optim.Optimizer):
     maximize are not supported (SplaTAM never sets them).
 
     CUDA-graph capture: a step() issued while the stream is capturing uses a device-side replay counter for the
-    bias corrections, so each replay is one more optimizer step; `add_replays(n)` (called by GraphedIteration) brings
-    the host-side `state[p]['step']` up to date afterwards."""
+    bias corrections, so each replay is one more optimizer step; GraphedIteration brackets the capture with
+    begin_capture() / end_capture() and brings the host-side `state[p]['step']` up to date in check()."""
 
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0, amsgrad=False):
         if weight_decay != 0 or amsgrad:
@@ -303,11 +303,18 @@ class FusedAdam(torch.optim.Optimizer):
             self._replay[dev] = (torch.zeros(1, dtype=torch.int32, device=dev), torch.zeros(32, dtype=torch.float32, device=dev))
         return self._replay[dev]
 
-    def add_replays(self, n):
-        """After a captured step was replayed n times: the capture itself executed nothing, so the host-side step
-        counters (advanced once at capture time) move by n - 1."""
-        for st in self._captured:
-            st['step'] += n - 1
+    def begin_capture(self):
+        """Called (eagerly) right before a step() is captured: replays count from zero for the new graph."""
+        for counter, _ in self._replay.values():
+            counter.zero_()
+
+    def end_capture(self):
+        """Called right after the capture: the captured step() advanced the host-side step counters although nothing
+        executed -- undo that, and hand the caller the state dicts the captured step touches."""
+        states, self._captured = self._captured, []
+        for st in states:
+            st['step'] -= 1
+        return states
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -376,7 +383,7 @@ class GraphedIteration:
 
     def __init__(self, fn, params, optimizer=None, warmup=1):
         from . import rasterizer
-        self.optimizer, self.replays = optimizer, 0
+        self.optimizer, self.replays, self._adam_states = optimizer, 0, []
         tensors = list(params.values()) if isinstance(params, dict) else list(params)
         dev = tensors[0].device
         self.device = dev
@@ -390,6 +397,8 @@ class GraphedIteration:
         for t in tensors:
             t.grad = None
         rasterizer.capture_guard(dev).zero_()
+        if optimizer is not None and hasattr(optimizer, "begin_capture"):
+            optimizer.begin_capture()
         # capture_begin / capture_end directly: torch.cuda.graph() would run gc.collect() + empty_cache() on entry
         # (tens of milliseconds -- as much as the 40 iterations of a Replica frame) and give every graph a fresh private
         # pool (cudaMalloc per capture); all GraphedIterations of a device share one pool and one capture stream.
@@ -411,6 +420,8 @@ class GraphedIteration:
         finally:
             warn(True)
         cur.wait_stream(side)
+        if optimizer is not None and hasattr(optimizer, "end_capture"):
+            self._adam_states = optimizer.end_capture()
 
     def replay(self):
         self.graph.replay()
@@ -424,9 +435,9 @@ class GraphedIteration:
         undefined -- re-run those iterations un-captured); brings the optimizer's host-side step counts up to date."""
         from . import rasterizer
         torch.cuda.synchronize(self.device)
-        if self.optimizer is not None and self.replays:
-            self.optimizer.add_replays(self.replays)
-            self.replays = 0
+        for st in self._adam_states:      # every replay was one optimizer step
+            st['step'] += self.replays
+        self.replays = 0
         flags = rasterizer.capture_guard(self.device)
         if int(flags[0]) != 0:
             raise RuntimeError("a replayed iteration rendered %d instances, more than the captured binning capacity"

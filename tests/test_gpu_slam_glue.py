@@ -303,8 +303,8 @@ def test_fused_adam_vs_torch_adam(eps, lr0):
 
 
 def test_graphed_tracking_iterations_match_eager():
-    """slam.GraphedIteration: 3 eager (warm-up) + 5 replayed tracking iterations (get_loss + backward + FusedAdam.step inside one
-    CUDA graph) land on the same pose, optimizer state and step count as 8 eager iterations."""
+    """slam.GraphedIteration: 3 eager (warm-up) + 5 replayed, then 1 eager + 2 replayed tracking iterations (get_loss + backward + FusedAdam.step inside one
+    CUDA graph) land on the same pose, optimizer state and step count as 11 eager iterations."""
     from splatam_b200 import slam
     base, curr = _slam_scene(6000, True)
     wts = dict(im=0.5, depth=1.0)
@@ -331,8 +331,13 @@ def test_graphed_tracking_iterations_match_eager():
             for _ in range(5):
                 loss = g.replay()
             g.check()
+            assert float(opt.state[p["cam_trans"]]["step"]) == 8.0
+            g2 = slam.GraphedIteration(it, p, opt, warmup=1)     # a second capture with the same optimizer continues
+            for _ in range(2):
+                loss = g2.replay()
+            g2.check()
         else:
-            for _ in range(8):
+            for _ in range(11):
                 opt.zero_grad(set_to_none=True)
                 loss = it()
         torch.cuda.synchronize()
@@ -345,8 +350,8 @@ def test_graphed_tracking_iterations_match_eager():
     assert abs(le - lg) <= 1e-4 * abs(le)
     for k in ("cam_unnorm_rots", "cam_trans"):
         assert float((pe[k] - base[k]).abs().max()) > 1e-4          # the pose did move
-        _close(pg[k].detach(), pe[k].detach(), 1e-5, "pose after 8 iterations " + k)
-        assert float(og.state[pg[k]]["step"]) == float(oe.state[pe[k]]["step"]) == 8.0
+        _close(pg[k].detach(), pe[k].detach(), 1e-5, "pose after 11 iterations " + k)
+        assert float(og.state[pg[k]]["step"]) == float(oe.state[pe[k]]["step"]) == 11.0
         _close(og.state[pg[k]]["exp_avg"], oe.state[pe[k]]["exp_avg"], 1e-3, "exp_avg " + k)
     assert torch.equal(pg["means3D"].detach(), base["means3D"])
 
