@@ -19,100 +19,166 @@
 // 6-pass device-wide sort.  Buckets that do not fit in shared memory take the same code path on
 // global ping-pong buffers.
 #include "kernels.cuh"
+#include <cooperative_groups.h>
 
 namespace splat {
 
 // ------------------------------------------------------------------------------------------ scan
-#define SCAN_KEEP 8192
-__global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* __restrict__ tile_count,
-                                                         uint32_t* __restrict__ tile_cursor,
-                                                         uint2* __restrict__ ranges, ImageHeader* hdr,
-                                                         uint32_t* __restrict__ num_rendered_out,
-                                                         uint32_t sort_cap, uint32_t* __restrict__ tile_order) {
-  __shared__ uint32_t warp_tot[32];
-  __shared__ uint32_t s_hist[64];
-  __shared__ uint32_t s_cnt[SCAN_KEEP];   // the counts, kept for the ordering passes below
+// One thread-block CLUSTER of 8 CTAs x 512 threads.  A single CTA was bound by one SM's memory pipeline:
+// the counters and cursors sit one per 256-byte block, so T=3225 tiles are ~13k separate sector requests
+// (count load, cursor store, range store, order store) at ~1.5 cycles each = 12.4 us (clock64 timeline,
+// scratch/scan_probe.cu).  Eight SMs each take a contiguous slice of T/8 tiles; the slice totals, the
+// maximum and the per-class histograms are exchanged through distributed shared memory.
+#define SCAN_CTAS 8
+#define SCAN_THREADS 512
+#define SCAN_KEEP 2048    // counts of a slice kept in shared memory (slices longer than this re-read global memory)
+#ifdef SPLAT_SCAN_PROBE   // scratch/scan_probe.cu: phase timeline (thread 0 of cluster rank 0)
+__device__ long long g_scan_stamps[16];
+#define SCAN_STAMP(i) do { if (threadIdx.x == 0 && blockIdx.x == 0) g_scan_stamps[i] = clock64(); } while (0)
+#else
+#define SCAN_STAMP(i) do {} while (0)
+#endif
+__global__ void __cluster_dims__(SCAN_CTAS, 1, 1) __launch_bounds__(SCAN_THREADS)
+tile_scan_kernel(int T, const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_cursor,
+                 uint2* __restrict__ ranges, ImageHeader* hdr, uint32_t* __restrict__ num_rendered_out,
+                 uint32_t sort_cap, uint32_t* __restrict__ tile_order) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  constexpr int NW = SCAN_THREADS / 32;
+  __shared__ uint32_t warp_tot[NW], warp_max[NW], warp_big[NW];
+  __shared__ uint32_t s_tot[4];           // this slice: sum, max, #big   (read by the other CTAs)
+  __shared__ uint32_t s_glob[4];          // base of this slice, R, global max, global #big
+  __shared__ uint32_t s_hist[64];         // this slice's length-class histogram (read by the other CTAs)
+  __shared__ uint32_t s_off[64];          // placement cursors of this slice
+  __shared__ uint32_t s_cnt[SCAN_KEEP];
   __shared__ uint32_t carry_s;
-  __shared__ uint32_t max_s, big_s;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  if (tid == 0) { carry_s = 0; max_s = 0; big_s = 0; }
-  __syncthreads();
-  uint32_t lmax = 0, lbig = 0;
-  uint32_t cnext = tid < T ? tile_count[(size_t)tid * CSTRIDE] : 0u;
-  for (int base = 0; base < T; base += 1024) {
-    const int t = base + tid;
-    const uint32_t c = cnext;
-    if (t < SCAN_KEEP) s_cnt[t] = c;
-    cnext = (t + 1024) < T ? tile_count[(size_t)(t + 1024) * CSTRIDE] : 0u;  // prefetch under this round's barriers
+  const int rank = (int)cluster.block_rank();
+  const int per = (T + SCAN_CTAS - 1) / SCAN_CTAS;
+  const int lo = min(T, rank * per), n = min(T, lo + per) - lo;
+  SCAN_STAMP(0);
+  if (tid < 64) s_hist[tid] = 0;
+  // ---- 1a: slice totals
+  uint32_t sum = 0, lmax = 0, lbig = 0;
+  for (int i = tid; i < n; i += SCAN_THREADS) {
+    const uint32_t c = tile_count[(size_t)(lo + i) * CSTRIDE];
+    if (i < SCAN_KEEP) s_cnt[i] = c;
+    sum += c;
     lmax = max(lmax, c);
     lbig += c > sort_cap;
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    lmax = max(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
+    lbig += __shfl_xor_sync(0xffffffffu, lbig, o);
+  }
+  if (lane == 0) { warp_tot[wid] = sum; warp_max[wid] = lmax; warp_big[wid] = lbig; }
+  __syncthreads();
+  if (wid == 0) {
+    uint32_t a = lane < NW ? warp_tot[lane] : 0u, m = lane < NW ? warp_max[lane] : 0u, g = lane < NW ? warp_big[lane] : 0u;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+      m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+      g += __shfl_xor_sync(0xffffffffu, g, o);
+    }
+    if (lane == 0) { s_tot[0] = a; s_tot[1] = m; s_tot[2] = g; }
+  }
+  SCAN_STAMP(1);
+  cluster.sync();
+  if (wid == 0) {  // lanes 0..7 fetch the eight slice totals
+    uint32_t a = 0, m = 0, g = 0;
+    if (lane < SCAN_CTAS) {
+      const uint32_t* r = cluster.map_shared_rank(s_tot, lane);
+      a = r[0]; m = r[1]; g = r[2];
+    }
+    uint32_t before = lane < rank ? a : 0u;
+#pragma unroll
+    for (int o = 4; o; o >>= 1) {
+      before += __shfl_xor_sync(0xffffffffu, before, o);
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+      m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+      g += __shfl_xor_sync(0xffffffffu, g, o);
+    }
+    if (lane == 0) { s_glob[0] = before; s_glob[1] = a; s_glob[2] = m; s_glob[3] = g; carry_s = before; }
+  }
+  __syncthreads();
+  SCAN_STAMP(2);
+  if (rank == 0 && tid == 0) {
+    hdr->num_rendered = s_glob[1];
+    hdr->max_tile_count = s_glob[2];
+    hdr->big_tile_count = s_glob[3];
+    *num_rendered_out = s_glob[1];   // may be mapped pinned host memory: the host reads it after the stream event
+  }
+  // ---- 1b: exclusive scan of the slice, starting at its base; cursors, ranges and the class histogram
+  const float cls_scale = 64.f / ((float)s_glob[2] + 1.f);   // length class = 63 - min(63, floor(c * 64 / (max + 1)))
+  for (int base = 0; base < n; base += SCAN_THREADS) {
+    const int i = base + tid;
+    const uint32_t c = i < n ? (i < SCAN_KEEP ? s_cnt[i] : tile_count[(size_t)(lo + i) * CSTRIDE]) : 0u;
     uint32_t v = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t n = __shfl_up_sync(0xffffffffu, v, o);
-      if (lane >= o) v += n;
+      const uint32_t nb = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += nb;
     }
     if (lane == 31) warp_tot[wid] = v;
     __syncthreads();
     if (wid == 0) {
-      uint32_t w = warp_tot[lane];
+      uint32_t w = lane < NW ? warp_tot[lane] : 0u;
 #pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t n = __shfl_up_sync(0xffffffffu, w, o);
-        if (lane >= o) w += n;
+      for (int o = 1; o < NW; o <<= 1) {
+        const uint32_t nb = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= o) w += nb;
       }
-      warp_tot[lane] = w;  // inclusive over warps
+      if (lane < NW) warp_tot[lane] = w;  // inclusive over warps
     }
     __syncthreads();
-    const uint32_t carry = carry_s;
-    const uint32_t incl = carry + v + (wid ? warp_tot[wid - 1] : 0u);
-    if (t < T) {
+    const uint32_t incl = carry_s + v + (wid ? warp_tot[wid - 1] : 0u);
+    if (i < n) {
       const uint32_t start = incl - c;
-      tile_cursor[(size_t)t * CSTRIDE] = start;
-      ranges[t] = c ? make_uint2(start, incl) : make_uint2(0u, 0u);
+      tile_cursor[(size_t)(lo + i) * CSTRIDE] = start;
+      ranges[lo + i] = c ? make_uint2(start, incl) : make_uint2(0u, 0u);
+      atomicAdd(&s_hist[63u - min(63u, (uint32_t)((float)c * cls_scale))], 1u);
     }
     __syncthreads();
-    if (tid == 1023) carry_s = incl;
+    if (tid == SCAN_THREADS - 1) carry_s = incl;
     __syncthreads();
   }
-  atomicMax(&max_s, lmax);
-  atomicAdd(&big_s, lbig);
-  __syncthreads();
-  if (tid == 0) {
-    hdr->num_rendered = carry_s;
-    hdr->max_tile_count = max_s;
-    hdr->big_tile_count = big_s;
-    *num_rendered_out = carry_s;   // may be mapped pinned host memory: the host reads it after the stream event
-    __threadfence_system();
-  }
-  // Launch order for the blend kernels: longest lists first (counting sort into 64 length classes), so
-  // the last CTAs of the grid are the cheap ones and the SMs drain together instead of waiting for a
-  // heavy tile that happened to sit at the end of the row-major order.  Results do not depend on it.
-  if (tid < 64) s_hist[tid] = 0;
-  __syncthreads();
-  const uint64_t mx = (uint64_t)max_s + 1;
-  for (int t = tid; t < T; t += 1024) {
-    const uint32_t c = t < SCAN_KEEP ? s_cnt[t] : tile_count[(size_t)t * CSTRIDE];
-    atomicAdd(&s_hist[63 - (uint32_t)(((uint64_t)c * 64) / mx)], 1u);
-  }
-  __syncthreads();
-  if (wid == 0) {  // exclusive scan of the 64 class sizes
-    uint32_t a = s_hist[lane], b = s_hist[lane + 32];
-    uint32_t ia = a, ib = b;
+  SCAN_STAMP(3);
+  // ---- 2: launch order for the blend kernels: longest lists first (counting sort into 64 length classes), so
+  // the last CTAs of the grid are the cheap ones and the SMs drain together instead of waiting for a heavy tile
+  // that happened to sit at the end of the row-major order.  Results do not depend on it.
+  cluster.sync();   // all eight slice histograms complete
+  if (tid < 64) {
+    uint32_t tot = 0, before = 0;
+#pragma unroll
+    for (int r = 0; r < SCAN_CTAS; ++r) {
+      const uint32_t h = cluster.map_shared_rank(s_hist, r)[tid];
+      tot += h;
+      before += r < rank ? h : 0u;
+    }
+    // exclusive scan of the 64 class totals over two warps
+    uint32_t v = tot;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t na = __shfl_up_sync(0xffffffffu, ia, o), nb = __shfl_up_sync(0xffffffffu, ib, o);
-      if (lane >= o) { ia += na; ib += nb; }
+      const uint32_t nb = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += nb;
     }
-    const uint32_t tot_a = __shfl_sync(0xffffffffu, ia, 31);
-    s_hist[lane] = ia - a;
-    s_hist[lane + 32] = tot_a + ib - b;
+    if (tid == 31) warp_max[0] = v;       // total of classes 0..31 (warp_max is free by now)
+    s_off[tid] = v - tot + before;
   }
   __syncthreads();
-  for (int t = tid; t < T; t += 1024) {
-    const uint32_t c = t < SCAN_KEEP ? s_cnt[t] : tile_count[(size_t)t * CSTRIDE];
-    tile_order[atomicAdd(&s_hist[63 - (uint32_t)(((uint64_t)c * 64) / mx)], 1u)] = (uint32_t)t;
+  if (tid >= 32 && tid < 64) s_off[tid] += warp_max[0];
+  __syncthreads();
+  SCAN_STAMP(4);
+  for (int i = tid; i < n; i += SCAN_THREADS) {
+    const uint32_t c = i < SCAN_KEEP ? s_cnt[i] : tile_count[(size_t)(lo + i) * CSTRIDE];
+    tile_order[atomicAdd(&s_off[63u - min(63u, (uint32_t)((float)c * cls_scale))], 1u)] = (uint32_t)(lo + i);
   }
+  SCAN_STAMP(5);
+  cluster.sync();   // no CTA may exit while another still reads its shared memory
+  SCAN_STAMP(6);
 }
 
 // --------------------------------------------------------------------------------------- scatter
@@ -287,7 +353,7 @@ __global__ void __launch_bounds__(256) emit_records_kernel(const uint32_t* __res
 
 int launch_tile_scan(int T, const ImageView& iv, uint32_t* num_rendered_out, uint32_t sort_cap, cudaStream_t st) {
   ProfScope prof_(K_TILE_SCAN, st);
-  tile_scan_kernel<<<1, 1024, 0, st>>>(T, iv.tile_count, iv.tile_cursor, iv.ranges, iv.hdr, num_rendered_out, sort_cap,
+  tile_scan_kernel<<<SCAN_CTAS, SCAN_THREADS, 0, st>>>(T, iv.tile_count, iv.tile_cursor, iv.ranges, iv.hdr, num_rendered_out, sort_cap,
                                        iv.tile_order);
   SPLAT_LAUNCH_CHECK("tile_scan_kernel");
   return SPLAT_OK;
