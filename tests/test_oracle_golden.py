@@ -19,7 +19,7 @@ from util import GOLDEN_DIR, build_case, frac_bad
 
 from oracle import raster_oracle as O
 
-FILES = sorted(f for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith("slam_glue_"))
+FILES = sorted(f for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith(("slam_glue_", "densify_")))
 NEAR = {"dg": 0.2, "hx": 0.001}
 
 
