@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define SPLAT_ABI_VERSION 4
+#define SPLAT_ABI_VERSION 5
 
 /* Error codes.  Positive values >= 1000 are 1000 + cudaError_t of a failed runtime call. */
 enum {
@@ -244,6 +244,55 @@ int splat_adam_step(const SplatAdamTensor* tensors, int32_t count, double beta1,
  * tell, after any number of replays, whether every one of them rendered. */
 int splat_forward_guard(const void* image_state, int32_t width, int32_t height, int64_t R_capacity,
                         uint32_t* flags, void* stream);
+
+/* ---- per-frame map surgery -----------------------------------------------------
+ * Replaces the torch boolean-index / torch.cat surgery of utils/slam_external.py:123-195 (remove_points,
+ * cat_params_to_optimizer, prune_gaussians) and scripts/splatam.py:73-123,354-426 (get_pointcloud,
+ * initialize_new_params, add_new_gaussians).  All pointers are device pointers unless noted.
+ *
+ * splat_prune_flags: keep[i] = !( sigmoid(logit_opacities[i]) < opacity_threshold
+ *                                 || (big_threshold >= 0 && max_j exp(log_scales[i,j]) > big_threshold) )
+ *   -- the `to_remove` mask of prune_gaussians (:180-186), big_threshold = 0.1 * scene_radius or < 0 for "not yet". */
+int splat_prune_flags(int32_t P, int32_t scale_dim, const float* logit_opacities, const float* log_scales,
+                      float opacity_threshold, float big_threshold, uint8_t* keep, void* stream);
+
+/* splat_compact_rows: dst = src[keep] for `count` (<= 24) float32 row tensors at once (parameters, Adam exp_avg /
+ * exp_avg_sq, per-Gaussian variables), order preserving, out of place (src != dst).  keep: n bytes, 4-byte aligned,
+ * non-zero = keep.  *n_kept_out (device or mapped pinned host uint32, may be NULL) receives the number of rows kept;
+ * scratch >= splat_compact_scratch_bytes(n), 16-byte aligned. */
+typedef struct SplatRowTensor {
+  const float* src;
+  float* dst;
+  int32_t width;      /* floats per row */
+} SplatRowTensor;
+size_t splat_compact_scratch_bytes(int64_t n);
+int splat_compact_rows(int64_t n, const uint8_t* keep, const SplatRowTensor* tensors, int32_t count, void* scratch,
+                       size_t scratch_bytes, uint32_t* n_kept_out, void* stream);
+
+/* splat_new_gaussian_mask: the pixels add_new_gaussians spawns Gaussians from (scripts/splatam.py:390-408):
+ *   depth_error = |gt - render_depth| * (gt > 0);   median = torch.median(depth_error)  (exact lower median, NaN
+ *   propagating);   pre = (silhouette < sil_thres) | ((render_depth > gt) & (depth_error > 50 * median));
+ *   flags = pre & (gt > 0).
+ * depth_sil: [3,H,W] silhouette render (depth, silhouette, depth^2), gt_depth: [H,W], flags: W*H bytes (4-byte
+ * aligned).  counts_out (device or mapped pinned uint32[2], may be NULL) = { sum(pre), sum(flags) } -- the reference
+ * appends only if sum(pre) > 0.  scratch >= splat_spawn_scratch_bytes(W,H); it also carries the scan that
+ * splat_spawn_gaussians consumes, so pass the SAME scratch, untouched, to that call. */
+size_t splat_spawn_scratch_bytes(int32_t width, int32_t height);
+int splat_new_gaussian_mask(int32_t width, int32_t height, const float* depth_sil, const float* gt_depth,
+                            float sil_thres, uint8_t* flags, void* scratch, size_t scratch_bytes,
+                            uint32_t* counts_out, void* stream);
+
+/* splat_spawn_gaussians: get_pointcloud (:73-123, transform_pts, projective mean-square distance) +
+ * initialize_new_params (:354-381) for the flagged pixels, in raster order, written to rows P_old.. of the six
+ * destination tensors (which must have room for P_old + counts_out[1] rows): means3D = c2w * (xx*z, yy*z, z, 1) with
+ * c2w the inverse of the frame's pose (cam_unnorm_rots [1,4,n_frames], cam_trans [1,3,n_frames], column time_idx),
+ * rgb = im[:, pixel], rotation (1,0,0,0), logit opacity 0, log_scales = log(sqrt((z / ((fx+fy)/2))^2)) x scale_dim,
+ * timestep = time_idx (timestep may be NULL). */
+int splat_spawn_gaussians(int32_t width, int32_t height, const uint8_t* flags, const void* scratch, const float* im,
+                          const float* gt_depth, float fx, float fy, float cx, float cy, const float* cam_unnorm_rots,
+                          const float* cam_trans, int32_t n_frames, int32_t time_idx, int32_t scale_dim, int64_t P_old,
+                          float* means3D, float* rgb_colors, float* unnorm_rotations, float* logit_opacities,
+                          float* log_scales, float* timestep, void* stream);
 
 /* ---- multi-GPU exchange (new; the reference is single-GPU, configs/replica/splatam.py:8) -------
  * Sum of one flat float32 bucket over the `world` ranks of one NVSwitch node, in place, on `stream`.

@@ -36,6 +36,11 @@ class SplatAdamTensor(C.Structure):
                 ("n", C.c_int64), ("lr", C.c_float), ("step", C.c_int32)]
 
 
+class SplatRowTensor(C.Structure):
+    """Mirror of `struct SplatRowTensor` (include/splat_b200.h)."""
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("width", C.c_int32)]
+
+
 _P = C.c_void_p
 _SIGNATURES = {
     "splat_geom_state_bytes": (C.c_size_t, [C.c_int32]),
@@ -66,6 +71,13 @@ _SIGNATURES = {
                                   _P, _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "splat_adam_step": (C.c_int, [C.POINTER(SplatAdamTensor), C.c_int32, C.c_double, C.c_double, C.c_double, _P, _P, _P]),
     "splat_forward_guard": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, _P, _P]),
+    "splat_prune_flags": (C.c_int, [C.c_int32, C.c_int32, _P, _P, C.c_float, C.c_float, _P, _P]),
+    "splat_compact_scratch_bytes": (C.c_size_t, [C.c_int64]),
+    "splat_compact_rows": (C.c_int, [C.c_int64, _P, C.POINTER(SplatRowTensor), C.c_int32, _P, C.c_size_t, _P, _P]),
+    "splat_spawn_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "splat_new_gaussian_mask": (C.c_int, [C.c_int32, C.c_int32, _P, _P, C.c_float, _P, _P, C.c_size_t, _P, _P]),
+    "splat_spawn_gaussians": (C.c_int, [C.c_int32, C.c_int32, _P, _P, _P, _P, C.c_float, C.c_float, C.c_float, C.c_float,
+                                        _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int64, _P, _P, _P, _P, _P, _P, _P]),
     "splat_peer_allreduce_sum": (C.c_int, [_P, _P, C.c_uint64, C.c_int32, C.c_int32, C.c_uint32, C.c_int64, _P]),
     "splat_profile_enable": (C.c_int, [C.c_int]),
     "splat_profile_read": (C.c_int, [_P, _P, C.c_int32]),
@@ -92,7 +104,7 @@ def _load():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing: intended
         fn.restype = res
         fn.argtypes = args
-    if lib.splat_abi_version() != 4:
+    if lib.splat_abi_version() != 5:
         raise ImportError("libsplat_b200.so ABI version mismatch")
     return lib
 

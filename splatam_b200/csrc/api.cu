@@ -340,7 +340,7 @@ int splat_profile_read_gaps(float* gap_ms_sum, int32_t n) {
 const char* splat_profile_kernel_name(int k) {
   static const char* names[K_COUNT] = {"preprocess_fwd", "tile_scan", "scatter", "tile_sort", "render_fwd",
                                        "render_bwd", "preprocess_bwd", "hessian_finalize", "emit_records",
-                                       "rendervar_fwd", "rendervar_bwd", "slam_loss", "adam"};
+                                       "rendervar_fwd", "rendervar_bwd", "slam_loss", "adam", "map_surgery"};
   return (k >= 0 && k < K_COUNT) ? names[k] : "";
 }
 

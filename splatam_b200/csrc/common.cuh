@@ -24,7 +24,7 @@ inline void count_launch(int n = 1) { g_launch_count += n; }
 
 // ---------------------------------------------------------------- per-kernel event profiling
 enum KernelId { K_PRE_FWD = 0, K_TILE_SCAN, K_SCATTER, K_TILE_SORT, K_RENDER_FWD, K_RENDER_BWD, K_PRE_BWD,
-                K_HESS_FIN, K_EMIT, K_RV_FWD, K_RV_BWD, K_LOSS, K_ADAM, K_COUNT };
+                K_HESS_FIN, K_EMIT, K_RV_FWD, K_RV_BWD, K_LOSS, K_ADAM, K_SURGERY, K_COUNT };
 extern int g_prof_on;
 void prof_record(int id, cudaStream_t st, bool start);
 struct ProfScope {  // cudaEvent pair around one launch, only when splat_profile_enable(1) was called
@@ -245,6 +245,7 @@ __device__ __forceinline__ unsigned lanemask_lt() {
 namespace splat {
 int fail(int code, const char* fmt, ...);
 int check_cuda(cudaError_t e, const char* what);
+int fail(int code, const char* fmt, ...);   // formats splat_last_error(), returns code
 }  // namespace splat
 #define SPLAT_CUDA(x)                                           \
   do {                                                          \
