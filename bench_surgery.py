@@ -1,0 +1,146 @@
+"""Per-frame map surgery on one B200: prune_gaussians and add_new_gaussians at Replica size
+(1M isotropic Gaussians, 1200x680 frame), ours (splatam_b200.densify, one compaction / spawn launch over a
+double-buffered arena) against the reference flow (the same torch boolean-index / torch.cat sequence the
+reference's utils/slam_external.py + scripts/splatam.py issue, on the same GPU, restated in
+oracle/densify_oracle.py -- the oracle is the measured thing ONLY in this `reference` leg).
+
+Every call is timed on its own with a device synchronize on both sides (both flows contain host read-backs, so
+wall time is the honest clock); the state is restored from a master copy between calls, outside the timed region.
+Prints one JSON line per operation.
+
+  python bench_surgery.py [--gaussians 1000000] [--steps 20] [--warmup 3]
+"""
+import argparse
+import ctypes as C
+import json
+import time
+
+import torch
+
+import bench
+from oracle import densify_oracle as DO
+from splatam_b200 import densify, slam
+from splatam_b200._lib import lib
+
+DEV = "cuda:0"
+
+
+def _timed(fn):
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    out = fn()
+    torch.cuda.synchronize()
+    return (time.perf_counter() - t0) * 1e3, out
+
+
+def _kernel_ms(calls):
+    n = 16
+    ms_sum = (C.c_float * n)(); cnt = (C.c_int32 * n)()
+    lib.splat_profile_read(ms_sum, cnt, n)
+    names = [lib.splat_profile_kernel_name(k).decode() for k in range(n)]
+    k = names.index("map_surgery")
+    return ms_sum[k] / max(calls, 1)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gaussians", type=int, default=1_000_000)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    args = ap.parse_args()
+    P = args.gaussians
+    torch.cuda.set_device(0)
+    p0, s0, v0 = DO.random_state(P, True, 5)
+    master_p = {k: v.to(DEV) for k, v in p0.items()}
+    master_s = {k: {n: t.to(DEV) for n, t in d.items()} for k, d in s0.items()}
+    master_v = {k: (v.to(DEV) if k != "scene_radius" else v) for k, v in v0.items()}
+    pd = dict(DO.PRUNE_DICT)
+    im, gt_depth, depth_sil, intr = DO.frame(680, 1200, 5)
+    im, gt_depth, depth_sil = im.to(DEV), gt_depth.to(DEV), depth_sil.to(DEV)
+    curr = {"cam": None, "im": im, "depth": gt_depth, "intrinsics": intr}
+    peaks, peak_src = bench.measured_peaks()
+
+    # ---- ours: one live state, restored in place (the arena stays warm, as in a running SLAM session) ----------
+    params = {k: torch.nn.Parameter(v.clone()) for k, v in master_p.items()}
+    groups = [{"params": [v], "name": k, "lr": 1e-3} for k, v in params.items()]
+    opt = slam.FusedAdam(groups, lr=0.0, eps=1e-15)
+    for k in DO.GAUSS_KEYS:
+        opt.state[params[k]] = {"step": torch.tensor(5.0), "exp_avg": master_s[k]["exp_avg"].clone(),
+                                "exp_avg_sq": master_s[k]["exp_avg_sq"].clone()}
+    variables = {k: (v.clone() if k != "scene_radius" else v) for k, v in master_v.items()}
+
+    def restore_ours():
+        nonlocal params, variables
+        # put the P master rows back behind the same Parameters' storage: grow the views to P rows again
+        arena = variables.get(densify.ARENA_KEY)
+        for k in DO.GAUSS_KEYS:
+            for name, src in (("p:", master_p[k]), ("m:", master_s[k]["exp_avg"]), ("v:", master_s[k]["exp_avg_sq"])):
+                arena.current(name + k)[:P].copy_(src)
+            moments = (arena.view("m:" + k, P, False), arena.view("v:" + k, P, False))
+            densify._swap_param(params, opt, k, arena.view("p:" + k, P, False), moments)
+        for k in DO.VAR_KEYS:
+            arena.current("var:" + k)[:P].copy_(master_v[k].view(P, 1))
+            variables[k] = arena.view("var:" + k, P, True)
+
+    def ours_prune():
+        nonlocal params, variables
+        params, variables = densify.prune_gaussians(params, variables, opt, 0, pd)
+        return params["means3D"].shape[0]
+
+    def ours_grow():
+        nonlocal params, variables
+        params, variables = densify.add_new_gaussians(params, variables, curr, 0.5, 2, "projective", "isotropic",
+                                                      optimizer=opt, depth_sil=depth_sil)
+        return params["means3D"].shape[0]
+
+    # ---- reference flow: torch boolean indexing / cat per tensor, on the same GPU -----------------------------
+    def ref_state():
+        return ({k: v.clone() for k, v in master_p.items()},
+                {k: {n: t.clone() for n, t in d.items()} for k, d in master_s.items()},
+                {k: (v.clone() if k != "scene_radius" else v) for k, v in master_v.items()})
+
+    results = []
+    for op, ours_fn, ref_fn in (
+            ("prune_gaussians", ours_prune, lambda st: DO.prune_gaussians(st[0], st[1], st[2], 0, pd)[0]["means3D"].shape[0]),
+            ("add_new_gaussians", ours_grow,
+             lambda st: DO.add_new_gaussians(st[0], st[1], st[2], depth_sil, im, gt_depth, intr, 0.5, 2)[0]["means3D"].shape[0])):
+        ours_fn()                                  # first call: the arena adopts the tensors (one-off copies)
+        t_ours, t_ref, rows = [], [], None
+        for i in range(args.warmup + args.steps):
+            restore_ours()
+            if i == args.warmup:
+                lib.splat_profile_enable(1)
+            ms, rows = _timed(ours_fn)
+            if i >= args.warmup:
+                t_ours.append(ms)
+        kms = _kernel_ms(args.steps)
+        lib.splat_profile_enable(0)
+        for i in range(args.warmup + args.steps):
+            st = ref_state()
+            ms, rows_ref = _timed(lambda: ref_fn(st))
+            if i >= args.warmup:
+                t_ref.append(ms)
+            del st
+        assert rows == rows_ref, (rows, rows_ref)
+        med = lambda x: sorted(x)[len(x) // 2]      # noqa: E731
+        floats_per_row = (3 + 3 + 4 + 1 + 1) * 3 + 4
+        if op == "prune_gaussians":
+            alg = P * (8 + 1) + P * 1 + (P + rows) * floats_per_row * 4     # flags pass + count + rows read / written
+        else:
+            N = 1200 * 680
+            alg = 3 * N * 8 + N * 13 + (rows - P) * (12 + 4 + (3 + 3 + 4 + 1 + 1 + 1) * 4)
+        results.append({"metric": op + " wall ms per call (1M Gaussians, Adam moments + variables included)",
+                        "unit": "ms", "higher_is_better": False, "value": round(med(t_ours), 4),
+                        "reference_flow_ms": round(med(t_ref), 4), "speedup": round(med(t_ref) / med(t_ours), 2),
+                        "rows_before": P, "rows_after": rows, "kernel_ms": round(kms, 5),
+                        "roofline": {"bound": "hbm", "algorithmic_bytes": alg, "achieved": round(alg / (kms * 1e-3) / 1e9, 1),
+                                     "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                     "frac": round(alg / (kms * 1e-3) / 1e9 / peaks["hbm_gbs"], 4), "peak_source": peak_src},
+                        "steps": args.steps, "warmup": args.warmup, "data": "synthetic",
+                        "config": {"workload": "replica_1200x680_1M_surgery", "gaussians": P, "image": [1200, 680]}})
+    for r in results:
+        print(json.dumps(r))
+
+
+if __name__ == "__main__":
+    main()

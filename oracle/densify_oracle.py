@@ -73,12 +73,14 @@ def prune_gaussians(params, state, variables, iter, prune_dict):
 def get_pointcloud(color, depth, intrinsics, w2c, mask):
     width, height = color.shape[2], color.shape[1]
     CX, CY, FX, FY = intrinsics[0][2], intrinsics[1][2], intrinsics[0][0], intrinsics[1][1]
-    x_grid, y_grid = torch.meshgrid(torch.arange(width).float(), torch.arange(height).float(), indexing="xy")
+    dev = depth.device
+    x_grid, y_grid = torch.meshgrid(torch.arange(width, device=dev).float(), torch.arange(height, device=dev).float(),
+                                    indexing="xy")
     xx = ((x_grid - CX) / FX).reshape(-1)
     yy = ((y_grid - CY) / FY).reshape(-1)
     depth_z = depth[0].reshape(-1)
     pts_cam = torch.stack((xx * depth_z, yy * depth_z, depth_z), dim=-1)
-    pts4 = torch.cat((pts_cam, torch.ones(height * width, 1)), dim=1)
+    pts4 = torch.cat((pts_cam, torch.ones(height * width, 1, device=dev)), dim=1)
     c2w = torch.inverse(w2c)
     pts = (c2w @ pts4.T).T[:, :3]
     scale_gaussian = depth_z / ((FX + FY) / 2)
@@ -108,7 +110,8 @@ def add_new_gaussians(params, state, variables, depth_sil, im, gt_depth, intrins
         return params, state, variables
     cam_rot = F.normalize(params["cam_unnorm_rots"][..., time_idx].detach())
     cam_tran = params["cam_trans"][..., time_idx].detach()
-    w2c = torch.eye(4)
+    dev = gt_depth.device
+    w2c = torch.eye(4, device=dev)
     w2c[:3, :3] = build_rotation(cam_rot)
     w2c[:3, 3] = cam_tran
     new_pt_cld, mean3_sq_dist = get_pointcloud(im, gt_depth, intrinsics, w2c, mask)
@@ -117,8 +120,8 @@ def add_new_gaussians(params, state, variables, depth_sil, im, gt_depth, intrins
     new = {  # initialize_new_params, scripts/splatam.py:354-381
         "means3D": new_pt_cld[:, :3],
         "rgb_colors": new_pt_cld[:, 3:6],
-        "unnorm_rotations": torch.tensor([1.0, 0, 0, 0]).repeat(n, 1),
-        "logit_opacities": torch.zeros(n, 1),
+        "unnorm_rotations": torch.tensor([1.0, 0, 0, 0], device=dev).repeat(n, 1),
+        "logit_opacities": torch.zeros(n, 1, device=dev),
         "log_scales": torch.tile(torch.log(torch.sqrt(mean3_sq_dist))[..., None], (1, 1 if iso else 3)),
     }
     params = dict(params)
@@ -132,8 +135,8 @@ def add_new_gaussians(params, state, variables, depth_sil, im, gt_depth, intrins
             state[k]["exp_avg_sq"] = torch.cat((state[k]["exp_avg_sq"], torch.zeros_like(v)), dim=0)
     num_pts = params["means3D"].shape[0]
     for k in ("means2D_gradient_accum", "denom", "max_2D_radius"):
-        variables[k] = torch.zeros(num_pts)
-    variables["timestep"] = torch.cat((variables["timestep"], time_idx * torch.ones(n)), dim=0)
+        variables[k] = torch.zeros(num_pts, device=dev)
+    variables["timestep"] = torch.cat((variables["timestep"], time_idx * torch.ones(n, device=dev)), dim=0)
     return params, state, variables
 
 

@@ -3,14 +3,15 @@
 // The reference does this with torch boolean indexing / torch.cat on every tensor separately
 // (utils/slam_external.py:123-165 remove_points / cat_params_to_optimizer, scripts/splatam.py:384-426
 // add_new_gaussians): per tensor one nonzero() + index kernel + allocation, ~20 tensors per prune, each a host sync.
-// Here: ONE flag pass, ONE scan, ONE order-preserving compaction over all row tensors (grid.y = tensor), into the
+// Here: ONE flag pass, ONE scan, ONE order-preserving compaction over all row tensors, into the
 // other half of a double-buffered arena (splatam_b200/densify.py) -- HBM-bound data movement, bit-exact by
 // construction (rows are copied, never recomputed; the order equals tensor[keep]).
 //
 //   prune_flags      keep[i] = !(sigmoid(logit) < thr  ||  max_j exp(log_scale_j) > big)       (prune_gaussians :172-186)
 //   flag_count       1024 flags per block -> block_count
 //   block_scan       one CTA: exclusive scan of the block counts -> block_base, total (to pinned host memory)
-//   compact_rows     block (b, tensor): ranks of the block's 1024 rows from the flags, coalesced element copy
+//   compact_rows     one block per 1024 rows: ranks from the flags once, then every tensor's rows streamed (16-byte
+//                    loads) and scattered to rank order
 //   err_hist x3      exact lower median of depth_error (= torch.median) by an 11/11/10-bit radix select
 //   spawn_mask       non-presence mask of add_new_gaussians (:390-408) + block counts
 //   spawn            back-projection (get_pointcloud :73-123), initialize_new_params (:354-381), appended in
@@ -147,28 +148,65 @@ struct CompactArgs {
   CompactTensorK t[COMPACT_MAX_TENSORS];
 };
 
-__global__ void __launch_bounds__(256) compact_rows_kernel(const __grid_constant__ CompactArgs a) {
+// One block per 1024 rows, ALL tensors: the ranks are formed once, then every tensor's 1024*w contiguous source
+// floats are streamed with 16-byte loads (four in flight per thread) and scattered to rank order -- consecutive kept
+// elements land on consecutive addresses, so the stores coalesce whenever runs of rows survive.
+__global__ void __launch_bounds__(256) compact_rows_kernel(const __grid_constant__ CompactArgs a, int count) {
   __shared__ uint8_t s_flag[ROWS_PER_BLOCK];
   __shared__ uint16_t s_rank[ROWS_PER_BLOCK];
   __shared__ uint32_t s_warp[8];
   const int64_t row0 = (int64_t)blockIdx.x * ROWS_PER_BLOCK;
   const uint32_t total = block_ranks(a.keep, a.n, row0, s_flag, s_rank, s_warp);
   if (total == 0) return;
-  const CompactTensorK t = a.t[blockIdx.y];
-  const int w = t.width;
   const int rows = (int)min((int64_t)ROWS_PER_BLOCK, a.n - row0);
-  const float* __restrict__ src = t.src + (size_t)row0 * w;
-  float* __restrict__ dst = t.dst + (size_t)a.block_base[blockIdx.x] * w;
-  const int elems = rows * w;
-  if (total == (uint32_t)rows) {          // nothing dropped in this block: straight copy
-    for (int e = threadIdx.x; e < elems; e += 256) dst[e] = src[e];
-    return;
-  }
+  const size_t base = a.block_base[blockIdx.x];
+  const bool all = total == (uint32_t)rows;
+  for (int ti = 0; ti < count; ++ti) {
+    const CompactTensorK t = a.t[ti];
+    const int w = t.width;
+    const float* __restrict__ src = t.src + (size_t)row0 * w;
+    float* __restrict__ dst = t.dst + base * w;
+    const int elems = rows * w;
+    const bool vec = ((elems & 3) == 0) && ((((uintptr_t)src) & 15) == 0);
+    if (all) {                              // nothing dropped in this block: straight copy
+      if (vec && ((((uintptr_t)dst) & 15) == 0)) {
+        for (int e = threadIdx.x; e < elems / 4; e += 256)
+          reinterpret_cast<float4*>(dst)[e] = __ldg(reinterpret_cast<const float4*>(src) + e);
+      } else {
+        for (int e = threadIdx.x; e < elems; e += 256) dst[e] = src[e];
+      }
+      continue;
+    }
+    if (vec) {
+      const int quads = elems / 4;
+      for (int q0 = threadIdx.x; q0 < quads; q0 += 4 * 256) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int q = q0 + u * 256;
+          if (q < quads) v[u] = __ldg(reinterpret_cast<const float4*>(src) + q);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int q = q0 + u * 256;
+          if (q >= quads) break;
+          const float f[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const int e = 4 * q + c;
+            const int row = w == 1 ? e : (w == 3 ? e / 3 : (w == 4 ? e >> 2 : e / w));
+            if (s_flag[row]) dst[(int)s_rank[row] * w + (e - row * w)] = f[c];
+          }
+        }
+      }
+    } else {
 #pragma unroll 4
-  for (int e = threadIdx.x; e < elems; e += 256) {
-    const int row = w == 1 ? e : (w == 3 ? e / 3 : (w == 4 ? e >> 2 : e / w));
-    const float v = src[e];
-    if (s_flag[row]) dst[(int)s_rank[row] * w + (e - row * w)] = v;
+      for (int e = threadIdx.x; e < elems; e += 256) {
+        const int row = w == 1 ? e : (w == 3 ? e / 3 : (w == 4 ? e >> 2 : e / w));
+        const float v = src[e];
+        if (s_flag[row]) dst[(int)s_rank[row] * w + (e - row * w)] = v;
+      }
+    }
   }
 }
 
@@ -413,7 +451,7 @@ int splat_compact_rows(int64_t n, const uint8_t* keep, const SplatRowTensor* ten
   block_scan_kernel<<<1, 1024, 0, st>>>(nblk, block_count, block_base, total, n_kept_out, 0, nullptr);
   SPLAT_LAUNCH_CHECK("block_scan_kernel");
   if (count) {
-    compact_rows_kernel<<<dim3(nblk, count), 256, 0, st>>>(a);
+    compact_rows_kernel<<<nblk, 256, 0, st>>>(a, count);
     SPLAT_LAUNCH_CHECK("compact_rows_kernel");
   }
   return SPLAT_OK;

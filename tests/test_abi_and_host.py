@@ -209,3 +209,51 @@ def test_camera_matrices_follow_setup_camera_layout():
     pix = ((ndc + 1.0) * torch.tensor([cam["w"], cam["h"]]) - 1.0) * 0.5
     assert torch.allclose(pix, torch.tensor([cam["cx"] - 0.5, cam["cy"] - 0.5]), atol=1e-3)
     assert torch.allclose(center, torch.inverse(w2c)[:3, 3])
+
+
+def test_map_surgery_entry_points_validate_before_cuda():
+    """splat_prune_flags / splat_compact_rows / splat_new_gaussian_mask / splat_spawn_gaussians (ABI v5)."""
+    from splatam_b200._lib import SplatRowTensor, lib
+    null, one = C.c_void_p(0), C.c_void_p(256)
+    assert lib.splat_prune_flags(0, 1, null, null, 0.005, -1.0, null, null) == 0           # P == 0 short-circuits
+    assert lib.splat_prune_flags(10, 2, one, one, 0.005, -1.0, one, null) == 1
+    assert lib.splat_prune_flags(10, 3, one, null, 0.005, -1.0, one, null) == 1 and b"NULL" in lib.splat_last_error()
+    a, b = lib.splat_compact_scratch_bytes(1_000_000), lib.splat_compact_scratch_bytes(0)
+    assert a % 256 == 0 and b >= 256 and a >= 2 * 4 * 977
+    d = (SplatRowTensor * 24)()
+    assert lib.splat_compact_rows(10, one, d, 25, one, 1 << 20, null, null) == 1
+    assert lib.splat_compact_rows(10, one, d, 1, C.c_void_p(260), 1 << 20, null, null) == 1 and b"aligned" in lib.splat_last_error()
+    assert lib.splat_compact_rows(10, one, d, 1, one, 16, null, null) == 2
+    assert lib.splat_compact_rows(10, one, d, 1, one, 1 << 20, null, null) == 1 and b"tensor 0" in lib.splat_last_error()
+    d[0].src = d[0].dst = 512
+    d[0].width = 3
+    assert lib.splat_compact_rows(10, one, d, 1, one, 1 << 20, null, null) == 1 and b"out of place" in lib.splat_last_error()
+    assert lib.splat_compact_rows(10, C.c_void_p(258), d, 0, one, 1 << 20, null, null) == 1 and b"4-byte" in lib.splat_last_error()
+    s = lib.splat_spawn_scratch_bytes(1200, 680)
+    assert s % 256 == 0 and s >= 5124 * 4 + 2 * 4 * 797
+    assert lib.splat_new_gaussian_mask(0, 10, one, one, 0.5, one, one, s, null, null) == 1
+    assert lib.splat_new_gaussian_mask(64, 64, one, null, 0.5, one, one, s, null, null) == 1
+    assert lib.splat_new_gaussian_mask(1200, 680, one, one, 0.5, one, one, 1024, null, null) == 2
+    args = [64, 64, one, one, one, one, 50.0, 50.0, 32.0, 32.0, one, one, 5, 2, 1, 100, one, one, one, one, one, null, null]
+    bad = list(args); bad[13] = 5
+    assert lib.splat_spawn_gaussians(*bad) == 1 and b"time_idx" in lib.splat_last_error()
+    bad = list(args); bad[14] = 2
+    assert lib.splat_spawn_gaussians(*bad) == 1 and b"scale_dim" in lib.splat_last_error()
+    bad = list(args); bad[18] = C.c_void_p(260)
+    assert lib.splat_spawn_gaussians(*bad) == 1 and b"16-byte" in lib.splat_last_error()
+    bad = list(args); bad[16] = null
+    assert lib.splat_spawn_gaussians(*bad) == 1 and b"NULL" in lib.splat_last_error()
+
+
+def test_densify_module_mirrors_reference_signatures():
+    """splatam_b200.densify keeps the parameter lists of utils/slam_external.py:143,172 and scripts/splatam.py:384-385."""
+    from splatam_b200 import densify
+    assert list(inspect.signature(densify.remove_points).parameters) == ["to_remove", "params", "variables", "optimizer"]
+    assert list(inspect.signature(densify.prune_gaussians).parameters) == ["params", "variables", "optimizer", "iter", "prune_dict"]
+    assert list(inspect.signature(densify.add_new_gaussians).parameters)[:7] == [
+        "params", "variables", "curr_data", "sil_thres", "time_idx", "mean_sq_dist_method", "gaussian_distribution"]
+    p = {"means3D": None, "log_scales": type("T", (), {"shape": (4, 1)})()}
+    with pytest.raises(ValueError):
+        densify.add_new_gaussians(p, {}, {}, 0.5, 0, "nearest", "isotropic")
+    with pytest.raises(ValueError):
+        densify.add_new_gaussians(p, {}, {}, 0.5, 0, "projective", "anisotropic")
