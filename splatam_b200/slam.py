@@ -367,6 +367,7 @@ class FusedAdam(torch.optim.Optimizer):
 
 # ------------------------------------------------------------------------------------------------ CUDA-graph replay
 _GRAPH_POOL = {}
+_GRAPH_KEEP = {}
 
 
 class GraphedIteration:
@@ -420,6 +421,10 @@ class GraphedIteration:
         finally:
             warn(True)
         cur.wait_stream(side)
+        # the shared pool lives only while some graph uses it: keep the most recent graph of the device alive until
+        # the next one has been captured (a caller that drops its GraphedIteration between frames would otherwise
+        # free the pool and the next capture_begin on the same handle asserts inside the caching allocator)
+        _GRAPH_KEEP[dev] = self.graph
         if optimizer is not None and hasattr(optimizer, "end_capture"):
             self._adam_states = optimizer.end_capture()
 
