@@ -245,6 +245,16 @@ int splat_adam_step(const SplatAdamTensor* tensors, int32_t count, double beta1,
 int splat_forward_guard(const void* image_state, int32_t width, int32_t height, int64_t R_capacity,
                         uint32_t* flags, void* stream);
 
+/* ---- per-iteration bookkeeping ---------------------------------------------------------------------------
+ * splat_seen_update: `seen = radius > 0; max_2D_radius[seen] = max(radius[seen], max_2D_radius[seen])`
+ * (scripts/splatam.py:348-350) in one pass over the radii the forward wrote; seen (P bytes, torch.bool) may be NULL.
+ * splat_best_pose_update: the tracking loop's candidate pose (scripts/splatam.py:726-731) on the device:
+ * if (*loss < *min_loss) { *min_loss = *loss; best_rot[4] / best_tran[3] = column time_idx of cam_unnorm_rots
+ * [1,4,n_frames] / cam_trans [1,3,n_frames] } -- no host read of the loss, capturable in a CUDA graph. */
+int splat_seen_update(int32_t P, const int32_t* radii, float* max_2D_radius, uint8_t* seen, void* stream);
+int splat_best_pose_update(const float* loss, float* min_loss, const float* cam_unnorm_rots, const float* cam_trans,
+                           int32_t n_frames, int32_t time_idx, float* best_rot, float* best_tran, void* stream);
+
 /* ---- per-frame map surgery -----------------------------------------------------
  * Replaces the torch boolean-index / torch.cat surgery of utils/slam_external.py:123-195 (remove_points,
  * cat_params_to_optimizer, prune_gaussians) and scripts/splatam.py:73-123,354-426 (get_pointcloud,

@@ -647,3 +647,64 @@ int launch_forward_guard(const ImageHeader* hdr, uint32_t Rcap, uint32_t* flags,
 }
 
 }  // namespace splat
+
+// ------------------------------------------------------------------------------------- per-iteration bookkeeping
+// Two pieces of get_loss / the tracking loop that the reference spreads over ~10 tiny torch kernels per iteration
+// (and, for the candidate pose, a blocking host read of the loss): scripts/splatam.py:348-350 and :726-731.
+namespace splat {
+
+__global__ void __launch_bounds__(256) seen_update_kernel(int P, const int* __restrict__ radii,
+                                                          float* __restrict__ max_2D_radius, uint8_t* __restrict__ seen) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  const int r = radii[i];
+  const bool s = r > 0;
+  if (seen) seen[i] = s ? 1 : 0;
+  if (s) {                                       // max_2D_radius[seen] = max(radius[seen], max_2D_radius[seen])
+    const float m = max_2D_radius[i], rf = (float)r;
+    if (!(m >= rf)) max_2D_radius[i] = (m != m) ? m : rf;     // torch.max propagates NaN
+  }
+}
+
+__global__ void best_pose_kernel(const float* __restrict__ loss, float* min_loss, const float* __restrict__ cam_unnorm_rots,
+                                 const float* __restrict__ cam_trans, int n_frames, int time_idx, float* best_rot,
+                                 float* best_tran) {
+  __shared__ int better;
+  if (threadIdx.x == 0) {
+    const float l = *loss;
+    better = l < *min_loss;
+    if (better) *min_loss = l;
+  }
+  __syncthreads();
+  if (!better) return;
+  if (threadIdx.x < 4) best_rot[threadIdx.x] = cam_unnorm_rots[threadIdx.x * n_frames + time_idx];
+  else if (threadIdx.x < 7) best_tran[threadIdx.x - 4] = cam_trans[(threadIdx.x - 4) * n_frames + time_idx];
+}
+
+}  // namespace splat
+
+extern "C" {
+
+int splat_seen_update(int32_t P, const int32_t* radii, float* max_2D_radius, uint8_t* seen, void* stream) {
+  using namespace splat;
+  if (P < 0) return fail(SPLAT_ERR_BAD_ARG, "P < 0");
+  if (P == 0) return SPLAT_OK;
+  if (!radii || !max_2D_radius) return fail(SPLAT_ERR_BAD_ARG, "radii / max_2D_radius is NULL");
+  seen_update_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream>>>(P, radii, max_2D_radius, seen);
+  SPLAT_LAUNCH_CHECK("seen_update_kernel");
+  return SPLAT_OK;
+}
+
+int splat_best_pose_update(const float* loss, float* min_loss, const float* cam_unnorm_rots, const float* cam_trans,
+                           int32_t n_frames, int32_t time_idx, float* best_rot, float* best_tran, void* stream) {
+  using namespace splat;
+  if (!loss || !min_loss || !cam_unnorm_rots || !cam_trans || !best_rot || !best_tran)
+    return fail(SPLAT_ERR_BAD_ARG, "NULL pointer");
+  if (n_frames <= 0 || time_idx < 0 || time_idx >= n_frames) return fail(SPLAT_ERR_BAD_ARG, "time_idx outside [0, n_frames)");
+  best_pose_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(loss, min_loss, cam_unnorm_rots, cam_trans, n_frames, time_idx,
+                                                      best_rot, best_tran);
+  SPLAT_LAUNCH_CHECK("best_pose_kernel");
+  return SPLAT_OK;
+}
+
+}  // extern "C"

@@ -15,12 +15,18 @@ configs/*/splatam.py) and no matplotlib visualisation.  curr_data['w2c'] must be
 both are first_frame_w2c, scripts/splatam.py:189-200) because the fused render takes depth from the view matrix.
 """
 import ctypes as C
+import os
 
 import torch
 
 from . import _lib
 from ._lib import check, lib
 from .rasterizer import SINK_ATTR, _f32, _on_device
+
+
+# A/B switch for measurements only: SPLAT_TORCH_BOOKKEEPING=1 issues the original torch statements instead of the
+# two fused bookkeeping kernels (same results; still on the GPU)
+_FUSED_BOOKKEEPING = os.environ.get("SPLAT_TORCH_BOOKKEEPING", "0") != "1"
 
 
 def _vp(t):
@@ -269,8 +275,15 @@ def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_
     # == `seen = radius > 0; max_2D_radius[seen] = max(radius[seen], max_2D_radius[seen])` (:348-350) without the
     # boolean-index host synchronisation: radius is 0 where not seen and max_2D_radius >= 0
     m2r = variables['max_2D_radius']
-    torch.maximum(m2r, radius.to(m2r.dtype), out=m2r)
-    variables['seen'] = radius > 0
+    if _FUSED_BOOKKEEPING and m2r.dtype == torch.float32 and m2r.is_contiguous() and radius.dtype == torch.int32 \
+            and radius.is_contiguous():
+        seen = torch.empty(radius.shape, dtype=torch.bool, device=radius.device)      # one launch for all three ops
+        with _on_device(radius.device):
+            check(lib.splat_seen_update(radius.numel(), _vp(radius), _vp(m2r), _vp(seen), _stream()))
+        variables['seen'] = seen
+    else:
+        torch.maximum(m2r, radius.to(m2r.dtype), out=m2r)
+        variables['seen'] = radius > 0
     return loss, variables, weighted_losses
 
 
@@ -458,17 +471,24 @@ class BestPose:
 
     def __init__(self, params, time_idx):
         self.t = int(time_idx)
-        self.rot = params['cam_unnorm_rots'][..., self.t].detach().clone()
-        self.tran = params['cam_trans'][..., self.t].detach().clone()
+        self.rot = params['cam_unnorm_rots'][..., self.t].detach().clone().contiguous()
+        self.tran = params['cam_trans'][..., self.t].detach().clone().contiguous()
         self.min_loss = torch.full((), 1e20, dtype=torch.float32, device=self.rot.device)
 
     @torch.no_grad()
     def update(self, loss, params):
         loss = loss.detach()
+        cr, ct = params['cam_unnorm_rots'], params['cam_trans']
+        if _FUSED_BOOKKEEPING and loss.dtype == torch.float32 and cr.is_contiguous() and ct.is_contiguous() \
+                and cr.dtype == torch.float32:
+            with _on_device(loss.device):   # one one-warp kernel instead of a compare, three where() and three copies
+                check(lib.splat_best_pose_update(_vp(loss), _vp(self.min_loss), _vp(cr), _vp(ct), cr.shape[-1], self.t,
+                                                 _vp(self.rot), _vp(self.tran), _stream()))
+            return
         better = loss < self.min_loss
         self.min_loss.copy_(torch.where(better, loss, self.min_loss))
-        self.rot.copy_(torch.where(better, params['cam_unnorm_rots'][..., self.t], self.rot))
-        self.tran.copy_(torch.where(better, params['cam_trans'][..., self.t], self.tran))
+        self.rot.copy_(torch.where(better, cr[..., self.t], self.rot))
+        self.tran.copy_(torch.where(better, ct[..., self.t], self.tran))
 
     @torch.no_grad()
     def write_back(self, params):

@@ -245,6 +245,16 @@ def test_map_surgery_entry_points_validate_before_cuda():
     assert lib.splat_spawn_gaussians(*bad) == 1 and b"NULL" in lib.splat_last_error()
 
 
+def test_bookkeeping_entry_points_validate_before_cuda():
+    from splatam_b200._lib import lib
+    null, one = C.c_void_p(0), C.c_void_p(256)
+    assert lib.splat_seen_update(0, null, null, null, null) == 0
+    assert lib.splat_seen_update(-1, one, one, null, null) == 1
+    assert lib.splat_seen_update(10, one, null, null, null) == 1 and b"NULL" in lib.splat_last_error()
+    assert lib.splat_best_pose_update(one, one, one, one, 5, 5, one, one, null) == 1 and b"time_idx" in lib.splat_last_error()
+    assert lib.splat_best_pose_update(one, null, one, one, 5, 1, one, one, null) == 1
+
+
 def test_densify_module_mirrors_reference_signatures():
     """splatam_b200.densify keeps the parameter lists of utils/slam_external.py:143,172 and scripts/splatam.py:384-385."""
     from splatam_b200 import densify

@@ -382,3 +382,44 @@ def test_fused_mapping_iteration_writes_the_raw_parameter_bucket():
     before = bk.params.clone()
     opt.step()                               # steps the flat parameter buffer through the views
     assert float((bk.params - before).abs().max()) > 0
+
+
+def test_bookkeeping_kernels_vs_torch():
+    """splat_seen_update / splat_best_pose_update vs the torch statements they replace (scripts/splatam.py:348-350,
+    :726-731), including never-seen Gaussians, ties and a NaN already stored in max_2D_radius."""
+    from splatam_b200 import slam
+    g = torch.Generator().manual_seed(3)
+    P = 10_007
+    radius = torch.randint(0, 40, (P,), generator=g, dtype=torch.int32)
+    radius[torch.rand(P, generator=g) < 0.3] = 0
+    m0 = torch.rand(P, generator=g) * 40
+    m0[5] = float("nan")
+    m0[6] = float(radius[6])
+    seen_ref = radius > 0
+    m_ref = m0.clone()
+    m_ref[seen_ref] = torch.max(radius[seen_ref].float(), m_ref[seen_ref])
+    m = m0.to(DEV)
+    seen = torch.zeros(P, dtype=torch.bool, device=DEV)
+    from splatam_b200._lib import lib, check
+    import ctypes as C
+    vp = lambda t: C.c_void_p(t.data_ptr())                                     # noqa: E731
+    check(lib.splat_seen_update(P, vp(radius.to(DEV)), vp(m), vp(seen), None))
+    torch.cuda.synchronize()
+    assert torch.equal(seen.cpu(), seen_ref)
+    assert torch.equal(torch.nan_to_num(m.cpu(), nan=-1.0), torch.nan_to_num(m_ref, nan=-1.0))
+    # candidate pose: strictly-less comparison, pose taken from column time_idx
+    params = {"cam_unnorm_rots": torch.randn(1, 4, 6, generator=g).to(DEV), "cam_trans": torch.randn(1, 3, 6, generator=g).to(DEV)}
+    best = slam.BestPose(params, 4)
+    rot0, tran0 = best.rot.clone(), best.tran.clone()
+    for loss, moved in ((5.0, True), (5.0, False), (7.0, False), (4.5, True)):
+        params["cam_unnorm_rots"].add_(1.0)
+        params["cam_trans"].sub_(1.0)
+        best.update(torch.tensor(loss, device=DEV), params)
+        torch.cuda.synchronize()
+        if moved:
+            rot0, tran0 = params["cam_unnorm_rots"][..., 4].clone(), params["cam_trans"][..., 4].clone()
+        assert torch.equal(best.rot, rot0) and torch.equal(best.tran, tran0)
+    assert float(best.min_loss) == 4.5
+    params["cam_unnorm_rots"].zero_()
+    best.write_back(params)
+    assert torch.equal(params["cam_unnorm_rots"][..., 4], rot0)
