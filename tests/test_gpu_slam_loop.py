@@ -192,3 +192,17 @@ def test_two_frame_slam_sequence_matches_reference_flow():
             a, b = sa[m].double(), sb[m].double()
             scale = float(b.abs().max()) + 1e-30
             assert float((a - b).abs().max()) <= 5e-3 * scale, (k, m, float((a - b).abs().max()), scale)
+
+
+def test_sequence_bench_short_run_tracks_the_trajectory():
+    """bench_sequence.py (C5) for a few frames with a short schedule: the fused loop runs end to end (graph-replayed
+    tracking, arena growth, pruning) and the estimated trajectory stays on the ground truth."""
+    import bench_sequence as BS
+    dev = torch.device(DEV)
+    rs, frames, intr, gt_poses = BS.make_sequence(200, 400_000, dev)
+    n = 6
+    arm = BS.OursArm(dev, "dg")
+    params, ms = BS.run(arm, rs, frames[:n], intr, n, 40, 10, 5, 20, dev)
+    assert params["means3D"].shape[0] >= 0.9 * 640 * 480 * 0.5
+    assert BS.ate_rmse(params, gt_poses, n) < 5e-3
+    assert ms["tracking"] > 0 and ms["mapping"] > 0
