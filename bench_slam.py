@@ -228,6 +228,12 @@ def main():
     for i in range(args.warmup):
         zero()
         step(kf_of(i))
+    if args.graph:   # one untimed captured frame: first-capture costs (graph pool, instantiate) are per process, not per frame
+        assert args.impl == "ours" and args.optimizer == "fused", "--graph needs --impl ours --optimizer fused"
+        w = slam.GraphedIteration(lambda: step(0), params, opt, warmup=1)
+        for _ in range(3):
+            w.replay()
+        w.check()
     barrier()
     l0 = lib.splat_kernel_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
