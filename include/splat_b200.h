@@ -252,6 +252,9 @@ int splat_forward_guard(const void* image_state, int32_t width, int32_t height, 
  * if (*loss < *min_loss) { *min_loss = *loss; best_rot[4] / best_tran[3] = column time_idx of cam_unnorm_rots
  * [1,4,n_frames] / cam_trans [1,3,n_frames] } -- no host read of the loss, capturable in a CUDA graph. */
 int splat_seen_update(int32_t P, const int32_t* radii, float* max_2D_radius, uint8_t* seen, void* stream);
+/* x[0..n) *= *scale (device scalar), skipped on the device when *scale == 1: applies the incoming gradient of the loss
+ * to the gradient image the loss kernel already formed (loss.backward() passes exactly 1). */
+int splat_scale_inplace(float* x, int64_t n, const float* scale, void* stream);
 int splat_best_pose_update(const float* loss, float* min_loss, const float* cam_unnorm_rots, const float* cam_trans,
                            int32_t n_frames, int32_t time_idx, float* best_rot, float* best_tran, void* stream);
 

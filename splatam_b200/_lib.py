@@ -71,6 +71,7 @@ _SIGNATURES = {
                                   _P, _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "splat_adam_step": (C.c_int, [C.POINTER(SplatAdamTensor), C.c_int32, C.c_double, C.c_double, C.c_double, _P, _P, _P]),
     "splat_forward_guard": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, _P, _P]),
+    "splat_scale_inplace": (C.c_int, [_P, C.c_int64, _P, _P]),
     "splat_seen_update": (C.c_int, [C.c_int32, _P, _P, _P, _P]),
     "splat_best_pose_update": (C.c_int, [_P, _P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P]),
     "splat_prune_flags": (C.c_int, [C.c_int32, C.c_int32, _P, _P, C.c_float, C.c_float, _P, _P]),

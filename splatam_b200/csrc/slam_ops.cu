@@ -681,9 +681,38 @@ __global__ void best_pose_kernel(const float* __restrict__ loss, float* min_loss
   else if (threadIdx.x < 7) best_tran[threadIdx.x - 4] = cam_trans[(threadIdx.x - 4) * n_frames + time_idx];
 }
 
+// grad *= *scale, skipped entirely when *scale == 1 (loss.backward() on the loss itself): every block reads the
+// scalar first and exits before touching the gradient image.
+__global__ void __launch_bounds__(256) scale_inplace_kernel(float4* __restrict__ x4, float* __restrict__ x, int64_t n,
+                                                            const float* __restrict__ scale) {
+  const float s = *scale;
+  if (s == 1.0f) return;
+  const int64_t n4 = x4 ? n / 4 : 0;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (int64_t)gridDim.x * 256) {
+    float4 v = x4[i];
+    v.x *= s; v.y *= s; v.z *= s; v.w *= s;
+    x4[i] = v;
+  }
+  for (int64_t i = n4 * 4 + (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) x[i] *= s;
+}
+
 }  // namespace splat
 
 extern "C" {
+
+int splat_scale_inplace(float* x, int64_t n, const float* scale, void* stream) {
+  using namespace splat;
+  if (n < 0) return fail(SPLAT_ERR_BAD_ARG, "n < 0");
+  if (n == 0) return SPLAT_OK;
+  if (!x || !scale) return fail(SPLAT_ERR_BAD_ARG, "NULL pointer");
+  const bool vec = (((uintptr_t)x) & 15) == 0;
+  const int64_t work = vec ? (n + 3) / 4 : n;
+  int blocks = (int)((work + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  scale_inplace_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(vec ? reinterpret_cast<float4*>(x) : nullptr, x, n, scale);
+  SPLAT_LAUNCH_CHECK("scale_inplace_kernel");
+  return SPLAT_OK;
+}
 
 int splat_seen_update(int32_t P, const int32_t* radii, float* max_2D_radius, uint8_t* seen, void* stream) {
   using namespace splat;

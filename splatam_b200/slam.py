@@ -186,6 +186,15 @@ def _check_images(render, nplanes, gt_im, gt_depth):
     return render, gt_im, gt_depth, H, W
 
 
+def _scale_grad(grad, g_loss):
+    """grad *= g_loss without a pass over the image in the usual case g_loss == 1 (decided on the device)."""
+    if _FUSED_BOOKKEEPING and g_loss.dtype == torch.float32 and g_loss.numel() == 1 and g_loss.is_cuda:
+        with _on_device(grad.device):
+            check(lib.splat_scale_inplace(_vp(grad), grad.numel(), _vp(g_loss), _stream()))
+        return grad
+    return grad.mul_(g_loss)
+
+
 class _ImageLoss6(torch.autograd.Function):
     """Loss on the six-plane fused render: planes 0-2 = im, 3-5 = (depth, silhouette, depth^2)."""
     @staticmethod
@@ -203,7 +212,7 @@ class _ImageLoss6(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_loss, _g_losses):
         grad, ctx.grad = ctx.grad, None
-        return grad.mul_(g_loss), None, None, None, None, None, None, None
+        return _scale_grad(grad, g_loss), None, None, None, None, None, None, None
 
 
 class _ImageLoss33(torch.autograd.Function):
@@ -226,7 +235,7 @@ class _ImageLoss33(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_loss, _g_losses):
         grad, ctx.grad = ctx.grad, None
-        grad.mul_(g_loss)
+        _scale_grad(grad, g_loss)
         return grad[:3], grad[3:], None, None, None, None, None, None, None
 
 

@@ -249,6 +249,8 @@ def test_bookkeeping_entry_points_validate_before_cuda():
     from splatam_b200._lib import lib
     null, one = C.c_void_p(0), C.c_void_p(256)
     assert lib.splat_seen_update(0, null, null, null, null) == 0
+    assert lib.splat_scale_inplace(null, 0, null, null) == 0 and lib.splat_scale_inplace(one, -1, one, null) == 1
+    assert lib.splat_scale_inplace(one, 8, null, null) == 1 and b"NULL" in lib.splat_last_error()
     assert lib.splat_seen_update(-1, one, one, null, null) == 1
     assert lib.splat_seen_update(10, one, null, null, null) == 1 and b"NULL" in lib.splat_last_error()
     assert lib.splat_best_pose_update(one, one, one, one, 5, 5, one, one, null) == 1 and b"time_idx" in lib.splat_last_error()

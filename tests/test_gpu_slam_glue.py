@@ -423,3 +423,27 @@ def test_bookkeeping_kernels_vs_torch():
     params["cam_unnorm_rots"].zero_()
     best.write_back(params)
     assert torch.equal(params["cam_unnorm_rots"][..., 4], rot0)
+
+
+@pytest.mark.parametrize("h,w,six", [(45, 70, True), (33, 41, True), (37, 53, False)])
+def test_loss_gradient_follows_the_incoming_gradient(h, w, six):
+    """loss.backward() (incoming gradient exactly 1: the scale kernel exits without touching the image) and
+    (2.5 * loss).backward() (every element scaled once) -- splat_scale_inplace, incl. sizes that are not multiples of 4."""
+    from splatam_b200 import slam
+    im, ds, gt_im, gt_d = SO.images(h, w, 9)
+    wts = dict(im=0.5, depth=1.0)
+    grads = {}
+    for scale in (1.0, 2.5):
+        if six:
+            r = torch.cat([im, ds], 0).to(DEV).requires_grad_(True)
+            loss, _ = slam.image_loss(r, None, gt_im.to(DEV), gt_d.to(DEV), wts, True, 0.99, True)
+            leaves = [r]
+        else:
+            a, b = im.to(DEV).requires_grad_(True), ds.to(DEV).requires_grad_(True)
+            loss, _ = slam.image_loss(a, b, gt_im.to(DEV), gt_d.to(DEV), wts, False, 0.5, False)
+            leaves = [a, b]
+        (loss * scale).backward() if scale != 1.0 else loss.backward()
+        grads[scale] = [x.grad.clone() for x in leaves]
+    for g1, g2 in zip(grads[1.0], grads[2.5]):
+        assert float(g1.abs().max()) > 0
+        assert torch.equal(g2, g1 * 2.5)
