@@ -91,8 +91,10 @@ def ate_rmse(params, gt_poses, n):
     with torch.no_grad():
         q = F.normalize(params["cam_unnorm_rots"][0, :, :n].t().cpu())
         t = params["cam_trans"][0, :, :n].t().cpu()
-        from oracle.slam_oracle import build_rotation
-        R = build_rotation(q)
+        r, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+        R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+                         2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+                         2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], -1).view(-1, 3, 3)
         centre = -(R.transpose(1, 2) @ t.unsqueeze(-1)).squeeze(-1)
         Rg, tg = gt_poses[:n, :3, :3], gt_poses[:n, :3, 3]
         centre_g = -(Rg.transpose(1, 2) @ tg.unsqueeze(-1)).squeeze(-1)

@@ -2,7 +2,8 @@
 (1M isotropic Gaussians, 1200x680 frame), ours (splatam_b200.densify, one compaction / spawn launch over a
 double-buffered arena) against the reference flow (the same torch boolean-index / torch.cat sequence the
 reference's utils/slam_external.py + scripts/splatam.py issue, on the same GPU, restated in
-oracle/densify_oracle.py -- the oracle is the measured thing ONLY in this `reference` leg).
+oracle/densify_oracle.py -- the oracle is the measured thing ONLY in this `reference` leg; the `ours` leg takes
+nothing from it but the seeded input generators random_state() / frame()).
 
 Every call is timed on its own with a device synchronize on both sides (both flows contain host read-backs, so
 wall time is the honest clock); the state is restored from a master copy between calls, outside the timed region.
