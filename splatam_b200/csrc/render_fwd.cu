@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
           if (hit) {
             const float4 q0 = lds128(sbase + j * INST_BYTES);
             const float2 q1 = lds64(sbase + j * INST_BYTES + 16);
-            hit = footprint_hits(make_float2(q0.x, q0.y), make_float4(q0.z, q0.w, q1.x, q1.y), tile_cx, tile_cy, st);
+            hit = footprint_hits<false>(make_float2(q0.x, q0.y), make_float4(q0.z, q0.w, q1.x, q1.y), tile_cx, tile_cy, st);
           }
         }
         unsigned m = __ballot_sync(0xffffffffu, hit);
