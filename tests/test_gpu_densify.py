@@ -262,3 +262,31 @@ def test_add_new_gaussians_with_own_silhouette_render_vs_reference_flow(tmp_path
     back = dict(np.load(os.path.join(tmp_path, "params.npz")))
     for k in params:
         assert back[k].shape == tuple(params[k].shape) and np.array_equal(back[k], to_save[k])
+
+
+def test_torch_adam_steps_on_arena_views_like_on_plain_tensors():
+    """torch.optim.Adam keeps working on what prune hands back (Parameters and moments that are VIEWS of the arena):
+    two steps after a prune give bit-identical parameters and moments to the same steps on the reference flow's
+    freshly allocated tensors."""
+    from splatam_b200 import densify
+    pd = dict(DO.PRUNE_DICT, removal_opacity_threshold=0.3)
+    params, opt, variables, (p0, s0, v0) = _setup(4000, False, 81, "torch")
+    params, variables = densify.prune_gaussians(params, variables, opt, 0, pd)
+    rp, rs, _ = DO.prune_gaussians({k: v.to(DEV) for k, v in p0.items()}, {k: {n: t.to(DEV) for n, t in d.items()} for k, d in s0.items()},
+                                   {k: (v.to(DEV) if k != "scene_radius" else v) for k, v in v0.items()}, 0, pd)
+    ref = {k: torch.nn.Parameter(v.clone()) for k, v in rp.items()}
+    ropt = torch.optim.Adam([{"params": [v], "name": k, "lr": 1e-3} for k, v in ref.items()], lr=0.0, eps=1e-15)
+    for k in DO.GAUSS_KEYS:
+        ropt.state[ref[k]] = {"step": torch.tensor(5.0), "exp_avg": rs[k]["exp_avg"].clone(), "exp_avg_sq": rs[k]["exp_avg_sq"].clone()}
+    g = torch.Generator().manual_seed(5)
+    for _ in range(2):
+        for k in DO.GAUSS_KEYS:
+            grad = torch.randn(ref[k].shape, generator=g).to(DEV)
+            params[k].grad, ref[k].grad = grad.clone(), grad.clone()
+        opt.step()
+        ropt.step()
+    for k in DO.GAUSS_KEYS:
+        _same(params[k].detach(), ref[k].detach(), "param " + k)
+        _same(opt.state[params[k]]["exp_avg"], ropt.state[ref[k]]["exp_avg"], "exp_avg " + k)
+        _same(opt.state[params[k]]["exp_avg_sq"], ropt.state[ref[k]]["exp_avg_sq"], "exp_avg_sq " + k)
+        assert float(opt.state[params[k]]["step"]) == 7.0
