@@ -404,13 +404,14 @@ def timed_run(runner, sched, rank, world, steps, warmup, device, dist, on_timed_
     l0 = runner.launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
-    from splatam_b200 import rasterizer as _R
-    w0, h0 = _R.host_stats["wait_s"], time.perf_counter()
+    # (the reference arm must not map libsplat_b200.so: the rasterizer module is only touched for OUR runner)
+    host_stats = sys.modules["splatam_b200.rasterizer"].host_stats if isinstance(runner, OursRunner) else {"wait_s": 0.0}
+    w0, h0 = host_stats["wait_s"], time.perf_counter()
     e0.record()
     for i in range(steps):
         full_step(i)
     e1.record()
-    h1, w1 = time.perf_counter(), _R.host_stats["wait_s"]
+    h1, w1 = time.perf_counter(), host_stats["wait_s"]
     barrier()
     # host view of the same region: time to enqueue the K steps, and how much of it the host spent blocked on the
     # per-forward num_rendered read-back (blocked ~ all of it => the GPU is the bottleneck, as it should be)

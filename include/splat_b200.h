@@ -348,6 +348,10 @@ int splat_debug_count_blended(const SplatCamera* cam, int32_t P, const float* co
                               void* image_state, const void* binning_state, int64_t R_capacity,
                               float* scratch_color, uint32_t* blended, void* stream);
 int splat_debug_fp32_peak(float* scratch_dev, float* tflops_out, void* stream);
+/* Parity probe for the blend kernels' packed exponential (csrc/packed.cuh): evaluates it and the device library's
+ * expf() -- what the reference build calls (HX/cuda_rasterizer/forward.cu:349) -- on the `count` consecutive float bit
+ * patterns starting at first_bits, and ADDS the number of bit-level disagreements to *mismatches_dev (device uint64). */
+int splat_debug_exp_mismatches(uint32_t first_bits, uint64_t count, unsigned long long* mismatches_dev, void* stream);
 
 /* ---- misc ------------------------------------------------------------------------------------ */
 int splat_abi_version(void);

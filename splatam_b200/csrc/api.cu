@@ -194,6 +194,7 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
   r.W = W; r.H = H; r.gx = gx; r.order = iv.tile_order; r.ranges = iv.ranges; r.inst = bv.inst; r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.dL_dpix = dL_dout_color; r.out_color = out_color;
   r.acc = acc;
+  r.hdr = iv.hdr; r.Rcap = (uint32_t)(R > 0xffffffffll ? 0xffffffffll : R);
   if (!hess) {
     // callers that need neither colour nor opacity gradients (pose-only tracking) get the blend backward without those sums
     const int mode = cam->depth_sil ? ((!dL_dcolors && !dL_dopacity) ? 3 : 2) : 0;
@@ -299,6 +300,12 @@ int splat_debug_fp32_peak(float* scratch_dev, float* tflops_out, void* stream) {
   cudaEventDestroy(e0); cudaEventDestroy(e1);
   *tflops_out = best;
   return SPLAT_OK;
+}
+
+int splat_debug_exp_mismatches(uint32_t first_bits, uint64_t count, unsigned long long* mismatches_dev, void* stream) {
+  if (!mismatches_dev) return fail(SPLAT_ERR_BAD_ARG, "mismatches_dev is NULL");
+  if (count > (1ull << 32)) return fail(SPLAT_ERR_BAD_ARG, "count exceeds the 2^32 float bit patterns");
+  return launch_exp_check(first_bits, count, mismatches_dev, (cudaStream_t)stream);
 }
 
 int splat_profile_enable(int on) { g_prof_on = on ? 1 : 0; return SPLAT_OK; }

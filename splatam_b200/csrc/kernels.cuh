@@ -58,6 +58,7 @@ struct RenderBwdArgs {
   const float* final_T; const uint32_t* n_contrib; const float* dL_dpix;
   const float* out_color;   // optional: the forward's image, reference level of the per-pixel feature sums (MODE 0/2)
   float* acc;   // MODE 0: [P,12] raw sums.  MODE 1: [P,20] moment accumulator.  Pre-zeroed.
+  const ImageHeader* hdr; uint32_t Rcap;   // R > Rcap (a graph replay that overflowed its binning capacity): nothing to walk
 };
 
 // SplaTAM glue (slam_ops.cu).  Render-variable builder: forward outputs o_*, backward inputs g_* (any may be NULL ==
@@ -115,5 +116,6 @@ int sort_smem_cap();
 int launch_render_fwd(const RenderFwdArgs& a, int T, cudaStream_t st);
 int launch_render_bwd(const RenderBwdArgs& a, int T, int mode, cudaStream_t st);
 extern int g_disable_cull;
+int launch_exp_check(uint32_t first, unsigned long long count, unsigned long long* out, cudaStream_t st);
 
 }  // namespace splat

@@ -1,16 +1,24 @@
 // render.cuh -- pieces shared by the forward and backward blend kernels.
 //
-// Tile = 16x16 pixels, covered by 8 warps in CTA_PARTS CTAs of CTA_WARPS warps (same tile semantics as the reference,
-// HX/cuda_rasterizer/config.h:15-17, so tile-rect culling is identical), but the thread->pixel
-// map is ours: warp w owns the 8x4 sub-tile (w&1, w>>1) so that a warp can reject a whole
-// Gaussian whose footprint misses its 32 pixels with ONE lane-parallel test + ballot.
+// Tile = 16x16 pixels = one CTA of CTA_WARPS = 4 warps (same tile semantics as the reference,
+// HX/cuda_rasterizer/config.h:15-17, so tile-rect culling is identical), but the thread->pixel map is ours: warp w owns
+// the 8x8 block (w&1, w>>1) of the tile and every lane owns TWO pixels of it -- column lane&7, rows lane>>3 and
+// (lane>>3)+4 -- so that
+//   * one lane-parallel footprint test + ballot rejects a Gaussian for 64 pixels at once,
+//   * one record read, one ballot pop and (in the backward) one transposed reduction serve 64 pixels, and
+//   * the per-pixel arithmetic of the pair is issued as packed FP32x2 instructions (packed.cuh): dx and every
+//     per-Gaussian scalar are shared by the lane's two pixels and enter as broadcast operands.
+// Round 1 ran one pixel per lane on 8x4 sub-tiles with scalar FP32: 49 warp-instructions per tested warp-pair in
+// the backward against ~7 algorithmic FMAs (profiles/r01e_ncu_full_summary.txt); both blend kernels are bound by
+// instruction issue, not by the FP32 pipe, and packing halves the issue slots per pixel.
 #pragma once
 #include "common.cuh"
+#include "packed.cuh"
 
 namespace splat {
 
 // Instance ring shared by both blend kernels: RING_NS stages of RING_CH records (48 B each), filled by
-// the TMA unit and consumed by the CTA's CTA_WARPS warps (one 8x4 sub-tile each).  There is no producer
+// the TMA unit and consumed by the CTA's CTA_WARPS warps (one 8x8 block each).  There is no producer
 // warp: a stage is released through a shared-memory counter, and the warp whose release is the
 // last issues the refill of that stage itself (one elected lane, ~10 instructions per 6 KB) -- a
 // polling producer lane cost 6.6% of the backward kernel's issue slots (profiles/r01c).
@@ -18,29 +26,37 @@ namespace splat {
 #ifndef RING_NS
 #define RING_NS 3
 #endif
-#ifndef CTA_WARPS
-#define CTA_WARPS 4            // warps (8x4 sub-tiles) per CTA: 8 = one CTA per 16x16 tile, 4 = two CTAs per tile (measured:
-                               // 4 warps + 3 ring stages beat 8 + 4 by ~1.5% in both blend kernels: finer scheduling grain)
-#endif
-#define CTA_PARTS (8 / CTA_WARPS)
+#define CTA_WARPS 4
 #define RING_THREADS (CTA_WARPS * 32)
 
 struct SubTile {
-  int px, py;        // this lane's pixel
-  float fx0, fx1;    // sub-tile x extent [fx0, fx1] in pixel coordinates
+  int px, pya, pyb;  // this lane's two pixels: (px, pya) and (px, pyb = pya + 4)
+  float fx0, fx1;    // block x extent [fx0, fx1] in pixel coordinates
   float fy0, fy1;
 };
 
-__device__ __forceinline__ SubTile make_subtile(int tile_x, int tile_y, int part = 0) {
-  const int lane = threadIdx.x & 31, wid = (threadIdx.x >> 5) + part * CTA_WARPS;
+__device__ __forceinline__ SubTile make_subtile(int tile_x, int tile_y) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   SubTile s;
   const int sx0 = tile_x * TILE_X + (wid & 1) * 8;
-  const int sy0 = tile_y * TILE_Y + (wid >> 1) * 4;
+  const int sy0 = tile_y * TILE_Y + (wid >> 1) * 8;
   s.px = sx0 + (lane & 7);
-  s.py = sy0 + (lane >> 3);
+  s.pya = sy0 + (lane >> 3);
+  s.pyb = s.pya + 4;
   s.fx0 = (float)sx0; s.fx1 = (float)(sx0 + 7);
-  s.fy0 = (float)sy0; s.fy1 = (float)(sy0 + 3);
+  s.fy0 = (float)sy0; s.fy1 = (float)(sy0 + 7);
   return s;
+}
+
+// power = -0.5 (A dx^2 + C dy^2) - B dx dy of one Gaussian at the lane's two pixels, with exactly the roundings of
+// the reference build (SASS of renderCUDA<3>, forward.cu:341-343 as nvcc 12.9 contracts it):
+//   fma( fma(dx, rn(A dx), rn(dy rn(C dy))), -0.5, -rn(dy rn(B dx)) ).
+// dx is shared by the two pixels (same column); 3 scalar + 6 packed instructions for the pair.
+__device__ __forceinline__ f2 pair_power(float dx, f2 dy2, float A, float B, float C) {
+  const float Adx = __fmul_rn(A, dx), nBdx = -__fmul_rn(B, dx);
+  const f2 t = mul2(dy2, mul2(bc(C), dy2));
+  const f2 s = fma2(bc(dx), bc(Adx), t);
+  return fma2(s, bc(-0.5f), mul2(dy2, bc(nBdx)));
 }
 
 // Conservative screen-space bounding box of the set of pixels at which the reference's tests
@@ -71,7 +87,7 @@ __device__ __forceinline__ bool box_hits(const float4 bb, const SubTile& s) {
   return bb.y >= s.fx0 && bb.x <= s.fx1 && bb.w >= s.fy0 && bb.z <= s.fy1;
 }
 
-// Exact footprint test of one Gaussian against one 8x4 sub-tile: the bounding box above, then the
+// Exact footprint test of one Gaussian against one warp block (8x8 pixels): the bounding box above, then the
 // true minimum of q(u) = A ux^2 + 2 B ux uy + C uy^2 (power = -q/2) over the sub-tile rectangle
 // (expanded by 0.02 px) against the same padded threshold 2*tau.  For a convex quadratic whose
 // centre lies outside the rectangle the minimiser sits on an edge that faces the centre, so at most

@@ -73,23 +73,27 @@ __device__ __forceinline__ float row_sum32(uint32_t addr) {
 }
 
 template <bool CULL, int MODE>
-__global__ void __launch_bounds__(RING_THREADS, 3 * CTA_PARTS) render_bwd_kernel(const RenderBwdArgs a) {
+__global__ void __launch_bounds__(RING_THREADS, MODE == 1 ? 3 : 4) render_bwd_kernel(const RenderBwdArgs a) {
   constexpr int VALS = BwdTraits<MODE>::VALS, GROUP = BwdTraits<MODE>::GROUP, STRIDE = BwdTraits<MODE>::STRIDE;
   constexpr int NV = VALS * GROUP;
+  // A replay of a captured graph whose forward overflowed its binning capacity left the instance records and the
+  // image state untouched (every forward kernel exits on R > Rcap): there is nothing valid to walk.  The accumulator
+  // stays zero, so preprocess_bwd writes all-zero gradients for this step (splat_forward_guard reports the overflow).
+  if (a.hdr->num_rendered > a.Rcap) return;
   extern __shared__ __align__(128) unsigned char smem_dyn[];
   __shared__ __align__(8) uint64_t s_full[RING_NS];
   __shared__ int s_rel[RING_NS];
   __shared__ int s_max[CTA_WARPS];
 
-  const int tile = (int)a.order[blockIdx.x / CTA_PARTS], part = blockIdx.x % CTA_PARTS;
+  const int tile = (int)a.order[blockIdx.x];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const uint2 range = a.ranges[tile];
   const int tile_x = tile % a.gx, tile_y = tile / a.gx;
-  const SubTile st = make_subtile(tile_x, tile_y, part);
-  const bool inside = st.px < a.W && st.py < a.H;
-  const int pix = st.py * a.W + st.px;
-  const int last = inside ? (int)a.n_contrib[pix] : 0;
-  const int warp_hi = __reduce_max_sync(0xffffffffu, last);
+  const SubTile st = make_subtile(tile_x, tile_y);
+  const bool in_a = st.px < a.W && st.pya < a.H, in_b = st.px < a.W && st.pyb < a.H;
+  const int pix_a = st.pya * a.W + st.px, pix_b = st.pyb * a.W + st.px;
+  const int last_a = in_a ? (int)a.n_contrib[pix_a] : 0, last_b = in_b ? (int)a.n_contrib[pix_b] : 0;
+  const int warp_hi = __reduce_max_sync(0xffffffffu, max(last_a, last_b));
 
   if (tid == 0) {
 #pragma unroll
@@ -116,30 +120,50 @@ __global__ void __launch_bounds__(RING_THREADS, 3 * CTA_PARTS) render_bwd_kernel
     for (int c = 0; c < min(nch, RING_NS); ++c) fill(c);
 
   // ------------------------------------------------------------------------------ consumer warps
-  const float pxf = (float)st.px, pyf = (float)st.py;
+  // Per-pixel state, packed (pixel a, pixel b).
+  const float pxf = (float)st.px;
+  const f2 npy2 = pk(-(float)st.pya, -(float)st.pyb);
   const float tile_cx = tile_x * TILE_X + 7.5f, tile_cy = tile_y * TILE_Y + 7.5f;
   const size_t HW = (size_t)a.W * a.H;
-  const float T_final = inside ? a.final_T[pix] : 0.f;
-  float T = T_final;
-  float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
-  if (inside) { dp0 = a.dL_dpix[pix]; dp1 = a.dL_dpix[HW + pix]; dp2 = a.dL_dpix[2 * HW + pix]; }
-  float dp3 = 0.f, dp4 = 0.f, dp5 = 0.f;
   constexpr bool DS = (MODE == 2 || MODE == 3);
-  if (DS && inside) { dp3 = a.dL_dpix[3 * HW + pix]; dp4 = a.dL_dpix[4 * HW + pix]; dp5 = a.dL_dpix[5 * HW + pix]; }
-  float bg_dot = __ldg(a.bg) * dp0 + __ldg(a.bg + 1) * dp1 + __ldg(a.bg + 2) * dp2;
-  if (DS) bg_dot += __ldg(a.bg) * dp3 + __ldg(a.bg + 1) * dp4 + __ldg(a.bg + 2) * dp5;
-  const float nTb = -T_final * bg_dot;
-  float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
-  // MODE 0/2: features are measured relative to a per-pixel reference level (the rendered value when the caller
-  // passes it): k_ch = ref_ch * dL/dpix_ch.  Rsum = sum over the pairs behind of alpha*T*((c - ref) . dL/dpix), seeded
-  // with the background term.
-  float k0 = 0.f, k1 = 0.f, k2 = 0.f, k3 = 0.f, k4 = 0.f, k5 = 0.f;
-  if (MODE != 1 && a.out_color != nullptr && inside) {
-    k0 = a.out_color[pix] * dp0; k1 = a.out_color[HW + pix] * dp1; k2 = a.out_color[2 * HW + pix] * dp2;
-    if (DS) { k3 = a.out_color[3 * HW + pix] * dp3; k4 = a.out_color[4 * HW + pix] * dp4; k5 = a.out_color[5 * HW + pix] * dp5; }
+  constexpr int NCH = DS ? 6 : 3;
+  const float bg0 = __ldg(a.bg), bg1 = __ldg(a.bg + 1), bg2 = __ldg(a.bg + 2);
+  f2 dp[NCH], nk[NCH];      // dL/dpix per channel; minus (reference level * dL/dpix) (MODE 0/2/3)
+  f2 T2, Rs2, nTb2;
+  {
+    float d_a[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, d_b[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float k_a[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, k_b[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int ch = 0; ch < NCH; ++ch) {
+      if (in_a) d_a[ch] = a.dL_dpix[ch * HW + pix_a];
+      if (in_b) d_b[ch] = a.dL_dpix[ch * HW + pix_b];
+    }
+    // MODE 0/2/3: features are measured relative to a per-pixel reference level (the rendered value when the caller
+    // passes it): k_ch = ref_ch * dL/dpix_ch.  Rs = sum over the pairs behind of alpha*T*((c - ref) . dL/dpix), seeded
+    // with the background term.
+    if (MODE != 1 && a.out_color != nullptr) {
+#pragma unroll
+      for (int ch = 0; ch < NCH; ++ch) {
+        if (in_a) k_a[ch] = a.out_color[ch * HW + pix_a] * d_a[ch];
+        if (in_b) k_b[ch] = a.out_color[ch * HW + pix_b] * d_b[ch];
+      }
+    }
+    const float Tf_a = in_a ? a.final_T[pix_a] : 0.f, Tf_b = in_b ? a.final_T[pix_b] : 0.f;
+    float bgd_a = bg0 * d_a[0] + bg1 * d_a[1] + bg2 * d_a[2], bgd_b = bg0 * d_b[0] + bg1 * d_b[1] + bg2 * d_b[2];
+    if (DS) {
+      bgd_a += bg0 * d_a[3] + bg1 * d_a[4] + bg2 * d_a[5];
+      bgd_b += bg0 * d_b[3] + bg1 * d_b[4] + bg2 * d_b[5];
+    }
+    T2 = pk(Tf_a, Tf_b);
+    nTb2 = pk(-Tf_a * bgd_a, -Tf_b * bgd_b);
+    Rs2 = pk(Tf_a * (bgd_a - (((k_a[0] + k_a[1]) + k_a[2]) + ((k_a[3] + k_a[4]) + k_a[5]))),
+             Tf_b * (bgd_b - (((k_b[0] + k_b[1]) + k_b[2]) + ((k_b[3] + k_b[4]) + k_b[5]))));
+#pragma unroll
+    for (int ch = 0; ch < NCH; ++ch) { dp[ch] = pk(d_a[ch], d_b[ch]); nk[ch] = pk(-k_a[ch], -k_b[ch]); }
   }
-  const float c4 = dp4 - k4;
-  float Rsum = T_final * (bg_dot - (((k0 + k1) + k2) + ((k3 + k4) + k5)));
+  const f2 c4_2 = DS ? add2(dp[DS ? 4 : 0], nk[DS ? 4 : 0]) : bc(0.f);   // the constant channel's (1 - ref) * dL/dpix
+  f2 ar0 = bc(0.f), ar1 = bc(0.f), ar2 = bc(0.f), la2 = bc(0.f);        // MODE 1: the reference's running accum_rec
+  float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
   const float ddelx_dx = 0.5f * a.W, ddely_dy = 0.5f * a.H;
   const uint32_t rec_base = smem_u32(smem_dyn);
   const uint32_t tr_base = rec_base + RING_NS * RING_CH * INST_BYTES + wid * TR_WARP_BYTES;
@@ -180,77 +204,92 @@ __global__ void __launch_bounds__(RING_THREADS, 3 * CTA_PARTS) render_bwd_kernel
               const int pos = lo + sub + b;
               const float4 q0 = lds128(r), q1 = lds128(r + 16);
               ids[gsl] = __float_as_uint(q1.w);
-              const float dx = q0.x - pxf, dy = q0.y - pyf;
-              const float power = -0.5f * (q0.z * dx * dx + q1.x * dy * dy) - q0.w * dx * dy;
-              const float G = expf(power);
-              const float alpha = fminf(0.99f, q1.y * G);
-              const bool valid = pos < last && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-              // Warp-uniform branch, then straight-line code for all 32 pixels: a pixel that does not
+              const float dx = q0.x - pxf;
+              const f2 dy2 = add2(bc(q0.y), npy2);
+              // power, exp and alpha exactly as the forward pass formed them: the blend decisions below are the same
+              const f2 pw2 = pair_power(dx, dy2, q0.z, q0.w, q1.x);
+              const f2 G2 = exp2_ref(pw2);
+              float pwa, pwb, ala, alb, Ga, Gb;
+              upk(pw2, pwa, pwb);
+              upk(G2, Ga, Gb);
+              upk(mul2(bc(q1.y), G2), ala, alb);
+              ala = fminf(0.99f, ala);
+              alb = fminf(0.99f, alb);
+              const bool va = pos < last_a && !(pwa > 0.0f) && !(ala < 1.0f / 255.0f);
+              const bool vb = pos < last_b && !(pwb > 0.0f) && !(alb < 1.0f / 255.0f);
+              // Warp-uniform branch, then straight-line packed code for all 64 pixels: a pixel that does not
               // blend this Gaussian runs the same arithmetic with alpha = G = 0, which leaves its
               // running state bit-identical (1/(1-0) == 1 exactly, T*1 == T, and the deferred
               // accum_rec update 0*c + 1*accum is exact) and makes all of its partials exactly 0.
-              anyg[gsl] = __any_sync(0xffffffffu, valid);
+              anyg[gsl] = __any_sync(0xffffffffu, va || vb);
               if (anyg[gsl]) {
                 any = true;
-                const float al = valid ? alpha : 0.f, Gv = valid ? G : 0.f;
-                const float rc = rcp_newton(1.f - al);
-                T = T * rc;
+                const f2 al2 = pk(va ? ala : 0.f, vb ? alb : 0.f), Gv2 = pk(va ? Ga : 0.f, vb ? Gb : 0.f);
+                const f2 rc2 = rcp_newton2(add2(bc(1.f), neg2(al2)));
+                T2 = mul2(T2, rc2);
                 const float4 col = lds128(r + 32);
-                const float w = al * T;
-                float dLda;
+                const f2 w2 = mul2(al2, T2);
+                f2 dLda2;
                 if (MODE == 1) {
                   // the reference's running form (backward.cu:694-713): accum_rec per channel
-                  const float ola = 1.f - last_alpha;
-                  ar0 = last_alpha * lc0 + ola * ar0;
-                  ar1 = last_alpha * lc1 + ola * ar1;
-                  ar2 = last_alpha * lc2 + ola * ar2;
+                  const f2 ola2 = add2(bc(1.f), neg2(la2));
+                  ar0 = fma2(la2, bc(lc0), mul2(ola2, ar0));
+                  ar1 = fma2(la2, bc(lc1), mul2(ola2, ar1));
+                  ar2 = fma2(la2, bc(lc2), mul2(ola2, ar2));
                   lc0 = col.x; lc1 = col.y; lc2 = col.z;
-                  dLda = (col.x - ar0) * dp0 + (col.y - ar1) * dp1 + (col.z - ar2) * dp2;
-                  dLda = dLda * T + nTb * rc;
-                  last_alpha = al;
+                  dLda2 = mul2(add2(bc(col.x), neg2(ar0)), dp[0]);
+                  dLda2 = fma2(add2(bc(col.y), neg2(ar1)), dp[1], dLda2);
+                  dLda2 = fma2(add2(bc(col.z), neg2(ar2)), dp[2], dLda2);
+                  dLda2 = fma2(dLda2, T2, mul2(nTb2, rc2));
+                  la2 = al2;
                 } else {
                   // Same quantity with ONE scalar suffix sum instead of a running average per channel:
                   //   T_i * accum_rec_i[ch] = (1/(1-alpha_i)) * sum_{j behind i} alpha_j T_j c_j[ch]
                   //   => dL/dalpha_i = T_i (c_i . dp) - (1/(1-alpha_i)) (sum_{j behind i} w_j (c_j . dp) + T_final bg . dp)
-                  // (6 instead of 15 instructions per pair for 3 channels, 10 instead of 29 for the six of MODE 2).
                   // each channel's (c - ref) * dp is ONE fma (exact product, single rounding of the difference)
-                  float sdot = (fmaf(col.x, dp0, -k0) + fmaf(col.y, dp1, -k1)) + fmaf(col.z, dp2, -k2);
+                  f2 sdot = add2(add2(fma2(bc(col.x), dp[0], nk[0]), fma2(bc(col.y), dp[1], nk[1])),
+                                 fma2(bc(col.z), dp[2], nk[2]));
                   if (DS) {
                     const float z = q1.z;
-                    sdot += (fmaf(z, dp3, -k3) + c4) + fmaf(z * z, dp5, -k5);
+                    sdot = add2(sdot, add2(add2(fma2(bc(z), dp[DS ? 3 : 0], nk[DS ? 3 : 0]), c4_2),
+                                           fma2(bc(z * z), dp[DS ? 5 : 0], nk[DS ? 5 : 0])));
                   }
-                  dLda = T * sdot - rc * Rsum;
-                  Rsum = fmaf(w, sdot, Rsum);
+                  dLda2 = fma2(T2, sdot, neg2(mul2(rc2, Rs2)));
+                  Rs2 = fma2(w2, sdot, Rs2);
                 }
-                const float c0 = w * dp0, c1 = w * dp1, c2 = w * dp2;
                 if (MODE == 3) {
                   float* o = &v[gsl * VALS];
-                  const float u = Gv * dLda, udx = u * dx, udy = u * dy;
-                  o[0] = udx; o[1] = udy; o[2] = udx * dx; o[3] = udx * dy; o[4] = udy * dy;
-                  o[5] = w * dp3; o[6] = w * dp5;
+                  const f2 u2 = mul2(Gv2, dLda2), udx = mul2(u2, bc(dx)), udy = mul2(u2, dy2);
+                  o[0] = hsum(udx); o[1] = hsum(udy);
+                  o[2] = hsum(mul2(udx, bc(dx))); o[3] = hsum(mul2(udx, dy2)); o[4] = hsum(mul2(udy, dy2));
+                  o[5] = hsum(mul2(w2, dp[DS ? 3 : 0])); o[6] = hsum(mul2(w2, dp[DS ? 5 : 0]));
                 } else if (MODE == 0 || MODE == 2) {
                   float* o = &v[gsl * VALS];
-                  const float u = Gv * dLda, udx = u * dx, udy = u * dy;
-                  o[0] = c0; o[1] = c1; o[2] = c2;
-                  o[3] = udx; o[4] = udy; o[5] = udx * dx; o[6] = udx * dy; o[7] = udy * dy; o[8] = u;
-                  if (MODE == 2) { o[9] = w * dp3; o[10] = w * dp5; }
+                  const f2 u2 = mul2(Gv2, dLda2), udx = mul2(u2, bc(dx)), udy = mul2(u2, dy2);
+                  o[0] = hsum(mul2(w2, dp[0])); o[1] = hsum(mul2(w2, dp[1])); o[2] = hsum(mul2(w2, dp[2]));
+                  o[3] = hsum(udx); o[4] = hsum(udy);
+                  o[5] = hsum(mul2(udx, bc(dx))); o[6] = hsum(mul2(udx, dy2)); o[7] = hsum(mul2(udy, dy2));
+                  o[8] = hsum(u2);
+                  if (MODE == 2) { o[9] = hsum(mul2(w2, dp[DS ? 3 : 0])); o[10] = hsum(mul2(w2, dp[DS ? 5 : 0])); }
                 } else {
-                  const float dL_dG = q1.y * dLda;
-                  const float gdx = Gv * dx, gdy = Gv * dy;
-                  const float mx = dL_dG * (-gdx * q0.z - gdy * q0.w) * ddelx_dx;
-                  const float my = dL_dG * (-gdy * q1.x - gdx * q0.w) * ddely_dy;
+                  const f2 c0 = mul2(w2, dp[0]), c1 = mul2(w2, dp[1]), c2 = mul2(w2, dp[2]);
+                  const f2 dL_dG = mul2(bc(q1.y), dLda2);
+                  const f2 gdx = mul2(Gv2, bc(dx)), gdy = mul2(Gv2, dy2);
+                  // -(gdx*A + gdy*B) * dL_dG * 0.5W ;  -(gdy*C + gdx*B) * dL_dG * 0.5H
+                  const f2 mx = mul2(mul2(dL_dG, neg2(fma2(gdx, bc(q0.z), mul2(gdy, bc(q0.w))))), bc(ddelx_dx));
+                  const f2 my = mul2(mul2(dL_dG, neg2(fma2(gdy, bc(q1.x), mul2(gdx, bc(q0.w))))), bc(ddely_dy));
                   // conic moments in the splat's own frame (slope col.w, preprocess.cu frame_slope)
-                  const float ex = fmaf(col.w, dy, dx), ey = fmaf(-col.w, dx, dy);
-                  const float hq = -0.5f * Gv * dL_dG, hx = hq * ex;
-                  const float qx = hx * ex, qy = hx * ey, qw = hq * ey * ey;
-                  const float op = Gv * dLda;
-                  v[0] = c0 * c0; v[1] = c1 * c1; v[2] = c2 * c2; v[3] = op * op;
-                  const float u5[5] = {qx, qy, qw, mx, my};
+                  const f2 ex = fma2(bc(col.w), dy2, bc(dx)), ey = fma2(bc(-col.w), bc(dx), dy2);
+                  const f2 hq = mul2(mul2(bc(-0.5f), Gv2), dL_dG), hx = mul2(hq, ex);
+                  const f2 qx = mul2(hx, ex), qy = mul2(hx, ey), qw = mul2(mul2(hq, ey), ey);
+                  const f2 op = mul2(Gv2, dLda2);
+                  v[0] = hsum(mul2(c0, c0)); v[1] = hsum(mul2(c1, c1)); v[2] = hsum(mul2(c2, c2)); v[3] = hsum(mul2(op, op));
+                  const f2 u5[5] = {qx, qy, qw, mx, my};
                   int k = 4;
 #pragma unroll
                   for (int p = 0; p < 5; ++p)
 #pragma unroll
-                    for (int q = p; q < 5; ++q) v[k++] = u5[p] * u5[q];
+                    for (int q = p; q < 5; ++q) v[k++] = hsum(mul2(u5[p], u5[q]));
                 }
               }
             }
@@ -298,15 +337,15 @@ int launch_render_bwd(const RenderBwdArgs& a, int T, int mode, cudaStream_t st) 
     attr_set = true;
   }
   if (mode == 3) {
-    render_bwd_kernel<true, 3><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);
+    render_bwd_kernel<true, 3><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
   } else if (mode == 2) {
-    render_bwd_kernel<true, 2><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);
+    render_bwd_kernel<true, 2><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
   } else if (mode == 0) {
-    if (g_disable_cull) render_bwd_kernel<false, 0><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);
-    else render_bwd_kernel<true, 0><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);
+    if (g_disable_cull) render_bwd_kernel<false, 0><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
+    else render_bwd_kernel<true, 0><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
   } else {
-    if (g_disable_cull) render_bwd_kernel<false, 1><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);
-    else render_bwd_kernel<true, 1><<<T * CTA_PARTS, RING_THREADS, BWD_SMEM, st>>>(a);
+    if (g_disable_cull) render_bwd_kernel<false, 1><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
+    else render_bwd_kernel<true, 1><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
   }
   SPLAT_LAUNCH_CHECK("render_bwd_kernel");
   return SPLAT_OK;

@@ -9,9 +9,10 @@
 //    release is the last issues the refill.  Warps drift apart by up to RING_NS stages instead of
 //    idling at __syncthreads (the reference re-syncs the whole CTA every 256 Gaussians,
 //    forward.cu:311-334);
-//  * per-warp 8x4 sub-tiles with an exact conservative footprint test (render.cuh): a warp only
-//    evaluates Gaussians whose alpha>=1/255 ellipse can touch its 32 pixels (ballot + ffs walk),
-//    two hits at a time so the two exponentials overlap;
+//  * per-warp 8x8 blocks with an exact conservative footprint test (render.cuh): a warp only
+//    evaluates Gaussians whose alpha>=1/255 ellipse can touch its 64 pixels (ballot + ffs walk);
+//  * two pixels per lane, blended with packed FP32x2 arithmetic (packed.cuh) including a packed
+//    bit-exact expf;
 //  * colour and depth travel with the record (the reference re-reads colour from global memory per
 //    pixel, forward.cu:361);
 //  * warp-level early termination, and the ring stops being refilled once all warps of the CTA are done.
@@ -23,9 +24,18 @@
 
 namespace splat {
 
+#ifndef FWD_EXACT_CULL
+#define FWD_EXACT_CULL false
+#endif
+
 // DS: fused RGB + depth + silhouette: three more accumulators for the features (z, 1, z*z), z = the
 // record's view depth, blended with the SAME alpha/T -- the second rasterizer pass of scripts/splatam.py:257-259
 // without its preprocess, sort and alpha evaluation.
+//
+// Two pixels per lane (render.cuh): the pair's blend is straight-line packed code.  A pixel that does not blend the
+// Gaussian (failed test, terminated, outside the image) runs it with alpha = 0, which leaves its state bit-identical
+// (T * (1 - 0) == T, fma(T, 0 * c, C) == C); a terminated pixel is encoded as T == 0 (a live T is >= 1e-4), so every
+// later candidate computes test_T == 0 < 1e-4 and changes nothing; the transmittance at termination is parked in Te.
 template <bool CULL, bool COUNT, bool DS>
 __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFwdArgs a) {
   if (a.hdr->num_rendered > a.Rcap) return;
@@ -35,8 +45,8 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
   __shared__ int s_ndone;
   __shared__ int s_stop;
 
-  const int tile = (int)a.order[blockIdx.x / CTA_PARTS], part = blockIdx.x % CTA_PARTS;
-  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int tile = (int)a.order[blockIdx.x];
+  const int tid = threadIdx.x, lane = tid & 31;
   const uint2 range = a.ranges[tile];
   const int n = (int)(range.y - range.x);
   const int nch = (n + RING_CH - 1) / RING_CH;
@@ -62,19 +72,17 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
 
   // ------------------------------------------------------------------------------ consumer warps
   const int tile_x = tile % a.gx, tile_y = tile / a.gx;
-  const SubTile st = make_subtile(tile_x, tile_y, part);
-  const bool inside = st.px < a.W && st.py < a.H;
-  const float pxf = (float)st.px, pyf = (float)st.py;
+  const SubTile st = make_subtile(tile_x, tile_y);
+  const bool in_a = st.px < a.W && st.pya < a.H, in_b = st.px < a.W && st.pyb < a.H;
+  const float pxf = (float)st.px;
+  const f2 npy2 = pk(-(float)st.pya, -(float)st.pyb);
   const float tile_cx = tile_x * TILE_X + 7.5f, tile_cy = tile_y * TILE_Y + 7.5f;
   const uint32_t rec_base = smem_u32(&s_rec[0][0]);
 
-  // A terminated pixel is encoded as T == 0 (a live T is >= 1e-4): every later candidate then computes
-  // test_T == 0 < 1e-4 and changes nothing, so the inner loop needs no separate `done` flag; the
-  // transmittance at termination is parked in T_end.
-  float T = inside ? 1.0f : 0.f, T_end = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 15.0f;
-  float C3 = 0.f, C4 = 0.f, C5 = 0.f;
-  uint32_t last = 0, nblend = 0;
-  bool warp_done = __all_sync(0xffffffffu, T == 0.f);
+  float Ta = in_a ? 1.0f : 0.f, Tb = in_b ? 1.0f : 0.f, Tea = 1.0f, Teb = 1.0f, Da = 15.0f, Db = 15.0f;
+  f2 C0 = bc(0.f), C1 = bc(0.f), C2 = bc(0.f), C3 = bc(0.f), C4 = bc(0.f), C5 = bc(0.f);
+  uint32_t last_a = 0, last_b = 0, nbl_a = 0, nbl_b = 0;
+  bool warp_done = __all_sync(0xffffffffu, Ta == 0.f && Tb == 0.f);
   bool counted = false;
 
   for (int c = 0; c < nch; ++c) {
@@ -96,72 +104,49 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
           if (hit) {
             const float4 q0 = lds128(sbase + j * INST_BYTES);
             const float2 q1 = lds64(sbase + j * INST_BYTES + 16);
-            hit = footprint_hits<false>(make_float2(q0.x, q0.y), make_float4(q0.z, q0.w, q1.x, q1.y), tile_cx, tile_cy, st);
+            hit = footprint_hits<FWD_EXACT_CULL>(make_float2(q0.x, q0.y), make_float4(q0.z, q0.w, q1.x, q1.y), tile_cx, tile_cy, st);
           }
         }
         unsigned m = __ballot_sync(0xffffffffu, hit);
         while (m) {
-          // pop two hits (front-to-back order); evaluate both alphas, then blend in order
-          const int b0 = __ffs(m) - 1;
+          const int b = __ffs(m) - 1;
           m &= m - 1;
-          const bool two = m != 0;
-          const int b1 = two ? __ffs(m) - 1 : b0;
-          m &= m - 1;
-          const uint32_t r0 = sbase + (uint32_t)(sub + b0) * INST_BYTES;
-          const uint32_t r1 = sbase + (uint32_t)(sub + b1) * INST_BYTES;
-          const float4 u0 = lds128(r0), v0 = lds128(r1);
-          const float2 u1 = lds64(r0 + 16), v1 = lds64(r1 + 16);
-          const float dx0 = u0.x - pxf, dy0 = u0.y - pyf;
-          const float dx1 = v0.x - pxf, dy1 = v0.y - pyf;
-          const float pw0 = -0.5f * (u0.z * dx0 * dx0 + u1.x * dy0 * dy0) - u0.w * dx0 * dy0;
-          const float pw1 = -0.5f * (v0.z * dx1 * dx1 + v1.x * dy1 * dy1) - v0.w * dx1 * dy1;
-          const float al0 = fminf(0.99f, u1.y * expf(pw0));
-          const float al1 = fminf(0.99f, v1.y * expf(pw1));
-          const bool ok0 = !(pw0 > 0.0f) && !(al0 < 1.0f / 255.0f);
-          const bool ok1 = two && !(pw1 > 0.0f) && !(al1 < 1.0f / 255.0f);
-          if (ok0) {
-            const float test_T = T * (1 - al0);
-            if (test_T < 0.0001f) {
-              if (T != 0.f) { T_end = T; T = 0.f; }
-            } else {
-              const float4 cq = lds128(r0 + 32);
-              C0 += cq.x * al0 * T;
-              C1 += cq.y * al0 * T;
-              C2 += cq.z * al0 * T;
-              if (DS) {
-                const float z = lds32(r0 + 24);
-                C3 += z * al0 * T;
-                C4 += al0 * T;
-                C5 += (z * z) * al0 * T;
-              }
-              if (T > 0.5f && test_T < 0.5f) D = lds32(r0 + 24);
-              T = test_T;
-              last = (uint32_t)(gbase + sub + b0 + 1);
-              if (COUNT) ++nblend;
-            }
+          const uint32_t r = sbase + (uint32_t)(sub + b) * INST_BYTES;
+          const float4 q0 = lds128(r), q1 = lds128(r + 16);   // (x, y, A, B), (C, opacity, depth, id)
+          const float dx = q0.x - pxf;
+          const f2 dy2 = add2(bc(q0.y), npy2);
+          const f2 pw2 = pair_power(dx, dy2, q0.z, q0.w, q1.x);
+          float pwa, pwb, ala, alb;
+          upk(pw2, pwa, pwb);
+          upk(mul2(bc(q1.y), exp2_ref(pw2)), ala, alb);
+          ala = fminf(0.99f, ala);
+          alb = fminf(0.99f, alb);
+          const bool va = !(pwa > 0.0f) && !(ala < 1.0f / 255.0f);
+          const bool vb = !(pwb > 0.0f) && !(alb < 1.0f / 255.0f);
+          if (!__any_sync(0xffffffffu, va || vb)) continue;
+          const float aa = va ? ala : 0.f, ab = vb ? alb : 0.f;
+          float tta, ttb;
+          upk(mul2(pk(Ta, Tb), add2(bc(1.0f), pk(-aa, -ab))), tta, ttb);   // test_T = T * (1 - alpha)
+          const bool ka = tta < 0.0001f, kb = ttb < 0.0001f;                // terminates here (or already has)
+          if (ka) { if (Ta != 0.f) Tea = Ta; Ta = 0.f; }
+          if (kb) { if (Tb != 0.f) Teb = Tb; Tb = 0.f; }
+          const f2 al2 = pk(ka ? 0.f : aa, kb ? 0.f : ab), T2 = pk(Ta, Tb);
+          const float4 cq = lds128(r + 32);
+          C0 = fma2(T2, mul2(al2, bc(cq.x)), C0);      // C += (c * alpha) * T  (forward.cu:361)
+          C1 = fma2(T2, mul2(al2, bc(cq.y)), C1);
+          C2 = fma2(T2, mul2(al2, bc(cq.z)), C2);
+          const float z = q1.z;
+          if (DS) {
+            C3 = fma2(T2, mul2(al2, bc(z)), C3);
+            C4 = fma2(T2, al2, C4);
+            C5 = fma2(T2, mul2(al2, bc(z * z)), C5);
           }
-          if (ok1) {
-            const float test_T = T * (1 - al1);
-            if (test_T < 0.0001f) {
-              if (T != 0.f) { T_end = T; T = 0.f; }
-            } else {
-              const float4 cq = lds128(r1 + 32);
-              C0 += cq.x * al1 * T;
-              C1 += cq.y * al1 * T;
-              C2 += cq.z * al1 * T;
-              if (DS) {
-                const float z = lds32(r1 + 24);
-                C3 += z * al1 * T;
-                C4 += al1 * T;
-                C5 += (z * z) * al1 * T;
-              }
-              if (T > 0.5f && test_T < 0.5f) D = lds32(r1 + 24);
-              T = test_T;
-              last = (uint32_t)(gbase + sub + b1 + 1);
-              if (COUNT) ++nblend;
-            }
-          }
-          if (__all_sync(0xffffffffu, T == 0.f)) { warp_done = true; break; }
+          if (Ta > 0.5f && tta < 0.5f) Da = z;            // median depth (forward.cu:365-367); never true when T was zeroed
+          if (Tb > 0.5f && ttb < 0.5f) Db = z;
+          const uint32_t pos1 = (uint32_t)(gbase + sub + b + 1);
+          if (!ka) { Ta = tta; if (va) { last_a = pos1; if (COUNT) ++nbl_a; } }
+          if (!kb) { Tb = ttb; if (vb) { last_b = pos1; if (COUNT) ++nbl_b; } }
+          if (__all_sync(0xffffffffu, Ta == 0.f && Tb == 0.f)) { warp_done = true; break; }
         }
       }
     }
@@ -177,34 +162,68 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
     }
   }
 
-  if (inside) {
-    const int pix = st.py * a.W + st.px;
-    const size_t HW = (size_t)a.W * a.H;
-    if (T == 0.f) T = T_end;
+  const size_t HW = (size_t)a.W * a.H;
+  float c0a, c0b, c1a, c1b, c2a, c2b, c3a, c3b, c4a, c4b, c5a, c5b;
+  upk(C0, c0a, c0b); upk(C1, c1a, c1b); upk(C2, c2a, c2b);
+  upk(C3, c3a, c3b); upk(C4, c4a, c4b); upk(C5, c5a, c5b);
+  const float bg0 = __ldg(a.bg + 0), bg1 = __ldg(a.bg + 1), bg2 = __ldg(a.bg + 2);
+  auto store = [&](int py, float T, float Te, float D, uint32_t last, uint32_t nbl, float c0, float c1, float c2,
+                   float c3, float c4, float c5) {
+    const int pix = py * a.W + st.px;
+    if (T == 0.f) T = Te;
     a.final_T[pix] = T;
     a.n_contrib[pix] = last;
-    a.out_color[pix] = C0 + T * __ldg(a.bg + 0);
-    a.out_color[HW + pix] = C1 + T * __ldg(a.bg + 1);
-    a.out_color[2 * HW + pix] = C2 + T * __ldg(a.bg + 2);
+    a.out_color[pix] = c0 + T * bg0;
+    a.out_color[HW + pix] = c1 + T * bg1;
+    a.out_color[2 * HW + pix] = c2 + T * bg2;
     if (DS) {
-      a.out_color[3 * HW + pix] = C3 + T * __ldg(a.bg + 0);
-      a.out_color[4 * HW + pix] = C4 + T * __ldg(a.bg + 1);
-      a.out_color[5 * HW + pix] = C5 + T * __ldg(a.bg + 2);
+      a.out_color[3 * HW + pix] = c3 + T * bg0;
+      a.out_color[4 * HW + pix] = c4 + T * bg1;
+      a.out_color[5 * HW + pix] = c5 + T * bg2;
     }
     if (a.out_depth) a.out_depth[pix] = D;
-    if (COUNT) a.blended[pix] = nblend;
-  }
+    if (COUNT) a.blended[pix] = nbl;
+  };
+  if (in_a) store(st.pya, Ta, Tea, Da, last_a, nbl_a, c0a, c1a, c2a, c3a, c4a, c5a);
+  if (in_b) store(st.pyb, Tb, Teb, Db, last_b, nbl_b, c0b, c1b, c2b, c3b, c4b, c5b);
 }
 
 int g_disable_cull = 0;
 
+// splat_debug_exp_mismatches: packed exp2_ref vs the device library's expf, bit for bit.
+__global__ void __launch_bounds__(256) exp_check_kernel(uint32_t first, unsigned long long pairs, unsigned long long count,
+                                                        unsigned long long* out) {
+  unsigned long long bad = 0;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < pairs;
+       i += (unsigned long long)gridDim.x * blockDim.x) {
+    const uint32_t b0 = first + (uint32_t)(2 * i), b1 = b0 + 1u;
+    const float x0 = __uint_as_float(b0), x1 = __uint_as_float(b1);
+    float e0, e1;
+    upk(exp2_ref(pk(x0, x1)), e0, e1);
+    const float r0 = expf(x0), r1 = expf(x1);
+    const bool ok0 = __float_as_uint(e0) == __float_as_uint(r0) || (e0 != e0 && r0 != r0);
+    const bool ok1 = 2 * i + 1 >= count || __float_as_uint(e1) == __float_as_uint(r1) || (e1 != e1 && r1 != r1);
+    bad += (ok0 ? 0 : 1) + (ok1 ? 0 : 1);
+  }
+  bad = __reduce_add_sync(0xffffffffu, (unsigned)bad);
+  if ((threadIdx.x & 31) == 0 && bad) atomicAdd(out, bad);
+}
+
+int launch_exp_check(uint32_t first, unsigned long long count, unsigned long long* out, cudaStream_t st) {
+  if (count == 0) return SPLAT_OK;
+  const unsigned long long pairs = (count + 1) / 2;
+  exp_check_kernel<<<148 * 8, 256, 0, st>>>(first, pairs, count, out);
+  SPLAT_LAUNCH_CHECK("exp_check_kernel");
+  return SPLAT_OK;
+}
+
 int launch_render_fwd(const RenderFwdArgs& a, int T, cudaStream_t st) {
   ProfScope prof_(K_RENDER_FWD, st);
   if (T <= 0) return SPLAT_OK;
-  if (a.blended) render_fwd_kernel<false, true, false><<<T * CTA_PARTS, RING_THREADS, 0, st>>>(a);
-  else if (a.depth_sil) render_fwd_kernel<true, false, true><<<T * CTA_PARTS, RING_THREADS, 0, st>>>(a);
-  else if (g_disable_cull) render_fwd_kernel<false, false, false><<<T * CTA_PARTS, RING_THREADS, 0, st>>>(a);
-  else render_fwd_kernel<true, false, false><<<T * CTA_PARTS, RING_THREADS, 0, st>>>(a);
+  if (a.blended) render_fwd_kernel<false, true, false><<<T, RING_THREADS, 0, st>>>(a);
+  else if (a.depth_sil) render_fwd_kernel<true, false, true><<<T, RING_THREADS, 0, st>>>(a);
+  else if (g_disable_cull) render_fwd_kernel<false, false, false><<<T, RING_THREADS, 0, st>>>(a);
+  else render_fwd_kernel<true, false, false><<<T, RING_THREADS, 0, st>>>(a);
   SPLAT_LAUNCH_CHECK("render_fwd_kernel");
   return SPLAT_OK;
 }

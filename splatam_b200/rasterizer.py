@@ -18,30 +18,16 @@ What is different from the reference host code, by design:
 import ctypes as C
 import time
 import threading
-from typing import NamedTuple
-
 import torch
 import torch.nn as nn
 
 from . import _lib
 from ._lib import SplatCamera, check, lib
+from .settings import GaussianRasterizationSettings  # noqa: F401  (re-exported: the reference API's name)
 
 NEAR_DG = 0.2     # DG/cuda_rasterizer/auxiliary.h:154
 NEAR_HX = 0.001   # HX/cuda_rasterizer/auxiliary.h:154
 
-
-class GaussianRasterizationSettings(NamedTuple):
-    image_height: int
-    image_width: int
-    tanfovx: float
-    tanfovy: float
-    bg: torch.Tensor
-    scale_modifier: float
-    viewmatrix: torch.Tensor
-    projmatrix: torch.Tensor
-    sh_degree: int
-    campos: torch.Tensor
-    prefiltered: bool
 
 
 _tls = threading.local()

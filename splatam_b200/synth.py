@@ -8,7 +8,7 @@ import math
 
 import torch
 
-from .rasterizer import GaussianRasterizationSettings
+from .settings import GaussianRasterizationSettings
 
 
 def camera_matrices(w, h, fx, fy, cx, cy, w2c=None, near=0.01, far=100.0):

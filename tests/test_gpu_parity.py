@@ -510,3 +510,122 @@ def test_full_size_properties():
     z = run_ours("hx", rs, sc, torch.zeros_like(dL))
     for k in z["grads"]:
         assert float(z["grads"][k].abs().max()) == 0.0, k
+
+
+# ------------------------------------------------------------------------------------------------
+# Round-2 parity holes (VERDICT r01 "What's weak" #1): the two branches of the tile sort that no seeded scene reached,
+# and the packed exponential of the two-pixels-per-lane blend kernels.
+def test_packed_exp_matches_expf():
+    """csrc/packed.cuh exp2_ref == the device library's expf (what the reference build evaluates, forward.cu:349) on
+    EVERY float bit pattern: the alpha >= 1/255 / T < 1e-4 / median-depth decisions rest on it."""
+    import ctypes as C
+    from splatam_b200._lib import lib, check
+    bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for first in (0x00000000, 0x40000000, 0x80000000, 0xC0000000):
+        check(lib.splat_debug_exp_mismatches(first, 1 << 30, C.c_void_p(bad.data_ptr()), st))
+    torch.cuda.synchronize()
+    assert int(bad.item()) == 0, "%d float inputs where the packed exp differs from expf" % int(bad.item())
+
+
+def _compare_forward_exact(ours, ref, rs):
+    H, W = rs.image_height, rs.image_width
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    assert torch.equal(ours["radii"], ref["radii"])
+    assert ours["num_rendered"] == ref["num_rendered"]
+    assert torch.equal(ours["views"]["ranges"], ref["ranges"][:T]), "tile ranges not bit-exact"
+    assert torch.equal(ours["views"]["point_list"], ref["point_list"]), "sorted point list differs at %d positions" % int(
+        (ours["views"]["point_list"] != ref["point_list"]).sum())
+    assert torch.equal(ours["views"]["n_contrib"].flatten(), ref["n_contrib"])
+    assert rel_err(ours["color"], ref["color"], 1e-6) <= FWD_TOL
+    assert rel_err(ours["depth"], ref["depth"], 1e-6) <= FWD_TOL
+
+
+def test_long_tile_lists_take_the_global_memory_sort_path():
+    """40k Gaussians on a 64x64 image: every tile list is longer than the 2048 keys the tile sort holds in shared
+    memory, so the bucket sort runs on the global ping-pong buffers (csrc/binning.cu, `keys_alt`)."""
+    cam = synth_mod().C1
+    rs = synth_mod().make_settings(device="cuda", **cam)
+    sc = {k: v.cuda() for k, v in synth_mod().cloud_scene(40000, cam["w"], cam["h"], cam["fx"], cam["fy"], seed=21).items()}
+    dL = torch.randn(3, cam["h"], cam["w"], generator=torch.Generator().manual_seed(5)).cuda()
+    ours = run_ours("dg", rs, sc, dL)
+    ref = run_ref("dg", rs, sc, dL)
+    lens = (ours["views"]["ranges"][:, 1] - ours["views"]["ranges"][:, 0])
+    assert int(lens.max()) > 2048 * 2, "scene does not exceed the shared-memory sort capacity: max list %d" % int(lens.max())
+    _compare_forward_exact(ours, ref, rs)
+    _check_grads(ours["grads"], ref["grads"], ref2=run_ref("dg", rs, sc, dL)["grads"])
+
+
+def synth_mod():
+    from splatam_b200 import synth
+    return synth
+
+
+def quantised_depth_scene(cam, stride=1, seed=9, wall=True):
+    """SplaTAM's frame-0 map (scripts/splatam.py:89-116,131-132): one Gaussian per pixel, back-projected from a depth
+    image quantised to 1/5000 m (TUM 16-bit PNG) with w2c = I -- view-space depths are bit-equal for hundreds of
+    Gaussians per tile, so the sort order inside a tile is decided by the Gaussian index (stable sort of the
+    reference, cub::DeviceRadixSort, rasterizer_impl.cu:304)."""
+    W, H, fx, fy, cx, cy = cam["w"], cam["h"], cam["fx"], cam["fy"], cam["cx"], cam["cy"]
+    v, u = torch.meshgrid(torch.arange(0, H, stride, dtype=torch.float32), torch.arange(0, W, stride, dtype=torch.float32),
+                          indexing="ij")
+    u, v = u.reshape(-1), v.reshape(-1)
+    z = 2.0 + 0.35 * torch.sin(u / 97.0) + 0.25 * torch.cos(v / 61.0)
+    if wall:
+        z = torch.where(u < W / 2, torch.full_like(z, 1.8), z)       # a fronto-parallel wall: every depth equal
+    z = torch.round(z * 5000.0) / 5000.0
+    P = z.numel()
+    g = torch.Generator().manual_seed(seed)
+    means = torch.stack([(u - cx) / fx * z, (v - cy) / fy * z, z], 1)
+    scale = (z / ((fx + fy) / 2)).unsqueeze(1).repeat(1, 3) * (1.0 + 0.5 * torch.rand(P, 1, generator=g))
+    rot = torch.zeros(P, 4); rot[:, 0] = 1.0
+    return dict(means3D=means.contiguous(), scales=scale.contiguous(), rotations=rot,
+                opacities=torch.full((P, 1), 0.5), colors_precomp=torch.rand(P, 3, generator=g))
+
+
+def test_quantised_depth_ties_sort_by_gaussian_index():
+    cam = dict(w=160, h=96, fx=80.0, fy=80.0, cx=79.5, cy=47.5)
+    rs = synth_mod().make_settings(device="cuda", **cam)
+    sc = {k: v.cuda() for k, v in quantised_depth_scene(cam).items()}
+    dL = torch.randn(3, cam["h"], cam["w"], generator=torch.Generator().manual_seed(6)).cuda()
+    ours = run_ours("dg", rs, sc, dL)
+    ref = run_ref("dg", rs, sc, dL)
+    # the scene really has ties: fewer distinct depth values than Gaussians on the wall
+    z = ours["views"]["depths"][ours["radii"] > 0]
+    assert z.unique().numel() < z.numel() // 4
+    _compare_forward_exact(ours, ref, rs)
+
+
+def test_quantised_depth_ties_full_frame_sort_time():
+    """TUM-size first frame (640x480, 307,200 Gaussians, half of them on a wall at ONE depth): point_list equal to the
+    reference's, and the tile sort's time recorded (gpurun_out/tie_sort_time.json) and bounded -- the in-bin ranking
+    must not degrade when a whole tile shares one depth value."""
+    import ctypes as C
+    import json
+    from splatam_b200._lib import lib
+    cam = synth_mod().TUM
+    rs = synth_mod().make_settings(device="cuda", **cam)
+    sc = {k: v.cuda() for k, v in quantised_depth_scene(cam).items()}
+    dL = torch.randn(3, cam["h"], cam["w"], generator=torch.Generator().manual_seed(7)).cuda()
+    ours = run_ours("dg", rs, sc, dL)
+    ref = run_ref("dg", rs, sc, dL)
+    _compare_forward_exact(ours, ref, rs)
+    times = {}
+    for name, wall in (("ties", True), ("smooth", False)):
+        s2 = {k: v.cuda() for k, v in quantised_depth_scene(cam, wall=wall).items()}
+        run_ours("dg", rs, s2, dL)
+        lib.splat_profile_enable(1)
+        for _ in range(5):
+            run_ours("dg", rs, s2, dL)
+        n = 16
+        ms = (C.c_float * n)(); cnt = (C.c_int32 * n)()
+        lib.splat_profile_read(ms, cnt, n)
+        lib.splat_profile_enable(0)
+        names = [lib.splat_profile_kernel_name(k).decode() for k in range(n)]
+        times[name] = {names[k]: ms[k] / cnt[k] for k in range(n) if cnt[k]}
+    lens = ours["views"]["ranges"][:, 1] - ours["views"]["ranges"][:, 0]
+    rec = dict(max_list=int(lens.max()), mean_list=float(lens.float().mean()), kernel_ms=times)
+    if os.path.isdir(os.path.join(os.path.dirname(GOLDEN_DIR), "..", "gpurun_out")):
+        with open(os.path.join(os.path.dirname(GOLDEN_DIR), "..", "gpurun_out", "tie_sort_time.json"), "w") as f:
+            json.dump(rec, f, indent=1)
+    assert times["ties"]["tile_sort"] < 4.0 * times["smooth"]["tile_sort"] + 0.05, rec
