@@ -49,6 +49,7 @@ struct RenderFwdArgs {
   float* final_T; uint32_t* n_contrib; float* out_color; float* out_depth;
   const ImageHeader* hdr; uint32_t Rcap;
   uint32_t* blended;  // debug: per-pixel count of blended pairs (NULL in production)
+  int zero;           // always 0: an operand ptxas cannot fold (packed.cuh ExpConsts)
 };
 
 struct RenderBwdArgs {
@@ -59,6 +60,7 @@ struct RenderBwdArgs {
   const float* out_color;   // optional: the forward's image, reference level of the per-pixel feature sums (MODE 0/2)
   float* acc;   // MODE 0: [P,12] raw sums.  MODE 1: [P,20] moment accumulator.  Pre-zeroed.
   const ImageHeader* hdr; uint32_t Rcap;   // R > Rcap (a graph replay that overflowed its binning capacity): nothing to walk
+  int zero;     // always 0 (packed.cuh ExpConsts)
 };
 
 // SplaTAM glue (slam_ops.cu).  Render-variable builder: forward outputs o_*, backward inputs g_* (any may be NULL ==

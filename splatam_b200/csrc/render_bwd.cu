@@ -72,8 +72,15 @@ __device__ __forceinline__ float row_sum32(uint32_t addr) {
   return s[0].x + s[0].y;
 }
 
+// Resident CTAs per SM the register allocation is held to: r02a (profiles/) had 120 registers = 4 CTAs = 16 warps per SM and
+// the kernel waited on latency (issue slots 62% busy); 6 CTAs = 24 warps need <= 80 registers.
+#ifndef BWD_CTAS
+#define BWD_CTAS 6
+#endif
+#define BWD_MIN_CTAS(MODE) ((MODE) == 1 ? 4 : BWD_CTAS)
+
 template <bool CULL, int MODE>
-__global__ void __launch_bounds__(RING_THREADS, MODE == 1 ? 3 : 4) render_bwd_kernel(const RenderBwdArgs a) {
+__global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_kernel(const RenderBwdArgs a) {
   constexpr int VALS = BwdTraits<MODE>::VALS, GROUP = BwdTraits<MODE>::GROUP, STRIDE = BwdTraits<MODE>::STRIDE;
   constexpr int NV = VALS * GROUP;
   // A replay of a captured graph whose forward overflowed its binning capacity left the instance records and the
@@ -120,7 +127,8 @@ __global__ void __launch_bounds__(RING_THREADS, MODE == 1 ? 3 : 4) render_bwd_ke
     for (int c = 0; c < min(nch, RING_NS); ++c) fill(c);
 
   // ------------------------------------------------------------------------------ consumer warps
-  // Per-pixel state, packed (pixel a, pixel b).
+  // Per-pixel state of the lane's two pixels (a, b).  Loop-carried values (T, Rs, MODE 1's running sums) are scalar
+  // pairs packed at the point of use: carried as 64-bit values ptxas copies them with two MOVs per hit.
   const float pxf = (float)st.px;
   const f2 npy2 = pk(-(float)st.pya, -(float)st.pyb);
   const float tile_cx = tile_x * TILE_X + 7.5f, tile_cy = tile_y * TILE_Y + 7.5f;
@@ -129,7 +137,8 @@ __global__ void __launch_bounds__(RING_THREADS, MODE == 1 ? 3 : 4) render_bwd_ke
   constexpr int NCH = DS ? 6 : 3;
   const float bg0 = __ldg(a.bg), bg1 = __ldg(a.bg + 1), bg2 = __ldg(a.bg + 2);
   f2 dp[NCH], nk[NCH];      // dL/dpix per channel; minus (reference level * dL/dpix) (MODE 0/2/3)
-  f2 T2, Rs2, nTb2;
+  float Ta, Tb, Rsa, Rsb;
+  f2 nTb2;
   {
     float d_a[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, d_b[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float k_a[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, k_b[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -154,15 +163,16 @@ __global__ void __launch_bounds__(RING_THREADS, MODE == 1 ? 3 : 4) render_bwd_ke
       bgd_a += bg0 * d_a[3] + bg1 * d_a[4] + bg2 * d_a[5];
       bgd_b += bg0 * d_b[3] + bg1 * d_b[4] + bg2 * d_b[5];
     }
-    T2 = pk(Tf_a, Tf_b);
+    Ta = Tf_a; Tb = Tf_b;
     nTb2 = pk(-Tf_a * bgd_a, -Tf_b * bgd_b);
-    Rs2 = pk(Tf_a * (bgd_a - (((k_a[0] + k_a[1]) + k_a[2]) + ((k_a[3] + k_a[4]) + k_a[5]))),
-             Tf_b * (bgd_b - (((k_b[0] + k_b[1]) + k_b[2]) + ((k_b[3] + k_b[4]) + k_b[5]))));
+    Rsa = Tf_a * (bgd_a - (((k_a[0] + k_a[1]) + k_a[2]) + ((k_a[3] + k_a[4]) + k_a[5])));
+    Rsb = Tf_b * (bgd_b - (((k_b[0] + k_b[1]) + k_b[2]) + ((k_b[3] + k_b[4]) + k_b[5])));
 #pragma unroll
     for (int ch = 0; ch < NCH; ++ch) { dp[ch] = pk(d_a[ch], d_b[ch]); nk[ch] = pk(-k_a[ch], -k_b[ch]); }
   }
   const f2 c4_2 = DS ? add2(dp[DS ? 4 : 0], nk[DS ? 4 : 0]) : bc(0.f);   // the constant channel's (1 - ref) * dL/dpix
-  f2 ar0 = bc(0.f), ar1 = bc(0.f), ar2 = bc(0.f), la2 = bc(0.f);        // MODE 1: the reference's running accum_rec
+  // MODE 1: the reference's running accum_rec per channel
+  float ar0a = 0.f, ar0b = 0.f, ar1a = 0.f, ar1b = 0.f, ar2a = 0.f, ar2b = 0.f, laa = 0.f, lab = 0.f;
   float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
   const float ddelx_dx = 0.5f * a.W, ddely_dy = 0.5f * a.H;
   const uint32_t rec_base = smem_u32(smem_dyn);
@@ -170,6 +180,9 @@ __global__ void __launch_bounds__(RING_THREADS, MODE == 1 ? 3 : 4) render_bwd_ke
   const uint32_t tr_st = tr_base + lane * 4;                 // this lane's column
   const uint32_t tr_ld = tr_base + lane * (TR_STRIDE * 4);   // this lane's row (lane < NV)
   const int my_g = lane / VALS, my_k = lane - my_g * VALS;
+  // MODE 3 keeps MODE 2's row layout: values 0-4 -> slots 3-7, values 5, 6 -> slots 9, 10
+  const int slot = (MODE == 3) ? (my_k < 5 ? my_k + 3 : my_k + 4) : my_k;
+  const ExpConsts ek = exp_consts(a.zero & tid);   // lane-dependent as far as ptxas knows: stays in vector registers
 
   for (int c = 0; c < nch; ++c) {
     const int s = c % RING_NS;
@@ -188,8 +201,9 @@ __global__ void __launch_bounds__(RING_THREADS, MODE == 1 ? 3 : 4) render_bwd_ke
           }
         }
         unsigned m = __ballot_sync(0xffffffffu, hit);
+        const uint32_t rsub = sbase + (uint32_t)sub * INST_BYTES;
+        const int pos_sub = lo + sub;
         while (m) {
-          float v[NV];
           uint32_t ids[GROUP];
           bool anyg[GROUP];
           bool any = false;
@@ -198,23 +212,23 @@ __global__ void __launch_bounds__(RING_THREADS, MODE == 1 ? 3 : 4) render_bwd_ke
             ids[gsl] = 0xffffffffu;
             anyg[gsl] = false;
             if (m) {
-              const int b = 31 - __clz(m);
-              m &= ~(1u << b);
-              const uint32_t r = sbase + (uint32_t)(sub + b) * INST_BYTES;
-              const int pos = lo + sub + b;
+              uint32_t b;
+              asm("bfind.u32 %0, %1;" : "=r"(b) : "r"(m));   // back to front: highest list position first
+              m ^= 1u << b;
+              const uint32_t r = rsub + b * INST_BYTES;
+              const int pos = pos_sub + (int)b;
               const float4 q0 = lds128(r), q1 = lds128(r + 16);
               ids[gsl] = __float_as_uint(q1.w);
               const float dx = q0.x - pxf;
               const f2 dy2 = add2(bc(q0.y), npy2);
               // power, exp and alpha exactly as the forward pass formed them: the blend decisions below are the same
               const f2 pw2 = pair_power(dx, dy2, q0.z, q0.w, q1.x);
-              const f2 G2 = exp2_ref(pw2);
+              const f2 G2 = exp2_ref(pw2, ek);
               float pwa, pwb, ala, alb, Ga, Gb;
               upk(pw2, pwa, pwb);
               upk(G2, Ga, Gb);
               upk(mul2(bc(q1.y), G2), ala, alb);
-              ala = fminf(0.99f, ala);
-              alb = fminf(0.99f, alb);
+              // min(0.99, x) < 1/255  <=>  x < 1/255: the test reads the unclamped product
               const bool va = pos < last_a && !(pwa > 0.0f) && !(ala < 1.0f / 255.0f);
               const bool vb = pos < last_b && !(pwb > 0.0f) && !(alb < 1.0f / 255.0f);
               // Warp-uniform branch, then straight-line packed code for all 64 pixels: a pixel that does not
@@ -224,24 +238,28 @@ __global__ void __launch_bounds__(RING_THREADS, MODE == 1 ? 3 : 4) render_bwd_ke
               anyg[gsl] = __any_sync(0xffffffffu, va || vb);
               if (anyg[gsl]) {
                 any = true;
-                const f2 al2 = pk(va ? ala : 0.f, vb ? alb : 0.f), Gv2 = pk(va ? Ga : 0.f, vb ? Gb : 0.f);
+                const f2 al2 = pk(va ? fminf(0.99f, ala) : 0.f, vb ? fminf(0.99f, alb) : 0.f);
+                const f2 Gv2 = pk(va ? Ga : 0.f, vb ? Gb : 0.f);
                 const f2 rc2 = rcp_newton2(add2(bc(1.f), neg2(al2)));
-                T2 = mul2(T2, rc2);
+                const f2 T2 = mul2(pk(Ta, Tb), rc2);
+                upk(T2, Ta, Tb);
                 const float4 col = lds128(r + 32);
                 const f2 w2 = mul2(al2, T2);
                 f2 dLda2;
                 if (MODE == 1) {
                   // the reference's running form (backward.cu:694-713): accum_rec per channel
+                  const f2 la2 = pk(laa, lab);
                   const f2 ola2 = add2(bc(1.f), neg2(la2));
-                  ar0 = fma2(la2, bc(lc0), mul2(ola2, ar0));
-                  ar1 = fma2(la2, bc(lc1), mul2(ola2, ar1));
-                  ar2 = fma2(la2, bc(lc2), mul2(ola2, ar2));
+                  const f2 ar0 = fma2(la2, bc(lc0), mul2(ola2, pk(ar0a, ar0b)));
+                  const f2 ar1 = fma2(la2, bc(lc1), mul2(ola2, pk(ar1a, ar1b)));
+                  const f2 ar2 = fma2(la2, bc(lc2), mul2(ola2, pk(ar2a, ar2b)));
+                  upk(ar0, ar0a, ar0b); upk(ar1, ar1a, ar1b); upk(ar2, ar2a, ar2b);
                   lc0 = col.x; lc1 = col.y; lc2 = col.z;
                   dLda2 = mul2(add2(bc(col.x), neg2(ar0)), dp[0]);
                   dLda2 = fma2(add2(bc(col.y), neg2(ar1)), dp[1], dLda2);
                   dLda2 = fma2(add2(bc(col.z), neg2(ar2)), dp[2], dLda2);
                   dLda2 = fma2(dLda2, T2, mul2(nTb2, rc2));
-                  la2 = al2;
+                  upk(al2, laa, lab);
                 } else {
                   // Same quantity with ONE scalar suffix sum instead of a running average per channel:
                   //   T_i * accum_rec_i[ch] = (1/(1-alpha_i)) * sum_{j behind i} alpha_j T_j c_j[ch]
@@ -254,23 +272,26 @@ __global__ void __launch_bounds__(RING_THREADS, MODE == 1 ? 3 : 4) render_bwd_ke
                     sdot = add2(sdot, add2(add2(fma2(bc(z), dp[DS ? 3 : 0], nk[DS ? 3 : 0]), c4_2),
                                            fma2(bc(z * z), dp[DS ? 5 : 0], nk[DS ? 5 : 0])));
                   }
+                  const f2 Rs2 = pk(Rsa, Rsb);
                   dLda2 = fma2(T2, sdot, neg2(mul2(rc2, Rs2)));
-                  Rs2 = fma2(w2, sdot, Rs2);
+                  upk(fma2(w2, sdot, Rs2), Rsa, Rsb);
                 }
+                // the lane's partials (summed over its two pixels) go straight into the warp's transpose tile: column =
+                // lane, row = value (the previous group's row sums were read before the __syncwarp below)
+                const uint32_t tr_row = tr_st + (uint32_t)(gsl * VALS) * (TR_STRIDE * 4);
+                auto put = [&](int i, f2 x) { sts32(tr_row + (uint32_t)i * (TR_STRIDE * 4), hsum(x)); };
                 if (MODE == 3) {
-                  float* o = &v[gsl * VALS];
                   const f2 u2 = mul2(Gv2, dLda2), udx = mul2(u2, bc(dx)), udy = mul2(u2, dy2);
-                  o[0] = hsum(udx); o[1] = hsum(udy);
-                  o[2] = hsum(mul2(udx, bc(dx))); o[3] = hsum(mul2(udx, dy2)); o[4] = hsum(mul2(udy, dy2));
-                  o[5] = hsum(mul2(w2, dp[DS ? 3 : 0])); o[6] = hsum(mul2(w2, dp[DS ? 5 : 0]));
+                  put(0, udx); put(1, udy);
+                  put(2, mul2(udx, bc(dx))); put(3, mul2(udx, dy2)); put(4, mul2(udy, dy2));
+                  put(5, mul2(w2, dp[DS ? 3 : 0])); put(6, mul2(w2, dp[DS ? 5 : 0]));
                 } else if (MODE == 0 || MODE == 2) {
-                  float* o = &v[gsl * VALS];
                   const f2 u2 = mul2(Gv2, dLda2), udx = mul2(u2, bc(dx)), udy = mul2(u2, dy2);
-                  o[0] = hsum(mul2(w2, dp[0])); o[1] = hsum(mul2(w2, dp[1])); o[2] = hsum(mul2(w2, dp[2]));
-                  o[3] = hsum(udx); o[4] = hsum(udy);
-                  o[5] = hsum(mul2(udx, bc(dx))); o[6] = hsum(mul2(udx, dy2)); o[7] = hsum(mul2(udy, dy2));
-                  o[8] = hsum(u2);
-                  if (MODE == 2) { o[9] = hsum(mul2(w2, dp[DS ? 3 : 0])); o[10] = hsum(mul2(w2, dp[DS ? 5 : 0])); }
+                  put(0, mul2(w2, dp[0])); put(1, mul2(w2, dp[1])); put(2, mul2(w2, dp[2]));
+                  put(3, udx); put(4, udy);
+                  put(5, mul2(udx, bc(dx))); put(6, mul2(udx, dy2)); put(7, mul2(udy, dy2));
+                  put(8, u2);
+                  if (MODE == 2) { put(9, mul2(w2, dp[DS ? 3 : 0])); put(10, mul2(w2, dp[DS ? 5 : 0])); }
                 } else {
                   const f2 c0 = mul2(w2, dp[0]), c1 = mul2(w2, dp[1]), c2 = mul2(w2, dp[2]);
                   const f2 dL_dG = mul2(bc(q1.y), dLda2);
@@ -283,26 +304,19 @@ __global__ void __launch_bounds__(RING_THREADS, MODE == 1 ? 3 : 4) render_bwd_ke
                   const f2 hq = mul2(mul2(bc(-0.5f), Gv2), dL_dG), hx = mul2(hq, ex);
                   const f2 qx = mul2(hx, ex), qy = mul2(hx, ey), qw = mul2(mul2(hq, ey), ey);
                   const f2 op = mul2(Gv2, dLda2);
-                  v[0] = hsum(mul2(c0, c0)); v[1] = hsum(mul2(c1, c1)); v[2] = hsum(mul2(c2, c2)); v[3] = hsum(mul2(op, op));
+                  put(0, mul2(c0, c0)); put(1, mul2(c1, c1)); put(2, mul2(c2, c2)); put(3, mul2(op, op));
                   const f2 u5[5] = {qx, qy, qw, mx, my};
                   int k = 4;
 #pragma unroll
                   for (int p = 0; p < 5; ++p)
 #pragma unroll
-                    for (int q = p; q < 5; ++q) v[k++] = hsum(mul2(u5[p], u5[q]));
+                    for (int q = p; q < 5; ++q) put(k++, mul2(u5[p], u5[q]));
                 }
               }
             }
           }
           if (!any) continue;
-          // transpose through shared memory: column = lane, row = value.  Gaussians of the group that no
-          // pixel of this warp blended (all-zero rows) are skipped on both sides (warp-uniform branches).
-#pragma unroll
-          for (int gsl = 0; gsl < GROUP; ++gsl)
-            if (anyg[gsl]) {
-#pragma unroll
-              for (int i = 0; i < VALS; ++i) sts32(tr_st + (gsl * VALS + i) * (TR_STRIDE * 4), v[gsl * VALS + i]);
-            }
+          // Gaussians of the group that no pixel of this warp blended are skipped on both sides (warp-uniform).
           __syncwarp();
           uint32_t id = ids[0];
           bool mine = anyg[0];
@@ -312,8 +326,6 @@ __global__ void __launch_bounds__(RING_THREADS, MODE == 1 ? 3 : 4) render_bwd_ke
           float tot = 0.f;
           if (mine) tot = row_sum32(tr_ld);
           __syncwarp();
-          // MODE 3 keeps MODE 2's row layout: values 0-4 -> slots 3-7, values 5, 6 -> slots 9, 10
-          const int slot = (MODE == 3) ? (my_k < 5 ? my_k + 3 : my_k + 4) : my_k;
           if (mine && tot != 0.f) red_add_f32(a.acc + (size_t)id * STRIDE + slot, tot);
         }
       }

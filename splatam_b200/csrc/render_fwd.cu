@@ -32,10 +32,10 @@ namespace splat {
 // record's view depth, blended with the SAME alpha/T -- the second rasterizer pass of scripts/splatam.py:257-259
 // without its preprocess, sort and alpha evaluation.
 //
-// Two pixels per lane (render.cuh): the pair's blend is straight-line packed code.  A pixel that does not blend the
-// Gaussian (failed test, terminated, outside the image) runs it with alpha = 0, which leaves its state bit-identical
-// (T * (1 - 0) == T, fma(T, 0 * c, C) == C); a terminated pixel is encoded as T == 0 (a live T is >= 1e-4), so every
-// later candidate computes test_T == 0 < 1e-4 and changes nothing; the transmittance at termination is parked in Te.
+// Two pixels per lane (render.cuh): the pair's blend is straight-line packed code.  A pixel that fails the alpha test
+// runs it with alpha = 0, which leaves its state bit-identical (T * (1 - 0) == T, fma(T, 0 * c, C) == C); a terminated
+// pixel carries T == -0.0f (see the kernel body).  r02a capture (profiles/): 3.45 M warp-level hits per launch at C3,
+// 91% of them with at least one blending pixel, 87 instructions per hit before this form, ~65 after.
 template <bool CULL, bool COUNT, bool DS>
 __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFwdArgs a) {
   if (a.hdr->num_rendered > a.Rcap) return;
@@ -79,11 +79,21 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
   const float tile_cx = tile_x * TILE_X + 7.5f, tile_cy = tile_y * TILE_Y + 7.5f;
   const uint32_t rec_base = smem_u32(&s_rec[0][0]);
 
-  float Ta = in_a ? 1.0f : 0.f, Tb = in_b ? 1.0f : 0.f, Tea = 1.0f, Teb = 1.0f, Da = 15.0f, Db = 15.0f;
-  f2 C0 = bc(0.f), C1 = bc(0.f), C2 = bc(0.f), C3 = bc(0.f), C4 = bc(0.f), C5 = bc(0.f);
+  // A pixel that has terminated (or lies outside the image) is DEAD and is encoded as T == -0.0f: every product with
+  // it is a signed zero, so C += (alpha c) * T and T *= (1 - alpha) leave its state bit-identical with no select, and
+  // the termination test below, an UNSIGNED compare of the bits of test_T against those of 1e-4, is false for it.
+  // The transmittance it terminated with is parked in Te.
+  constexpr uint32_t T_MIN_BITS = 0x38d1b717u;   // 0.0001f (forward.cu:355)
+  const float DEAD = __int_as_float(0x80000000);
+  float Ta = in_a ? 1.0f : DEAD, Tb = in_b ? 1.0f : DEAD, Tea = 1.0f, Teb = 1.0f, Da = 15.0f, Db = 15.0f;
+  // loop-carried accumulators live as scalar pairs and are packed at the point of use: ptxas coalesces the pair
+  // into the FFMA2 destination that way; carried as 64-bit values it copied each of them with two MOVs per hit
+  float c0a = 0.f, c0b = 0.f, c1a = 0.f, c1b = 0.f, c2a = 0.f, c2b = 0.f;
+  float c3a = 0.f, c3b = 0.f, c4a = 0.f, c4b = 0.f, c5a = 0.f, c5b = 0.f;
   uint32_t last_a = 0, last_b = 0, nbl_a = 0, nbl_b = 0;
-  bool warp_done = __all_sync(0xffffffffu, Ta == 0.f && Tb == 0.f);
+  bool warp_done = __all_sync(0xffffffffu, !in_a && !in_b);
   bool counted = false;
+  const ExpConsts ek = exp_consts(a.zero & tid);   // lane-dependent as far as ptxas knows: stays in VECTOR registers
 
   for (int c = 0; c < nch; ++c) {
     const int s = c % RING_NS;
@@ -107,46 +117,57 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
             hit = footprint_hits<FWD_EXACT_CULL>(make_float2(q0.x, q0.y), make_float4(q0.z, q0.w, q1.x, q1.y), tile_cx, tile_cy, st);
           }
         }
-        unsigned m = __ballot_sync(0xffffffffu, hit);
+        // hits in list order = ascending lane = descending bit of the REVERSED ballot: the pop is one FLO (highest
+        // set bit t, lane = 31 - t), and record address and list position are affine in t
+        unsigned m = __brev(__ballot_sync(0xffffffffu, hit));
+        const uint32_t r31 = sbase + (uint32_t)(sub + 31) * INST_BYTES;
+        const uint32_t pos31 = (uint32_t)(gbase + sub + 32);
         while (m) {
-          const int b = __ffs(m) - 1;
-          m &= m - 1;
-          const uint32_t r = sbase + (uint32_t)(sub + b) * INST_BYTES;
+          uint32_t t;
+          asm("bfind.u32 %0, %1;" : "=r"(t) : "r"(m));
+          m ^= 1u << t;
+          const uint32_t r = r31 - t * INST_BYTES;
           const float4 q0 = lds128(r), q1 = lds128(r + 16);   // (x, y, A, B), (C, opacity, depth, id)
+          const float4 cq = lds128(r + 32);                     // (r, g, b, -)
           const float dx = q0.x - pxf;
           const f2 dy2 = add2(bc(q0.y), npy2);
           const f2 pw2 = pair_power(dx, dy2, q0.z, q0.w, q1.x);
           float pwa, pwb, ala, alb;
           upk(pw2, pwa, pwb);
-          upk(mul2(bc(q1.y), exp2_ref(pw2)), ala, alb);
-          ala = fminf(0.99f, ala);
-          alb = fminf(0.99f, alb);
+          upk(mul2(bc(q1.y), exp2_ref(pw2, ek)), ala, alb);
+          // min(0.99, x) < 1/255  <=>  x < 1/255: the test reads the unclamped product
           const bool va = !(pwa > 0.0f) && !(ala < 1.0f / 255.0f);
           const bool vb = !(pwb > 0.0f) && !(alb < 1.0f / 255.0f);
-          if (!__any_sync(0xffffffffu, va || vb)) continue;
-          const float aa = va ? ala : 0.f, ab = vb ? alb : 0.f;
+          float aa = va ? fminf(0.99f, ala) : 0.f, ab = vb ? fminf(0.99f, alb) : 0.f;
           float tta, ttb;
           upk(mul2(pk(Ta, Tb), add2(bc(1.0f), pk(-aa, -ab))), tta, ttb);   // test_T = T * (1 - alpha)
-          const bool ka = tta < 0.0001f, kb = ttb < 0.0001f;                // terminates here (or already has)
-          if (ka) { if (Ta != 0.f) Tea = Ta; Ta = 0.f; }
-          if (kb) { if (Tb != 0.f) Teb = Tb; Tb = 0.f; }
-          const f2 al2 = pk(ka ? 0.f : aa, kb ? 0.f : ab), T2 = pk(Ta, Tb);
-          const float4 cq = lds128(r + 32);
-          C0 = fma2(T2, mul2(al2, bc(cq.x)), C0);      // C += (c * alpha) * T  (forward.cu:361)
-          C1 = fma2(T2, mul2(al2, bc(cq.y)), C1);
-          C2 = fma2(T2, mul2(al2, bc(cq.z)), C2);
+          // termination EVENT of a live pixel: 0 < test_T < 1e-4 (a live T is >= 1e-4 and 1 - alpha >= 0.01, so its
+          // test_T is > 0; a dead pixel's is -0 = 0x80000000, above the threshold as an unsigned integer)
+          const bool ea = __float_as_uint(tta) < T_MIN_BITS, eb = __float_as_uint(ttb) < T_MIN_BITS;
+          if (__any_sync(0xffffffffu, ea || eb)) {   // rare: at most once per pixel
+            if (ea) { Tea = Ta; tta = DEAD; aa = 0.f; }   // `done = true; continue` (forward.cu:356-359): no contribution
+            if (eb) { Teb = Tb; ttb = DEAD; ab = 0.f; }
+            warp_done = __all_sync(0xffffffffu, __float_as_uint(tta) == 0x80000000u && __float_as_uint(ttb) == 0x80000000u);
+          }
+          const f2 al2 = pk(aa, ab), T2 = pk(Ta, Tb);
+          upk(fma2(T2, mul2(al2, bc(cq.x)), pk(c0a, c0b)), c0a, c0b);      // C += (c * alpha) * T  (forward.cu:361)
+          upk(fma2(T2, mul2(al2, bc(cq.y)), pk(c1a, c1b)), c1a, c1b);
+          upk(fma2(T2, mul2(al2, bc(cq.z)), pk(c2a, c2b)), c2a, c2b);
           const float z = q1.z;
           if (DS) {
-            C3 = fma2(T2, mul2(al2, bc(z)), C3);
-            C4 = fma2(T2, al2, C4);
-            C5 = fma2(T2, mul2(al2, bc(z * z)), C5);
+            upk(fma2(T2, mul2(al2, bc(z)), pk(c3a, c3b)), c3a, c3b);
+            upk(fma2(T2, al2, pk(c4a, c4b)), c4a, c4b);
+            upk(fma2(T2, mul2(al2, bc(z * z)), pk(c5a, c5b)), c5a, c5b);
           }
-          if (Ta > 0.5f && tta < 0.5f) Da = z;            // median depth (forward.cu:365-367); never true when T was zeroed
+          if (Ta > 0.5f && tta < 0.5f) Da = z;            // median depth (forward.cu:365-367); false for a dead pixel
           if (Tb > 0.5f && ttb < 0.5f) Db = z;
-          const uint32_t pos1 = (uint32_t)(gbase + sub + b + 1);
-          if (!ka) { Ta = tta; if (va) { last_a = pos1; if (COUNT) ++nbl_a; } }
-          if (!kb) { Tb = ttb; if (vb) { last_b = pos1; if (COUNT) ++nbl_b; } }
-          if (__all_sync(0xffffffffu, Ta == 0.f && Tb == 0.f)) { warp_done = true; break; }
+          const uint32_t pos1 = pos31 - t;
+          // contributor = valid, live and not terminating: test_T >= 1e-4 (false for -0)
+          if (va && tta >= 0.0001f) { last_a = pos1; if (COUNT) ++nbl_a; }
+          if (vb && ttb >= 0.0001f) { last_b = pos1; if (COUNT) ++nbl_b; }
+          Ta = tta;
+          Tb = ttb;
+          if (warp_done) break;
         }
       }
     }
@@ -163,14 +184,11 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
   }
 
   const size_t HW = (size_t)a.W * a.H;
-  float c0a, c0b, c1a, c1b, c2a, c2b, c3a, c3b, c4a, c4b, c5a, c5b;
-  upk(C0, c0a, c0b); upk(C1, c1a, c1b); upk(C2, c2a, c2b);
-  upk(C3, c3a, c3b); upk(C4, c4a, c4b); upk(C5, c5a, c5b);
   const float bg0 = __ldg(a.bg + 0), bg1 = __ldg(a.bg + 1), bg2 = __ldg(a.bg + 2);
   auto store = [&](int py, float T, float Te, float D, uint32_t last, uint32_t nbl, float c0, float c1, float c2,
                    float c3, float c4, float c5) {
     const int pix = py * a.W + st.px;
-    if (T == 0.f) T = Te;
+    if (__float_as_uint(T) == 0x80000000u) T = Te;
     a.final_T[pix] = T;
     a.n_contrib[pix] = last;
     a.out_color[pix] = c0 + T * bg0;
