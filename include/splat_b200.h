@@ -217,6 +217,22 @@ int splat_slam_loss(int32_t width, int32_t height, int32_t tracking, int32_t use
                     float* losses, float* dL_dim, float* dL_ddepth_sil,
                     void* scratch, size_t scratch_bytes, void* stream);
 
+/* splat_slam_track_loss_noalloc: NO COUNTERPART IN THE REFERENCE -- added for
+ *      callers that cannot allocate device memory (code under CUDA-graph capture, tight serving loops, harnesses that
+ *      forbid cudaMalloc).  Same kernels, arguments and results as splat_slam_loss(tracking = 1, ...), but the scratch
+ *      (per-block partial sums + stats, 19,200 bytes) is a `static __device__` array inside the library
+ *      (csrc/noalloc.cu) instead of a caller buffer: the call allocates and frees nothing.
+ *      Limit: width * height <= SPLAT_NOALLOC_MAX_PIXELS; larger images return SPLAT_ERR_SCRATCH_TOO_SMALL (use
+ *      splat_slam_loss with your own scratch).  Every GPU that loads the library holds the array until exit.  All calls
+ *      share it: calls that OVERLAP on the GPU (two streams, two host threads) race on it -- serialise them.  Nothing in
+ *      it needs to start at zero (each call writes every row it reads), so back-to-back calls need no clearing.  The
+ *      first call on each device looks the array's device address up (cudaGetSymbolAddress, no allocation). */
+#define SPLAT_NOALLOC_MAX_PIXELS (4096 * 4096)
+int splat_slam_track_loss_noalloc(int32_t width, int32_t height, int32_t use_sil_for_loss, float sil_thres,
+                                  float w_im, float w_depth,
+                                  const float* im, const float* depth_sil, const float* gt_im, const float* gt_depth,
+                                  float* losses, float* dL_dim, float* dL_ddepth_sil, void* stream);
+
 /* splat_adam_step  <-  the per-iteration optimizer.step() of SplaTAM (scripts/splatam.py:724-725, :889-890):
  *      torch.optim.Adam over one param group per tensor (scripts/splatam.py:166-172; betas (0.9, 0.999), eps 1e-8 while
  *      tracking / 1e-15 while mapping, no weight decay, no amsgrad), all tensors in ONE launch.  Arithmetic as torch/optim/adam.py::_single_tensor_adam:

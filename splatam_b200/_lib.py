@@ -69,6 +69,8 @@ _SIGNATURES = {
     "splat_slam_loss_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     "splat_slam_loss": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_float,
                                   _P, _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
+    "splat_slam_track_loss_noalloc": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_float,
+                                                _P, _P, _P, _P, _P, _P, _P, _P]),
     "splat_adam_step": (C.c_int, [C.POINTER(SplatAdamTensor), C.c_int32, C.c_double, C.c_double, C.c_double, _P, _P, _P]),
     "splat_forward_guard": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, _P, _P]),
     "splat_scale_inplace": (C.c_int, [_P, C.c_int64, _P, _P]),
