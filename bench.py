@@ -63,6 +63,8 @@ def parse():
                          "(torch symmetric memory for the allocation); nccl = torch.distributed.all_reduce")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-mapping", action="store_true",
+                    help="skip the mapping leg (the metric's second half: mapping frames/sec, reported as `mapping`)")
     return ap.parse_args()
 
 
@@ -104,14 +106,18 @@ class ClockSampler:
                      ("sw_thermal_slowdown", pynvml.nvmlClocksEventReasonSwThermalSlowdown),
                      ("sw_power_cap", pynvml.nvmlClocksEventReasonSwPowerCap))
 
+            def sample():
+                try:
+                    sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                    bits = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                    self.rows.append((time.time(), float(sm), float(mx), {n for n, b in names if bits & b}))
+                except Exception:
+                    pass
+            self.sample_now = sample
+
             def loop():
                 while not self._stop.is_set():
-                    try:
-                        sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
-                        bits = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
-                        self.rows.append((time.time(), float(sm), float(mx), {n for n, b in names if bits & b}))
-                    except Exception:
-                        pass
+                    sample()
                     self._stop.wait(self.PERIOD)
             self.thread = threading.Thread(target=loop, daemon=True)
             self.thread.start()
@@ -141,10 +147,18 @@ class ClockSampler:
             except ValueError:
                 continue
 
+    sample_now = None   # NVML mode: takes one sample synchronously
+
     def mark_start(self):
+        # one synchronous sample at each end of the timed region: a 20-step run (25 ms) is shorter than the polling
+        # period, and the line must never ship without a clock sample
         self.t0 = time.time()
+        if self.sample_now:
+            self.sample_now()
 
     def mark_end(self):
+        if self.sample_now:
+            self.sample_now()
         self.t1 = time.time()
 
     def stop(self):
@@ -362,6 +376,7 @@ def pair_counts(runner, keyframes):
     from splatam_b200 import rasterizer as R
     from splatam_b200._lib import lib, check
     tested = blended = 0.0
+    R.keep_last_state = True
     for kf in keyframes:
         runner.step(kf)
         st = R.last_state
@@ -378,14 +393,18 @@ def pair_counts(runner, keyframes):
                                             C.c_void_p(torch.cuda.current_stream().cuda_stream)))
         blended += float(cnt.sum())
     n = float(len(keyframes))
-    return tested / n, blended / n, float(R.last_state.num_rendered)
+    R_last = float(R.last_state.num_rendered)
+    R.keep_last_state, R.last_state = False, None
+    return tested / n, blended / n, R_last
 
 
 LAST_HOST = {}
 
 
 def timed_run(runner, sched, rank, world, steps, warmup, device, dist, on_timed_start=None):
-    """W warm-up + K timed steps of the device-resident loop.  Returns ms (max over ranks)."""
+    """W warm-up + K timed steps of the device-resident loop.  Returns ms (max over ranks).  The caller passes
+    W >= the number of keyframes for the headline pass: every keyframe has a different num_rendered, and the step time
+    is only stable once each has been seen (capacity hints, caching-allocator blocks) -- SCALE_r01's N=1 was 18% off BENCH_r01's with 5 warm-ups."""
     def full_step(i):
         runner.step(int(sched[i % sched.shape[0], rank]))
         if world > 1:
@@ -501,6 +520,114 @@ def e2e_run(runner, sched, rank, world, steps, device, dist):
     return float(t[0].item()), float(t[1].item())
 
 
+MAP_ITERS_PER_FRAME = 60    # configs/replica/splatam.py:81 (mapping num_iters), BASELINE.json configs[2]
+
+
+def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, warmup):
+    """The metric's second half: the REAL mapping iteration of scripts/splatam.py:848-905 at C3 (1200x680, 1M Gaussians,
+    24-keyframe window) -- get_loss(mapping=True) (0.8 L1 + 0.2 (1 - SSIM) colour + masked L1 depth over an RGB + depth +
+    silhouette render), backward, [N > 1: ONE exchange of the raw-parameter gradient bucket], Adam step -- keyframes sharded
+    over the ranks (rank r runs keyframe schedule[step, r]).  A mapped frame = 60 iterations = ceil(60/N) steps.
+    ours: fused builder / render / loss kernels + FusedAdam.  reference (N = 1 only): the restated torch glue around the
+    unmodified reference extension + torch.optim.Adam, as the reference builds it."""
+    import math
+    import bench_slam as BS
+    from splatam_b200 import mapping
+    nf = 24
+    cam, rs, params = BS.build("mapping", device, nf)
+    P = params["means3D"].shape[0]
+    targets = BS.make_targets(params, rs, nf, device) if impl == "ours" else BS.make_targets_ref(params, rs, nf, device, variant)
+    variables = {"max_2D_radius": torch.zeros(P, device=device)}
+    wts = dict(im=0.5, depth=1.0)                             # configs/replica/splatam.py:88-91
+    bucket, how = None, "none (single GPU)"
+    if impl == "ours":
+        from splatam_b200 import slam
+        raw = {k: params[k].detach() for k, _ in mapping.raw_layout(1)}
+        if world > 1 and collective == "peer":
+            why = ""
+            try:
+                bucket = mapping.GradBucket(raw, device, direct=True, peer_group=dist.group.WORLD, layout=mapping.raw_layout(1))
+            except Exception as e:  # noqa: BLE001
+                why, bucket = repr(e)[:160], None
+            ok = torch.tensor([0.0 if bucket is None else 1.0], device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if float(ok.item()) != 1.0:
+                sys.stderr.write("mapping leg: peer-memory all-reduce unavailable (%s); using NCCL\n" % why)
+                bucket = None
+        if bucket is None:
+            bucket = mapping.GradBucket(raw, device, direct=True, layout=mapping.raw_layout(1))
+            how = "NCCL all_reduce" if world > 1 else how
+        else:
+            how = "own kernel, " + ("NVSwitch in-switch reduction (multimem)" if bucket.peer.multicast else
+                                    "two-shot over NVLink peer loads/stores")
+        params = dict(bucket.leaves(), cam_unnorm_rots=params["cam_unnorm_rots"], cam_trans=params["cam_trans"])
+        Adam = slam.FusedAdam
+    else:
+        Adam = torch.optim.Adam
+    step = BS.make_step(impl, variant, params, targets, variables, wts, False, 0.5)
+    opt = Adam([{'params': [v], 'name': k, 'lr': BS.MAPPING_LRS[k]} for k, v in params.items()], lr=0.0, eps=1e-15)
+    sched = mapping.keyframe_schedule(nf, steps + warmup, world, seed=11)
+    check = {}
+
+    def full(i, verify=False):
+        if bucket is None:
+            opt.zero_grad(set_to_none=True)    # a direct bucket is fully overwritten by the next backward
+        loss = step(int(sched[i % sched.shape[0], rank]))
+        if world > 1 and bucket is not None:
+            if verify:
+                local = bucket.grads.clone()
+            bucket.all_reduce()
+            if verify:   # correctness of the exchange, carried by the bench line itself
+                parts = [torch.empty_like(local) for _ in range(world)]
+                dist.all_gather(parts, local)
+                ordered = parts[0].clone()
+                for q in parts[1:]:
+                    ordered += q                  # rank order 0, 1, ...: what the peer kernel's slice owners compute
+                nccl = local.clone()
+                dist.all_reduce(nccl)
+                scale = float(ordered.abs().max())
+                d_ord = float((bucket.grads - ordered).abs().max())
+                d_nccl = float((bucket.grads - nccl).abs().max())
+                t = torch.tensor([d_ord, d_nccl, scale], device=device)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                check.update(max_abs_diff_vs_rank_ordered_sum=float(t[0]), max_abs_diff_vs_nccl=float(t[1]),
+                             max_abs_value=float(t[2]), bit_exact_vs_rank_ordered_sum=float(t[0]) == 0.0,
+                             rel_diff_vs_nccl=float(t[1]) / max(float(t[2]), 1e-30), elements=int(local.numel()))
+                del parts, ordered, nccl, local
+        with torch.no_grad():
+            opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    full(0, verify=True)
+    for i in range(1, max(warmup, 3)):
+        full(i)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        loss = full(warmup + i)
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / steps
+    spf = math.ceil(MAP_ITERS_PER_FRAME / world)
+    out = {"iters_per_s": world * 1e3 / ms, "ms_per_step": ms, "frames_per_s": 1e3 / (spf * ms), "unit": "mapped frames/s",
+           "iters_per_frame": MAP_ITERS_PER_FRAME, "steps_per_frame": spf, "steps": steps, "warmup": max(warmup, 3),
+           "workload": "replica_1200x680_1M_mapping: 24-keyframe window, get_loss(mapping) + backward + exchange + Adam",
+           "optimizer": "FusedAdam (one launch)" if impl == "ours" else "torch.optim.Adam",
+           "collective": how, "last_loss": float(loss.detach())}
+    if check:
+        out["collective_check"] = check
+    return out
+
+
 _REAL_STDOUT = None
 
 
@@ -562,7 +689,7 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=device)
     from splatam_b200 import mapping
-    sched = mapping.keyframe_schedule(len(cams), max(args.steps, 8), world, seed=11)
+    sched = mapping.keyframe_schedule(len(cams), max(args.steps, len(cams), 8), world, seed=11)
     RunnerCls = OursRunner if args.impl == "ours" else RefCudaRunner
     if args.rgbd != "off":
         if args.impl != "ours" and args.rgbd == "fused":
@@ -607,7 +734,9 @@ def main():
     def on_timed_start():
         sampler.mark_start()
 
-    ms, launches = timed_run(runner, sched, rank, world, args.steps, args.warmup, device, dist, on_timed_start)
+    warm_run = max(args.warmup, len(cams), 3)   # at least one pass over the keyframe window (both arms)
+    base["config"]["warmup_steps_run"] = warm_run
+    ms, launches = timed_run(runner, sched, rank, world, args.steps, warm_run, device, dist, on_timed_start)
     sampler.mark_end()
     LAST_HOST_MAIN = dict(LAST_HOST)
     clocks = sampler.stop()
@@ -640,6 +769,14 @@ def main():
                "ms_per_step": ems / args.steps, "wall_ms_per_step": ewall / args.steps,
                "pipeline": "3 streams, double-buffered: H2D(i+1) | render(i) | D2H(i-1)"}
 
+    # ---- mapping: the metric's second half (ours at every N; reference at N = 1)
+    mapping_out = None
+    if not args.no_mapping and args.workload == "replica_1200x680_1M" and args.rgbd == "off" and \
+            (args.impl == "ours" or world == 1):
+        msteps = args.steps if args.impl == "ours" else min(args.steps, 24)
+        mwarm = max(args.warmup, 24) if args.impl == "ours" else 3    # ours: one pass over the 24 keyframes
+        mapping_out = mapping_leg(args.impl, args.variant, rank, world, device, dist, args.collective, msteps, mwarm)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -647,6 +784,8 @@ def main():
 
     host = dict(LAST_HOST_MAIN)
     out = dict(base, value=value, ms_per_step=ms / args.steps, clocks=clocks, e2e=e2e, gpu_launches=launches)
+    if mapping_out is not None:
+        out["mapping"] = mapping_out
     if args.impl == "ours":
         out["host"] = {k: round(v, 4) for k, v in host.items()}
     if args.impl != "ours":

@@ -77,6 +77,84 @@ def make_targets(params, rs, n_frames, device):
     return out
 
 
+def make_targets_ref(params, rs, n_frames, device, variant):
+    """make_targets for the reference arm: the same perturbed-pose ground truth rendered by the UNMODIFIED reference
+    extension (two passes, scripts/splatam.py:255-259) through the restated torch glue -- libsplat_b200.so is not
+    touched."""
+    from oracle import ref_ext, slam_oracle as SO
+    ref_ext.load(variant)
+    Renderer = ref_ext.renderer_class(variant)
+    g = torch.Generator().manual_seed(5)
+    out = []
+    with torch.no_grad():
+        pert = {k: v.detach().clone() for k, v in params.items()}
+        pert["cam_unnorm_rots"] += 0.004 * torch.randn(pert["cam_unnorm_rots"].shape, generator=g).to(device)
+        pert["cam_trans"] += 0.005 * torch.randn(pert["cam_trans"].shape, generator=g).to(device)
+        w2c = torch.eye(4, device=device)
+        for k in range(n_frames):
+            tg = SO.transform_to_frame(pert, k, False, False)
+            rv = SO.transformed_params2rendervar(pert, tg)
+            rv["means2D"] = torch.zeros_like(pert["means3D"])
+            im, _, _ = Renderer(rs)(**rv)
+            rv2 = dict(rv)
+            rv2["colors_precomp"] = SO.get_depth_and_silhouette(tg["means3D"], w2c)
+            ds, _, _ = Renderer(rs)(**rv2)
+            depth = ds[0:1].clone()
+            depth[ds[1:2] < 0.5] = 0.0
+            out.append({"cam": rs, "im": im.clamp(0, 1).contiguous(), "depth": depth.contiguous(), "w2c": w2c})
+    return out
+
+
+MAPPING_LRS = dict(means3D=0.0001, rgb_colors=0.0025, unnorm_rotations=0.001, logit_opacities=0.05, log_scales=0.001,
+                   cam_unnorm_rots=0.0, cam_trans=0.0)     # configs/replica/splatam.py:92-100
+TRACKING_LRS = dict(means3D=0.0, rgb_colors=0.0, unnorm_rotations=0.0, logit_opacities=0.0, log_scales=0.0,
+                    cam_unnorm_rots=0.0004, cam_trans=0.002)   # configs/replica/splatam.py:71-79
+
+
+def make_step(impl, variant, params, targets, variables, wts, tracking, sil_thres, pose_only=False):
+    """One get_loss + backward (scripts/splatam.py:226-353) as a callable step(kf) -> loss, for impl in
+    ours (fused kernels) | dropin (reference torch glue around OUR 3-channel rasterizer) | reference (same glue around
+    the unmodified reference extension)."""
+    if impl == "ours":
+        from splatam_b200 import slam
+
+        def step(kf):
+            loss, _, wl = slam.get_loss(params, targets[kf], variables, kf, wts, tracking, sil_thres, True, False,
+                                        tracking=tracking, mapping=not tracking, tracking_pose_only=pose_only)
+            loss.backward()
+            return loss
+        return step
+    from oracle import slam_oracle as SO
+    if impl == "dropin":
+        from diff_gaussian_rasterization import GaussianRasterizer as R
+        Renderer = lambda raster_settings: R(raster_settings)   # noqa: E731
+    else:
+        from oracle import ref_ext
+        ref_ext.load(variant)
+        Renderer = ref_ext.renderer_class(variant)
+
+    def step(kf):   # scripts/splatam.py:226-353 (get_loss) with the restated glue
+        cur = targets[kf]
+        gg, cg = (False, True) if tracking else (True, False)
+        tg = SO.transform_to_frame(params, kf, gg, cg)
+        rv = SO.transformed_params2rendervar(params, tg)
+        rv["means2D"] = torch.zeros_like(params["means3D"], requires_grad=True) + 0
+        rv["means2D"].retain_grad()
+        im, radius, _ = Renderer(cur["cam"])(**rv)
+        variables["means2D"] = rv["means2D"]
+        rv2 = dict(rv)
+        rv2["colors_precomp"] = SO.get_depth_and_silhouette(tg["means3D"], cur["w2c"])
+        rv2["means2D"] = torch.zeros_like(params["means3D"], requires_grad=True) + 0
+        ds, _, _ = Renderer(cur["cam"])(**rv2)
+        loss, wl = SO.image_loss(im, ds, cur["im"], cur["depth"], wts, tracking, sil_thres, True, False, tracking)
+        seen = radius > 0
+        variables["max_2D_radius"][seen] = torch.max(radius[seen], variables["max_2D_radius"][seen])
+        variables["seen"] = seen
+        loss.backward()
+        return loss
+    return step
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--mode", default="tracking", choices=["tracking", "mapping"])
@@ -149,49 +227,11 @@ def main():
         leaves = bucket.leaves()
         params = dict(leaves, cam_unnorm_rots=params["cam_unnorm_rots"], cam_trans=params["cam_trans"])
         sched = mapping.keyframe_schedule(nf, max(args.steps, 8) + args.warmup, world, seed=11)
-    if args.impl == "ours":
-        def step(kf):
-            loss, _, wl = slam.get_loss(params, targets[kf], variables, kf, wts, tracking, sil_thres, True, False,
-                                        tracking=tracking, mapping=not tracking,
-                                        tracking_pose_only=args.pose_only)
-            loss.backward()
-            return loss
-    else:
-        from oracle import slam_oracle as SO
-        if args.impl == "dropin":
-            from diff_gaussian_rasterization import GaussianRasterizer as R
-            Renderer = lambda raster_settings: R(raster_settings)   # noqa: E731
-        else:
-            from oracle import ref_ext
-            ref_ext.load(args.variant)
-            Renderer = ref_ext.renderer_class(args.variant)
-
-        def step(kf):   # scripts/splatam.py:226-353 (get_loss) with the restated glue
-            cur = targets[kf]
-            gg, cg = (False, True) if tracking else (True, False)
-            tg = SO.transform_to_frame(params, kf, gg, cg)
-            rv = SO.transformed_params2rendervar(params, tg)
-            rv["means2D"] = torch.zeros_like(params["means3D"], requires_grad=True) + 0
-            rv["means2D"].retain_grad()
-            im, radius, _ = Renderer(cur["cam"])(**rv)
-            variables["means2D"] = rv["means2D"]
-            rv2 = dict(rv)
-            rv2["colors_precomp"] = SO.get_depth_and_silhouette(tg["means3D"], cur["w2c"])
-            rv2["means2D"] = torch.zeros_like(params["means3D"], requires_grad=True) + 0
-            ds, _, _ = Renderer(cur["cam"])(**rv2)
-            loss, wl = SO.image_loss(im, ds, cur["im"], cur["depth"], wts, tracking, sil_thres, True, False, tracking)
-            seen = radius > 0
-            variables["max_2D_radius"][seen] = torch.max(radius[seen], variables["max_2D_radius"][seen])
-            variables["seen"] = seen
-            loss.backward()
-            return loss
+    step = make_step(args.impl, args.variant, params, targets, variables, wts, tracking, sil_thres, args.pose_only)
 
     opt = None
     if args.optimizer != "none":   # initialize_optimizer (scripts/splatam.py:166-172) with the config's learning rates
-        lrs = (dict(means3D=0.0, rgb_colors=0.0, unnorm_rotations=0.0, logit_opacities=0.0, log_scales=0.0,
-                    cam_unnorm_rots=0.0004, cam_trans=0.002) if tracking else
-               dict(means3D=0.0001, rgb_colors=0.0025, unnorm_rotations=0.001, logit_opacities=0.05, log_scales=0.001,
-                    cam_unnorm_rots=0.0, cam_trans=0.0))     # configs/replica/splatam.py:71-79, :92-100
+        lrs = TRACKING_LRS if tracking else MAPPING_LRS
         Adam = slam.FusedAdam if args.optimizer == "fused" else torch.optim.Adam
         groups = [{'params': [v], 'name': k, 'lr': lrs[k]} for k, v in params.items()]
         opt = Adam(groups) if tracking else Adam(groups, lr=0.0, eps=1e-15)

@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsplat_b200.so")
+# SPLAT_B200_LIB: developer override, used by the A/B scripts to load an alternative build of the same ABI
+LIB_PATH = os.environ.get("SPLAT_B200_LIB") or os.path.join(_HERE, "libsplat_b200.so")
 
 
 class SplatCamera(C.Structure):

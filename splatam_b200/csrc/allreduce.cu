@@ -14,6 +14,7 @@
 // every peer's pad (st.release.sys) and spins on its own pad until all words reach `epoch`
 // (ld.acquire.sys).  A spin that outlives ~4 s traps instead of hanging the GPU.
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -28,6 +29,7 @@ struct PeerArgs {
   int rank, world;
   uint32_t epoch;
   size_t n4;            // bucket length in float4
+  long long timeout_cycles;   // a peer that has not arrived after this many SM cycles: trap (0 = wait forever)
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -52,7 +54,7 @@ __global__ void __launch_bounds__(32) peer_barrier_kernel(const PeerArgs a, int 
   const uint32_t* mine = a.pad[a.rank] + slot * PAD_STRIDE + j;
   const long long t0 = clock64();
   while ((int32_t)(ld_acquire_sys(mine) - a.epoch) < 0) {
-    if (clock64() - t0 > 8000000000LL) __trap();   // a peer never arrived: fail loudly, do not hang
+    if (a.timeout_cycles && clock64() - t0 > a.timeout_cycles) __trap();   // a peer never arrived: fail loudly
     __nanosleep(64);
   }
 }
@@ -137,6 +139,11 @@ extern "C" int splat_peer_allreduce_sum(const uint64_t* buffers, const uint64_t*
     a.pad[j] = reinterpret_cast<uint32_t*>(flag_pads[j]);
   }
   a.rank = rank; a.world = world; a.epoch = epoch; a.n4 = (size_t)n_floats / 4;
+  {  // SPLAT_PEER_TIMEOUT_S: seconds a rank waits for its peers before the barrier traps (default 60; 0 = forever, as
+     // NCCL would).  A rank can legitimately stall for seconds: first-iteration allocation, a checkpoint, a debugger.
+    static const double timeout_s = [] { const char* e = getenv("SPLAT_PEER_TIMEOUT_S"); return e ? atof(e) : 60.0; }();
+    a.timeout_cycles = timeout_s > 0.0 ? (long long)(timeout_s * 2.0e9) : 0;
+  }
   cudaStream_t st = (cudaStream_t)stream;
   peer_barrier_kernel<<<1, 32, 0, st>>>(a, 0);
   SPLAT_LAUNCH_CHECK("peer_barrier_kernel");

@@ -42,10 +42,15 @@ template <> struct BwdTraits<1> { static const int VALS = 19, GROUP = 1, STRIDE 
 template <> struct BwdTraits<2> { static const int VALS = 11, GROUP = 2, STRIDE = 12; };
 template <> struct BwdTraits<3> { static const int VALS = 7, GROUP = 4, STRIDE = 12; };   // MODE 2 without rows 0-2 and 8
 
+// The backward ring's chunk length is its own (the forward keeps RING_CH): with 64-record stages the CTA's dynamic
+// shared memory is 3*64*48 + 4*28*36*4 = 25.3 KB, so BWD_CTAS = 8 CTAs fit an SM (34.5 KB with 128-record stages = 6).
+#ifndef BWD_CH
+#define BWD_CH 128
+#endif
 #define TR_STRIDE 36                        // words per transposed row (32 lanes + 4 pad)
 #define TR_ROWS 28
 #define TR_WARP_BYTES (TR_ROWS * TR_STRIDE * 4)
-#define BWD_SMEM (RING_NS * RING_CH * INST_BYTES + CTA_WARPS * TR_WARP_BYTES)
+#define BWD_SMEM (RING_NS * BWD_CH * INST_BYTES + CTA_WARPS * TR_WARP_BYTES)
 
 __device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
   float2 r;
@@ -112,16 +117,16 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
   int hi = 0;  // list positions >= max(n_contrib) over the tile are never touched by anyone
 #pragma unroll
   for (int w = 0; w < CTA_WARPS; ++w) hi = max(hi, s_max[w]);
-  const int nch = (hi + RING_CH - 1) / RING_CH;
+  const int nch = (hi + BWD_CH - 1) / BWD_CH;
 
-  // chunk c = list positions [max(0, hi-(c+1)*RING_CH), hi - c*RING_CH), streamed into stage c % RING_NS
+  // chunk c = list positions [max(0, hi-(c+1)*BWD_CH), hi - c*BWD_CH), streamed into stage c % RING_NS
   const char* src = reinterpret_cast<const char*>(a.inst) + (size_t)range.x * INST_BYTES;
   auto fill = [&](int c) {
     const int s = c % RING_NS;
-    const int top = hi - c * RING_CH, lo = max(0, top - RING_CH);
+    const int top = hi - c * BWD_CH, lo = max(0, top - BWD_CH);
     const uint32_t bytes = (uint32_t)(top - lo) * INST_BYTES;
     mbar_arrive_expect_tx(&s_full[s], bytes);
-    tma_load_1d(smem_dyn + s * (RING_CH * INST_BYTES), src + (size_t)lo * INST_BYTES, bytes, &s_full[s]);
+    tma_load_1d(smem_dyn + s * (BWD_CH * INST_BYTES), src + (size_t)lo * INST_BYTES, bytes, &s_full[s]);
   };
   if (tid == 0)
     for (int c = 0; c < min(nch, RING_NS); ++c) fill(c);
@@ -176,7 +181,7 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
   float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
   const float ddelx_dx = 0.5f * a.W, ddely_dy = 0.5f * a.H;
   const uint32_t rec_base = smem_u32(smem_dyn);
-  const uint32_t tr_base = rec_base + RING_NS * RING_CH * INST_BYTES + wid * TR_WARP_BYTES;
+  const uint32_t tr_base = rec_base + RING_NS * BWD_CH * INST_BYTES + wid * TR_WARP_BYTES;
   const uint32_t tr_st = tr_base + lane * 4;                 // this lane's column
   const uint32_t tr_ld = tr_base + lane * (TR_STRIDE * 4);   // this lane's row (lane < NV)
   const int my_g = lane / VALS, my_k = lane - my_g * VALS;
@@ -187,9 +192,9 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
   for (int c = 0; c < nch; ++c) {
     const int s = c % RING_NS;
     mbar_wait(&s_full[s], (c / RING_NS) & 1);
-    const int top = hi - c * RING_CH, lo = max(0, top - RING_CH), cnt = top - lo;
+    const int top = hi - c * BWD_CH, lo = max(0, top - BWD_CH), cnt = top - lo;
     if (warp_hi > lo) {
-      const uint32_t sbase = rec_base + (uint32_t)s * (RING_CH * INST_BYTES);
+      const uint32_t sbase = rec_base + (uint32_t)s * (BWD_CH * INST_BYTES);
       for (int sub = ((cnt - 1) >> 5) << 5; sub >= 0; sub -= 32) {
         const int j = sub + lane;
         bool hit = j < cnt && (lo + j) < warp_hi;

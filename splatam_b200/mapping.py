@@ -151,7 +151,7 @@ class PeerAllReduce:
     def __call__(self):
         import ctypes as C
         from ._lib import check, lib
-        self.epoch = (self.epoch + 1) & 0x7fffffff
+        self.epoch = (self.epoch + 1) & 0xffffffff   # full 32-bit epochs: the kernel's (int32)(flag - epoch) < 0 is wrap-safe
         check(lib.splat_peer_allreduce_sum(self._bufs, self._pads, self.multicast, self.rank, self.world, self.epoch,
                                            self.numel,
                                            C.c_void_p(torch.cuda.current_stream().cuda_stream)))

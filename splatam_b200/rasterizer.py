@@ -31,8 +31,17 @@ NEAR_HX = 0.001   # HX/cuda_rasterizer/auxiliary.h:154
 
 
 _tls = threading.local()
-_capacity_hint = {}   # (device index, H, W) -> last num_rendered
-_CAP_GROWTH, _CAP_SLACK = 1.25, 65536   # speculative binning capacity = hint * growth + slack
+# (device index, H, W) -> slowly decaying maximum of the recent num_rendered values.  The speculative binning capacity is
+# derived from it and rounded up to _CAP_STEP instances, so consecutive calls (the 24 keyframes of a mapping window have
+# 24 different R) ask the caching allocator for the SAME block size instead of a new one every step, and a caller that
+# alternates a small and a large map at one image size keeps the large capacity instead of re-running phase 2.
+_capacity_hint = {}
+_CAP_GROWTH, _CAP_SLACK, _CAP_STEP, _CAP_DECAY = 1.25, 65536, 1 << 20, 0.98
+
+
+def _spec_capacity(hint):
+    cap = int(hint * _CAP_GROWTH) + _CAP_SLACK
+    return (cap + _CAP_STEP - 1) // _CAP_STEP * _CAP_STEP
 
 
 def _pinned_scalar(device):
@@ -141,7 +150,10 @@ class RasterState:
             depths=grec[:, 6], means2D=grec[:, 0:2], conic_opacity=grec[:, 2:6], colors=grec[:, 8:11])
 
 
-last_state = None   # most recent RasterState (debug / parity tests only)
+# Debug / parity tests only: with keep_last_state = True the most recent RasterState is kept in last_state (it pins that
+# call's geometry / image / binning buffers, ~200 MB at Replica size, until the next call).  Off by default.
+keep_last_state = False
+last_state = None
 
 
 def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rotations, cov3D_precomp, sh, bwd=None,
@@ -200,18 +212,19 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
             # established; the guard kernel records (device side) whether a replay ever exceeds it.
             if hint is None:
                 raise RuntimeError("run one un-captured forward at this image size before capturing a CUDA graph")
-            phase2(int(hint * _CAP_GROWTH) + _CAP_SLACK)
+            phase2(_spec_capacity(hint))
             check(lib.splat_forward_guard(_ptr(st.image), W, H, st.capacity, C.c_void_p(capture_guard(dev).data_ptr()),
                                           stream))
             if bwd is not None:
                 st.plan = _plan_backward(st, dev, bwd[0], bwd[1], means3D, colors_precomp, scales, rotations,
                                          cov3D_precomp, sh, radii, bwd[2], bwd[3] if len(bwd) > 3 else frozenset())
             st.num_rendered = hint
-            last_state = st
+            if keep_last_state:
+                last_state = st
             return out_color, radii, out_depth, st
         launched = False
         if hint is not None:
-            phase2(int(hint * _CAP_GROWTH) + _CAP_SLACK)
+            phase2(_spec_capacity(hint))
             launched = True
         if bwd is not None:
             st.plan = _plan_backward(st, dev, bwd[0], bwd[1], means3D, colors_precomp, scales, rotations,
@@ -221,11 +234,12 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
         host_stats["wait_s"] += time.perf_counter() - t_w
         host_stats["forwards"] += 1
         R = int(pinned.item())
-        _capacity_hint[key] = R
+        _capacity_hint[key] = max(R, int(hint * _CAP_DECAY)) if hint is not None else R
         if not launched or R > st.capacity:
-            phase2(max(R, 1))
+            phase2(_spec_capacity(R))
         st.num_rendered = R
-    last_state = st
+    if keep_last_state:
+        last_state = st
     return out_color, radii, out_depth, st
 
 

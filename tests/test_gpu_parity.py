@@ -36,6 +36,7 @@ def _pkg(variant):
 
 def run_ours(variant, rs, sc, dL, power=1):
     from splatam_b200 import rasterizer as R
+    R.keep_last_state = True   # the parity tests read the call's internal state (ranges, point_list, n_contrib ...)
     m = _pkg(variant)
     leaves = {k: v.clone().requires_grad_(True) for k, v in sc.items()}
     means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
@@ -226,8 +227,9 @@ def test_edge_cases():
     run(small)
     R._capacity_hint[(torch.cuda.current_device(), 64, 64)] = 1   # force the speculative launch to overflow
     slack, R._CAP_SLACK = R._CAP_SLACK, 0
+    step, R._CAP_STEP = R._CAP_STEP, 1          # no rounding up: capacity 1 < R, phase 2 must be re-run
     a = run(sc)
-    R._CAP_SLACK = slack
+    R._CAP_SLACK, R._CAP_STEP = slack, step
     R._capacity_hint.clear()
     b = run(sc)
     assert torch.equal(a, b)
