@@ -108,5 +108,67 @@ def build(force=False, verbose=True):
     return {n: p for n, p in built.items() if os.path.exists(p)}
 
 
+# ---------------------------------------------------------------------------------------------------------------
+# The reference's own PYTHON, staged next to the compiled extensions (oracle/_ref is git-ignored: nothing of this
+# enters the repository) so that the GPU box -- which has no /root/reference -- can run it UNCHANGED on top of either
+# rasterizer (tests/test_gpu_reference_python.py):
+#   _ref/refpy/utils/{slam_helpers,slam_external,recon_helpers,keyframe_selection}.py   verbatim copies
+#   _ref/refpy/splatam_fns.py    the functions of scripts/splatam.py listed in SPLATAM_FUNCS, cut out of the file with
+#                                `ast` (the module itself is not importable: cv2, wandb, datasets ...), under the
+#                                reference's own `from utils...` / `from diff_gaussian_rasterization ...` import lines
+#   _ref/refpy_dg/diff_gaussian_rasterization/__init__.py   verbatim copy of DG's Python package; its `from . import _C`
+#                                resolves to a generated two-line _C.py that loads _ref/ref_dg_C.so
+PY_UTILS = ["slam_helpers.py", "slam_external.py", "recon_helpers.py", "keyframe_selection.py"]
+SPLATAM_FUNCS = ["get_pointcloud", "initialize_params", "initialize_optimizer", "get_loss", "initialize_new_params",
+                 "add_new_gaussians", "initialize_camera_pose"]
+
+
+def stage_python(verbose=True):
+    """Returns the staging directory (or None when /root/reference is absent and nothing was staged before)."""
+    import ast
+    import shutil
+    dst = os.path.join(OUT, "refpy")
+    if not available():
+        return dst if os.path.isdir(dst) else None
+    os.makedirs(os.path.join(dst, "utils"), exist_ok=True)
+    open(os.path.join(dst, "utils", "__init__.py"), "w").close()
+    for f in PY_UTILS:
+        shutil.copyfile(os.path.join(REF_ROOT, "utils", f), os.path.join(dst, "utils", f))
+    src = open(os.path.join(REF_ROOT, "scripts", "splatam.py")).read()
+    tree = ast.parse(src)
+    keep_imports, funcs = [], {}
+    for node in tree.body:
+        if isinstance(node, ast.ImportFrom) and node.module and (
+                node.module in ("utils.keyframe_selection", "utils.recon_helpers", "utils.slam_helpers",
+                                "utils.slam_external", "diff_gaussian_rasterization")):
+            keep_imports.append(ast.get_source_segment(src, node))
+        elif isinstance(node, ast.FunctionDef) and node.name in SPLATAM_FUNCS:
+            funcs[node.name] = ast.get_source_segment(src, node)
+    missing = [f for f in SPLATAM_FUNCS if f not in funcs]
+    if missing:
+        raise RuntimeError("scripts/splatam.py no longer defines %s" % missing)
+    with open(os.path.join(dst, "splatam_fns.py"), "w") as f:
+        f.write("# GENERATED by oracle/build_ref.py::stage_python from scripts/splatam.py of the reference (ast source\n"
+                "# segments, unchanged).  Third-party modules the cut functions only touch on their visualisation\n"
+                "# branches (cv2, matplotlib) are not imported.\n"
+                "import os\nimport numpy as np\nimport torch\nimport torch.nn.functional as F\n\n")
+        f.write("\n".join(keep_imports) + "\n\n\n")
+        f.write("\n\n\n".join(funcs[n] for n in SPLATAM_FUNCS) + "\n")
+    pkg = os.path.join(OUT, "refpy_dg", "diff_gaussian_rasterization")
+    os.makedirs(pkg, exist_ok=True)
+    shutil.copyfile(os.path.join(REF_ROOT, VARIANTS["ref_dg_C"], "diff_gaussian_rasterization", "__init__.py"),
+                    os.path.join(pkg, "__init__.py"))
+    with open(os.path.join(pkg, "_C.py"), "w") as f:
+        f.write("# GENERATED by oracle/build_ref.py: the reference package's `from . import _C`, bound to the compiled\n"
+                "# reference extension oracle/_ref/ref_dg_C.so\n"
+                "from oracle import ref_ext as _r\n_m = _r.load('dg')\n"
+                "rasterize_gaussians = _m.rasterize_gaussians\n"
+                "rasterize_gaussians_backward = _m.rasterize_gaussians_backward\nmark_visible = _m.mark_visible\n")
+    if verbose:
+        print("[build_ref] staged the reference's Python into", dst, flush=True)
+    return dst
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv))
+    print(stage_python())
