@@ -11,8 +11,10 @@ SLAM starts from the back-projection of frame 0 and grows the map.  Two arms, sa
   --impl reference   the reference flow: torch glue (oracle/slam_oracle.py restates it) around the UNMODIFIED reference
                      extension (oracle/_ref, --variant dg), two passes per iteration, torch.optim.Adam, torch boolean-index
                      surgery (oracle/densify_oracle.py) -- the oracle is the measured thing ONLY in this leg
-Out of the hot path and simplified identically in both arms: keyframe selection is "the most recent window-2
-keyframes" (the reference's overlap-based keyframe_selection_overlap is control plane), no evaluation / logging.
+Control plane, shared by both arms: keyframe selection is the reference's own `keyframe_selection_overlap`
+(utils/keyframe_selection.py:41-95), loaded AS-IS from the copy oracle/build_ref.py stages in oracle/_ref/refpy, with the
+reference's keyframe-list bookkeeping (scripts/splatam.py:826-843, 931-945); if that copy is missing the run falls back to
+"the most recent window-2 keyframes" and says so in its JSON line.  No evaluation / logging.
 Prints one JSON line: frames/sec, ms per frame split into tracking / growing / mapping, trajectory error (ATE RMSE),
 final map size.
 """
@@ -280,9 +282,46 @@ class ReferenceArm:
         return params, variables
 
 
+def load_keyframe_selection():
+    """The reference's keyframe_selection_overlap, unchanged (control plane, SURVEY section 2 row 14: "re-used as-is"),
+    from the staged copy; None when it is not there."""
+    import importlib.util
+    path = os.path.join(ROOT, "oracle", "_ref", "refpy", "utils", "keyframe_selection.py")
+    if not os.path.exists(path):
+        return None
+    spec = importlib.util.spec_from_file_location("ref_keyframe_selection", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.keyframe_selection_overlap
+
+
+def est_w2c(params, t, device):
+    """scripts/splatam.py:826-831: the estimated world-to-camera of frame t."""
+    with torch.no_grad():
+        q = F.normalize(params['cam_unnorm_rots'][..., t].detach())[0]
+        r, x, y, z = [float(v) for v in q]
+        R = torch.tensor([[1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y)],
+                          [2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x)],
+                          [2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)]], device=device)   # build_rotation
+        w2c = torch.eye(4, device=device)
+        w2c[:3, :3] = R
+        w2c[:3, 3] = params['cam_trans'][..., t].detach()[0]
+    return w2c
+
+
+KEYFRAME_POLICY = {"name": None}
+TRACK_MS_PER_FRAME = []
+
+
 def run(arm, rs, frames, intr, n_frames, track_iters, map_iters, kf_every, window, device, seed=0):
     """scripts/splatam.py:660-900 (rgbd_slam main loop), hot path only."""
     rng = np.random.RandomState(seed)
+    torch.manual_seed(seed)      # keyframe_selection_overlap draws from the global torch / numpy generators
+    np.random.seed(seed)
+    select = load_keyframe_selection()
+    KEYFRAME_POLICY["name"] = ("reference keyframe_selection_overlap (utils/keyframe_selection.py, as-is; both arms)"
+                               if select else "most recent window-2 keyframes + last + current (staged reference copy missing)")
+    keyframe_list = []
     first_w2c = torch.eye(4, device=device)
     intr_d = intr.to(device)
     data = lambda t: {"cam": rs, "im": frames[t]["im"], "depth": frames[t]["depth"], "id": t, "intrinsics": intr_d,  # noqa: E731
@@ -291,6 +330,7 @@ def run(arm, rs, frames, intr, n_frames, track_iters, map_iters, kf_every, windo
     variables["scene_radius"] = torch.max(frames[0]["depth"]).cpu() / 2.0       # scene_radius_depth_ratio = 2
     keyframes = []
     ms = {"tracking": 0.0, "growing": 0.0, "mapping": 0.0}
+    TRACK_MS_PER_FRAME.clear()
 
     def clock(key, t0):
         torch.cuda.synchronize(device)
@@ -302,19 +342,29 @@ def run(arm, rs, frames, intr, n_frames, track_iters, map_iters, kf_every, windo
             initialize_camera_pose(params, t)
             t0 = time.perf_counter()
             arm.track(params, variables, curr, t, track_iters)
+            before = ms["tracking"]
             clock("tracking", t0)
+            TRACK_MS_PER_FRAME.append(ms["tracking"] - before)
             t0 = time.perf_counter()
             params, variables = arm.grow(params, variables, curr, t)
             clock("growing", t0)
         t0 = time.perf_counter()
-        selected = [k for k in keyframes[-(window - 2) - 1:-1]] + keyframes[-1:] + [t]
+        if select is not None:                                                    # scripts/splatam.py:826-843
+            picked = select(curr["depth"], est_w2c(params, t, device), intr_d, keyframe_list[:-1], window - 2)
+            selected = [keyframe_list[i]['id'] for i in picked]
+            if keyframe_list:
+                selected.append(keyframe_list[-1]['id'])
+            selected.append(t)
+        else:
+            selected = [k for k in keyframes[-(window - 2) - 1:-1]] + keyframes[-1:] + [t]
         opt = optimizer_of(arm.Adam, params, MAP_LRS, False)
         for it in range(map_iters):
             t_iter = selected[rng.randint(0, len(selected))]
             params, variables = arm.map_iteration(params, variables, data(t_iter), t_iter, opt, it)
         clock("mapping", t0)
-        if t == 0 or (t + 1) % kf_every == 0:                                     # scripts/splatam.py:935-945
+        if t == 0 or (t + 1) % kf_every == 0 or t == n_frames - 2:                # scripts/splatam.py:931-945
             keyframes.append(t)
+            keyframe_list.append({'id': t, 'est_w2c': est_w2c(params, t, device), 'color': curr["im"], 'depth': curr["depth"]})
     return params, ms
 
 
@@ -322,18 +372,20 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--variant", default="dg", choices=["dg", "hx"])
-    ap.add_argument("--frames", type=int, default=None, help="frames to run (default 500 ours, 10 reference)")
+    ap.add_argument("--frames", type=int, default=None, help="frames to run (default 500 ours, 100 reference)")
     ap.add_argument("--sequence-frames", type=int, default=500, help="length of the trajectory the frames are cut from")
     ap.add_argument("--room", type=int, default=1_500_000, help="Gaussians of the ground-truth room")
     ap.add_argument("--tracking-iters", type=int, default=200)
     ap.add_argument("--mapping-iters", type=int, default=30)
+    ap.add_argument("--profile-end", action="store_true",
+                    help="ours: after the run, profile 20 eager pose-only tracking iterations on the final state (per-kernel ms)")
     args = ap.parse_args()
     real_stdout = os.fdopen(os.dup(1), "w")
     os.dup2(2, 1)
     assert torch.cuda.is_available(), "bench_sequence.py needs a CUDA device"
     device = torch.device("cuda", 0)
     torch.cuda.set_device(0)
-    n = args.frames or (500 if args.impl == "ours" else 10)
+    n = args.frames or (500 if args.impl == "ours" else 100)
     n = min(n, args.sequence_frames)
     rs, frames, intr, gt_poses = make_sequence(args.sequence_frames, args.room, device)
     frames = frames[:n]
@@ -359,8 +411,39 @@ def main():
            "config": {"workload": "tum_640x480_sequence", "image": [TUM["w"], TUM["h"]], "room_gaussians": args.room,
                       "tracking_iters": args.tracking_iters, "mapping_iters": args.mapping_iters, "keyframe_every": 5,
                       "mapping_window": 20, "variant": args.variant if args.impl == "reference" else "fused",
-                      "keyframe_selection": "most recent window-2 keyframes + last + current (both arms)"},
+                      "keyframe_selection": KEYFRAME_POLICY["name"]},
+           "tracking_ms_per_frame_by_50": [round(sum(TRACK_MS_PER_FRAME[i:i + 50]) / len(TRACK_MS_PER_FRAME[i:i + 50]), 1)
+                                           for i in range(0, len(TRACK_MS_PER_FRAME), 50)],
            "gpu_launches": lib.splat_kernel_launch_count() - l0, "clocks": sampler.stop()}
+    if args.profile_end and args.impl == "ours":
+        import ctypes as C
+        from splatam_b200 import slam
+        t = n - 1
+        curr = {"cam": rs, "im": frames[t]["im"], "depth": frames[t]["depth"], "id": t, "intrinsics": intr.to(device),
+                "w2c": torch.eye(4, device=device)}
+        variables = {"max_2D_radius": torch.zeros(params["means3D"].shape[0], device=device)}
+
+        def it():
+            for v in params.values():
+                v.grad = None
+            loss, _, _ = slam.get_loss(params, curr, variables, t, WTS, True, 0.99, True, False, tracking=True,
+                                       tracking_pose_only=True)
+            loss.backward()
+        for _ in range(5):
+            it()
+        lib.splat_profile_enable(1)
+        for _ in range(20):
+            it()
+        k = 16
+        msb = (C.c_float * k)(); cnt = (C.c_int32 * k)()
+        lib.splat_profile_read(msb, cnt, k)
+        lib.splat_profile_enable(0)
+        names = [lib.splat_profile_kernel_name(j).decode() for j in range(k)]
+        out["final_state_tracking_kernel_ms"] = {names[j]: round(msb[j] / 20, 4) for j in range(k) if cnt[j]}
+        with torch.no_grad():
+            sc = torch.exp(params["log_scales"])
+            out["final_state"] = {"gaussians": int(params["means3D"].shape[0]), "scale_mean": float(sc.mean()),
+                                  "scale_median": float(sc.median()), "opacity_mean": float(torch.sigmoid(params["logit_opacities"]).mean())}
     real_stdout.write(json.dumps(out) + "\n")
     real_stdout.flush()
 

@@ -364,6 +364,12 @@ int splat_debug_count_blended(const SplatCamera* cam, int32_t P, const float* co
                               void* image_state, const void* binning_state, int64_t R_capacity,
                               float* scratch_color, uint32_t* blended, void* stream);
 int splat_debug_fp32_peak(float* scratch_dev, float* tflops_out, void* stream);
+/* How the blend kernels get a tile's records (process-wide; returns the previous setting; also SPLAT_B200_GATHER=0/1):
+ *   1  gather: three 16-byte cp.async per instance straight from the Gaussians' own 48-byte records (L2 resident),
+ *      addressed through the sorted id list -- no emit_records pass, the instance-record area of binning_state unused;
+ *   0  stream: emit_records re-writes the records in list order and the blend kernels stream them with the TMA unit.
+ * Results are identical; which one is the default is a measured choice. */
+int splat_set_gather(int on);
 /* Parity probe for the blend kernels' packed exponential (csrc/packed.cuh): evaluates it and the device library's
  * expf() -- what the reference build calls (HX/cuda_rasterizer/forward.cu:349) -- on the `count` consecutive float bit
  * patterns starting at first_bits, and ADDS the number of bit-level disagreements to *mismatches_dev (device uint64). */

@@ -91,6 +91,7 @@ _SIGNATURES = {
     "splat_profile_kernel_name": (C.c_char_p, [C.c_int]),
     "splat_debug_count_blended": (C.c_int, [C.POINTER(SplatCamera), C.c_int32, _P, _P, _P, _P, C.c_int64, _P, _P, _P]),
     "splat_debug_fp32_peak": (C.c_int, [_P, _P, _P]),
+    "splat_set_gather": (C.c_int, [C.c_int]),
     "splat_debug_exp_mismatches": (C.c_int, [C.c_uint32, C.c_uint64, _P, _P]),
     "splat_abi_version": (C.c_int, []),
     "splat_strerror": (C.c_char_p, [C.c_int]),

@@ -61,6 +61,8 @@ static void read_env_once() {
   done = true;
   const char* e = getenv("SPLAT_B200_NO_CULL");
   if (e && e[0] == '1') g_disable_cull = 1;
+  e = getenv("SPLAT_B200_GATHER");   // "0": blend kernels stream the re-written instance records (emit_records + TMA)
+  if (e) g_gather = e[0] != '0';
 }
 
 }  // namespace splat
@@ -139,6 +141,7 @@ int splat_forward_render(const SplatCamera* cam, int32_t P, const float* colors_
   r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.out_color = out_color; r.out_depth = out_depth;
   r.hdr = iv.hdr; r.Rcap = Rcap; r.blended = nullptr; r.depth_sil = cam->depth_sil ? 1 : 0; r.zero = 0;
+  r.grec = gv.grec; r.plist = bv.point_list;
   return launch_render_fwd(r, T, st);
 }
 
@@ -195,6 +198,7 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.dL_dpix = dL_dout_color; r.out_color = out_color;
   r.acc = acc;
   r.hdr = iv.hdr; r.Rcap = (uint32_t)(R > 0xffffffffll ? 0xffffffffll : R); r.zero = 0;
+  r.grec = gv.grec; r.plist = bv.point_list;
   if (!hess) {
     // callers that need neither colour nor opacity gradients (pose-only tracking) get the blend backward without those sums
     const int mode = cam->depth_sil ? ((!dL_dcolors && !dL_dopacity) ? 3 : 2) : 0;
@@ -253,10 +257,11 @@ int splat_debug_count_blended(const SplatCamera* cam, int32_t P, const float* co
   GeomView gv = geom_view(const_cast<void*>(geom_state), P);
   BinView bv = bin_view(const_cast<void*>(binning_state), R_capacity);
   RenderFwdArgs r;
-  (void)colors; (void)gv;
+  (void)colors;
   r.W = W; r.H = H; r.gx = gx; r.order = iv.tile_order; r.ranges = iv.ranges; r.inst = bv.inst; r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.out_color = scratch_color; r.out_depth = nullptr;
   r.hdr = iv.hdr; r.Rcap = (uint32_t)R_capacity; r.blended = blended; r.depth_sil = 0; r.zero = 0;
+  r.grec = gv.grec; r.plist = bv.point_list;
   return launch_render_fwd(r, gx * gy, (cudaStream_t)stream);
 }
 
@@ -306,6 +311,13 @@ int splat_debug_exp_mismatches(uint32_t first_bits, uint64_t count, unsigned lon
   if (!mismatches_dev) return fail(SPLAT_ERR_BAD_ARG, "mismatches_dev is NULL");
   if (count > (1ull << 32)) return fail(SPLAT_ERR_BAD_ARG, "count exceeds the 2^32 float bit patterns");
   return launch_exp_check(first_bits, count, mismatches_dev, (cudaStream_t)stream);
+}
+
+int splat_set_gather(int on) {
+  read_env_once();
+  const int prev = g_gather;
+  g_gather = on ? 1 : 0;
+  return prev;
 }
 
 int splat_profile_enable(int on) { g_prof_on = on ? 1 : 0; return SPLAT_OK; }

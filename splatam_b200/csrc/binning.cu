@@ -241,6 +241,12 @@ __global__ void __launch_bounds__(256) scatter_kernel(int P, int gx, int gy, con
 // path on global ping-pong buffers.
 #define SORT_THREADS 256
 #define SORT_NB 2048
+// Bins above HEAVY_BIN keys get their own second-level bucket pass.  The pass costs ~10 CTA barriers (~1 us), pairwise
+// ranking of an m-key bin costs m compares per key: break-even is a few hundred keys.  With the threshold at 64 a C5
+// map whose depths cluster (many bins of 100-200 keys) spent 81 us in this kernel instead of 34 us (r02 A/B).
+#define HEAVY_BIN 384
+#define MAX_HEAVY 32     // heavy bins handled per tile (beyond that the rest fall back to pairwise ranking)
+#define SUB_NB 512       // sub-bins of one heavy bin (2 KB of shared memory: the CTA count per SM stays at 5)
 
 struct BinMap {
   uint32_t dmin, scale;
@@ -260,7 +266,11 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
   if (hdr->num_rendered > Rcap) return;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ uint32_t bins[SORT_NB];
+  __shared__ uint32_t bins2[SUB_NB];                       // sub-bins of one heavy bin
   __shared__ uint32_t red_min[8], red_max[8], wsum[8];
+  __shared__ uint64_t red_kmin[8], red_kmax[8];
+  __shared__ uint32_t heavy_lo[MAX_HEAVY], heavy_hi[MAX_HEAVY];
+  __shared__ int n_heavy;
   const uint2 rg = ranges[blockIdx.x];
   const int n = (int)(rg.y - rg.x);
   if (n <= 0) return;
@@ -322,11 +332,90 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
     B[atomicAdd(&bins[bin(k)], 1u)] = k;
   }
   __syncthreads();
-  // in-bin ranking by the full key; bins[b] now holds the END of bin b
+  // Heavy bins.  A tile whose depths are bit-equal or clustered -- the frame-0 map back-projected from quantised
+  // sensor depth and seen fronto-parallel (TUM depth is 16-bit / 5000: hundreds of Gaussians per tile at ONE view.z), or
+  // one far outlier stretching [dmin, dmax] -- puts hundreds to thousands of keys in one bin, and ranking them by
+  // pairwise comparison is quadratic (r02: 87 us instead of 17 us for a 640x480 wall; a 20k-key bin would take
+  // milliseconds).  Bins above HEAVY_BIN keys therefore get a second bucket pass of their own, by the whole CTA, on the
+  // FULL 64-bit key (depth bits, id) -- the id is unique within a tile, so the second level has no ties: keys spread over
+  // SUB_NB sub-bins between the bin's min and max key, and the final pairwise ranking runs inside sub-bins of ~1 key.
+  // bins[b] now holds the END of bin b.
+  {
+    if (tid == 0) n_heavy = 0;
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int b = tid * 8 + q;
+      const uint32_t lo = b ? bins[b - 1] : 0u, hi = bins[b];
+      if (hi - lo > HEAVY_BIN) {
+        const int slot = atomicAdd(&n_heavy, 1);
+        if (slot < MAX_HEAVY) { heavy_lo[slot] = lo; heavy_hi[slot] = hi; }
+      }
+    }
+    __syncthreads();
+    const int nh = min(n_heavy, MAX_HEAVY);   // (more than n / HEAVY_BIN heavy bins cannot exist; MAX_HEAVY covers the shared-memory path)
+    for (int h = 0; h < nh; ++h) {
+      const int lo = (int)heavy_lo[h], hi = (int)heavy_hi[h], m = hi - lo;
+      // range of the full keys
+      uint64_t kmin = ~0ull, kmax = 0ull;
+      for (int i = lo + tid; i < hi; i += SORT_THREADS) { const uint64_t k = B[i]; kmin = min(kmin, k); kmax = max(kmax, k); }
+#pragma unroll
+      for (int o = 16; o; o >>= 1) {
+        kmin = min(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
+        kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
+      }
+      if (lane == 0) { red_kmin[wid] = kmin; red_kmax[wid] = kmax; }
+      for (int i = tid; i < SUB_NB; i += SORT_THREADS) bins2[i] = 0;
+      __syncthreads();
+#pragma unroll
+      for (int w = 0; w < 8; ++w) { kmin = min(kmin, red_kmin[w]); kmax = max(kmax, red_kmax[w]); }
+      // monotone map of (key - kmin) onto [0, SUB_NB): both reduced to 21 bits so the product fits 32
+      const uint64_t range64 = kmax - kmin;
+      const int sh = max(0, 43 - __clzll((long long)(range64 | 1ull)));   // (range >> sh) < 2^21
+      const uint32_t rdiv = (uint32_t)(range64 >> sh) + 1u;
+      auto sub = [&](uint64_t k) { return (uint32_t)(((uint32_t)((k - kmin) >> sh) * (uint32_t)SUB_NB) / rdiv); };
+      for (int i = lo + tid; i < hi; i += SORT_THREADS) atomicAdd(&bins2[sub(B[i])], 1u);
+      __syncthreads();
+      {   // exclusive scan of bins2 (thread t owns sub-bins [2t, 2t+2)), offset by lo
+        constexpr int PER = SUB_NB / SORT_THREADS;
+        uint32_t c[PER], tot = 0;
+#pragma unroll
+        for (int q = 0; q < PER; ++q) { c[q] = bins2[tid * PER + q]; tot += c[q]; }
+        uint32_t v = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t nn = __shfl_up_sync(0xffffffffu, v, o);
+          if (lane >= o) v += nn;
+        }
+        if (lane == 31) wsum[wid] = v;
+        __syncthreads();
+        uint32_t base = (uint32_t)lo + v - tot;
+        for (int w = 0; w < wid; ++w) base += wsum[w];
+#pragma unroll
+        for (int q = 0; q < PER; ++q) { bins2[tid * PER + q] = base; base += c[q]; }
+      }
+      __syncthreads();
+      // placement into A (free since the first-level placement), then ranking inside the sub-bins
+      for (int i = lo + tid; i < hi; i += SORT_THREADS) { const uint64_t k = B[i]; A[atomicAdd(&bins2[sub(k)], 1u)] = k; }
+      __syncthreads();
+      for (int i = lo + tid; i < hi; i += SORT_THREADS) {
+        const uint64_t k = A[i];
+        const uint32_t b2 = sub(k);
+        const int l2 = b2 ? (int)bins2[b2 - 1] : lo, h2 = (int)bins2[b2];
+        int rank = 0;
+        for (int q = l2; q < h2; ++q) rank += A[q] < k;
+        out[l2 + rank] = (uint32_t)k;
+      }
+      __syncthreads();
+      (void)m;
+    }
+  }
+  // in-bin ranking by the full key for the light bins
   for (int p = tid; p < n; p += SORT_THREADS) {
     const uint64_t k = B[p];
     const uint32_t b = bin(k);
     const int lo = b ? (int)bins[b - 1] : 0, hi = (int)bins[b];
+    if (hi - lo > HEAVY_BIN && n_heavy <= MAX_HEAVY) continue;   // already written by its own pass
     int rank = 0;
     for (int q = lo; q < hi; ++q) rank += B[q] < k;
     out[lo + rank] = (uint32_t)k;
@@ -374,16 +463,18 @@ int sort_smem_cap() { return kSortSmemCap; }
 int launch_tile_sort(int T, const ImageView& iv, const GeomView& g, const BinView& b, uint32_t Rcap, cudaStream_t st) {
   {
     ProfScope prof_(K_TILE_SORT, st);
-    static bool attr_set = false;
+    static bool attr_set[64] = {};   // cudaFuncSetAttribute is per device
     const int smem = kSortSmemCap * 8 * 2;
-    if (!attr_set) {
+    int dev = 0;
+    SPLAT_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
       SPLAT_CUDA(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      attr_set = true;
+      attr_set[dev] = true;
     }
     tile_sort_kernel<<<T, SORT_THREADS, smem, st>>>(iv.ranges, b.keys, b.keys_alt, b.point_list, iv.hdr, Rcap, kSortSmemCap);
     SPLAT_LAUNCH_CHECK("tile_sort_kernel");
   }
-  if (Rcap > 0) {
+  if (Rcap > 0 && !g_gather) {   // gather mode: the blend kernels fetch the Gaussians' own records by id
     ProfScope prof_(K_EMIT, st);
     const size_t quads = (size_t)Rcap * INST_F4;
     emit_records_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, st>>>(b.point_list, g.grec, b.inst, iv.hdr, Rcap);

@@ -50,6 +50,7 @@ struct RenderFwdArgs {
   const ImageHeader* hdr; uint32_t Rcap;
   uint32_t* blended;  // debug: per-pixel count of blended pairs (NULL in production)
   int zero;           // always 0: an operand ptxas cannot fold (packed.cuh ExpConsts)
+  const float4* grec; const uint32_t* plist;   // gather mode: per-Gaussian records + the sorted id list (inst is not written)
 };
 
 struct RenderBwdArgs {
@@ -61,6 +62,7 @@ struct RenderBwdArgs {
   float* acc;   // MODE 0: [P,12] raw sums.  MODE 1: [P,20] moment accumulator.  Pre-zeroed.
   const ImageHeader* hdr; uint32_t Rcap;   // R > Rcap (a graph replay that overflowed its binning capacity): nothing to walk
   int zero;     // always 0 (packed.cuh ExpConsts)
+  const float4* grec; const uint32_t* plist;   // gather mode (see RenderFwdArgs)
 };
 
 // SplaTAM glue (slam_ops.cu).  Render-variable builder: forward outputs o_*, backward inputs g_* (any may be NULL ==
@@ -118,6 +120,7 @@ int sort_smem_cap();
 int launch_render_fwd(const RenderFwdArgs& a, int T, cudaStream_t st);
 int launch_render_bwd(const RenderBwdArgs& a, int T, int mode, cudaStream_t st);
 extern int g_disable_cull;
+extern int g_gather;   // 1: the blend kernels gather the Gaussians' own records by id (no emit_records pass)
 int launch_exp_check(uint32_t first, unsigned long long count, unsigned long long* out, cudaStream_t st);
 
 }  // namespace splat

@@ -152,7 +152,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreFwdArgs a)
           }
           float4* rec = a.g.grec + (size_t)idx * INST_F4;
           rec[0] = make_float4(pix.x, pix.y, conic.x, conic.y);
-          rec[1] = make_float4(conic.z, opacity, pv.z, 0.f);
+          rec[1] = make_float4(conic.z, opacity, pv.z, __uint_as_float((uint32_t)idx));   // id: the row IS the blend kernels' record
           rec[2] = make_float4(rgb.x, rgb.y, rgb.z, frame_slope(cov.x, cov.y, cov.z));
         }
       }

@@ -84,7 +84,8 @@ __device__ __forceinline__ float row_sum32(uint32_t addr) {
 #endif
 #define BWD_MIN_CTAS(MODE) ((MODE) == 1 ? 4 : BWD_CTAS)
 
-template <bool CULL, int MODE>
+// GATHER: the ring is filled from the Gaussians' own records by id (see render_fwd.cu); no instance-record copy exists.
+template <bool CULL, int MODE, bool GATHER>
 __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_kernel(const RenderBwdArgs a) {
   constexpr int VALS = BwdTraits<MODE>::VALS, GROUP = BwdTraits<MODE>::GROUP, STRIDE = BwdTraits<MODE>::STRIDE;
   constexpr int NV = VALS * GROUP;
@@ -109,7 +110,7 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
 
   if (tid == 0) {
 #pragma unroll
-    for (int s = 0; s < RING_NS; ++s) { mbar_init(&s_full[s], 1); s_rel[s] = 0; }
+    for (int s = 0; s < RING_NS; ++s) { mbar_init(&s_full[s], GATHER ? 32 : 1); s_rel[s] = 0; }
     mbar_fence_init();
   }
   if (lane == 0) s_max[wid] = warp_hi;
@@ -128,8 +129,34 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
     mbar_arrive_expect_tx(&s_full[s], bytes);
     tma_load_1d(smem_dyn + s * (BWD_CH * INST_BYTES), src + (size_t)lo * INST_BYTES, bytes, &s_full[s]);
   };
-  if (tid == 0)
+  const uint32_t* plist = a.plist + range.x;
+  auto gather = [&](int c) {   // whole warp
+    const int s = c % RING_NS;
+    const int top = hi - c * BWD_CH, lo = max(0, top - BWD_CH), cnt = top - lo;
+    const uint32_t dst = smem_u32(smem_dyn + s * (BWD_CH * INST_BYTES));
+    uint32_t id[BWD_CH / 32];
+#pragma unroll
+    for (int k = 0; k < BWD_CH / 32; ++k) {
+      const int j = lane + 32 * k;
+      id[k] = j < cnt ? __ldg(plist + lo + j) : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < BWD_CH / 32; ++k) {
+      const int j = lane + 32 * k;
+      if (j < cnt) {
+        const float4* src = a.grec + (size_t)id[k] * INST_F4;
+#pragma unroll
+        for (int q = 0; q < INST_F4; ++q) cp_async16(dst + (uint32_t)(j * INST_F4 + q) * 16u, src + q);
+      }
+    }
+    cp_async_mbar_arrive_noinc(&s_full[s]);
+  };
+  if (GATHER) {
+    if (tid < 32)
+      for (int c = 0; c < min(nch, RING_NS); ++c) gather(c);
+  } else if (tid == 0) {
     for (int c = 0; c < min(nch, RING_NS); ++c) fill(c);
+  }
 
   // ------------------------------------------------------------------------------ consumer warps
   // Per-pixel state of the lane's two pixels (a, b).  Loop-carried values (T, Rs, MODE 1's running sums) are scalar
@@ -336,34 +363,45 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
       }
     }
     __syncwarp();
-    if (lane == 0 && ring_release(&s_rel[s], CTA_WARPS) && c + RING_NS < nch) fill(c + RING_NS);
+    if (GATHER) {
+      const bool refill = __shfl_sync(0xffffffffu, (int)(lane == 0 && ring_release(&s_rel[s], CTA_WARPS) && c + RING_NS < nch), 0) != 0;
+      if (refill) gather(c + RING_NS);
+    } else if (lane == 0 && ring_release(&s_rel[s], CTA_WARPS) && c + RING_NS < nch) {
+      fill(c + RING_NS);
+    }
   }
+}
+
+// cudaFuncSetAttribute is per DEVICE: remember which devices have had the dynamic shared memory limit raised.
+static int raise_smem_limits() {
+  static bool done[64] = {};
+  int dev = 0;
+  SPLAT_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || done[dev]) return SPLAT_OK;
+#define BWD_ATTR(C, M)                                                                                                      \
+  SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<C, M, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));  \
+  SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<C, M, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM))
+  BWD_ATTR(true, 0); BWD_ATTR(false, 0); BWD_ATTR(true, 1); BWD_ATTR(false, 1); BWD_ATTR(true, 2); BWD_ATTR(true, 3);
+#undef BWD_ATTR
+  done[dev] = true;
+  return SPLAT_OK;
 }
 
 int launch_render_bwd(const RenderBwdArgs& a, int T, int mode, cudaStream_t st) {
   ProfScope prof_(K_RENDER_BWD, st);
   if (T <= 0) return SPLAT_OK;
-  static bool attr_set = false;
-  if (!attr_set) {
-    SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
-    SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
-    SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
-    SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
-    SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
-    SPLAT_CUDA(cudaFuncSetAttribute(render_bwd_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM));
-    attr_set = true;
-  }
-  if (mode == 3) {
-    render_bwd_kernel<true, 3><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
-  } else if (mode == 2) {
-    render_bwd_kernel<true, 2><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
-  } else if (mode == 0) {
-    if (g_disable_cull) render_bwd_kernel<false, 0><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
-    else render_bwd_kernel<true, 0><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
-  } else {
-    if (g_disable_cull) render_bwd_kernel<false, 1><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
-    else render_bwd_kernel<true, 1><<<T, RING_THREADS, BWD_SMEM, st>>>(a);
-  }
+  if (int rc = raise_smem_limits()) return rc;
+  const bool g = g_gather != 0 && a.grec && a.plist;
+#define BWD_LAUNCH(C, M)                                                                       \
+  do {                                                                                         \
+    if (g) render_bwd_kernel<C, M, true><<<T, RING_THREADS, BWD_SMEM, st>>>(a);                \
+    else render_bwd_kernel<C, M, false><<<T, RING_THREADS, BWD_SMEM, st>>>(a);                 \
+  } while (0)
+  if (mode == 3) BWD_LAUNCH(true, 3);
+  else if (mode == 2) BWD_LAUNCH(true, 2);
+  else if (mode == 0) { if (g_disable_cull) BWD_LAUNCH(false, 0); else BWD_LAUNCH(true, 0); }
+  else { if (g_disable_cull) BWD_LAUNCH(false, 1); else BWD_LAUNCH(true, 1); }
+#undef BWD_LAUNCH
   SPLAT_LAUNCH_CHECK("render_bwd_kernel");
   return SPLAT_OK;
 }

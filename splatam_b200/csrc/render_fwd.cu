@@ -36,7 +36,13 @@ namespace splat {
 // runs it with alpha = 0, which leaves its state bit-identical (T * (1 - 0) == T, fma(T, 0 * c, C) == C); a terminated
 // pixel carries T == -0.0f (see the kernel body).  r02a capture (profiles/): 3.45 M warp-level hits per launch at C3,
 // 91% of them with at least one blending pixel, 87 instructions per hit before this form, ~65 after.
-template <bool CULL, bool COUNT, bool DS>
+//
+// GATHER: the ring stages are not streamed from a re-written copy of the records (emit_records: 100 B per instance of
+// extra traffic, 60 us at C3) but GATHERED: the refilling warp reads the chunk's 128 sorted ids (4 coalesced loads) and
+// issues three 16-byte cp.async per record straight from the Gaussians' own 48-byte rows -- which preprocess writes in
+// exactly the record layout, id included, and which sit in L2 (48 MB at 1M Gaussians) -- completing on the same
+// per-stage mbarrier (cp.async.mbarrier.arrive.noinc, expected count 32 lanes instead of the TMA path's 1).
+template <bool CULL, bool COUNT, bool DS, bool GATHER>
 __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFwdArgs a) {
   if (a.hdr->num_rendered > a.Rcap) return;
   __shared__ __align__(128) float4 s_rec[RING_NS][RING_CH * INST_F4];
@@ -53,7 +59,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
 
   if (tid == 0) {
 #pragma unroll
-    for (int s = 0; s < RING_NS; ++s) { mbar_init(&s_full[s], 1); s_rel[s] = 0; }
+    for (int s = 0; s < RING_NS; ++s) { mbar_init(&s_full[s], GATHER ? 32 : 1); s_rel[s] = 0; }
     s_ndone = 0;
     s_stop = 0x7fffffff;
     mbar_fence_init();
@@ -67,8 +73,34 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
     mbar_arrive_expect_tx(&s_full[s], bytes);
     tma_load_1d(&s_rec[s][0], src + (size_t)c * RING_CH * INST_BYTES, bytes, &s_full[s]);
   };
-  if (tid == 0)
+  // whole-warp refill of stage c % RING_NS in gather mode
+  const uint32_t* plist = a.plist + range.x;
+  auto gather = [&](int c) {
+    const int s = c % RING_NS, base = c * RING_CH, cnt = min(RING_CH, n - base);
+    const uint32_t dst = smem_u32(&s_rec[s][0]);
+    uint32_t id[RING_CH / 32];
+#pragma unroll
+    for (int k = 0; k < RING_CH / 32; ++k) {
+      const int j = lane + 32 * k;
+      id[k] = j < cnt ? __ldg(plist + base + j) : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < RING_CH / 32; ++k) {
+      const int j = lane + 32 * k;
+      if (j < cnt) {
+        const float4* src = a.grec + (size_t)id[k] * INST_F4;
+#pragma unroll
+        for (int q = 0; q < INST_F4; ++q) cp_async16(dst + (uint32_t)(j * INST_F4 + q) * 16u, src + q);
+      }
+    }
+    cp_async_mbar_arrive_noinc(&s_full[s]);
+  };
+  if (GATHER) {
+    if (tid < 32)
+      for (int c = 0; c < min(nch, RING_NS); ++c) gather(c);
+  } else if (tid == 0) {
     for (int c = 0; c < min(nch, RING_NS); ++c) fill(c);
+  }
 
   // ------------------------------------------------------------------------------ consumer warps
   const int tile_x = tile % a.gx, tile_y = tile / a.gx;
@@ -172,7 +204,20 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
       }
     }
     __syncwarp();
-    if (lane == 0 && ring_release(&s_rel[s], CTA_WARPS) && c + RING_NS < nch) {
+    if (GATHER) {
+      int act = 0;   // 0: nothing, 1: refill, 2: stop streaming
+      if (lane == 0 && ring_release(&s_rel[s], CTA_WARPS) && c + RING_NS < nch) {
+        act = 1;
+        if (*(volatile int*)&s_ndone == CTA_WARPS) {
+          atomicMin(&s_stop, c + RING_NS);
+          __threadfence_block();
+          act = 2;
+        }
+      }
+      act = __shfl_sync(0xffffffffu, act, 0);
+      if (act == 1) gather(c + RING_NS);
+      else if (act == 2) mbar_arrive(&s_full[s]);   // all 32 lanes: completes the phase so waiting warps see s_stop
+    } else if (lane == 0 && ring_release(&s_rel[s], CTA_WARPS) && c + RING_NS < nch) {
       if (*(volatile int*)&s_ndone == CTA_WARPS) {  // every pixel of the tile has terminated: stop streaming
         atomicMin(&s_stop, c + RING_NS);  // stages already in flight drain; every warp leaves at this chunk
         __threadfence_block();
@@ -235,13 +280,22 @@ int launch_exp_check(uint32_t first, unsigned long long count, unsigned long lon
   return SPLAT_OK;
 }
 
+int g_gather = 1;   // measured default (r02 A/B at C3: 1023 vs 982 it/s; mapping iteration 747 vs 704): see splat_set_gather
+
 int launch_render_fwd(const RenderFwdArgs& a, int T, cudaStream_t st) {
   ProfScope prof_(K_RENDER_FWD, st);
   if (T <= 0) return SPLAT_OK;
-  if (a.blended) render_fwd_kernel<false, true, false><<<T, RING_THREADS, 0, st>>>(a);
-  else if (a.depth_sil) render_fwd_kernel<true, false, true><<<T, RING_THREADS, 0, st>>>(a);
-  else if (g_disable_cull) render_fwd_kernel<false, false, false><<<T, RING_THREADS, 0, st>>>(a);
-  else render_fwd_kernel<true, false, false><<<T, RING_THREADS, 0, st>>>(a);
+  const bool g = g_gather != 0 && a.grec && a.plist;
+#define FWD_LAUNCH(C, N, D)                                                                  \
+  do {                                                                                       \
+    if (g) render_fwd_kernel<C, N, D, true><<<T, RING_THREADS, 0, st>>>(a);                  \
+    else render_fwd_kernel<C, N, D, false><<<T, RING_THREADS, 0, st>>>(a);                   \
+  } while (0)
+  if (a.blended) FWD_LAUNCH(false, true, false);
+  else if (a.depth_sil) FWD_LAUNCH(true, false, true);
+  else if (g_disable_cull) FWD_LAUNCH(false, false, false);
+  else FWD_LAUNCH(true, false, false);
+#undef FWD_LAUNCH
   SPLAT_LAUNCH_CHECK("render_fwd_kernel");
   return SPLAT_OK;
 }

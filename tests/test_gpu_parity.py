@@ -487,10 +487,8 @@ def test_full_size_properties():
     ends = torch.sort(rg[nz, 1])[0]
     assert int(starts[0]) == 0 and int(ends[-1]) == a["num_rendered"] and torch.equal(starts[1:], ends[:-1])
     # inside every tile list: ascending (depth bits, id)
-    inst = v["instances"]
-    depth_bits = inst[:, 6].contiguous().view(torch.int32).long()
-    ids = inst[:, 7].contiguous().view(torch.int32).long()
-    assert torch.equal(ids, v["point_list"].long())
+    ids = v["point_list"].long()
+    depth_bits = v["depths"][ids].contiguous().view(torch.int32).long()
     key = depth_bits * (1 << 32) + ids
     tile_of = torch.repeat_interleave(torch.arange(rg.shape[0], device="cuda"), lens)
     same_tile = tile_of[1:] == tile_of[:-1]
@@ -631,3 +629,51 @@ def test_quantised_depth_ties_full_frame_sort_time():
         with open(os.path.join(os.path.dirname(GOLDEN_DIR), "..", "gpurun_out", "tie_sort_time.json"), "w") as f:
             json.dump(rec, f, indent=1)
     assert times["ties"]["tile_sort"] < 4.0 * times["smooth"]["tile_sort"] + 0.05, rec
+
+
+def test_gather_and_streamed_records_give_identical_results():
+    """splat_set_gather: blend kernels fed by cp.async gathers of the Gaussians' own records vs by the TMA stream of the
+    re-written instance records -- same records, same order, so forward outputs are bit-identical and gradients agree
+    to atomic-order noise; in streamed mode the instance records equal the gathered rows (id in slot 7)."""
+    from splatam_b200._lib import lib
+    rs, sc, dL = build_case("surface_small", "cuda")
+    prev = lib.splat_set_gather(1)
+    try:
+        g = run_ours("hx", rs, sc, dL)
+        lib.splat_set_gather(0)
+        t = run_ours("hx", rs, sc, dL)
+        inst = t["views"]["instances"]
+        ids = t["views"]["point_list"].long()
+        assert torch.equal(inst[:, 7].contiguous().view(torch.int32).long(), ids)
+        assert torch.equal(inst[:, :7], torch.cat([t["views"]["means2D"], t["views"]["conic_opacity"],
+                                                    t["views"]["depths"][:, None]], 1)[ids])
+    finally:
+        lib.splat_set_gather(prev)
+    for k in ("color", "depth", "radii"):
+        assert torch.equal(g[k], t[k]), k
+    for k in ("n_contrib", "final_T", "point_list", "ranges"):
+        assert torch.equal(g["views"][k], t["views"][k]), k
+    _check_grads(g["grads"], t["grads"])
+
+
+@pytest.mark.parametrize("P,step", [(40000, 0.5), (90000, 0.15)])
+def test_depth_ties_on_long_lists(P, step):
+    """Depth ties on lists that take the global-memory sort path (> 2048 keys per tile): bins of hundreds of bit-equal
+    depths get the tile sort's second-level pass on the global ping-pong buffers; the second case has more heavy bins
+    per tile than the pass handles (MAX_HEAVY), so the rest fall back to pairwise ranking.  point_list must equal the
+    reference's stable radix sort either way."""
+    cam = synth_mod().C1
+    rs = synth_mod().make_settings(device="cuda", **cam)
+    sc = synth_mod().cloud_scene(P, cam["w"], cam["h"], cam["fx"], cam["fy"], seed=31)
+    z = sc["means3D"][:, 2]
+    zq = torch.where(z > 0.2, torch.clamp(torch.round(z / step), min=1.0) * step, z)   # everything in front of the near plane
+    sc["means3D"] = torch.stack([sc["means3D"][:, 0] / z * zq, sc["means3D"][:, 1] / z * zq, zq], 1).contiguous()
+    sc = {k: v.cuda() for k, v in sc.items()}
+    dL = torch.randn(3, cam["h"], cam["w"], generator=torch.Generator().manual_seed(8)).cuda()
+    ours = run_ours("dg", rs, sc, dL)
+    ref = run_ref("dg", rs, sc, dL)
+    lens = ours["views"]["ranges"][:, 1] - ours["views"]["ranges"][:, 0]
+    assert int(lens.max()) > 2048
+    vis = ours["radii"] > 0
+    assert ours["views"]["depths"][vis].unique().numel() <= 64
+    _compare_forward_exact(ours, ref, rs)

@@ -47,3 +47,13 @@ def test_reference_schedule_constants_match_tum_config():
     assert BS.MAP_LRS["logit_opacities"] == 0.05 and BS.MAP_LRS["cam_trans"] == 0.0
     assert BS.PRUNE["prune_every"] == 20 and BS.PRUNE["stop_after"] == 20
     assert (BS.TUM["w"], BS.TUM["h"]) == (640, 480)
+
+
+def test_estimated_w2c_matches_build_rotation():
+    q = torch.tensor([[0.9, 0.1, -0.2, 0.05]])
+    params = {"cam_unnorm_rots": q.view(1, 4, 1).repeat(1, 1, 3).contiguous(),
+              "cam_trans": torch.tensor([0.1, -0.2, 0.3]).view(1, 3, 1).repeat(1, 1, 3).contiguous()}
+    w2c = BS.est_w2c(params, 1, "cpu")
+    assert torch.allclose(w2c[:3, :3], build_rotation(F.normalize(q))[0], atol=1e-6)
+    assert torch.allclose(w2c[:3, 3], torch.tensor([0.1, -0.2, 0.3]))
+    assert torch.equal(w2c[3], torch.tensor([0.0, 0.0, 0.0, 1.0]))
