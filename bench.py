@@ -401,6 +401,23 @@ def pair_counts(runner, keyframes):
 LAST_HOST = {}
 
 
+def keyframe_costs(step_fn, n_keyframes, device, dist, world):
+    """Measured cost (ms, CUDA events) of one step on each keyframe of the window, identical on every rank (MAX over
+    ranks): input of mapping.keyframe_schedule(cost=...).  One untimed pass first (capacity hints, allocator)."""
+    for k in range(n_keyframes):
+        step_fn(k)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_keyframes)]
+    for k in range(n_keyframes):
+        ev[k][0].record()
+        step_fn(k)
+        ev[k][1].record()
+    torch.cuda.synchronize()
+    t = torch.tensor([a.elapsed_time(b) for a, b in ev], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.cpu()
+
+
 def timed_run(runner, sched, rank, world, steps, warmup, device, dist, on_timed_start=None):
     """W warm-up + K timed steps of the device-resident loop.  Returns ms (max over ranks).  The caller passes
     W >= the number of keyframes for the headline pass: every keyframe has a different num_rendered, and the step time
@@ -568,6 +585,15 @@ def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, war
     opt = Adam([{'params': [v], 'name': k, 'lr': BS.MAPPING_LRS[k]} for k, v in params.items()], lr=0.0, eps=1e-15)
     sched = mapping.keyframe_schedule(nf, steps + warmup, world, seed=11)
     check = {}
+    balanced = None
+    if world > 1 and nf >= world:
+        def probe(k):
+            if bucket is None:
+                opt.zero_grad(set_to_none=True)
+            step(k)
+        cost = keyframe_costs(probe, nf, device, dist, world)
+        sched = mapping.keyframe_schedule(nf, steps + warmup, world, seed=11, cost=cost)
+        balanced = "cost-balanced (per-keyframe iteration %.3f-%.3f ms)" % (float(cost.min()), float(cost.max()))
 
     def full(i, verify=False):
         if bucket is None:
@@ -623,6 +649,8 @@ def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, war
            "workload": "replica_1200x680_1M_mapping: 24-keyframe window, get_loss(mapping) + backward + exchange + Adam",
            "optimizer": "FusedAdam (one launch)" if impl == "ours" else "torch.optim.Adam",
            "collective": how, "last_loss": float(loss.detach())}
+    if balanced:
+        out["keyframe_schedule"] = balanced
     if check:
         out["collective_check"] = check
     return out
@@ -736,6 +764,11 @@ def main():
 
     warm_run = max(args.warmup, len(cams), 3)   # at least one pass over the keyframe window (both arms)
     base["config"]["warmup_steps_run"] = warm_run
+    if world > 1 and len(cams) >= world:
+        # a step ends at its slowest rank: group keyframes of similar measured cost into the same step (both arms)
+        cost = keyframe_costs(lambda k: runner.step(k), len(cams), device, dist, world)
+        sched = mapping.keyframe_schedule(len(cams), max(args.steps, len(cams), 8), world, seed=11, cost=cost)
+        base["config"]["keyframe_schedule"] = "cost-balanced (per-keyframe step time %.3f-%.3f ms)" % (float(cost.min()), float(cost.max()))
     ms, launches = timed_run(runner, sched, rank, world, args.steps, warm_run, device, dist, on_timed_start)
     sampler.mark_end()
     LAST_HOST_MAIN = dict(LAST_HOST)

@@ -157,10 +157,24 @@ class OursArm:
             opt.step()
             best.update(loss, params)
             return loss
-        it = slam.GraphedIteration(iteration, params, opt, warmup=1)      # 1 eager iteration + capture, then replays
-        for _ in range(iters - 1):
-            it.replay()
-        it.check()
+        # pose of this frame before tracking: the fall-back point if a replay overflows its captured binning capacity
+        pose0 = (params["cam_unnorm_rots"].detach()[..., t].clone(), params["cam_trans"].detach()[..., t].clone())
+        try:
+            it = slam.GraphedIteration(iteration, params, opt, warmup=1)  # 1 eager iteration + capture, then replays
+            for _ in range(iters - 1):
+                it.replay()
+            it.check()
+        except slam.CaptureOverflow:
+            self.overflow_frames = getattr(self, "overflow_frames", 0) + 1
+            with torch.no_grad():
+                params["cam_unnorm_rots"][..., t] = pose0[0]
+                params["cam_trans"][..., t] = pose0[1]
+            opt = optimizer_of(self.Adam, params, TRACK_LRS, True)
+            best = slam.BestPose(params, t)
+            for _ in range(iters):                                        # the reference's loop, un-captured
+                for v in params.values():
+                    v.grad = None
+                iteration()
         best.write_back(params)
         for v in params.values():
             v.grad = None

@@ -18,14 +18,17 @@
 //  * warp-level early termination, and the ring stops being refilled once all warps of the CTA are done.
 // Per-pixel arithmetic keeps the reference's expression order and precise expf so the discrete
 // tests (power>0, alpha<1/255, T<1e-4, median crossing) take the same branches.
+#include <type_traits>
 #include "render.cuh"
 #include "kernels.cuh"
 #include "pipeline.cuh"
 
 namespace splat {
 
+// Exact corner test of the footprint cull in the forward too: with 64-pixel hits a rejected hit saves ~40 instructions,
+// more than the test costs (r02 A/B at C3: 0.2945 vs 0.3015 ms; with round 1's 32-pixel hits it lost 2%).
 #ifndef FWD_EXACT_CULL
-#define FWD_EXACT_CULL false
+#define FWD_EXACT_CULL true
 #endif
 
 // DS: fused RGB + depth + silhouette: three more accumulators for the features (z, 1, z*z), z = the
@@ -154,6 +157,8 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
         unsigned m = __brev(__ballot_sync(0xffffffffu, hit));
         const uint32_t r31 = sbase + (uint32_t)(sub + 31) * INST_BYTES;
         const uint32_t pos31 = (uint32_t)(gbase + sub + 32);
+        auto walk = [&](auto median_tag) {
+        constexpr bool MEDIAN = decltype(median_tag)::value;
         while (m) {
           uint32_t t;
           asm("bfind.u32 %0, %1;" : "=r"(t) : "r"(m));
@@ -191,8 +196,10 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
             upk(fma2(T2, al2, pk(c4a, c4b)), c4a, c4b);
             upk(fma2(T2, mul2(al2, bc(z * z)), pk(c5a, c5b)), c5a, c5b);
           }
-          if (Ta > 0.5f && tta < 0.5f) Da = z;            // median depth (forward.cu:365-367); false for a dead pixel
-          if (Tb > 0.5f && ttb < 0.5f) Db = z;
+          if (MEDIAN) {
+            if (Ta > 0.5f && tta < 0.5f) Da = z;          // median depth (forward.cu:365-367); false for a dead pixel
+            if (Tb > 0.5f && ttb < 0.5f) Db = z;
+          }
           const uint32_t pos1 = pos31 - t;
           // contributor = valid, live and not terminating: test_T >= 1e-4 (false for -0)
           if (va && tta >= 0.0001f) { last_a = pos1; if (COUNT) ++nbl_a; }
@@ -201,6 +208,12 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
           Tb = ttb;
           if (warp_done) break;
         }
+        };
+        // The median-depth test can only fire while some pixel of the warp still has T > 0.5 (T never grows): once all
+        // 64 are at or below it -- after the first one to three blends on an opaque surface, i.e. for most of the list --
+        // the walk runs a body without those six instructions.  Checked once per 32 candidates.
+        if (__any_sync(0xffffffffu, Ta > 0.5f || Tb > 0.5f)) walk(std::true_type{});
+        else walk(std::false_type{});
       }
     }
     __syncwarp();

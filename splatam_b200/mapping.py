@@ -25,13 +25,24 @@ def raw_layout(scale_dim=1):
     return (("unnorm_rotations", 4), ("means3D", 3), ("rgb_colors", 3), ("logit_opacities", 1), ("log_scales", int(scale_dim)))
 
 
-def keyframe_schedule(n_keyframes, steps, world, seed=0):
+def keyframe_schedule(n_keyframes, steps, world, seed=0, cost=None):
     """int64 [steps, world]: keyframe rendered by each rank at each step.  Identical on every rank
     (seeded, CPU generator) -- it replaces the reference's per-iteration `np.random.randint`
     (scripts/splatam.py:851).  Within a step the ranks get DISTINCT keyframes whenever
-    world <= n_keyframes (consecutive slices of concatenated random permutations)."""
+    world <= n_keyframes (consecutive slices of concatenated random permutations).
+
+    cost (optional, one positive number per keyframe, the SAME values on every rank -- e.g. the measured time or the
+    num_rendered of one render of each keyframe): a step ends when its slowest rank does, so with costs the keyframes of
+    a pass are grouped by similar cost (sorted, cut into groups of `world`, groups visited in random order, ranks
+    assigned in random order inside a group).  Every pass still renders each (usable) keyframe exactly once; only
+    which keyframes share a step changes.  Measured at N = 8 / C3 (r01): keyframes differ by ~6% in cost and the step
+    waited for the slowest of eight random ones."""
     if n_keyframes <= 0 or steps < 0 or world <= 0:
         raise ValueError("keyframe_schedule: n_keyframes, world must be positive and steps non-negative")
+    if cost is not None:
+        cost = torch.as_tensor(cost, dtype=torch.float64).flatten()
+        if cost.numel() != n_keyframes:
+            raise ValueError("keyframe_schedule: cost must have one entry per keyframe")
     g = torch.Generator().manual_seed(int(seed))
     need = steps * world
     if world <= n_keyframes:
@@ -41,7 +52,12 @@ def keyframe_schedule(n_keyframes, steps, world, seed=0):
         while sum(len(o) for o in out) < need:
             perm = torch.randperm(n_keyframes, generator=g)
             usable = (n_keyframes // world) * world
-            out.append(perm[:usable])
+            perm = perm[:usable]
+            if cost is not None and world > 1:
+                by_cost = perm[torch.argsort(cost[perm], descending=True, stable=True)].reshape(-1, world)
+                by_cost = by_cost[torch.randperm(by_cost.shape[0], generator=g)]            # group order
+                perm = torch.stack([row[torch.randperm(world, generator=g)] for row in by_cost]).reshape(-1)
+            out.append(perm)
         flat = torch.cat(out)[:need] if need else torch.zeros(0, dtype=torch.int64)
     else:
         flat = torch.randint(0, n_keyframes, (need,), generator=g)

@@ -392,6 +392,13 @@ _GRAPH_POOL = {}
 _GRAPH_KEEP = {}
 
 
+class CaptureOverflow(RuntimeError):
+    """A replayed iteration rendered more instances than the binning capacity its graph was captured with.  Every kernel
+    of such a replay that depends on the binning state exits untouched (forward AND backward blend: the gradients of that
+    step are all zero, never read out of bounds), so nothing is corrupted -- but the steps taken since are not the ones an
+    eager loop would have taken: restore the state saved before the frame and re-run it un-captured."""
+
+
 class GraphedIteration:
     """Captures ONE optimisation iteration -- `fn()` = get_loss + loss.backward() + FusedAdam.step(), no zero_grad --
     into a CUDA graph and replays it: the 40-200 tracking iterations SplaTAM runs on one frame (scripts/splatam.py:
@@ -467,8 +474,9 @@ class GraphedIteration:
         self.replays = 0
         flags = rasterizer.capture_guard(self.device)
         if int(flags[0]) != 0:
-            raise RuntimeError("a replayed iteration rendered %d instances, more than the captured binning capacity"
-                               % int(flags[1]))
+            flags[0] = 0
+            raise CaptureOverflow("a replayed iteration rendered %d instances, more than the captured binning capacity"
+                                  % int(flags[1]))
 
 
 class BestPose:

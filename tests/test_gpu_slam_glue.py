@@ -447,3 +447,49 @@ def test_loss_gradient_follows_the_incoming_gradient(h, w, six):
     for g1, g2 in zip(grads[1.0], grads[2.5]):
         assert float(g1.abs().max()) > 0
         assert torch.equal(g2, g1 * 2.5)
+
+
+def test_graph_replay_overflow_is_detected_and_harmless():
+    """a replay that renders more instances than the captured binning capacity must not walk stale
+    state.  The Gaussians are inflated AFTER capture so every replay overflows: the blend kernels exit untouched, the
+    gradients of those steps are exactly zero (so Adam only coasts on its momentum), everything stays finite, and check()
+    raises CaptureOverflow so the caller can restore the pose and re-run the frame eagerly."""
+    from splatam_b200 import rasterizer as R
+    from splatam_b200 import slam
+    base, curr = _slam_scene(6000, True)
+    wts = dict(im=0.5, depth=1.0)
+    lrs = dict(means3D=0.0, rgb_colors=0.0, unnorm_rotations=0.0, logit_opacities=0.0, log_scales=0.0,
+               cam_unnorm_rots=0.0004, cam_trans=0.002)
+    p = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+    va = {"max_2D_radius": torch.zeros(6000, device=DEV)}
+    opt = slam.FusedAdam([{'params': [v], 'name': k, 'lr': lrs[k]} for k, v in p.items()])
+
+    def it():
+        loss, _, _ = slam.get_loss(p, curr, va, 1, wts, True, 0.99, True, False, tracking=True, tracking_pose_only=True)
+        loss.backward()
+        opt.step()
+        return loss
+
+    saved = (R._CAP_SLACK, R._CAP_STEP, R._CAP_GROWTH)
+    R._CAP_SLACK, R._CAP_STEP, R._CAP_GROWTH = 0, 1, 1.0      # capacity == exactly the warm-up's num_rendered
+    try:
+        R._capacity_hint.clear()
+        g = slam.GraphedIteration(it, p, opt, warmup=2)
+        g.replay()
+        g.check()                                              # same scene: fits
+        pose_before = (p["cam_unnorm_rots"].detach().clone(), p["cam_trans"].detach().clone())
+        with torch.no_grad():
+            p["log_scales"] += 1.2                             # 3.3x larger splats: far more (tile, Gaussian) instances
+        for _ in range(3):
+            g.replay()
+        torch.cuda.synchronize()
+        for k in ("cam_unnorm_rots", "cam_trans"):
+            assert torch.isfinite(p[k]).all()
+            assert float(p[k].grad.abs().max()) == 0.0, "an overflowed replay must produce all-zero pose gradients"
+        drift = float((p["cam_trans"].detach() - pose_before[1]).abs().max())
+        assert drift <= 3 * lrs["cam_trans"] * 1.01            # at most lr per step: momentum only
+        with pytest.raises(slam.CaptureOverflow):
+            g.check()
+    finally:
+        R._CAP_SLACK, R._CAP_STEP, R._CAP_GROWTH = saved
+        R._capacity_hint.clear()

@@ -151,3 +151,25 @@ def test_raw_parameter_layout_bucket():
         assert torch.equal(bk.views["means3D"], p["means3D"])
         (lv["means3D"].sum() + lv["log_scales"].sum() * 2).backward()   # autograd accumulates into the bucket views
         assert float(bk.gviews["log_scales"].min()) == 2.0 and lv["means3D"].grad.data_ptr() == bk.gviews["means3D"].data_ptr()
+
+
+def test_cost_balanced_schedule_groups_similar_keyframes():
+    """keyframe_schedule(cost=...): every pass still visits each keyframe once, ranks of a step get distinct keyframes,
+    and the spread of cost inside a step is the smallest possible (consecutive groups of the sorted costs)."""
+    from splatam_b200 import mapping
+    n, world = 24, 8
+    cost = torch.linspace(1.0, 2.0, n)[torch.randperm(n, generator=torch.Generator().manual_seed(3))]
+    s = mapping.keyframe_schedule(n, 12, world, seed=5, cost=cost)
+    assert s.shape == (12, world)
+    for p in range(4):                                   # 3 steps per pass
+        block = s[3 * p:3 * p + 3]
+        assert sorted(block.flatten().tolist()) == list(range(n))
+    spread = (cost[s].max(1)[0] - cost[s].min(1)[0])
+    assert float(spread.max()) <= float((cost.sort()[0][world - 1::world] - cost.sort()[0][0::world]).max()) + 1e-12
+    plain = mapping.keyframe_schedule(n, 12, world, seed=5)
+    assert float((cost[plain].max(1)[0] - cost[plain].min(1)[0]).mean()) > 2.0 * float(spread.mean())
+    # same seed + same cost -> same schedule on every rank; world = 1 ignores the cost
+    assert torch.equal(s, mapping.keyframe_schedule(n, 12, world, seed=5, cost=cost.clone()))
+    assert torch.equal(mapping.keyframe_schedule(n, 12, 1, seed=5, cost=cost), mapping.keyframe_schedule(n, 12, 1, seed=5))
+    with pytest.raises(ValueError):
+        mapping.keyframe_schedule(n, 4, world, cost=cost[:5])
