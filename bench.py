@@ -63,6 +63,9 @@ def parse():
                          "(torch symmetric memory for the allocation); nccl = torch.distributed.all_reduce")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--mapping-step", default="fused", choices=["fused", "plain"],
+                    help="N>1 mapping leg: fused = exchange + Adam as one kernel per rank (mapping.ShardedAdam); plain = "
+                         "all-reduce of the gradient bucket, then FusedAdam on every replica")
     ap.add_argument("--no-mapping", action="store_true",
                     help="skip the mapping leg (the metric's second half: mapping frames/sec, reported as `mapping`)")
     return ap.parse_args()
@@ -540,7 +543,7 @@ def e2e_run(runner, sched, rank, world, steps, device, dist):
 MAP_ITERS_PER_FRAME = 60    # configs/replica/splatam.py:81 (mapping num_iters), BASELINE.json configs[2]
 
 
-def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, warmup):
+def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, warmup, fused_step=True):
     """The metric's second half: the REAL mapping iteration of scripts/splatam.py:848-905 at C3 (1200x680, 1M Gaussians,
     24-keyframe window) -- get_loss(mapping=True) (0.8 L1 + 0.2 (1 - SSIM) colour + masked L1 depth over an RGB + depth +
     silhouette render), backward, [N > 1: ONE exchange of the raw-parameter gradient bucket], Adam step -- keyframes sharded
@@ -563,7 +566,8 @@ def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, war
         if world > 1 and collective == "peer":
             why = ""
             try:
-                bucket = mapping.GradBucket(raw, device, direct=True, peer_group=dist.group.WORLD, layout=mapping.raw_layout(1))
+                bucket = mapping.GradBucket(raw, device, direct=True, peer_group=dist.group.WORLD, layout=mapping.raw_layout(1),
+                                            shard_optimizer=fused_step)
             except Exception as e:  # noqa: BLE001
                 why, bucket = repr(e)[:160], None
             ok = torch.tensor([0.0 if bucket is None else 1.0], device=device)
@@ -582,7 +586,17 @@ def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, war
     else:
         Adam = torch.optim.Adam
     step = BS.make_step(impl, variant, params, targets, variables, wts, False, 0.5)
-    opt = Adam([{'params': [v], 'name': k, 'lr': BS.MAPPING_LRS[k]} for k, v in params.items()], lr=0.0, eps=1e-15)
+    sharded = None
+    if bucket is not None and bucket.peer is not None and bucket.peer.params is not None:
+        # exchange + Adam on the Gaussian tensors as ONE kernel per rank (reduce-scatter -> Adam on the rank's slice ->
+        # all-gather of the updated parameters); the two camera tensors (lr 0 while mapping) keep their own tiny step
+        sharded = mapping.ShardedAdam(bucket, BS.MAPPING_LRS)
+        how = "fused reduce-scatter + Adam + all-gather, own kernel, " + (
+            "NVSwitch in-switch reduction / multicast store (multimem)" if bucket.peer.multicast else "NVLink peer loads / stores")
+        opt = Adam([{'params': [params[k]], 'name': k, 'lr': BS.MAPPING_LRS[k]} for k in ("cam_unnorm_rots", "cam_trans")],
+                   lr=0.0, eps=1e-15)
+    else:
+        opt = Adam([{'params': [v], 'name': k, 'lr': BS.MAPPING_LRS[k]} for k, v in params.items()], lr=0.0, eps=1e-15)
     sched = mapping.keyframe_schedule(nf, steps + warmup, world, seed=11)
     check = {}
     balanced = None
@@ -599,7 +613,41 @@ def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, war
         if bucket is None:
             opt.zero_grad(set_to_none=True)    # a direct bucket is fully overwritten by the next backward
         loss = step(int(sched[i % sched.shape[0], rank]))
-        if world > 1 and bucket is not None:
+        if sharded is not None:
+            if verify:   # reference: gather + rank-ordered gradient sum, then full-size FusedAdam on a copy
+                local = bucket.grads.clone()
+                parts = [torch.empty_like(local) for _ in range(world)]
+                dist.all_gather(parts, local)
+                ordered = parts[0].clone()
+                for q in parts[1:]:
+                    ordered += q
+                P_, copy, off = bucket.P, {}, 0
+                for k, w in bucket.layout:
+                    copy[k] = bucket.views[k].detach().clone().requires_grad_(True)
+                    copy[k].grad = ordered[off:off + P_ * w].view(P_, w).clone()
+                    off += P_ * w
+                ref_opt = Adam([{'params': [v], 'name': k, 'lr': BS.MAPPING_LRS[k]} for k, v in copy.items()], lr=0.0, eps=1e-15)
+                with torch.no_grad():
+                    ref_opt.step()
+            sharded.step()
+            if verify:
+                d = max(float((bucket.views[k] - copy[k].detach()).abs().max()) for k in copy)
+                scale = max(float(copy[k].detach().abs().max()) for k in copy)
+                cs = bucket.params.double().sum().reshape(1)
+                lo_, hi_ = cs.clone(), cs.clone()
+                dist.all_reduce(lo_, op=dist.ReduceOp.MIN)
+                dist.all_reduce(hi_, op=dist.ReduceOp.MAX)
+                t = torch.tensor([d, scale], device=device)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                check.update(what="parameters after the fused step vs gather + rank-ordered gradient sum + FusedAdam",
+                             max_abs_diff=float(t[0]), max_abs_value=float(t[1]), bit_exact=float(t[0]) == 0.0,
+                             replicas_identical=bool(lo_ == hi_), elements=int(local.numel()),
+                             note="peer path: bit-exact expected.  In-switch path: the switch sums in its own order, and "
+                                  "SplaTAM's Adam (eps 1e-15) turns a rounding-level difference of a near-zero gradient sum "
+                                  "into a step of up to lr -- so max_abs_diff is bounded by 2*lr (0.1), not by rounding; what "
+                                  "must hold is replicas_identical")
+                del parts, ordered, copy, ref_opt, local
+        elif world > 1 and bucket is not None:
             if verify:
                 local = bucket.grads.clone()
             bucket.all_reduce()
@@ -647,7 +695,8 @@ def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, war
     out = {"iters_per_s": world * 1e3 / ms, "ms_per_step": ms, "frames_per_s": 1e3 / (spf * ms), "unit": "mapped frames/s",
            "iters_per_frame": MAP_ITERS_PER_FRAME, "steps_per_frame": spf, "steps": steps, "warmup": max(warmup, 3),
            "workload": "replica_1200x680_1M_mapping: 24-keyframe window, get_loss(mapping) + backward + exchange + Adam",
-           "optimizer": "FusedAdam (one launch)" if impl == "ours" else "torch.optim.Adam",
+           "optimizer": ("Adam sharded over the ranks, fused with the exchange" if sharded is not None else
+                         "FusedAdam (one launch)") if impl == "ours" else "torch.optim.Adam",
            "collective": how, "last_loss": float(loss.detach())}
     if balanced:
         out["keyframe_schedule"] = balanced
@@ -808,7 +857,8 @@ def main():
             (args.impl == "ours" or world == 1):
         msteps = args.steps if args.impl == "ours" else min(args.steps, 24)
         mwarm = max(args.warmup, 24) if args.impl == "ours" else 3    # ours: one pass over the 24 keyframes
-        mapping_out = mapping_leg(args.impl, args.variant, rank, world, device, dist, args.collective, msteps, mwarm)
+        mapping_out = mapping_leg(args.impl, args.variant, rank, world, device, dist, args.collective, msteps, mwarm,
+                                  fused_step=args.mapping_step == "fused")
 
     if rank != 0:
         if world > 1:

@@ -335,6 +335,23 @@ int splat_spawn_gaussians(int32_t width, int32_t height, const uint8_t* flags, c
 int splat_peer_allreduce_sum(const uint64_t* buffers, const uint64_t* flag_pads, uint64_t multicast_buffer,
                              int32_t rank, int32_t world, uint32_t epoch, int64_t n_floats, void* stream);
 
+/* Fused exchange + optimizer step of the keyframe-sharded mapping iteration (scripts/splatam.py:889's optimizer.step()
+ * after a gradient sum over ranks): ONE kernel per rank does reduce-scatter -> Adam -> all-gather over peer memory.
+ * Rank r sums slice r of the gradient bucket (multimem.ld_reduce in the NVSwitch when multicast addresses are given, else
+ * peer loads in rank order), applies Adam (arithmetic of splat_adam_step, shared code) to slice r of the PARAMETER
+ * bucket with its own 1/N shard of the moments, and stores the updated parameters into every replica.  grad_buffers[j] /
+ * param_buffers[j] are rank j's two buckets (same layout, n_floats each, symmetric memory); segment k covers the elements
+ * [segment_ends[k-1], segment_ends[k]) and has learning rate segment_lrs[k] (one segment per parameter tensor).  `step`
+ * (>= 1, same on every rank) is the Adam step number; the shards hold splat_peer_adam_shard_floats(n_floats, world)
+ * floats each and must start zeroed.  `epoch` as for splat_peer_allreduce_sum (shared counter: every call of either
+ * function advances it by one). */
+size_t splat_peer_adam_shard_floats(int64_t n_floats, int32_t world);
+int splat_peer_reduce_adam(const uint64_t* grad_buffers, const uint64_t* param_buffers, const uint64_t* flag_pads,
+                           uint64_t grad_multicast, uint64_t param_multicast, int32_t rank, int32_t world,
+                           uint32_t epoch, int64_t n_floats, const int64_t* segment_ends, const float* segment_lrs,
+                           int32_t n_segments, int32_t step, double beta1, double beta2, double eps,
+                           float* exp_avg_shard, float* exp_avg_sq_shard, void* stream);
+
 /* ---- introspection used by the parity tests (read-only views into the states) ---------------
  * ranges: uint2[T] exactly as identifyTileRanges leaves them (untouched tiles are (0,0));
  * point_list: uint32[R] sorted Gaussian ids; n_contrib uint32[N]; final_T float[N]. */

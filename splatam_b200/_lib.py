@@ -85,6 +85,9 @@ _SIGNATURES = {
     "splat_spawn_gaussians": (C.c_int, [C.c_int32, C.c_int32, _P, _P, _P, _P, C.c_float, C.c_float, C.c_float, C.c_float,
                                         _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int64, _P, _P, _P, _P, _P, _P, _P]),
     "splat_peer_allreduce_sum": (C.c_int, [_P, _P, C.c_uint64, C.c_int32, C.c_int32, C.c_uint32, C.c_int64, _P]),
+    "splat_peer_adam_shard_floats": (C.c_size_t, [C.c_int64, C.c_int32]),
+    "splat_peer_reduce_adam": (C.c_int, [_P, _P, _P, C.c_uint64, C.c_uint64, C.c_int32, C.c_int32, C.c_uint32, C.c_int64,
+                                         _P, _P, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double, _P, _P, _P]),
     "splat_profile_enable": (C.c_int, [C.c_int]),
     "splat_profile_read": (C.c_int, [_P, _P, C.c_int32]),
     "splat_profile_read_gaps": (C.c_int, [_P, C.c_int32]),

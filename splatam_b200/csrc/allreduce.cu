@@ -14,6 +14,7 @@
 // every peer's pad (st.release.sys) and spins on its own pad until all words reach `epoch`
 // (ld.acquire.sys).  A spin that outlives ~4 s traps instead of hanging the GPU.
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
 
 #include "common.cuh"
@@ -122,6 +123,73 @@ __global__ void __launch_bounds__(512) multimem_reduce_kernel(float4* mc, int ra
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Fused exchange + optimizer step of the keyframe-sharded mapping iteration: reduce-scatter -> Adam -> all-gather in ONE
+// kernel over peer memory.  The plain path (all-reduce the gradient bucket, then run Adam on every replica) moves the
+// bucket twice over the links (sum out, sum back), runs the same 280 MB Adam pass on all N GPUs and needs N full copies
+// of the moments.  Here rank r
+//     sums slice r of the GRADIENT bucket   (in-switch: multimem.ld_reduce; peer path: loads from every rank, rank order)
+//     runs Adam on slice r only             (its 1/N shard of exp_avg / exp_avg_sq lives on this rank alone)
+//     stores the updated PARAMETERS of slice r into every replica (multimem.st, or one store per peer)
+// so the links carry gradient slices in and parameter slices out (the same bytes as one all-reduce), the optimizer pass
+// shrinks to 1/N per GPU, and one launch + two barriers replace two launches + Adam's launch + two barriers.  Every
+// replica receives identical parameters (one owner per slice), so replicas cannot drift.
+#define ADAM_MAX_SEG 8
+struct ReduceAdamArgs {
+  PeerArgs p;                  // gradient buckets, flag pads, rank / world / epoch / n4
+  float4* param[PEER_MAX];     // parameter buckets (same layout and length as the gradient bucket)
+  float4* grad_mc; float4* param_mc;   // NVSwitch multicast addresses of both buckets, or NULL (peer path)
+  float4* m; float4* v;        // this rank's shard of the moments: float4 index i - lo
+  int nseg;
+  long long seg_end[ADAM_MAX_SEG];     // element (float) index where segment k ends: per-tensor learning rates
+  float lr1[ADAM_MAX_SEG];             // lr / bias_correction1 per segment
+  float w1, w2, beta2, inv_b2, eps;
+};
+
+template <bool MC>
+__global__ void __launch_bounds__(512) reduce_adam_kernel(const ReduceAdamArgs a) {
+  const size_t per = (a.p.n4 + a.p.world - 1) / a.p.world;
+  const size_t lo = (size_t)a.p.rank * per, hi = min(a.p.n4, lo + per);
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  const float4* mine = a.param[a.p.rank];
+  for (size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
+    float4 g;
+    if (MC) {
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                   : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w) : "l"(a.grad_mc + i) : "memory");
+    } else {
+      g = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int j = 0; j < a.p.world; ++j) {        // fixed rank order: the sum every replica would have formed
+        const float4 t = ld_cg_f4(a.p.buf[j] + i);
+        g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+      }
+    }
+    float4 m = a.m[i - lo], v = a.v[i - lo], p = mine[i];
+    const long long e = (long long)i * 4;
+    int s0 = 0;
+    while (s0 < a.nseg - 1 && e >= a.seg_end[s0]) ++s0;
+    float lr[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {                  // a float4 may straddle a tensor boundary when P is not a multiple of 4
+      int sc = s0;
+      while (sc < a.nseg - 1 && e + c >= a.seg_end[sc]) ++sc;
+      lr[c] = a.lr1[sc];
+    }
+    adam_update(g.x, m.x, v.x, p.x, a.w1, a.w2, a.beta2, lr[0], a.inv_b2, a.eps);
+    adam_update(g.y, m.y, v.y, p.y, a.w1, a.w2, a.beta2, lr[1], a.inv_b2, a.eps);
+    adam_update(g.z, m.z, v.z, p.z, a.w1, a.w2, a.beta2, lr[2], a.inv_b2, a.eps);
+    adam_update(g.w, m.w, v.w, p.w, a.w1, a.w2, a.beta2, lr[3], a.inv_b2, a.eps);
+    a.m[i - lo] = m;
+    a.v[i - lo] = v;
+    if (MC) {
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                   ::"l"(a.param_mc + i), "f"(p.x), "f"(p.y), "f"(p.z), "f"(p.w) : "memory");
+    } else {
+      for (int j = 0; j < a.p.world; ++j) a.param[j][i] = p;
+    }
+  }
+}
+
 }  // namespace splat
 
 using namespace splat;
@@ -168,6 +236,67 @@ extern "C" int splat_peer_allreduce_sum(const uint64_t* buffers, const uint64_t*
   peer_reduce_kernel<4, false><<<blocks, 512, 0, st>>>(a);
   SPLAT_LAUNCH_CHECK("peer_reduce_kernel");
   peer_barrier_kernel<<<1, 32, 0, st>>>(a, 1);
+  SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
+  return SPLAT_OK;
+}
+
+extern "C" size_t splat_peer_adam_shard_floats(int64_t n_floats, int32_t world) {
+  if (n_floats <= 0 || world <= 0) return 0;
+  const size_t n4 = ((size_t)n_floats + 3) / 4;
+  return ((n4 + world - 1) / world) * 4;
+}
+
+extern "C" int splat_peer_reduce_adam(const uint64_t* grad_buffers, const uint64_t* param_buffers, const uint64_t* flag_pads,
+                                      uint64_t grad_multicast, uint64_t param_multicast, int32_t rank, int32_t world,
+                                      uint32_t epoch, int64_t n_floats, const int64_t* segment_ends, const float* segment_lrs,
+                                      int32_t n_segments, int32_t step, double beta1, double beta2, double eps,
+                                      float* exp_avg_shard, float* exp_avg_sq_shard, void* stream) {
+  if (!grad_buffers || !param_buffers || !flag_pads) return fail(SPLAT_ERR_BAD_ARG, "NULL pointer table");
+  if (world < 1 || world > PEER_MAX || rank < 0 || rank >= world) return fail(SPLAT_ERR_BAD_ARG, "bad rank/world %d/%d", rank, world);
+  if (n_floats <= 0 || (n_floats & 3)) return fail(SPLAT_ERR_BAD_ARG, "bucket length must be a positive multiple of 4 floats");
+  if (!segment_ends || !segment_lrs || n_segments < 1 || n_segments > ADAM_MAX_SEG)
+    return fail(SPLAT_ERR_BAD_ARG, "need 1..%d (segment end, learning rate) pairs", ADAM_MAX_SEG);
+  if (step < 1) return fail(SPLAT_ERR_BAD_ARG, "step must be >= 1");
+  if (!exp_avg_shard || !exp_avg_sq_shard || (((uintptr_t)exp_avg_shard | (uintptr_t)exp_avg_sq_shard) & 15))
+    return fail(SPLAT_ERR_BAD_ARG, "moment shards must be 16-byte aligned device buffers of splat_peer_adam_shard_floats() floats");
+  if ((grad_multicast != 0) != (param_multicast != 0) || ((grad_multicast | param_multicast) & 15))
+    return fail(SPLAT_ERR_BAD_ARG, "multicast addresses: both or neither, 16-byte aligned");
+  ReduceAdamArgs a = {};
+  for (int j = 0; j < world; ++j) {
+    if (!grad_buffers[j] || !param_buffers[j] || !flag_pads[j] || ((grad_buffers[j] | param_buffers[j]) & 15))
+      return fail(SPLAT_ERR_BAD_ARG, "peer %d: NULL or misaligned buffer", j);
+    a.p.buf[j] = reinterpret_cast<float4*>(grad_buffers[j]);
+    a.param[j] = reinterpret_cast<float4*>(param_buffers[j]);
+    a.p.pad[j] = reinterpret_cast<uint32_t*>(flag_pads[j]);
+  }
+  long long prev = 0;
+  for (int k = 0; k < n_segments; ++k) {
+    if (segment_ends[k] < prev) return fail(SPLAT_ERR_BAD_ARG, "segment ends must be non-decreasing");
+    prev = a.seg_end[k] = segment_ends[k];
+  }
+  a.p.rank = rank; a.p.world = world; a.p.epoch = epoch; a.p.n4 = (size_t)n_floats / 4;
+  {
+    static const double timeout_s = [] { const char* e = getenv("SPLAT_PEER_TIMEOUT_S"); return e ? atof(e) : 60.0; }();
+    a.p.timeout_cycles = timeout_s > 0.0 ? (long long)(timeout_s * 2.0e9) : 0;
+  }
+  // bias corrections exactly as splat_adam_step forms them (double pow, rounded once)
+  const float bc1 = (float)(1.0 - pow(beta1, (double)step));
+  const float bc2s = (float)sqrt(1.0 - pow(beta2, (double)step));
+  for (int k = 0; k < n_segments; ++k) a.lr1[k] = segment_lrs[k] / bc1;
+  a.nseg = n_segments;
+  a.w1 = (float)(1.0 - beta1); a.w2 = (float)(1.0 - beta2); a.beta2 = (float)beta2; a.inv_b2 = 1.f / bc2s; a.eps = (float)eps;
+  a.grad_mc = reinterpret_cast<float4*>(grad_multicast); a.param_mc = reinterpret_cast<float4*>(param_multicast);
+  a.m = reinterpret_cast<float4*>(exp_avg_shard); a.v = reinterpret_cast<float4*>(exp_avg_sq_shard);
+  cudaStream_t st = (cudaStream_t)stream;
+  peer_barrier_kernel<<<1, 32, 0, st>>>(a.p, 0);          // every rank's gradients are complete
+  SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
+  const size_t per = (a.p.n4 + world - 1) / world;
+  int blocks = (int)std::min<size_t>((per + 511) / 512, (size_t)148 * 2);
+  if (blocks < 1) blocks = 1;
+  if (grad_multicast) reduce_adam_kernel<true><<<blocks, 512, 0, st>>>(a);
+  else reduce_adam_kernel<false><<<blocks, 512, 0, st>>>(a);
+  SPLAT_LAUNCH_CHECK("reduce_adam_kernel");
+  peer_barrier_kernel<<<1, 32, 0, st>>>(a.p, 1);          // every replica holds the updated parameters
   SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
   return SPLAT_OK;
 }

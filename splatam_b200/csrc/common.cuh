@@ -227,6 +227,17 @@ __device__ __forceinline__ float3 cov2d_ewa(const float3 mean, float fx, float f
   return make_float3(__fadd_rn(c.m[0][0], 0.3f), c.m[0][1], __fadd_rn(c.m[1][1], 0.3f));
 }
 
+// ---------------------------------------------------------------- Adam element update
+// torch/optim/adam.py::_single_tensor_adam for one element (no weight decay, no amsgrad); w1 = 1 - beta1, w2 = 1 - beta2,
+// lr1 = lr / bias_correction1, inv_b2 = 1 / sqrt(bias_correction2).  ONE definition for splat_adam_step's kernel and for the
+// fused reduce + Adam + broadcast kernel of the multi-GPU mapping step, so both round identically.
+__device__ __forceinline__ void adam_update(float g, float& m, float& v, float& p, float w1, float w2, float beta2,
+                                            float lr1, float inv_b2, float eps) {
+  m = m + w1 * (g - m);
+  v = v * beta2 + w2 * (g * g);
+  p = p - lr1 * (m / (sqrtf(v) * inv_b2 + eps));
+}
+
 // ---------------------------------------------------------------- warp helpers
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -603,22 +603,19 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamArgs a) {
     float4 m = *reinterpret_cast<float4*>(T.exp_avg + base);
     float4 v = *reinterpret_cast<float4*>(T.exp_avg_sq + base);
     float4 p = *reinterpret_cast<float4*>(T.param + base);
-#define ADAM1(c)                                                        \
-    m.c = m.c + w1 * (g.c - m.c);                                       \
-    v.c = v.c * a.beta2 + w2 * (g.c * g.c);                             \
-    p.c = p.c - lr1 * (m.c / (sqrtf(v.c) * inv_b2 + a.eps));
-    ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
-#undef ADAM1
+    adam_update(g.x, m.x, v.x, p.x, w1, w2, a.beta2, lr1, inv_b2, a.eps);
+    adam_update(g.y, m.y, v.y, p.y, w1, w2, a.beta2, lr1, inv_b2, a.eps);
+    adam_update(g.z, m.z, v.z, p.z, w1, w2, a.beta2, lr1, inv_b2, a.eps);
+    adam_update(g.w, m.w, v.w, p.w, w1, w2, a.beta2, lr1, inv_b2, a.eps);
     *reinterpret_cast<float4*>(T.exp_avg + base) = m;
     *reinterpret_cast<float4*>(T.exp_avg_sq + base) = v;
     *reinterpret_cast<float4*>(T.param + base) = p;
   } else {
     for (int64_t i = base; i < T.n && i < base + 4; ++i) {
-      const float g = T.grad[i];
-      const float m = T.exp_avg[i] + w1 * (g - T.exp_avg[i]);
-      const float v = T.exp_avg_sq[i] * a.beta2 + w2 * (g * g);
+      float m = T.exp_avg[i], v = T.exp_avg_sq[i], pp = T.param[i];
+      adam_update(T.grad[i], m, v, pp, w1, w2, a.beta2, lr1, inv_b2, a.eps);
       T.exp_avg[i] = m; T.exp_avg_sq[i] = v;
-      T.param[i] = T.param[i] - lr1 * (m / (sqrtf(v) * inv_b2 + a.eps));
+      T.param[i] = pp;
     }
   }
 }

@@ -74,10 +74,14 @@ class GradBucket:
     every row.  Use it when a step is exactly one render per bucket (the mapping step); leave it off
     when several losses accumulate into the same leaves."""
 
-    def __init__(self, scene, device="cpu", direct=False, peer_group=None, layout=LAYOUT):
+    def __init__(self, scene, device="cpu", direct=False, peer_group=None, layout=LAYOUT, shard_optimizer=False,
+                 multicast="auto"):
         """peer_group: a torch.distributed process group whose ranks share one NVSwitch node.  The gradient buffer
         is then allocated in symmetric memory and `all_reduce` runs the library's own peer-memory two-shot kernel
-        (csrc/allreduce.cu) on the current stream instead of NCCL."""
+        (csrc/allreduce.cu) on the current stream instead of NCCL.
+        shard_optimizer (needs peer_group): the PARAMETER buffer lives in symmetric memory too, so that ShardedAdam can
+        run exchange + optimizer step as one fused kernel (reduce-scatter -> Adam on this rank's slice -> all-gather of
+        the updated parameters)."""
         self.direct = bool(direct)
         self.peer = None
         self.layout = tuple(layout)
@@ -88,9 +92,17 @@ class GradBucket:
                 raise ValueError("GradBucket: %s must be [%d, %d], got %s" % (k, self.P, w, tuple(scene[k].shape)))
         self.params = torch.cat([scene[k].reshape(-1).float() for k, _ in LAYOUT]).to(device)
         if peer_group is not None:
-            self.peer = PeerAllReduce(self.params.numel(), self.params.device, peer_group)
+            self.peer = PeerAllReduce(self.params.numel(), self.params.device, peer_group, multicast=multicast,
+                                      with_params=bool(shard_optimizer))
             self.grads = self.peer.buffer[:self.params.numel()]
             self.grads.zero_()
+            if shard_optimizer:
+                flat = self.params
+                self.params = self.peer.params[:flat.numel()]
+                self.params.copy_(flat)
+                torch.cuda.synchronize(self.params.device)
+                import torch.distributed as dist
+                dist.barrier(peer_group)     # every replica holds the initial parameters before anyone's first step
         else:
             self.grads = torch.zeros_like(self.params)
         self.views, self.gviews = {}, {}
@@ -137,11 +149,20 @@ class PeerAllReduce:
     itself is `splat_peer_allreduce_sum` (two-shot over NVLink loads/stores, csrc/allreduce.cu), launched on the
     current stream -- no NCCL stream hop, and every replica receives bit-identical sums."""
 
-    def __init__(self, numel, device, group, multicast="auto"):
+    def __init__(self, numel, device, group, multicast="auto", with_params=False):
         import ctypes as C
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm_mem
         self.numel = (int(numel) + 3) // 4 * 4
+        self.params = None
+        if with_params:      # a second symmetric bucket of the same length: the replicated parameters (ShardedAdam)
+            self.params = symm_mem.empty(self.numel, dtype=torch.float32, device=device)
+            self.params.zero_()
+            torch.cuda.synchronize(device)
+            hp = symm_mem.rendezvous(self.params, group)
+            self._pbufs = (C.c_uint64 * int(hp.world_size))(*[int(p) for p in hp.buffer_ptrs])
+            self._param_multicast_ptr = int(getattr(hp, "multicast_ptr", 0) or 0)
+            self._param_handle = hp
         self.buffer = symm_mem.empty(self.numel, dtype=torch.float32, device=device)
         self.flags = symm_mem.empty(256, dtype=torch.int32, device=device)
         self.buffer.zero_()
@@ -160,6 +181,9 @@ class PeerAllReduce:
         if multicast == "auto":
             multicast = self.world > 4
         self.multicast = mc if multicast else 0
+        self.param_multicast = (self._param_multicast_ptr if (with_params and self.multicast) else 0)
+        if with_params and self.multicast and not self.param_multicast:
+            self.multicast = 0          # both buckets through the switch, or neither
         self.epoch = 0
         dist.barrier(group)   # every rank's flag pad is zeroed before anyone signals into it
         torch.cuda.synchronize(device)
@@ -183,3 +207,48 @@ def mapping_step(bucket, render_fn, cams, schedule, step, rank, group=None, aver
     render_fn(cams[kf], bucket.leaves())
     bucket.all_reduce(group, average)
     return kf
+
+
+class ShardedAdam:
+    """Exchange + optimizer step of the keyframe-sharded mapping iteration as ONE kernel per rank
+    (`splat_peer_reduce_adam`, csrc/allreduce.cu): rank r sums slice r of the gradient bucket over the ranks (inside the
+    NVSwitch when the fabric has a multicast mapping, else over peer loads in rank order), applies Adam -- the arithmetic
+    of FusedAdam / torch.optim.Adam as SplaTAM builds it (initialize_optimizer, scripts/splatam.py:166-172: one learning
+    rate per tensor, eps 1e-15 while mapping) -- to slice r of the parameter bucket with ITS shard of the moments, and
+    stores the updated parameters into every replica.  Replaces `bucket.all_reduce(); optimizer.step()`: the links carry
+    the same bytes as one all-reduce, the optimizer pass and the moment memory shrink to 1/N per GPU, and every replica
+    receives bit-identical parameters.  `bucket` must have been built with peer_group and shard_optimizer=True."""
+
+    def __init__(self, bucket, lrs, betas=(0.9, 0.999), eps=1e-15):
+        import ctypes as C
+        from ._lib import lib
+        peer = bucket.peer
+        if peer is None or peer.params is None:
+            raise ValueError("ShardedAdam needs a GradBucket(peer_group=..., shard_optimizer=True)")
+        self.bucket, self.peer, self.betas, self.eps = bucket, peer, (float(betas[0]), float(betas[1])), float(eps)
+        self.steps = 0
+        n = int(lib.splat_peer_adam_shard_floats(peer.numel, peer.world))
+        dev = bucket.params.device
+        self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
+        ends, off = [], 0
+        for k, w in bucket.layout:
+            off += bucket.P * w
+            ends.append(off)
+        ends[-1] = peer.numel                       # the padding up to a multiple of 4 floats rides with the last tensor
+        self._ends = (C.c_int64 * len(ends))(*ends)
+        self._lrs = (C.c_float * len(ends))(*[float(lrs[k]) for k, _ in bucket.layout])
+        self._n = len(ends)
+
+    def step(self):
+        """Sums the gradient bucket over the ranks and takes one Adam step on every replica (current stream)."""
+        import ctypes as C
+        from ._lib import check, lib
+        peer = self.peer
+        self.steps += 1
+        peer.epoch = (peer.epoch + 1) & 0xffffffff
+        check(lib.splat_peer_reduce_adam(peer._bufs, peer._pbufs, peer._pads, peer.multicast, peer.param_multicast,
+                                         peer.rank, peer.world, peer.epoch, peer.numel, self._ends, self._lrs, self._n,
+                                         self.steps, self.betas[0], self.betas[1], self.eps,
+                                         C.c_void_p(self.exp_avg.data_ptr()), C.c_void_p(self.exp_avg_sq.data_ptr()),
+                                         C.c_void_p(torch.cuda.current_stream().cuda_stream)))
