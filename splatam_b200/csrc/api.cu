@@ -141,7 +141,7 @@ int splat_forward_render(const SplatCamera* cam, int32_t P, const float* colors_
   r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.out_color = out_color; r.out_depth = out_depth;
   r.hdr = iv.hdr; r.Rcap = Rcap; r.blended = nullptr; r.depth_sil = cam->depth_sil ? 1 : 0; r.zero = 0;
-  r.grec = gv.grec; r.plist = bv.point_list;
+  r.grec = gv.grec; r.plist = bv.point_list; r.P = P;
   return launch_render_fwd(r, T, st);
 }
 
@@ -198,7 +198,7 @@ int splat_backward(const SplatCamera* cam, int32_t P, int64_t R, const float* me
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.dL_dpix = dL_dout_color; r.out_color = out_color;
   r.acc = acc;
   r.hdr = iv.hdr; r.Rcap = (uint32_t)(R > 0xffffffffll ? 0xffffffffll : R); r.zero = 0;
-  r.grec = gv.grec; r.plist = bv.point_list;
+  r.grec = gv.grec; r.plist = bv.point_list; r.P = P;
   if (!hess) {
     // callers that need neither colour nor opacity gradients (pose-only tracking) get the blend backward without those sums
     const int mode = cam->depth_sil ? ((!dL_dcolors && !dL_dopacity) ? 3 : 2) : 0;
@@ -261,7 +261,7 @@ int splat_debug_count_blended(const SplatCamera* cam, int32_t P, const float* co
   r.W = W; r.H = H; r.gx = gx; r.order = iv.tile_order; r.ranges = iv.ranges; r.inst = bv.inst; r.bg = cam->bg;
   r.final_T = iv.final_T; r.n_contrib = iv.n_contrib; r.out_color = scratch_color; r.out_depth = nullptr;
   r.hdr = iv.hdr; r.Rcap = (uint32_t)R_capacity; r.blended = blended; r.depth_sil = 0; r.zero = 0;
-  r.grec = gv.grec; r.plist = bv.point_list;
+  r.grec = gv.grec; r.plist = bv.point_list; r.P = P;
   return launch_render_fwd(r, gx * gy, (cudaStream_t)stream);
 }
 

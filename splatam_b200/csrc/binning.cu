@@ -212,6 +212,7 @@ __global__ void __launch_bounds__(256) scatter_kernel(int P, int gx, int gy, con
     for (int y = y0; y < y1; ++y)
       for (int x = x0; x < x1; ++x) {
         const uint32_t pos = atomicAdd(tile_cursor + (size_t)(y * gx + x) * CSTRIDE, 1u);
+        SPLAT_CHECK(pos < Rcap && y * gx + x < gx * gy);
         keys[pos] = kv;
       }
   }
@@ -225,6 +226,7 @@ __global__ void __launch_bounds__(256) scatter_kernel(int P, int gx, int gy, con
     const int w = bx1 - bx0, n = w * (by1 - by0);
     for (int t = lane; t < n; t += 32) {
       const uint32_t pos = atomicAdd(tile_cursor + (size_t)((by0 + t / w) * gx + bx0 + t % w) * CSTRIDE, 1u);
+      SPLAT_CHECK(pos < Rcap);
       keys[pos] = bkv;
     }
   }
@@ -305,7 +307,7 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
   bin.direct = range < SORT_NB;
   bin.scale = bin.direct ? 0u : (uint32_t)(((uint64_t)SORT_NB << 32) / ((uint64_t)range + 1ull));
   // histogram
-  for (int i = tid; i < n; i += SORT_THREADS) atomicAdd(&bins[bin(A[i])], 1u);
+  for (int i = tid; i < n; i += SORT_THREADS) { SPLAT_CHECK(bin(A[i]) < SORT_NB); atomicAdd(&bins[bin(A[i])], 1u); }
   __syncthreads();
   // exclusive scan over SORT_NB bins: thread t owns bins [8t, 8t+8)
   {
@@ -329,7 +331,9 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
   // placement: bins[] are cursors (start -> end)
   for (int i = tid; i < n; i += SORT_THREADS) {
     const uint64_t k = A[i];
-    B[atomicAdd(&bins[bin(k)], 1u)] = k;
+    const uint32_t dstp = atomicAdd(&bins[bin(k)], 1u);
+    SPLAT_CHECK(dstp < (uint32_t)n);
+    B[dstp] = k;
   }
   __syncthreads();
   // Heavy bins.  A tile whose depths are bit-equal or clustered -- the frame-0 map back-projected from quantised
@@ -374,7 +378,7 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
       const int sh = max(0, 43 - __clzll((long long)(range64 | 1ull)));   // (range >> sh) < 2^21
       const uint32_t rdiv = (uint32_t)(range64 >> sh) + 1u;
       auto sub = [&](uint64_t k) { return (uint32_t)(((uint32_t)((k - kmin) >> sh) * (uint32_t)SUB_NB) / rdiv); };
-      for (int i = lo + tid; i < hi; i += SORT_THREADS) atomicAdd(&bins2[sub(B[i])], 1u);
+      for (int i = lo + tid; i < hi; i += SORT_THREADS) { SPLAT_CHECK(sub(B[i]) < SUB_NB); atomicAdd(&bins2[sub(B[i])], 1u); }
       __syncthreads();
       {   // exclusive scan of bins2 (thread t owns sub-bins [2t, 2t+2)), offset by lo
         constexpr int PER = SUB_NB / SORT_THREADS;
@@ -396,7 +400,12 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
       }
       __syncthreads();
       // placement into A (free since the first-level placement), then ranking inside the sub-bins
-      for (int i = lo + tid; i < hi; i += SORT_THREADS) { const uint64_t k = B[i]; A[atomicAdd(&bins2[sub(k)], 1u)] = k; }
+      for (int i = lo + tid; i < hi; i += SORT_THREADS) {
+        const uint64_t k = B[i];
+        const uint32_t dstp = atomicAdd(&bins2[sub(k)], 1u);
+        SPLAT_CHECK(dstp >= (uint32_t)lo && dstp < (uint32_t)hi);
+        A[dstp] = k;
+      }
       __syncthreads();
       for (int i = lo + tid; i < hi; i += SORT_THREADS) {
         const uint64_t k = A[i];
@@ -404,6 +413,7 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
         const int l2 = b2 ? (int)bins2[b2 - 1] : lo, h2 = (int)bins2[b2];
         int rank = 0;
         for (int q = l2; q < h2; ++q) rank += A[q] < k;
+        SPLAT_CHECK(l2 >= lo && h2 <= hi && l2 + rank < hi);
         out[l2 + rank] = (uint32_t)k;
       }
       __syncthreads();
@@ -418,6 +428,7 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
     if (hi - lo > HEAVY_BIN && n_heavy <= MAX_HEAVY) continue;   // already written by its own pass
     int rank = 0;
     for (int q = lo; q < hi; ++q) rank += B[q] < k;
+    SPLAT_CHECK(lo >= 0 && hi <= n && lo + rank < hi);
     out[lo + rank] = (uint32_t)k;
   }
 }

@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stddef.h>
+#include <stdio.h>
 #include "../../include/splat_b200.h"
 
 #define TILE_X 16
@@ -122,6 +123,17 @@ inline BinView bin_view(void* base, int64_t Rcap) {
   v.inst = (float4*)c;
   return v;
 }
+
+// ---------------------------------------------------------------- bounds checks (debug build)
+// -DSPLAT_BOUNDS_CHECK: every index the blend kernels, the scatter and the tile sort form (Gaussian ids, list positions,
+// ring / transpose-tile / bin addresses, accumulator rows) is checked on the device and a violation traps -- the
+// parity suite is run against that build (scripts/gpu_bounds_check.sh, profiles/r02_bounds_check.txt).  It stands in for
+// compute-sanitizer, which is closed on this pool.  Compiled out (zero instructions) in the product build.
+#ifdef SPLAT_BOUNDS_CHECK
+#define SPLAT_CHECK(cond) do { if (!(cond)) { printf("SPLAT_CHECK failed: %s (%s:%d) block %d thread %d\n", #cond, __FILE__, __LINE__, (int)blockIdx.x, (int)threadIdx.x); __trap(); } } while (0)
+#else
+#define SPLAT_CHECK(cond) do {} while (0)
+#endif
 
 // ---------------------------------------------------------------- small math
 struct Mat3 {  // column-major: m[c][r]

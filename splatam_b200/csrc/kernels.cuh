@@ -51,6 +51,7 @@ struct RenderFwdArgs {
   uint32_t* blended;  // debug: per-pixel count of blended pairs (NULL in production)
   int zero;           // always 0: an operand ptxas cannot fold (packed.cuh ExpConsts)
   const float4* grec; const uint32_t* plist;   // gather mode: per-Gaussian records + the sorted id list (inst is not written)
+  int P;              // number of Gaussians (bounds checks)
 };
 
 struct RenderBwdArgs {
@@ -63,6 +64,7 @@ struct RenderBwdArgs {
   const ImageHeader* hdr; uint32_t Rcap;   // R > Rcap (a graph replay that overflowed its binning capacity): nothing to walk
   int zero;     // always 0 (packed.cuh ExpConsts)
   const float4* grec; const uint32_t* plist;   // gather mode (see RenderFwdArgs)
+  int P;        // number of Gaussians (bounds checks)
 };
 
 // SplaTAM glue (slam_ops.cu).  Render-variable builder: forward outputs o_*, backward inputs g_* (any may be NULL ==

@@ -93,6 +93,7 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
   // image state untouched (every forward kernel exits on R > Rcap): there is nothing valid to walk.  The accumulator
   // stays zero, so preprocess_bwd writes all-zero gradients for this step (splat_forward_guard reports the overflow).
   if (a.hdr->num_rendered > a.Rcap) return;
+  SPLAT_CHECK(a.ranges[a.order[blockIdx.x]].y <= a.hdr->num_rendered);
   extern __shared__ __align__(128) unsigned char smem_dyn[];
   __shared__ __align__(8) uint64_t s_full[RING_NS];
   __shared__ int s_rel[RING_NS];
@@ -149,6 +150,7 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
     for (int k = 0; k < BWD_CH / 32; ++k) {
       const int j = lane + 32 * k;
       if (j < cnt) {
+        SPLAT_CHECK(id[k] < (uint32_t)a.P && lo >= 0 && lo + j < (int)(range.y - range.x) && j < BWD_CH);
         const float4* src = a.grec + (size_t)id[k] * INST_F4;
 #pragma unroll
         for (int q = 0; q < INST_F4; ++q) cp_async16(dst + (uint32_t)(j * INST_F4 + q) * 16u, src + q);
@@ -259,8 +261,10 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
               m ^= 1u << b;
               const uint32_t r = rsub + b * INST_BYTES;
               const int pos = pos_sub + (int)b;
+              SPLAT_CHECK(r >= sbase && r + INST_BYTES <= sbase + BWD_CH * INST_BYTES && sub + (int)b < cnt && pos < hi);
               const float4 q0 = lds128(r), q1 = lds128(r + 16);
               ids[gsl] = __float_as_uint(q1.w);
+              SPLAT_CHECK(ids[gsl] < (uint32_t)a.P);
               const float dx = q0.x - pxf;
               const f2 dy2 = add2(bc(q0.y), npy2);
               // power, exp and alpha exactly as the forward pass formed them: the blend decisions below are the same
@@ -321,7 +325,10 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
                 // the lane's partials (summed over its two pixels) go straight into the warp's transpose tile: column =
                 // lane, row = value (the previous group's row sums were read before the __syncwarp below)
                 const uint32_t tr_row = tr_st + (uint32_t)(gsl * VALS) * (TR_STRIDE * 4);
-                auto put = [&](int i, f2 x) { sts32(tr_row + (uint32_t)i * (TR_STRIDE * 4), hsum(x)); };
+                auto put = [&](int i, f2 x) {
+                  SPLAT_CHECK(gsl * VALS + i < TR_ROWS && tr_row + (uint32_t)i * (TR_STRIDE * 4) + 4 <= tr_base + TR_WARP_BYTES);
+                  sts32(tr_row + (uint32_t)i * (TR_STRIDE * 4), hsum(x));
+                };
                 if (MODE == 3) {
                   const f2 u2 = mul2(Gv2, dLda2), udx = mul2(u2, bc(dx)), udy = mul2(u2, dy2);
                   put(0, udx); put(1, udy);
@@ -368,6 +375,7 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
           float tot = 0.f;
           if (mine) tot = row_sum32(tr_ld);
           __syncwarp();
+          SPLAT_CHECK(!mine || (id < (uint32_t)a.P && slot < STRIDE));
           if (mine && tot != 0.f) red_add_f32(a.acc + (size_t)id * STRIDE + slot, tot);
         }
       }

@@ -59,6 +59,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
   const uint2 range = a.ranges[tile];
   const int n = (int)(range.y - range.x);
   const int nch = (n + RING_CH - 1) / RING_CH;
+  SPLAT_CHECK(range.x <= range.y && range.y <= a.hdr->num_rendered && a.hdr->num_rendered <= a.Rcap);
 
   if (tid == 0) {
 #pragma unroll
@@ -91,6 +92,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
     for (int k = 0; k < RING_CH / 32; ++k) {
       const int j = lane + 32 * k;
       if (j < cnt) {
+        SPLAT_CHECK(id[k] < (uint32_t)a.P && base + j < n && j < RING_CH);
         const float4* src = a.grec + (size_t)id[k] * INST_F4;
 #pragma unroll
         for (int q = 0; q < INST_F4; ++q) cp_async16(dst + (uint32_t)(j * INST_F4 + q) * 16u, src + q);
@@ -164,7 +166,9 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
           asm("bfind.u32 %0, %1;" : "=r"(t) : "r"(m));
           m ^= 1u << t;
           const uint32_t r = r31 - t * INST_BYTES;
+          SPLAT_CHECK(r >= sbase && r + INST_BYTES <= sbase + RING_CH * INST_BYTES && (int)(sub + 31 - t) < cnt);
           const float4 q0 = lds128(r), q1 = lds128(r + 16);   // (x, y, A, B), (C, opacity, depth, id)
+          SPLAT_CHECK(__float_as_uint(q1.w) < (uint32_t)a.P);
           const float4 cq = lds128(r + 32);                     // (r, g, b, -)
           const float dx = q0.x - pxf;
           const f2 dy2 = add2(bc(q0.y), npy2);

@@ -279,6 +279,12 @@ def get_loss(params, curr_data, variables, iter_time_idx, loss_weights, use_sil_
     Renderer = Renderer or _default_renderer()
     out, radius, _ = Renderer(raster_settings=curr_data['cam']).render_rgbd_sil(**rendervar)
     variables['means2D'] = rendervar['means2D']
+    # NOTE (deviation): the reference gives its depth/silhouette pass a separate means2D, so
+    # only the COLOUR pass feeds means2D.grad (utils/slam_helpers.py:196-249).  The fused six-plane render has one
+    # means2D: its gradient also carries the depth and silhouette planes' screen-space terms.  Nothing in SplaTAM's
+    # shipped configs reads it (use_gaussian_splatting_densification=False); a caller that enables GS-style
+    # densification (utils/slam_external.py:101-102 accumulates means2D.grad) should use the two-pass drop-in path.
+    variables['means2D_grad_source'] = 'rgb+depth+silhouette planes (fused render)'
     loss, weighted_losses = image_loss(out, None, curr_data['im'], curr_data['depth'], loss_weights,
                                        use_sil_for_loss, sil_thres, tracking)
     # == `seen = radius > 0; max_2D_radius[seen] = max(radius[seen], max_2D_radius[seen])` (:348-350) without the
