@@ -18,6 +18,8 @@ Contract (one JSON line on rank 0):  python bench.py --gpus N --steps K --warmup
     oracle port when the prebuilt extension is not loadable.
 """
 import argparse
+import contextlib
+import gc
 import json
 import os
 import subprocess
@@ -409,6 +411,21 @@ def pair_counts(runner, keyframes):
 LAST_HOST = {}
 
 
+@contextlib.contextmanager
+def no_gc():
+    """Timed regions run with Python's cyclic garbage collector paused (as timeit does), after one explicit collection:
+    a generation-2 collection walks the whole process's object graph -- 13 to 87 ms here, at a deterministic step of the
+    loop (it hit the SECOND timed step of the 20-step mapping leg in 3 runs of 6: 1.33 -> 5.6 ms per step).  Both arms."""
+    gc.collect()
+    was = gc.isenabled()
+    gc.disable()
+    try:
+        yield
+    finally:
+        if was:
+            gc.enable()
+
+
 def keyframe_costs(step_fn, n_keyframes, device, dist, world):
     """Measured cost (ms, CUDA events) of one step on each keyframe of the window, identical on every rank (MAX over
     ranks): input of mapping.keyframe_schedule(cost=...).  One untimed pass first (capacity hints, allocator)."""
@@ -451,10 +468,12 @@ def timed_run(runner, sched, rank, world, steps, warmup, device, dist, on_timed_
     # (the reference arm must not map libsplat_b200.so: the rasterizer module is only touched for OUR runner)
     host_stats = sys.modules["splatam_b200.rasterizer"].host_stats if isinstance(runner, OursRunner) else {"wait_s": 0.0}
     w0, h0 = host_stats["wait_s"], time.perf_counter()
-    e0.record()
-    for i in range(steps):
-        full_step(i)
-    e1.record()
+    with no_gc():
+        w0, h0 = host_stats["wait_s"], time.perf_counter()
+        e0.record()
+        for i in range(steps):
+            full_step(i)
+        e1.record()
     h1, w1 = time.perf_counter(), host_stats["wait_s"]
     barrier()
     # host view of the same region: time to enqueue the K steps, and how much of it the host spent blocked on the
@@ -533,10 +552,12 @@ def e2e_run(runner, sched, rank, world, steps, device, dist):
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    run(steps)
-    e1.record()
-    torch.cuda.synchronize()
+    with no_gc():
+        t0 = time.perf_counter()
+        e0.record()
+        run(steps)
+        e1.record()
+        torch.cuda.synchronize()
     wall_ms = (time.perf_counter() - t0) * 1e3
     ms = max(e0.elapsed_time(e1), 0.0)
     t = torch.tensor([ms, wall_ms], device=device)
@@ -687,11 +708,22 @@ def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, war
         full(i)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(steps):
-        loss = full(warmup + i)
-    e1.record()
+    trace = [] if os.environ.get("SPLAT_BENCH_TRACE") else None
+    with no_gc():
+        e0.record()
+        for i in range(steps):
+            if trace is not None:
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record()
+                trace.append((ev, time.perf_counter()))
+            loss = full(warmup + i)
+        e1.record()
     barrier()
+    if trace:
+        gpu = [trace[i][0].elapsed_time(trace[i + 1][0]) for i in range(len(trace) - 1)]
+        host = [(trace[i + 1][1] - trace[i][1]) * 1e3 for i in range(len(trace) - 1)]
+        sys.stderr.write("mapping leg per-step gpu ms: %s\nmapping leg per-step host ms: %s\n" % (
+            " ".join("%.2f" % v for v in gpu), " ".join("%.2f" % v for v in host)))
     t = torch.tensor([e0.elapsed_time(e1)], device=device)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -738,6 +770,7 @@ def main():
                        "backward_power": power, "variant": args.variant,
                        "parallelism": "keyframe-sharded x%d + 1 all-reduce of the flat gradient bucket" % world
                        if world > 1 else "single GPU",
+                       "host": "Python's cyclic GC is paused inside every timed region (one gc.collect() before it), both arms",
                        "l2": "per-step working set (56 MB parameters + 56 MB gradients + ~190 MB geometry/binning/"
                              "instance state) exceeds the 126 MB L2 and the camera moves over the keyframe window "
                              "every step; no explicit flush"}}

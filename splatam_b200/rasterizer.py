@@ -44,6 +44,19 @@ def _spec_capacity(hint):
     return (cap + _CAP_STEP - 1) // _CAP_STEP * _CAP_STEP
 
 
+def _sticky_capacity(key, want):
+    """The capacity actually allocated: the previous one for this key as long as it still covers `want` and is not more
+    than twice too large.  Without the hysteresis the slowly decaying hint crosses a _CAP_STEP boundary every few dozen
+    calls, the allocator is asked for a new block size, and a cudaMalloc (0.5 - 35 ms measured) lands in the caller's
+    loop -- bench.py's 20-step mapping leg caught exactly one of those at its second timed step."""
+    bkey = ("block",) + key
+    cur = _capacity_hint.get(bkey)
+    if cur is None or want > cur or want * 2 < cur:
+        cur = want
+        _capacity_hint[bkey] = cur
+    return cur
+
+
 def _pinned_scalar(device):
     cache = getattr(_tls, "pinned", None)
     if cache is None:
@@ -212,7 +225,7 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
             # established; the guard kernel records (device side) whether a replay ever exceeds it.
             if hint is None:
                 raise RuntimeError("run one un-captured forward at this image size before capturing a CUDA graph")
-            phase2(_spec_capacity(hint))
+            phase2(_sticky_capacity(key, _spec_capacity(hint)))
             check(lib.splat_forward_guard(_ptr(st.image), W, H, st.capacity, C.c_void_p(capture_guard(dev).data_ptr()),
                                           stream))
             if bwd is not None:
@@ -224,7 +237,7 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
             return out_color, radii, out_depth, st
         launched = False
         if hint is not None:
-            phase2(_spec_capacity(hint))
+            phase2(_sticky_capacity(key, _spec_capacity(hint)))
             launched = True
         if bwd is not None:
             st.plan = _plan_backward(st, dev, bwd[0], bwd[1], means3D, colors_precomp, scales, rotations,
@@ -236,7 +249,7 @@ def rasterize_forward(rs, near, means3D, colors_precomp, opacities, scales, rota
         R = int(pinned.item())
         _capacity_hint[key] = max(R, int(hint * _CAP_DECAY)) if hint is not None else R
         if not launched or R > st.capacity:
-            phase2(_spec_capacity(R))
+            phase2(_sticky_capacity(key, _spec_capacity(R)))
         st.num_rendered = R
     if keep_last_state:
         last_state = st
