@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define SPLAT_ABI_VERSION 5
+#define SPLAT_ABI_VERSION 6   /* v6 (round 2): splat_peer_reduce_adam, splat_peer_adam_shard_floats, splat_set_gather, splat_slam_track_loss_noalloc, splat_debug_exp_mismatches */
 
 /* Error codes.  Positive values >= 1000 are 1000 + cudaError_t of a failed runtime call. */
 enum {

@@ -115,7 +115,7 @@ def _load():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing: intended
         fn.restype = res
         fn.argtypes = args
-    if lib.splat_abi_version() != 5:
+    if lib.splat_abi_version() != 6:
         raise ImportError("libsplat_b200.so ABI version mismatch")
     return lib
 
