@@ -10,7 +10,7 @@
 
 namespace splat {
 
-int g_launch_count = 0;
+std::atomic<int> g_launch_count{0};
 int g_prof_on = 0;
 struct ProfPair { cudaEvent_t a, b, prev; };   // prev = end event of the launch before this one (idle-gap accounting)
 static cudaEvent_t g_prof_last_end = nullptr;
@@ -499,7 +499,7 @@ int splat_forward_guard(const void* image_state, int32_t W, int32_t H, int64_t R
 
 int splat_abi_version(void) { return SPLAT_ABI_VERSION; }
 const char* splat_last_error(void) { return g_err; }
-int splat_kernel_launch_count(void) { return g_launch_count; }
+int splat_kernel_launch_count(void) { return g_launch_count.load(std::memory_order_relaxed); }
 const char* splat_strerror(int code) {
   switch (code) {
     case SPLAT_OK: return "ok";

@@ -6,6 +6,7 @@
 // Appendix A).  Expression trees are kept in the reference's association order on purpose:
 // radii / tile rects must come out bit-identical, and nvcc's FMA contraction follows the tree.
 #pragma once
+#include <atomic>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stddef.h>
@@ -20,8 +21,12 @@
 namespace splat {
 
 // ---------------------------------------------------------------- launch bookkeeping
-extern int g_launch_count;
-inline void count_launch(int n = 1) { g_launch_count += n; }
+// Process-wide state of the library, all of it measurement / configuration, none of it on the data path: the launch
+// counter (atomic: entry points may be called from several host threads), the per-launch event profiler (off unless
+// splat_profile_enable(1); NOT thread-safe, a bench-only facility), and the two switches read once from the environment
+// (SPLAT_B200_NO_CULL, SPLAT_B200_GATHER / splat_set_gather).  Everything else an entry point touches is caller-owned.
+extern std::atomic<int> g_launch_count;
+inline void count_launch(int n = 1) { g_launch_count.fetch_add(n, std::memory_order_relaxed); }
 
 // ---------------------------------------------------------------- per-kernel event profiling
 enum KernelId { K_PRE_FWD = 0, K_TILE_SCAN, K_SCATTER, K_TILE_SORT, K_RENDER_FWD, K_RENDER_BWD, K_PRE_BWD,
