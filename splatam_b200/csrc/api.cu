@@ -11,6 +11,7 @@
 namespace splat {
 
 std::atomic<int> g_launch_count{0};
+int g_pdl = 1;
 int g_prof_on = 0;
 struct ProfPair { cudaEvent_t a, b, prev; };   // prev = end event of the launch before this one (idle-gap accounting)
 static cudaEvent_t g_prof_last_end = nullptr;
@@ -61,9 +62,13 @@ static void read_env_once() {
   done = true;
   const char* e = getenv("SPLAT_B200_NO_CULL");
   if (e && e[0] == '1') g_disable_cull = 1;
+  e = getenv("SPLAT_B200_PDL");      // "0": plain stream-ordered launches (no programmatic dependent launch)
+  if (e) g_pdl = e[0] != '0';
   e = getenv("SPLAT_B200_GATHER");   // "0": blend kernels stream the re-written instance records (emit_records + TMA)
   if (e) g_gather = e[0] != '0';
 }
+
+static const bool g_env_read_at_load = (read_env_once(), true);   // switches apply to every entry point from the first call
 
 }  // namespace splat
 

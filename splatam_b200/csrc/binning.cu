@@ -42,6 +42,8 @@ __global__ void __cluster_dims__(SCAN_CTAS, 1, 1) __launch_bounds__(SCAN_THREADS
 tile_scan_kernel(int T, const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_cursor,
                  uint2* __restrict__ ranges, ImageHeader* hdr, uint32_t* __restrict__ num_rendered_out,
                  uint32_t sort_cap, uint32_t* __restrict__ tile_order) {
+  pdl_wait();
+  pdl_trigger();
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
   constexpr int NW = SCAN_THREADS / 32;
@@ -187,6 +189,8 @@ __global__ void __launch_bounds__(256) scatter_kernel(int P, int gx, int gy, con
                                                       uint32_t* __restrict__ tile_cursor,
                                                       uint64_t* __restrict__ keys,
                                                       const ImageHeader* __restrict__ hdr, uint32_t Rcap) {
+  pdl_wait();
+  pdl_trigger();
   if (hdr->num_rendered > Rcap) return;  // capacity exceeded: caller re-runs phase 2
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned lane = threadIdx.x & 31u;
@@ -265,6 +269,8 @@ __global__ void __launch_bounds__(SORT_THREADS) tile_sort_kernel(const uint2* __
                                                                  uint32_t* __restrict__ point_list,
                                                                  const ImageHeader* __restrict__ hdr,
                                                                  uint32_t Rcap, int smem_cap) {
+  pdl_wait();
+  pdl_trigger();
   if (hdr->num_rendered > Rcap) return;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ uint32_t bins[SORT_NB];
@@ -440,6 +446,8 @@ __global__ void __launch_bounds__(256) emit_records_kernel(const uint32_t* __res
                                                            const float4* __restrict__ grec,
                                                            float4* __restrict__ inst,
                                                            const ImageHeader* __restrict__ hdr, uint32_t Rcap) {
+  pdl_wait();
+  pdl_trigger();
   const uint32_t R = hdr->num_rendered;
   if (R > Rcap) return;
   const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -453,8 +461,8 @@ __global__ void __launch_bounds__(256) emit_records_kernel(const uint32_t* __res
 
 int launch_tile_scan(int T, const ImageView& iv, uint32_t* num_rendered_out, uint32_t sort_cap, cudaStream_t st) {
   ProfScope prof_(K_TILE_SCAN, st);
-  tile_scan_kernel<<<SCAN_CTAS, SCAN_THREADS, 0, st>>>(T, iv.tile_count, iv.tile_cursor, iv.ranges, iv.hdr, num_rendered_out, sort_cap,
-                                       iv.tile_order);
+  SPLAT_CUDA(launch_k(tile_scan_kernel, dim3(SCAN_CTAS), dim3(SCAN_THREADS), 0, st, T, iv.tile_count, iv.tile_cursor, iv.ranges, iv.hdr,
+                      num_rendered_out, sort_cap, iv.tile_order));
   SPLAT_LAUNCH_CHECK("tile_scan_kernel");
   return SPLAT_OK;
 }
@@ -463,7 +471,7 @@ int launch_scatter(int P, int gx, int gy, const int* radii, const GeomView& g, c
                    const BinView& b, uint32_t Rcap, cudaStream_t st) {
   ProfScope prof_(K_SCATTER, st);
   if (P <= 0) return SPLAT_OK;
-  scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, gx, gy, radii, g.grec, iv.tile_cursor, b.keys, iv.hdr, Rcap);
+  SPLAT_CUDA(launch_k(scatter_kernel, dim3((P + 255) / 256), dim3(256), 0, st, P, gx, gy, radii, g.grec, iv.tile_cursor, b.keys, iv.hdr, Rcap));
   SPLAT_LAUNCH_CHECK("scatter_kernel");
   return SPLAT_OK;
 }
@@ -482,13 +490,14 @@ int launch_tile_sort(int T, const ImageView& iv, const GeomView& g, const BinVie
       SPLAT_CUDA(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
       attr_set[dev] = true;
     }
-    tile_sort_kernel<<<T, SORT_THREADS, smem, st>>>(iv.ranges, b.keys, b.keys_alt, b.point_list, iv.hdr, Rcap, kSortSmemCap);
+    SPLAT_CUDA(launch_k(tile_sort_kernel, dim3(T), dim3(SORT_THREADS), (size_t)smem, st, iv.ranges, b.keys, b.keys_alt, b.point_list, iv.hdr, Rcap,
+                        kSortSmemCap));
     SPLAT_LAUNCH_CHECK("tile_sort_kernel");
   }
   if (Rcap > 0 && !g_gather) {   // gather mode: the blend kernels fetch the Gaussians' own records by id
     ProfScope prof_(K_EMIT, st);
     const size_t quads = (size_t)Rcap * INST_F4;
-    emit_records_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, st>>>(b.point_list, g.grec, b.inst, iv.hdr, Rcap);
+    SPLAT_CUDA(launch_k(emit_records_kernel, dim3((unsigned)((quads + 255) / 256)), dim3(256), 0, st, b.point_list, g.grec, b.inst, iv.hdr, Rcap));
     SPLAT_LAUNCH_CHECK("emit_records_kernel");
   }
   return SPLAT_OK;

@@ -39,6 +39,37 @@ struct ProfScope {  // cudaEvent pair around one launch, only when splat_profile
   ~ProfScope() { if (g_prof_on) prof_record(id, st, false); }
 };
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// Every kernel of the library is launched with the programmatic-stream-serialization attribute (unless SPLAT_B200_PDL=0):
+// its CTAs may be scheduled, and run up to pdl_wait(), while the previous kernel of the stream is still draining, so the
+// ~2.6 us launch gap per kernel boundary (8 per render iteration, ~20 per fused SLAM iteration) overlaps the predecessor's
+// tail.  pdl_wait() (griddepcontrol.wait) is the FIRST statement of every such kernel: nothing a predecessor wrote is read
+// before it.  Works inside CUDA-graph capture (the edge is captured as a programmatic dependency).
+extern int g_pdl;
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// Early trigger: lets the NEXT kernel's CTAs be scheduled before this grid has finished (they still block in their own
+// pdl_wait() until it has).  Measured at C3 (r02): 1050 it/s with the trigger (right after the wait in the short kernels,
+// after the main loop in the blend kernels) vs 1052 without -- waiting CTAs take slots the draining grid could use -- so it
+// is compiled out; the implicit trigger at grid completion keeps the launch-latency overlap (1052 vs 1034 it/s without PDL).
+#ifndef SPLAT_PDL_TRIGGER
+#define SPLAT_PDL_TRIGGER 0
+#endif
+__device__ __forceinline__ void pdl_trigger() {
+#if SPLAT_PDL_TRIGGER
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = g_pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ---------------------------------------------------------------- state layouts
 __host__ __device__ inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 

@@ -87,6 +87,8 @@ __device__ __forceinline__ float frame_slope(float a, float b, float c) {
 }
 
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreFwdArgs a) {
+  pdl_wait();
+  pdl_trigger();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned lane = threadIdx.x & 31u;
   bool vis = false;
@@ -335,6 +337,8 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means, cons
 // backward in one pass.  Every output row is written (zeros for culled Gaussians: their
 // accumulator rows were never touched), so the caller need not pre-zero the outputs.
 __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a) {
+  pdl_wait();
+  pdl_trigger();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= a.P) return;
   float dmean[3] = {0.f, 0.f, 0.f}, dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -437,7 +441,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a)
 int launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t st) {
   ProfScope prof_(K_PRE_BWD, st);
   if (a.P <= 0) return SPLAT_OK;
-  preprocess_bwd_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+  SPLAT_CUDA(launch_k(preprocess_bwd_kernel, dim3((a.P + 255) / 256), dim3(256), 0, st, a));
   SPLAT_LAUNCH_CHECK("preprocess_bwd_kernel");
   return SPLAT_OK;
 }
@@ -451,6 +455,8 @@ int launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t st) {
 // pushing the five unit vectors through the same chain_apply() used for power == 1.
 
 __global__ void __launch_bounds__(128) hessian_finalize_kernel(const HessArgs a) {
+  pdl_wait();
+  pdl_trigger();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= a.P) return;
   float out[16];
@@ -530,7 +536,7 @@ __global__ void __launch_bounds__(128) hessian_finalize_kernel(const HessArgs a)
 int launch_hessian_finalize(const HessArgs& a, cudaStream_t st) {
   ProfScope prof_(K_HESS_FIN, st);
   if (a.P <= 0) return SPLAT_OK;
-  hessian_finalize_kernel<<<(a.P + 127) / 128, 128, 0, st>>>(a);
+  SPLAT_CUDA(launch_k(hessian_finalize_kernel, dim3((a.P + 127) / 128), dim3(128), 0, st, a));
   SPLAT_LAUNCH_CHECK("hessian_finalize_kernel");
   return SPLAT_OK;
 }
@@ -538,7 +544,7 @@ int launch_hessian_finalize(const HessArgs& a, cudaStream_t st) {
 int launch_preprocess_fwd(const PreFwdArgs& a, cudaStream_t st) {
   ProfScope prof_(K_PRE_FWD, st);
   if (a.P <= 0) return SPLAT_OK;
-  preprocess_fwd_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+  SPLAT_CUDA(launch_k(preprocess_fwd_kernel, dim3((a.P + 255) / 256), dim3(256), 0, st, a));
   SPLAT_LAUNCH_CHECK("preprocess_fwd_kernel");
   return SPLAT_OK;
 }

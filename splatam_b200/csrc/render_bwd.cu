@@ -87,6 +87,7 @@ __device__ __forceinline__ float row_sum32(uint32_t addr) {
 // GATHER: the ring is filled from the Gaussians' own records by id (see render_fwd.cu); no instance-record copy exists.
 template <bool CULL, int MODE, bool GATHER>
 __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_kernel(const RenderBwdArgs a) {
+  pdl_wait();
   constexpr int VALS = BwdTraits<MODE>::VALS, GROUP = BwdTraits<MODE>::GROUP, STRIDE = BwdTraits<MODE>::STRIDE;
   constexpr int NV = VALS * GROUP;
   // A replay of a captured graph whose forward overflowed its binning capacity left the instance records and the
@@ -388,6 +389,7 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
       fill(c + RING_NS);
     }
   }
+  pdl_trigger();
 }
 
 // cudaFuncSetAttribute is per DEVICE: remember which devices have had the dynamic shared memory limit raised.
@@ -412,8 +414,8 @@ int launch_render_bwd(const RenderBwdArgs& a, int T, int mode, cudaStream_t st) 
   const bool g = g_gather != 0 && a.grec && a.plist;
 #define BWD_LAUNCH(C, M)                                                                       \
   do {                                                                                         \
-    if (g) render_bwd_kernel<C, M, true><<<T, RING_THREADS, BWD_SMEM, st>>>(a);                \
-    else render_bwd_kernel<C, M, false><<<T, RING_THREADS, BWD_SMEM, st>>>(a);                 \
+    if (g) SPLAT_CUDA(launch_k(render_bwd_kernel<C, M, true>, dim3(T), dim3(RING_THREADS), (size_t)BWD_SMEM, st, a));    \
+    else SPLAT_CUDA(launch_k(render_bwd_kernel<C, M, false>, dim3(T), dim3(RING_THREADS), (size_t)BWD_SMEM, st, a));  \
   } while (0)
   if (mode == 3) BWD_LAUNCH(true, 3);
   else if (mode == 2) BWD_LAUNCH(true, 2);

@@ -47,6 +47,7 @@ namespace splat {
 // per-stage mbarrier (cp.async.mbarrier.arrive.noinc, expected count 32 lanes instead of the TMA path's 1).
 template <bool CULL, bool COUNT, bool DS, bool GATHER>
 __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFwdArgs a) {
+  pdl_wait();
   if (a.hdr->num_rendered > a.Rcap) return;
   __shared__ __align__(128) float4 s_rec[RING_NS][RING_CH * INST_F4];
   __shared__ __align__(8) uint64_t s_full[RING_NS];
@@ -245,6 +246,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
     }
   }
 
+  pdl_trigger();   // this CTA's list is done: the next kernel's CTAs may start taking the freed slots
   const size_t HW = (size_t)a.W * a.H;
   const float bg0 = __ldg(a.bg + 0), bg1 = __ldg(a.bg + 1), bg2 = __ldg(a.bg + 2);
   auto store = [&](int py, float T, float Te, float D, uint32_t last, uint32_t nbl, float c0, float c1, float c2,
@@ -305,8 +307,8 @@ int launch_render_fwd(const RenderFwdArgs& a, int T, cudaStream_t st) {
   const bool g = g_gather != 0 && a.grec && a.plist;
 #define FWD_LAUNCH(C, N, D)                                                                  \
   do {                                                                                       \
-    if (g) render_fwd_kernel<C, N, D, true><<<T, RING_THREADS, 0, st>>>(a);                  \
-    else render_fwd_kernel<C, N, D, false><<<T, RING_THREADS, 0, st>>>(a);                   \
+    if (g) SPLAT_CUDA(launch_k(render_fwd_kernel<C, N, D, true>, dim3(T), dim3(RING_THREADS), 0, st, a));    \
+    else SPLAT_CUDA(launch_k(render_fwd_kernel<C, N, D, false>, dim3(T), dim3(RING_THREADS), 0, st, a));  \
   } while (0)
   if (a.blended) FWD_LAUNCH(false, true, false);
   else if (a.depth_sil) FWD_LAUNCH(true, false, true);

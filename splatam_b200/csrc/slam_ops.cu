@@ -67,6 +67,8 @@ __device__ __forceinline__ float4 quat_mul(const float* c, const float4 n) {
 
 // ------------------------------------------------------------------------------------------------ builder fwd
 __global__ void __launch_bounds__(256) rendervar_fwd_kernel(const RvArgs a) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ Pose ps;   // R(q), t: built by one thread per CTA (two square roots + eight divides), broadcast from shared memory
   if (threadIdx.x == 0) ps = load_pose(a.cam_rots, a.cam_trans, a.n_frames, a.t);
   __syncthreads();
@@ -95,6 +97,8 @@ __global__ void __launch_bounds__(256) rendervar_fwd_kernel(const RvArgs a) {
 
 template <bool GG, bool CG, bool ANISO>
 __global__ void __launch_bounds__(256) rendervar_bwd_kernel(const RvArgs a, float* __restrict__ partial) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ Pose ps;
   if (threadIdx.x == 0) ps = load_pose(a.cam_rots, a.cam_trans, a.n_frames, a.t);
   __syncthreads();
@@ -178,6 +182,8 @@ __global__ void __launch_bounds__(256) rendervar_bwd_kernel(const RvArgs a, floa
 // One block: sums the per-block partials (double), then runs the 7-scalar chain
 // dR, dt, dq1 -> cam_unnorm_rots[:, :, t], cam_trans[:, :, t].
 __global__ void __launch_bounds__(512) pose_finalize_kernel(const RvArgs a, const float* __restrict__ partial, int nblk) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ double S[RV_SUMS];
   const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;   // 16 warps, one per sum
   double v = 0.0;
@@ -226,7 +232,7 @@ int rendervar_bwd_blocks(int P) {
 int launch_rendervar_fwd(const RvArgs& a, cudaStream_t st) {
   ProfScope prof_(K_RV_FWD, st);
   if (a.P <= 0) return SPLAT_OK;
-  rendervar_fwd_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+  SPLAT_CUDA(launch_k(rendervar_fwd_kernel, dim3((a.P + 255) / 256), dim3(256), 0, st, a));
   SPLAT_LAUNCH_CHECK("rendervar_fwd_kernel");
   return SPLAT_OK;
 }
@@ -236,7 +242,7 @@ int launch_rendervar_bwd(const RvArgs& a, bool gg, bool cg, float* partial, cuda
   if (!gg && !cg && !a.d_logit && !a.d_logscales) return SPLAT_OK;
   const int nb = rendervar_bwd_blocks(a.P);
   if (a.P > 0) {
-#define RV_CASE(G, C, A) rendervar_bwd_kernel<G, C, A><<<nb, 256, 0, st>>>(a, partial)
+#define RV_CASE(G, C, A) SPLAT_CUDA(launch_k(rendervar_bwd_kernel<G, C, A>, dim3(nb), dim3(256), 0, st, a, partial))
     const int key = (gg ? 4 : 0) | (cg ? 2 : 0) | (a.aniso ? 1 : 0);
     switch (key) {
       case 0: RV_CASE(false, false, false); break;
@@ -252,7 +258,7 @@ int launch_rendervar_bwd(const RvArgs& a, bool gg, bool cg, float* partial, cuda
     SPLAT_LAUNCH_CHECK("rendervar_bwd_kernel");
   }
   if (cg) {
-    pose_finalize_kernel<<<1, 512, 0, st>>>(a, partial, a.P > 0 ? nb : 0);
+    SPLAT_CUDA(launch_k(pose_finalize_kernel, dim3(1), dim3(512), 0, st, a, (const float*)partial, a.P > 0 ? nb : 0));
     SPLAT_LAUNCH_CHECK("pose_finalize_kernel");
   }
   return SPLAT_OK;
@@ -292,6 +298,8 @@ __device__ __forceinline__ bool loss_mask(float gt_d, float d, float d2, float s
 
 // get_loss(tracking=True): sums over the mask, gradient written in the same pass.
 __global__ void __launch_bounds__(256) track_loss_kernel(const LossArgs a, float* __restrict__ partial) {
+  pdl_wait();
+  pdl_trigger();
   const int N = a.W * a.H;
   float s[LOSS_SUMS] = {0.f, 0.f, 0.f, 0.f};
   for (int p = blockIdx.x * 256 + threadIdx.x; p < N; p += gridDim.x * 256) {
@@ -335,6 +343,8 @@ __device__ __forceinline__ void lds16(const float* row, float (&u)[16]) {
 }
 
 __global__ void __launch_bounds__(256) map_loss_fwd_kernel(const LossArgs a, float* __restrict__ partial) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ __align__(16) float sx[SW][SWP], sy[SW][SWP];
   __shared__ __align__(16) float hz[5][SW][HZP];
   const int W = a.W, H = a.H, N = W * H, c = blockIdx.z;
@@ -428,6 +438,8 @@ __global__ void __launch_bounds__(256) map_loss_fwd_kernel(const LossArgs a, flo
 }
 
 __global__ void __launch_bounds__(256) map_loss_bwd_kernel(const LossArgs a, const float* __restrict__ stats) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ __align__(16) float sm[3][SW][SWP];
   __shared__ __align__(16) float hz[3][SW][HZP];
   const int W = a.W, H = a.H, N = W * H, c = blockIdx.z;
@@ -498,6 +510,8 @@ __global__ void __launch_bounds__(256) map_loss_bwd_kernel(const LossArgs a, con
 // losses = (w_im * im, w_depth * depth, total, mask count)   (scripts/splatam.py:342-346)
 __global__ void __launch_bounds__(256) loss_finalize_kernel(const LossArgs a, const float* __restrict__ partial, int nblk,
                                                             float* __restrict__ stats) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ double S[8][LOSS_SUMS];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   double v[LOSS_SUMS] = {0.0, 0.0, 0.0, 0.0};
@@ -544,19 +558,19 @@ int launch_slam_loss(const LossArgs& a, float* partial, float* stats, cudaStream
   const int nb = slam_loss_blocks(a.W, a.H, a.tracking);
   if (a.tracking) {
     ProfScope prof_(K_LOSS, st);
-    track_loss_kernel<<<nb, 256, 0, st>>>(a, partial);
+    SPLAT_CUDA(launch_k(track_loss_kernel, dim3(nb), dim3(256), 0, st, a, partial));
     SPLAT_LAUNCH_CHECK("track_loss_kernel");
-    loss_finalize_kernel<<<1, 256, 0, st>>>(a, partial, nb, stats);
+    SPLAT_CUDA(launch_k(loss_finalize_kernel, dim3(1), dim3(256), 0, st, a, (const float*)partial, nb, stats));
     SPLAT_LAUNCH_CHECK("loss_finalize_kernel");
     return SPLAT_OK;
   }
   ProfScope prof_(K_LOSS, st);
   dim3 grid((a.W + ST - 1) / ST, (a.H + ST - 1) / ST, 3);
-  map_loss_fwd_kernel<<<grid, 256, 0, st>>>(a, partial);
+  SPLAT_CUDA(launch_k(map_loss_fwd_kernel, grid, dim3(256), 0, st, a, partial));
   SPLAT_LAUNCH_CHECK("map_loss_fwd_kernel");
-  loss_finalize_kernel<<<1, 256, 0, st>>>(a, partial, nb, stats);
+  SPLAT_CUDA(launch_k(loss_finalize_kernel, dim3(1), dim3(256), 0, st, a, (const float*)partial, nb, stats));
   SPLAT_LAUNCH_CHECK("loss_finalize_kernel");
-  map_loss_bwd_kernel<<<grid, 256, 0, st>>>(a, stats);
+  SPLAT_CUDA(launch_k(map_loss_bwd_kernel, grid, dim3(256), 0, st, a, (const float*)stats));
   SPLAT_LAUNCH_CHECK("map_loss_bwd_kernel");
   return SPLAT_OK;
 }
@@ -569,6 +583,8 @@ int launch_slam_loss(const LossArgs& a, float* partial, float* stats, cudaStream
 // HBM roofline: 16 B read + 12 B written per element.
 // capturable mode: bias corrections for step[i] + *replay_counter, formed on the device in double; one block
 __global__ void adam_prep_kernel(const AdamArgs a) {
+  pdl_wait();
+  pdl_trigger();
   const int i = threadIdx.x;
   const int replays = *a.replay_counter;
   if (i < a.count) {
@@ -581,12 +597,16 @@ __global__ void adam_prep_kernel(const AdamArgs a) {
 }
 
 __global__ void forward_guard_kernel(const ImageHeader* hdr, uint32_t Rcap, uint32_t* flags) {
+  pdl_wait();
+  pdl_trigger();
   const uint32_t R = hdr->num_rendered;
   if (R > Rcap) flags[0] = 1u;
   if (R > flags[1]) flags[1] = R;
 }
 
 __global__ void __launch_bounds__(256) adam_kernel(const AdamArgs a) {
+  pdl_wait();
+  pdl_trigger();
   int t = 0;
   int b = (int)blockIdx.x;
 #pragma unroll 1
@@ -629,16 +649,16 @@ int launch_adam(AdamArgs& a, cudaStream_t st) {
   }
   if (total == 0) return SPLAT_OK;
   if (a.replay_counter) {
-    adam_prep_kernel<<<1, 32, 0, st>>>(a);
+    SPLAT_CUDA(launch_k(adam_prep_kernel, dim3(1), dim3(32), 0, st, a));
     SPLAT_LAUNCH_CHECK("adam_prep_kernel");
   }
-  adam_kernel<<<total, 256, 0, st>>>(a);
+  SPLAT_CUDA(launch_k(adam_kernel, dim3(total), dim3(256), 0, st, a));
   SPLAT_LAUNCH_CHECK("adam_kernel");
   return SPLAT_OK;
 }
 
 int launch_forward_guard(const ImageHeader* hdr, uint32_t Rcap, uint32_t* flags, cudaStream_t st) {
-  forward_guard_kernel<<<1, 1, 0, st>>>(hdr, Rcap, flags);
+  SPLAT_CUDA(launch_k(forward_guard_kernel, dim3(1), dim3(1), 0, st, hdr, Rcap, flags));
   SPLAT_LAUNCH_CHECK("forward_guard_kernel");
   return SPLAT_OK;
 }
