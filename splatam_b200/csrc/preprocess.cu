@@ -336,7 +336,10 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means, cons
 // dL_dcolors / dL_dopacity / dL_dmean2D / dL_dconic, then DG's computeCov2DCUDA + preprocessCUDA
 // backward in one pass.  Every output row is written (zeros for culled Gaussians: their
 // accumulator rows were never touched), so the caller need not pre-zero the outputs.
-__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs a) {
+#ifndef PREBWD_CTAS
+#define PREBWD_CTAS 4   // r02 A/B at C3: 62.1 us at 2 CTAs per SM (98 registers), 51.5 at 3, 49.4 at 4 (64 registers, 120 B of spills)
+#endif
+__global__ void __launch_bounds__(256, PREBWD_CTAS) preprocess_bwd_kernel(const PreBwdArgs a) {
   pdl_wait();
   pdl_trigger();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -454,7 +457,10 @@ int launch_preprocess_bwd(const PreBwdArgs& a, cudaStream_t st) {
 // (backward.cu:1041-1137 with grad_power == 2) which equals J_k^T Mom J_k.  J is obtained by
 // pushing the five unit vectors through the same chain_apply() used for power == 1.
 
-__global__ void __launch_bounds__(128) hessian_finalize_kernel(const HessArgs a) {
+#ifndef HESSFIN_CTAS
+#define HESSFIN_CTAS 3
+#endif
+__global__ void __launch_bounds__(128, HESSFIN_CTAS) hessian_finalize_kernel(const HessArgs a) {
   pdl_wait();
   pdl_trigger();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
