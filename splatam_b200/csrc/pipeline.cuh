@@ -35,6 +35,9 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// (A suspend-time hint on the probe -- SASS `NANOSLEEP.SYNCS` instead of re-issuing TRYWAIT every ~0.2 us, which is 9 %
+// of the forward kernel's executed instructions -- measured no change at C3, 20 us and 1 ms hints: the re-probes only
+// take issue slots nobody else wanted.)
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }

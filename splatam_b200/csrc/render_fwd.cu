@@ -123,6 +123,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
   // The transmittance it terminated with is parked in Te.
   constexpr uint32_t T_MIN_BITS = 0x38d1b717u;   // 0.0001f (forward.cu:355)
   const float DEAD = __int_as_float(0x80000000);
+  constexpr uint32_t LAST_FROZEN = 0x80000000u;
   float Ta = in_a ? 1.0f : DEAD, Tb = in_b ? 1.0f : DEAD, Tea = 1.0f, Teb = 1.0f, Da = 15.0f, Db = 15.0f;
   // loop-carried accumulators live as scalar pairs and are packed at the point of use: ptxas coalesces the pair
   // into the FFMA2 destination that way; carried as 64-bit values it copied each of them with two MOVs per hit
@@ -165,7 +166,11 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
         while (m) {
           uint32_t t;
           asm("bfind.u32 %0, %1;" : "=r"(t) : "r"(m));
-          m ^= 1u << t;
+          {
+            uint32_t below;   // bits under the popped one
+            asm("bmsk.clamp.b32 %0, %1, %2;" : "=r"(below) : "r"(0u), "r"(t));
+            m &= below;
+          }
           const uint32_t r = r31 - t * INST_BYTES;
           SPLAT_CHECK(r >= sbase && r + INST_BYTES <= sbase + RING_CH * INST_BYTES && (int)(sub + 31 - t) < cnt);
           const float4 q0 = lds128(r), q1 = lds128(r + 16);   // (x, y, A, B), (C, opacity, depth, id)
@@ -181,17 +186,26 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
           const bool va = !(pwa > 0.0f) && !(ala < 1.0f / 255.0f);
           const bool vb = !(pwb > 0.0f) && !(alb < 1.0f / 255.0f);
           float aa = va ? fminf(0.99f, ala) : 0.f, ab = vb ? fminf(0.99f, alb) : 0.f;
+          const f2 T2 = pk(Ta, Tb);
+          f2 om2 = add2(bc(1.0f), pk(-aa, -ab));
           float tta, ttb;
-          upk(mul2(pk(Ta, Tb), add2(bc(1.0f), pk(-aa, -ab))), tta, ttb);   // test_T = T * (1 - alpha)
+          upk(mul2(T2, om2), tta, ttb);   // test_T = T * (1 - alpha)
           // termination EVENT of a live pixel: 0 < test_T < 1e-4 (a live T is >= 1e-4 and 1 - alpha >= 0.01, so its
           // test_T is > 0; a dead pixel's is -0 = 0x80000000, above the threshold as an unsigned integer)
           const bool ea = __float_as_uint(tta) < T_MIN_BITS, eb = __float_as_uint(ttb) < T_MIN_BITS;
           if (__any_sync(0xffffffffu, ea || eb)) {   // rare: at most once per pixel
-            if (ea) { Tea = Ta; tta = DEAD; aa = 0.f; }   // `done = true; continue` (forward.cu:356-359): no contribution
-            if (eb) { Teb = Tb; ttb = DEAD; ab = 0.f; }
-            warp_done = __all_sync(0xffffffffu, __float_as_uint(tta) == 0x80000000u && __float_as_uint(ttb) == 0x80000000u);
+            float oma, omb;
+            upk(om2, oma, omb);
+            // `done = true; continue` (forward.cu:356-359): no contribution, and last_contributor is frozen (top bit)
+            if (ea) { Tea = Ta; tta = DEAD; aa = 0.f; oma = DEAD; last_a |= LAST_FROZEN; }
+            if (eb) { Teb = Tb; ttb = DEAD; ab = 0.f; omb = DEAD; last_b |= LAST_FROZEN; }
+            om2 = pk(oma, omb);
+            if (__all_sync(0xffffffffu, __float_as_uint(tta) == 0x80000000u && __float_as_uint(ttb) == 0x80000000u)) {
+              warp_done = true;   // this hit's (zero) contribution is still accumulated below; the walk ends with it
+              m = 0;
+            }
           }
-          const f2 al2 = pk(aa, ab), T2 = pk(Ta, Tb);
+          const f2 al2 = pk(aa, ab);
           upk(fma2(T2, mul2(al2, bc(cq.x)), pk(c0a, c0b)), c0a, c0b);      // C += (c * alpha) * T  (forward.cu:361)
           upk(fma2(T2, mul2(al2, bc(cq.y)), pk(c1a, c1b)), c1a, c1b);
           upk(fma2(T2, mul2(al2, bc(cq.z)), pk(c2a, c2b)), c2a, c2b);
@@ -206,12 +220,21 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
             if (Tb > 0.5f && ttb < 0.5f) Db = z;
           }
           const uint32_t pos1 = pos31 - t;
-          // contributor = valid, live and not terminating: test_T >= 1e-4 (false for -0)
-          if (va && tta >= 0.0001f) { last_a = pos1; if (COUNT) ++nbl_a; }
-          if (vb && ttb >= 0.0001f) { last_b = pos1; if (COUNT) ++nbl_b; }
-          Ta = tta;
-          Tb = ttb;
-          if (warp_done) break;
+          // contributor = valid, live and not terminating.  A pixel dies only through a termination event, which froze
+          // its last_contributor by setting the top bit: an unsigned max then leaves it alone, so the walk needs no
+          // liveness test here (positions are tile-relative and far below 2^31); the stats variant keeps the plain form.
+          if (COUNT) {
+            if (va && tta >= 0.0001f) { last_a = pos1; ++nbl_a; }
+            if (vb && ttb >= 0.0001f) { last_b = pos1; ++nbl_b; }
+          } else {
+            if (va) last_a = max(last_a, pos1);
+            if (vb) last_b = max(last_b, pos1);
+          }
+          // T <- test_T, formed again IN PLACE (same operands, same bits; an event's factor is -0, which parks the pixel
+          // at DEAD): the loop-carried pair keeps its registers, where `T = test_T` cost two to four MOVs per hit.
+          // The empty asm hides the factor from common-subexpression elimination.
+          asm("" : "+l"(om2));
+          upk(mul2(T2, om2), Ta, Tb);
         }
         };
         // The median-depth test can only fire while some pixel of the warp still has T > 0.5 (T never grows): once all
@@ -254,7 +277,7 @@ __global__ void __launch_bounds__(RING_THREADS) render_fwd_kernel(const RenderFw
     const int pix = py * a.W + st.px;
     if (__float_as_uint(T) == 0x80000000u) T = Te;
     a.final_T[pix] = T;
-    a.n_contrib[pix] = last;
+    a.n_contrib[pix] = last & ~LAST_FROZEN;
     a.out_color[pix] = c0 + T * bg0;
     a.out_color[HW + pix] = c1 + T * bg1;
     a.out_color[2 * HW + pix] = c2 + T * bg2;
