@@ -8,5 +8,5 @@ for spec in "$@"; do
   timeout 600 python bench.py --no-cpu-baseline --no-e2e --no-mapping --warmup 30 > gpurun_out/ab_$tag.json 2> gpurun_out/ab_$tag.err || { echo "$tag failed"; tail -3 gpurun_out/ab_$tag.err; continue; }
   python -c "
 import json; d=json.loads(open('gpurun_out/ab_$tag.json').read().strip().splitlines()[-1])
-print('$tag', 'value %.1f ms %.4f' % (d['value'], d['ms_per_step']), {k: d['kernel_ms_per_step'][k] for k in ('render_fwd','render_bwd')})"
+print('$tag', 'value %.1f ms %.4f' % (d['value'], d['ms_per_step']), {k: round(v, 4) for k, v in d['kernel_ms_per_step'].items()})"
 done

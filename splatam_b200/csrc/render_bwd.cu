@@ -259,7 +259,7 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
             if (m) {
               uint32_t b;
               asm("bfind.u32 %0, %1;" : "=r"(b) : "r"(m));   // back to front: highest list position first
-              m ^= 1u << b;
+              m ^= 1u << b;   // (UBMSK pop, no id preset, group mask instead of flags: each measured at C3, 0 to +1.5 % time)
               const uint32_t r = rsub + b * INST_BYTES;
               const int pos = pos_sub + (int)b;
               SPLAT_CHECK(r >= sbase && r + INST_BYTES <= sbase + BWD_CH * INST_BYTES && sub + (int)b < cnt && pos < hi);
