@@ -263,6 +263,8 @@ __global__ void __launch_bounds__(RING_THREADS, BWD_MIN_CTAS(MODE)) render_bwd_k
               const uint32_t r = rsub + b * INST_BYTES;
               const int pos = pos_sub + (int)b;
               SPLAT_CHECK(r >= sbase && r + INST_BYTES <= sbase + BWD_CH * INST_BYTES && sub + (int)b < cnt && pos < hi);
+              // (Reading the next hit's record one hit ahead -- q0/q1, or all three quads -- to hide this latency costs 8-12
+              // loop-carried register copies per hit: 0.54 ms instead of 0.476 at C3.)
               const float4 q0 = lds128(r), q1 = lds128(r + 16);
               ids[gsl] = __float_as_uint(q1.w);
               SPLAT_CHECK(ids[gsl] < (uint32_t)a.P);
