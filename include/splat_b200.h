@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define SPLAT_ABI_VERSION 6   /* v6 (round 2): splat_peer_reduce_adam, splat_peer_adam_shard_floats, splat_set_gather, splat_slam_track_loss_noalloc, splat_debug_exp_mismatches */
+#define SPLAT_ABI_VERSION 7   /* v6 (round 2): splat_peer_reduce_adam, splat_peer_adam_shard_floats, splat_set_gather, splat_slam_track_loss_noalloc, splat_debug_exp_mismatches; v7: splat_peer_set_tuning */
 
 /* Error codes.  Positive values >= 1000 are 1000 + cudaError_t of a failed runtime call. */
 enum {
@@ -346,6 +346,10 @@ int splat_peer_allreduce_sum(const uint64_t* buffers, const uint64_t* flag_pads,
  * floats each and must start zeroed.  `epoch` as for splat_peer_allreduce_sum (shared counter: every call of either
  * function advances it by one). */
 size_t splat_peer_adam_shard_floats(int64_t n_floats, int32_t world);
+/* Measurement knobs of the two in-switch (multicast) kernels, no reference counterpart: CTAs per launch (0 = the measured
+ * default) and multimem loads in flight per thread of the plain all-reduce (1, 2, 4 or 8; anything else = the default).  Results do
+ * not depend on either.  Process-wide; set the same values on every rank. */
+void splat_peer_set_tuning(int32_t blocks, int32_t unroll);
 int splat_peer_reduce_adam(const uint64_t* grad_buffers, const uint64_t* param_buffers, const uint64_t* flag_pads,
                            uint64_t grad_multicast, uint64_t param_multicast, int32_t rank, int32_t world,
                            uint32_t epoch, int64_t n_floats, const int64_t* segment_ends, const float* segment_lrs,

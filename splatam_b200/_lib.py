@@ -86,6 +86,7 @@ _SIGNATURES = {
                                         _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int64, _P, _P, _P, _P, _P, _P, _P]),
     "splat_peer_allreduce_sum": (C.c_int, [_P, _P, C.c_uint64, C.c_int32, C.c_int32, C.c_uint32, C.c_int64, _P]),
     "splat_peer_adam_shard_floats": (C.c_size_t, [C.c_int64, C.c_int32]),
+    "splat_peer_set_tuning": (None, [C.c_int32, C.c_int32]),
     "splat_peer_reduce_adam": (C.c_int, [_P, _P, _P, C.c_uint64, C.c_uint64, C.c_int32, C.c_int32, C.c_uint32, C.c_int64,
                                          _P, _P, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double, _P, _P, _P]),
     "splat_profile_enable": (C.c_int, [C.c_int]),
@@ -115,7 +116,7 @@ def _load():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing: intended
         fn.restype = res
         fn.argtypes = args
-    if lib.splat_abi_version() != 6:
+    if lib.splat_abi_version() != 7:
         raise ImportError("libsplat_b200.so ABI version mismatch")
     return lib
 

@@ -100,21 +100,22 @@ __global__ void __launch_bounds__(512) peer_reduce_kernel(const PeerArgs a) {
 // multimem.st writes every rank's copy.  Rank r does that for slice r.  Per GPU and direction the links
 // carry the bucket once (N-1)/N in + 1/N out and vice versa) instead of 2(N-1)/N of it.  The switch's
 // summation order is its own, but every replica receives the SAME sums (one owner per slice).
+template <int U>
 __global__ void __launch_bounds__(512) multimem_reduce_kernel(float4* mc, int rank, int world, size_t n4) {
   const size_t per = (n4 + world - 1) / world;
   const size_t lo = (size_t)rank * per, hi = min(n4, lo + per);
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t base = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; base < hi; base += stride * 4) {
-    float4 v[4];
+  for (size_t base = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; base < hi; base += stride * U) {
+    float4 v[U];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < U; ++u) {
       const size_t i = base + (size_t)u * stride;
       if (i < hi)
         asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
                      : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w) : "l"(mc + i) : "memory");
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < U; ++u) {
       const size_t i = base + (size_t)u * stride;
       if (i < hi)
         asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
@@ -194,6 +195,13 @@ __global__ void __launch_bounds__(512) reduce_adam_kernel(const ReduceAdamArgs a
 
 using namespace splat;
 
+// Grid size (0 = default) and loads in flight per thread of the in-switch kernels: measurement knobs.
+static int g_peer_blocks = 0, g_peer_unroll = 0;
+extern "C" void splat_peer_set_tuning(int32_t blocks, int32_t unroll) {
+  g_peer_blocks = blocks > 0 ? blocks : 0;
+  g_peer_unroll = (unroll == 1 || unroll == 2 || unroll == 4 || unroll == 8) ? unroll : 0;
+}
+
 extern "C" int splat_peer_allreduce_sum(const uint64_t* buffers, const uint64_t* flag_pads, uint64_t multicast_buffer,
                                         int32_t rank, int32_t world, uint32_t epoch, int64_t n_floats, void* stream) {
   if (!buffers || !flag_pads) return fail(SPLAT_ERR_BAD_ARG, "NULL pointer table");
@@ -221,9 +229,18 @@ extern "C" int splat_peer_allreduce_sum(const uint64_t* buffers, const uint64_t*
     // (A hybrid split -- part of each slice through the switch, the rest through peer loads/stores in the same
     // launch -- was swept at N=8: 0.184 ms at 90/10 rising to 0.234 ms at 35/65 vs 0.178 ms all in-switch: both
     // halves contend for the same links.)
-    int mblocks = (int)std::min<size_t>((per + 512 * 4 - 1) / (512 * 4), (size_t)148 * 2);
+    // Few CTAs that LOOP over the slice, not one pass of many: with the whole slice in flight at once every GPU first
+    // only loads (its links busy outbound with the data the switch sums) and then only stores (busy inbound with the
+    // multicast), one direction idle each time.  Looping interleaves the two.  N=8 sweep (tests/peer_tune_sweep.py,
+    // profiles/r02i_peer_tune_n8.log): 0.178 ms at 213 CTAs x 4 loads in flight, 0.142-0.144 ms anywhere in 32-64 CTAs x 1-2.
+    const int U = g_peer_unroll > 0 ? g_peer_unroll : 2;
+    int mblocks = (int)std::min<size_t>((per + 512 * U - 1) / (512 * U), (size_t)(g_peer_blocks > 0 ? g_peer_blocks : 48));
     if (mblocks < 1) mblocks = 1;
-    multimem_reduce_kernel<<<mblocks, 512, 0, st>>>(reinterpret_cast<float4*>(multicast_buffer), rank, world, a.n4);
+    float4* mc = reinterpret_cast<float4*>(multicast_buffer);
+    if (U == 1) multimem_reduce_kernel<1><<<mblocks, 512, 0, st>>>(mc, rank, world, a.n4);
+    else if (U == 2) multimem_reduce_kernel<2><<<mblocks, 512, 0, st>>>(mc, rank, world, a.n4);
+    else if (U == 8) multimem_reduce_kernel<8><<<mblocks, 512, 0, st>>>(mc, rank, world, a.n4);
+    else multimem_reduce_kernel<4><<<mblocks, 512, 0, st>>>(mc, rank, world, a.n4);
     SPLAT_LAUNCH_CHECK("multimem_reduce_kernel");
     peer_barrier_kernel<<<1, 32, 0, st>>>(a, 1);
     SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
@@ -231,7 +248,7 @@ extern "C" int splat_peer_allreduce_sum(const uint64_t* buffers, const uint64_t*
   }
   // Link-bound: at N=2 the 56 MB bucket moves 56 MB per direction per GPU in ~80 us (~700 GB/s, NVLink 5's
   // practical rate); .cg vs volatile loads, unroll 8 and 1 vs 2 CTAs per SM all measure the same +-2%.
-  int blocks = (int)std::min<size_t>((per + 512 * 4 - 1) / (512 * 4), (size_t)148 * 2);
+  int blocks = (int)std::min<size_t>((per + 512 * 4 - 1) / (512 * 4), (size_t)(g_peer_blocks > 0 ? g_peer_blocks : 148 * 2));
   if (blocks < 1) blocks = 1;
   peer_reduce_kernel<4, false><<<blocks, 512, 0, st>>>(a);
   SPLAT_LAUNCH_CHECK("peer_reduce_kernel");
@@ -291,7 +308,8 @@ extern "C" int splat_peer_reduce_adam(const uint64_t* grad_buffers, const uint64
   peer_barrier_kernel<<<1, 32, 0, st>>>(a.p, 0);          // every rank's gradients are complete
   SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
   const size_t per = (a.p.n4 + world - 1) / world;
-  int blocks = (int)std::min<size_t>((per + 511) / 512, (size_t)148 * 2);
+  // in-switch: 64 looping CTAs (0.121 ms at N=8 against 0.133 ms at 296, same sweep); peer loads / stores: 444 (N=2: 0.094 ms against 0.099 at 296)
+  int blocks = (int)std::min<size_t>((per + 511) / 512, (size_t)(g_peer_blocks > 0 ? g_peer_blocks : (grad_multicast ? 64 : 148 * 3)));
   if (blocks < 1) blocks = 1;
   if (grad_multicast) reduce_adam_kernel<true><<<blocks, 512, 0, st>>>(a);
   else reduce_adam_kernel<false><<<blocks, 512, 0, st>>>(a);

@@ -179,7 +179,9 @@ class PeerAllReduce:
         # 0.165 at N=4, 0.264 at N=8; in-switch 0.171 at N=2, 0.178 at N=8; NCCL 0.129 / 0.160 / 0.241.
         mc = int(getattr(hb, "multicast_ptr", 0) or 0)
         if multicast == "auto":
-            multicast = self.world > 4
+            # 56 MB bucket, tuned grids (profiles/r02i_peer_tune_*.log): N=2 peer loads / stores 0.100 ms vs in-switch 0.157;
+            # N=4 0.149-0.165 vs 0.143; N=8 0.26 vs 0.142
+            multicast = self.world >= 4
         self.multicast = mc if multicast else 0
         self.param_multicast = (self._param_multicast_ptr if (with_params and self.multicast) else 0)
         if with_params and self.multicast and not self.param_multicast:

@@ -34,7 +34,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_abi_version_and_error_strings():
     from splatam_b200._lib import lib
-    assert lib.splat_abi_version() == 6
+    assert lib.splat_abi_version() == 7
     assert lib.splat_strerror(0) == b"ok"
     assert lib.splat_strerror(1) == b"bad argument"
     assert lib.splat_strerror(2) == b"scratch buffer too small"
