@@ -60,14 +60,53 @@ __global__ void __launch_bounds__(32) peer_barrier_kernel(const PeerArgs a, int 
   }
 }
 
+// The same two barriers INSIDE the exchange kernel (FUSED): no separate launches, and the waits overlap the kernel's own
+// ramp-up.  begin: thread j of CTA 0 posts this rank's arrival to peer j; every CTA then spins on the LOCAL pad.  end: every
+// thread fences its stores, the last CTA to finish (counter in word 63 of the local pad) posts the completion flags and
+// waits for the peers' -- the kernel, hence the stream, does not get past it before every replica is complete.
+#define PAD_COUNTER (2 * PAD_STRIDE - 1)
+__device__ __forceinline__ void spin_until(const uint32_t* flag, uint32_t epoch, long long timeout_cycles) {
+  const long long t0 = clock64();
+  while ((int32_t)(ld_acquire_sys(flag) - epoch) < 0) {   // a few threads per CTA on a local line: no back-off needed
+    if (timeout_cycles && clock64() - t0 > timeout_cycles) __trap();
+  }
+}
+__device__ __forceinline__ void fused_begin(const PeerArgs& a) {
+  const int j = threadIdx.x;
+  if (j < a.world) {
+    if (blockIdx.x == 0) st_release_sys(a.pad[j] + a.rank, a.epoch);   // release.sys: the stream's earlier kernels are visible first
+    spin_until(a.pad[a.rank] + j, a.epoch, a.timeout_cycles);
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ void fused_end(const PeerArgs& a) {
+  __threadfence_system();            // this thread's stores to the replicas are ordered before the flags below
+  __syncthreads();
+  __shared__ int s_last;
+  if (threadIdx.x == 0) {
+    uint32_t* cnt = a.pad[a.rank] + PAD_COUNTER;
+    __threadfence();
+    s_last = atomicAdd(cnt, 1u) == gridDim.x - 1;
+    if (s_last) *(volatile uint32_t*)cnt = 0u;    // nobody else touches it until the next call
+  }
+  __syncthreads();
+  if (!s_last) return;
+  const int j = threadIdx.x;
+  if (j < a.world) {
+    st_release_sys(a.pad[j] + PAD_STRIDE + a.rank, a.epoch);
+    spin_until(a.pad[a.rank] + PAD_STRIDE + j, a.epoch, a.timeout_cycles);
+  }
+}
+
 __device__ __forceinline__ float4 ld_cg_f4(const float4* p) {
   float4 v;
   asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
   return v;
 }
 
-template <int RED_UNROLL, bool CG>
+template <int RED_UNROLL, bool CG, bool FUSED>
 __global__ void __launch_bounds__(512) peer_reduce_kernel(const PeerArgs a) {
+  if (FUSED) fused_begin(a);
   const size_t per = (a.n4 + a.world - 1) / a.world;
   const size_t lo = (size_t)a.rank * per, hi = min(a.n4, lo + per);
   const size_t stride = (size_t)gridDim.x * blockDim.x;
@@ -93,6 +132,7 @@ __global__ void __launch_bounds__(512) peer_reduce_kernel(const PeerArgs a) {
       }
     }
   }
+  if (FUSED) fused_end(a);
 }
 
 // NVSwitch in-switch reduction (NVLS): the bucket is also mapped at a MULTICAST address.  A
@@ -100,8 +140,11 @@ __global__ void __launch_bounds__(512) peer_reduce_kernel(const PeerArgs a) {
 // multimem.st writes every rank's copy.  Rank r does that for slice r.  Per GPU and direction the links
 // carry the bucket once (N-1)/N in + 1/N out and vice versa) instead of 2(N-1)/N of it.  The switch's
 // summation order is its own, but every replica receives the SAME sums (one owner per slice).
-template <int U>
-__global__ void __launch_bounds__(512) multimem_reduce_kernel(float4* mc, int rank, int world, size_t n4) {
+template <int U, bool FUSED>
+__global__ void __launch_bounds__(512) multimem_reduce_kernel(float4* mc, const PeerArgs a) {
+  if (FUSED) fused_begin(a);
+  const int rank = a.rank, world = a.world;
+  const size_t n4 = a.n4;
   const size_t per = (n4 + world - 1) / world;
   const size_t lo = (size_t)rank * per, hi = min(n4, lo + per);
   const size_t stride = (size_t)gridDim.x * blockDim.x;
@@ -122,6 +165,7 @@ __global__ void __launch_bounds__(512) multimem_reduce_kernel(float4* mc, int ra
                      ::"l"(mc + i), "f"(v[u].x), "f"(v[u].y), "f"(v[u].z), "f"(v[u].w) : "memory");
     }
   }
+  if (FUSED) fused_end(a);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -147,8 +191,9 @@ struct ReduceAdamArgs {
   float w1, w2, beta2, inv_b2, eps;
 };
 
-template <bool MC>
+template <bool MC, bool FUSED>
 __global__ void __launch_bounds__(512) reduce_adam_kernel(const ReduceAdamArgs a) {
+  if (FUSED) fused_begin(a.p);
   const size_t per = (a.p.n4 + a.p.world - 1) / a.p.world;
   const size_t lo = (size_t)a.p.rank * per, hi = min(a.p.n4, lo + per);
   const size_t stride = (size_t)gridDim.x * blockDim.x;
@@ -189,6 +234,7 @@ __global__ void __launch_bounds__(512) reduce_adam_kernel(const ReduceAdamArgs a
       for (int j = 0; j < a.p.world; ++j) a.param[j][i] = p;
     }
   }
+  if (FUSED) fused_end(a.p);
 }
 
 }  // namespace splat
@@ -196,6 +242,11 @@ __global__ void __launch_bounds__(512) reduce_adam_kernel(const ReduceAdamArgs a
 using namespace splat;
 
 // Grid size (0 = default) and loads in flight per thread of the in-switch kernels: measurement knobs.
+// SPLAT_PEER_FUSED_BARRIER=0: the two barriers as separate one-warp kernels around the exchange kernel (the round-1 form).
+static bool fused_barriers() {
+  static const bool on = [] { const char* e = getenv("SPLAT_PEER_FUSED_BARRIER"); return !(e && e[0] == '0'); }();
+  return on;
+}
 static int g_peer_blocks = 0, g_peer_unroll = 0;
 extern "C" void splat_peer_set_tuning(int32_t blocks, int32_t unroll) {
   g_peer_blocks = blocks > 0 ? blocks : 0;
@@ -221,8 +272,11 @@ extern "C" int splat_peer_allreduce_sum(const uint64_t* buffers, const uint64_t*
     a.timeout_cycles = timeout_s > 0.0 ? (long long)(timeout_s * 2.0e9) : 0;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  peer_barrier_kernel<<<1, 32, 0, st>>>(a, 0);
-  SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
+  const bool fused = fused_barriers();
+  if (!fused) {
+    peer_barrier_kernel<<<1, 32, 0, st>>>(a, 0);
+    SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
+  }
   const size_t per = (a.n4 + world - 1) / world;
   if (multicast_buffer) {
     if (multicast_buffer & 15) return fail(SPLAT_ERR_BAD_ARG, "misaligned multicast address");
@@ -237,23 +291,34 @@ extern "C" int splat_peer_allreduce_sum(const uint64_t* buffers, const uint64_t*
     int mblocks = (int)std::min<size_t>((per + 512 * U - 1) / (512 * U), (size_t)(g_peer_blocks > 0 ? g_peer_blocks : 48));
     if (mblocks < 1) mblocks = 1;
     float4* mc = reinterpret_cast<float4*>(multicast_buffer);
-    if (U == 1) multimem_reduce_kernel<1><<<mblocks, 512, 0, st>>>(mc, rank, world, a.n4);
-    else if (U == 2) multimem_reduce_kernel<2><<<mblocks, 512, 0, st>>>(mc, rank, world, a.n4);
-    else if (U == 8) multimem_reduce_kernel<8><<<mblocks, 512, 0, st>>>(mc, rank, world, a.n4);
-    else multimem_reduce_kernel<4><<<mblocks, 512, 0, st>>>(mc, rank, world, a.n4);
+#define MM_LAUNCH(UU)                                                                       \
+  do {                                                                                      \
+    if (fused) multimem_reduce_kernel<UU, true><<<mblocks, 512, 0, st>>>(mc, a);            \
+    else multimem_reduce_kernel<UU, false><<<mblocks, 512, 0, st>>>(mc, a);                 \
+  } while (0)
+    if (U == 1) MM_LAUNCH(1);
+    else if (U == 4) MM_LAUNCH(4);
+    else if (U == 8) MM_LAUNCH(8);
+    else MM_LAUNCH(2);
+#undef MM_LAUNCH
     SPLAT_LAUNCH_CHECK("multimem_reduce_kernel");
-    peer_barrier_kernel<<<1, 32, 0, st>>>(a, 1);
-    SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
+    if (!fused) {
+      peer_barrier_kernel<<<1, 32, 0, st>>>(a, 1);
+      SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
+    }
     return SPLAT_OK;
   }
   // Link-bound: at N=2 the 56 MB bucket moves 56 MB per direction per GPU in ~80 us (~700 GB/s, NVLink 5's
   // practical rate); .cg vs volatile loads, unroll 8 and 1 vs 2 CTAs per SM all measure the same +-2%.
   int blocks = (int)std::min<size_t>((per + 512 * 4 - 1) / (512 * 4), (size_t)(g_peer_blocks > 0 ? g_peer_blocks : 148 * 2));
   if (blocks < 1) blocks = 1;
-  peer_reduce_kernel<4, false><<<blocks, 512, 0, st>>>(a);
+  if (fused) peer_reduce_kernel<4, false, true><<<blocks, 512, 0, st>>>(a);
+  else peer_reduce_kernel<4, false, false><<<blocks, 512, 0, st>>>(a);
   SPLAT_LAUNCH_CHECK("peer_reduce_kernel");
-  peer_barrier_kernel<<<1, 32, 0, st>>>(a, 1);
-  SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
+  if (!fused) {
+    peer_barrier_kernel<<<1, 32, 0, st>>>(a, 1);
+    SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
+  }
   return SPLAT_OK;
 }
 
@@ -305,16 +370,26 @@ extern "C" int splat_peer_reduce_adam(const uint64_t* grad_buffers, const uint64
   a.grad_mc = reinterpret_cast<float4*>(grad_multicast); a.param_mc = reinterpret_cast<float4*>(param_multicast);
   a.m = reinterpret_cast<float4*>(exp_avg_shard); a.v = reinterpret_cast<float4*>(exp_avg_sq_shard);
   cudaStream_t st = (cudaStream_t)stream;
-  peer_barrier_kernel<<<1, 32, 0, st>>>(a.p, 0);          // every rank's gradients are complete
-  SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
+  const bool fused = fused_barriers();
+  if (!fused) {
+    peer_barrier_kernel<<<1, 32, 0, st>>>(a.p, 0);          // every rank's gradients are complete
+    SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
+  }
   const size_t per = (a.p.n4 + world - 1) / world;
   // in-switch: 64 looping CTAs (0.121 ms at N=8 against 0.133 ms at 296, same sweep); peer loads / stores: 444 (N=2: 0.094 ms against 0.099 at 296)
   int blocks = (int)std::min<size_t>((per + 511) / 512, (size_t)(g_peer_blocks > 0 ? g_peer_blocks : (grad_multicast ? 64 : 148 * 3)));
   if (blocks < 1) blocks = 1;
-  if (grad_multicast) reduce_adam_kernel<true><<<blocks, 512, 0, st>>>(a);
-  else reduce_adam_kernel<false><<<blocks, 512, 0, st>>>(a);
+  if (grad_multicast) {
+    if (fused) reduce_adam_kernel<true, true><<<blocks, 512, 0, st>>>(a);
+    else reduce_adam_kernel<true, false><<<blocks, 512, 0, st>>>(a);
+  } else {
+    if (fused) reduce_adam_kernel<false, true><<<blocks, 512, 0, st>>>(a);
+    else reduce_adam_kernel<false, false><<<blocks, 512, 0, st>>>(a);
+  }
   SPLAT_LAUNCH_CHECK("reduce_adam_kernel");
-  peer_barrier_kernel<<<1, 32, 0, st>>>(a.p, 1);          // every replica holds the updated parameters
-  SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
+  if (!fused) {
+    peer_barrier_kernel<<<1, 32, 0, st>>>(a.p, 1);          // every replica holds the updated parameters
+    SPLAT_LAUNCH_CHECK("peer_barrier_kernel");
+  }
   return SPLAT_OK;
 }
