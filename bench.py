@@ -703,9 +703,12 @@ def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, war
             dist.barrier()
         torch.cuda.synchronize()
 
-    full(0, verify=True)
+    # the warm-up holds the previous step's loss across the next call exactly as the timed loop does: with the result
+    # dropped here, the timed loop's second step was the first to have two losses alive and sent the caching allocator
+    # to cudaMalloc inside the timed region (0.7 ms, occasionally 80 ms: per-step trace, SPLAT_BENCH_TRACE=1)
+    loss = full(0, verify=True)
     for i in range(1, max(warmup, 3)):
-        full(i)
+        loss = full(i)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     trace = [] if os.environ.get("SPLAT_BENCH_TRACE") else None
@@ -715,7 +718,8 @@ def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, war
             if trace is not None:
                 ev = torch.cuda.Event(enable_timing=True)
                 ev.record()
-                trace.append((ev, time.perf_counter()))
+                ms_ = torch.cuda.memory_stats(device)
+                trace.append((ev, time.perf_counter(), ms_.get("num_device_alloc", 0), ms_.get("num_device_free", 0)))
             loss = full(warmup + i)
         e1.record()
     barrier()
@@ -724,6 +728,8 @@ def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, war
         host = [(trace[i + 1][1] - trace[i][1]) * 1e3 for i in range(len(trace) - 1)]
         sys.stderr.write("mapping leg per-step gpu ms: %s\nmapping leg per-step host ms: %s\n" % (
             " ".join("%.2f" % v for v in gpu), " ".join("%.2f" % v for v in host)))
+        sys.stderr.write("mapping leg per-step cudaMalloc / cudaFree calls of the caching allocator: %s\n" % " ".join(
+            "%d/%d" % (trace[i + 1][2] - trace[i][2], trace[i + 1][3] - trace[i][3]) for i in range(len(trace) - 1)))
     t = torch.tensor([e0.elapsed_time(e1)], device=device)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -267,7 +267,7 @@ def main():
         sampler.start()
     for i in range(args.warmup):
         zero()
-        step(kf_of(i))
+        loss = step(kf_of(i))   # held across the next call, as in the timed loop (same caching-allocator pattern)
     if args.graph:   # one untimed captured frame: first-capture costs (graph pool, instantiate) are per process, not per frame
         assert args.impl == "ours" and args.optimizer == "fused", "--graph needs --impl ours --optimizer fused"
         w = slam.GraphedIteration(lambda: step(0), params, opt, warmup=1)
