@@ -873,8 +873,10 @@ def main():
         # ~30-50 us of stream time, which would be charged to the headline number.
         import ctypes as C
         from splatam_b200._lib import lib
-        lib.splat_profile_enable(1)
-        ms_prof, _ = timed_run(runner, sched, rank, world, args.steps, 3, device, dist)
+        # switched on AFTER the pass's own warm-up and barrier: the gap before the first profiled kernel would otherwise
+        # contain that barrier (tens of ms at N > 1) and show up as a per-step idle time that no step has
+        ms_prof, _ = timed_run(runner, sched, rank, world, args.steps, 3, device, dist,
+                               on_timed_start=lambda: lib.splat_profile_enable(1))
         n = 16
         ms_sum = (C.c_float * n)(); cnt = (C.c_int32 * n)(); gaps = (C.c_float * n)()
         lib.splat_profile_read(ms_sum, cnt, n)
@@ -883,8 +885,7 @@ def main():
         names = [lib.splat_profile_kernel_name(k).decode() for k in range(n)]
         prof = {names[k]: (ms_sum[k], cnt[k]) for k in range(n) if cnt[k]}
         prof_gaps = {names[k]: gaps[k] for k in range(n) if cnt[k]}
-        # the profiled pass runs 3 warm-up steps first: scale the sums to the K timed steps
-        prof_steps = args.steps + 3
+        prof_steps = args.steps
 
     # ---- e2e: host buffers in, image + gradients out, every step
     e2e = e2e_res = None
