@@ -3,16 +3,20 @@
 //
 // The reference has no multi-GPU code; this is the exchange step of SURVEY.md 8(e).  Every rank's
 // bucket lives in symmetric memory (same size on every rank, every rank holds the peers' device
-// pointers).  Two-shot all-reduce in stream order:
-//   1. peer_barrier  -- every rank's gradient kernels are complete and visible system-wide;
-//   2. peer_reduce   -- rank r owns slice r of the bucket: it reads that slice from every rank over
-//                       NVLink (128-bit volatile loads, fixed rank order so all replicas get bit-identical sums),
-//                       adds, and stores the sum into every rank's bucket.  Per GPU and direction the
-//                       links carry (N-1)/N of the bucket, loads and stores in opposite directions;
-//   3. peer_barrier  -- every rank's stores have landed before anyone reads its bucket.
+// pointers).  Two-shot all-reduce in stream order, ONE kernel per rank:
+//   1. arrival barrier -- every rank's gradient kernels are complete and visible system-wide;
+//   2. reduce          -- rank r owns slice r of the bucket: it reads that slice from every rank over
+//                         NVLink (128-bit volatile loads, fixed rank order so all replicas get bit-identical sums),
+//                         adds, and stores the sum into every rank's bucket.  Per GPU and direction the
+//                         links carry (N-1)/N of the bucket, loads and stores in opposite directions.
+//                         From 4 ranks on the sum is formed inside the NVSwitch instead (multimem.ld_reduce /
+//                         multimem.st on the bucket's multicast address);
+//   3. completion barrier -- every rank's stores have landed before anyone reads its bucket.
 // Barriers are epoch counters in a symmetric flag pad: rank r writes `epoch` into word [slot][r] of
 // every peer's pad (st.release.sys) and spins on its own pad until all words reach `epoch`
-// (ld.acquire.sys).  A spin that outlives ~4 s traps instead of hanging the GPU.
+// (ld.acquire.sys).  They run inside the exchange kernel (fused_begin / fused_end below); with
+// SPLAT_PEER_FUSED_BARRIER=0 they are two one-warp kernels around it, as in round 1.  A spin that outlives
+// SPLAT_PEER_TIMEOUT_S (default 60 s) traps instead of hanging the GPU.
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
