@@ -257,6 +257,45 @@ def test_bookkeeping_entry_points_validate_before_cuda():
     assert lib.splat_best_pose_update(one, null, one, one, 5, 1, one, one, null) == 1
 
 
+def test_peer_exchange_entry_points_validate_before_cuda():
+    """splat_peer_allreduce_sum / splat_peer_reduce_adam / splat_peer_set_tuning: argument checks and the
+    single-rank no-op need no GPU and launch nothing."""
+    from splatam_b200._lib import lib
+    null = C.c_void_p(0)
+    one_buf = (C.c_uint64 * 1)(256)
+    two_buf = (C.c_uint64 * 2)(256, 512)
+    misaligned = (C.c_uint64 * 2)(256, 520)
+    n0 = lib.splat_kernel_launch_count()
+    lib.splat_peer_set_tuning(0, 0)      # defaults
+    lib.splat_peer_set_tuning(64, 3)     # an unroll the kernels are not built for falls back to the default
+    lib.splat_peer_set_tuning(0, 0)
+    assert lib.splat_peer_allreduce_sum(null, null, 0, 0, 2, 1, 1024, null) == 1 and b"NULL" in lib.splat_last_error()
+    assert lib.splat_peer_allreduce_sum(two_buf, two_buf, 0, 2, 2, 1, 1024, null) == 1 and b"rank" in lib.splat_last_error()
+    assert lib.splat_peer_allreduce_sum(two_buf, two_buf, 0, 0, 17, 1, 1024, null) == 1
+    assert lib.splat_peer_allreduce_sum(two_buf, two_buf, 0, 0, 2, 1, 1022, null) == 1 and b"multiple of 4" in lib.splat_last_error()
+    assert lib.splat_peer_allreduce_sum(misaligned, two_buf, 0, 0, 2, 1, 1024, null) == 1 and b"misaligned" in lib.splat_last_error()
+    assert lib.splat_peer_allreduce_sum(one_buf, one_buf, 0, 0, 1, 1, 1024, null) == 0      # one rank: nothing to exchange
+    assert lib.splat_peer_allreduce_sum(two_buf, two_buf, 0, 0, 2, 1, 0, null) == 0         # empty bucket
+    assert lib.splat_peer_adam_shard_floats(14_000_000, 8) == 1_750_000
+    assert lib.splat_peer_adam_shard_floats(1_000_003, 8) % 4 == 0 and lib.splat_peer_adam_shard_floats(1_000_003, 8) * 8 >= 1_000_003
+    assert lib.splat_peer_adam_shard_floats(0, 8) == 0
+    ends = (C.c_int64 * 2)(512, 1024)
+    lrs = (C.c_float * 2)(1e-3, 1e-2)
+    shard = C.c_void_p(1024)
+    args = [two_buf, two_buf, two_buf, 0, 0, 0, 2, 1, 1024, ends, lrs, 2, 1, 0.9, 0.999, 1e-15, shard, shard, null]
+    bad = list(args); bad[12] = 0
+    assert lib.splat_peer_reduce_adam(*bad) == 1 and b"step" in lib.splat_last_error()
+    bad = list(args); bad[11] = 0
+    assert lib.splat_peer_reduce_adam(*bad) == 1 and b"segment" in lib.splat_last_error()
+    bad = list(args); bad[9] = (C.c_int64 * 2)(1024, 512)
+    assert lib.splat_peer_reduce_adam(*bad) == 1 and b"non-decreasing" in lib.splat_last_error()
+    bad = list(args); bad[3] = 4096      # one multicast address without the other
+    assert lib.splat_peer_reduce_adam(*bad) == 1 and b"multicast" in lib.splat_last_error()
+    bad = list(args); bad[16] = null
+    assert lib.splat_peer_reduce_adam(*bad) == 1 and b"moment" in lib.splat_last_error()
+    assert lib.splat_kernel_launch_count() == n0
+
+
 def test_densify_module_mirrors_reference_signatures():
     """splatam_b200.densify keeps the parameter lists of utils/slam_external.py:143,172 and scripts/splatam.py:384-385."""
     from splatam_b200 import densify
