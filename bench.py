@@ -412,11 +412,14 @@ LAST_HOST = {}
 
 
 @contextlib.contextmanager
-def no_gc():
+def no_gc(collect=True):
     """Timed regions run with Python's cyclic garbage collector paused (as timeit does), after one explicit collection:
-    a generation-2 collection walks the whole process's object graph -- 13 to 87 ms here, at a deterministic step of the
-    loop (it hit the SECOND timed step of the 20-step mapping leg in 3 runs of 6: 1.33 -> 5.6 ms per step).  Both arms."""
-    gc.collect()
+    a generation-2 collection walks the whole process's object graph -- 13 to 87 ms here.  Both arms.  The explicit
+    collection itself belongs BEFORE the warm-up steps (collect=False here): right after it the interpreter runs its first
+    step ~0.6 ms slower (the traversal evicted the hot objects from the caches) and the GPU idles through it -- at K = 20
+    that was 2-3 % of the timed region (first timed mapping step 1.8 ms vs 1.5 with the collection moved)."""
+    if collect:   # False: the caller collected before its warm-up steps and has kept the collector off since, so that
+        gc.collect()  # the GPU does not sit idle through a full collection between the warm-up and the first timed step
     was = gc.isenabled()
     gc.disable()
     try:
@@ -457,6 +460,9 @@ def timed_run(runner, sched, rank, world, steps, warmup, device, dist, on_timed_
             dist.barrier()
         torch.cuda.synchronize()
 
+    gc_was = gc.isenabled()
+    gc.collect()
+    gc.disable()     # from here to the end of the timed loop (re-enabled below)
     for i in range(max(warmup, 3)):
         full_step(i)
     barrier()
@@ -468,12 +474,14 @@ def timed_run(runner, sched, rank, world, steps, warmup, device, dist, on_timed_
     # (the reference arm must not map libsplat_b200.so: the rasterizer module is only touched for OUR runner)
     host_stats = sys.modules["splatam_b200.rasterizer"].host_stats if isinstance(runner, OursRunner) else {"wait_s": 0.0}
     w0, h0 = host_stats["wait_s"], time.perf_counter()
-    with no_gc():
+    with no_gc(collect=False):
         w0, h0 = host_stats["wait_s"], time.perf_counter()
         e0.record()
         for i in range(steps):
             full_step(i)
         e1.record()
+    if gc_was:
+        gc.enable()
     h1, w1 = time.perf_counter(), host_stats["wait_s"]
     barrier()
     # host view of the same region: time to enqueue the K steps, and how much of it the host spent blocked on the
@@ -546,18 +554,23 @@ def e2e_run(runner, sched, rank, world, steps, device, dist):
                                  ("h2d0", "h2d1", "r0", "r1", "d2h0", "d2h1") if (k, i) in trace) + "\n")
             trace.clear()
 
+    gc_was = gc.isenabled()
+    gc.collect()
+    gc.disable()     # collected BEFORE the warm-up (see no_gc); re-enabled after the timed loop
     run(3)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with no_gc():
+    with no_gc(collect=False):
         t0 = time.perf_counter()
         e0.record()
         run(steps)
         e1.record()
         torch.cuda.synchronize()
+    if gc_was:
+        gc.enable()
     wall_ms = (time.perf_counter() - t0) * 1e3
     ms = max(e0.elapsed_time(e1), 0.0)
     t = torch.tensor([ms, wall_ms], device=device)
@@ -707,12 +720,15 @@ def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, war
     # dropped here, the timed loop's second step was the first to have two losses alive and sent the caching allocator
     # to cudaMalloc inside the timed region (0.7 ms, occasionally 80 ms: per-step trace, SPLAT_BENCH_TRACE=1)
     loss = full(0, verify=True)
+    gc_was = gc.isenabled()
+    gc.collect()
+    gc.disable()     # from here to the end of the timed loop (re-enabled below)
     for i in range(1, max(warmup, 3)):
         loss = full(i)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     trace = [] if os.environ.get("SPLAT_BENCH_TRACE") else None
-    with no_gc():
+    with no_gc(collect=False):
         e0.record()
         for i in range(steps):
             if trace is not None:
@@ -722,6 +738,8 @@ def mapping_leg(impl, variant, rank, world, device, dist, collective, steps, war
                 trace.append((ev, time.perf_counter(), ms_.get("num_device_alloc", 0), ms_.get("num_device_free", 0)))
             loss = full(warmup + i)
         e1.record()
+    if gc_was:
+        gc.enable()
     barrier()
     if trace:
         gpu = [trace[i][0].elapsed_time(trace[i + 1][0]) for i in range(len(trace) - 1)]
