@@ -794,7 +794,7 @@ def main():
                        "backward_power": power, "variant": args.variant,
                        "parallelism": "keyframe-sharded x%d + 1 all-reduce of the flat gradient bucket" % world
                        if world > 1 else "single GPU",
-                       "host": "Python's cyclic GC is paused inside every timed region (one gc.collect() before it), both arms",
+                       "host": "Python's cyclic GC is paused from before the warm-up steps to the end of every timed region (one gc.collect() before the warm-up), both arms",
                        "l2": "per-step working set (56 MB parameters + 56 MB gradients + ~190 MB geometry/binning/"
                              "instance state) exceeds the 126 MB L2 and the camera moves over the keyframe window "
                              "every step; no explicit flush"}}
